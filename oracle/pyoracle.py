@@ -1,0 +1,181 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes access to the two CPU checkers.
+
+* ``oracle()``    -> oracle/libvkt_oracle.so, the plain-C restatement (oracle/vkt_oracle.c)
+* ``reference()`` -> oracle/_ref/libvkt_ref.so, the UNMODIFIED reference serial path compiled from
+                    /root/reference by oracle/Makefile (prebuilt file travels to the GPU box)
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this module.  The product
+package (volkit_b200/) must never do so.
+
+Volumes are numpy arrays shaped (Z, Y, X) (x fastest, as reference src/vkt/StructuredVolume.cpp:311-317)
+wrapped in ``Vol`` together with DataFormat and the (lo, hi) voxel mapping.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+# numeric values of vkt::DataFormat (reference include/cpp/vkt/common.hpp:53-66)
+INT8, INT16, INT32, UINT8, UINT16, UINT32, FLOAT32 = 1, 2, 3, 4, 5, 6, 7
+DTYPES = {INT8: np.int8, INT16: np.int16, INT32: np.int32, UINT8: np.uint8, UINT16: np.uint16,
+          UINT32: np.uint32, FLOAT32: np.float32}
+FORMAT_NAMES = {UINT8: "UInt8", UINT16: "UInt16", UINT32: "UInt32", FLOAT32: "Float32", INT16: "Int16"}
+
+# arithmetic op ids, order of reference include/cpp/vkt/Arithmetic.hpp
+SUM, DIFF, PROD, QUOT, ABSDIFF, SAFESUM, SAFEDIFF, SAFEPROD, SAFEQUOT, SAFEABSDIFF = range(10)
+ARITH_NAMES = ["Sum", "Diff", "Prod", "Quot", "AbsDiff", "SafeSum", "SafeDiff", "SafeProd", "SafeQuot",
+               "SafeAbsDiff"]
+NEAREST, LINEAR, TRILINEAR = 0, 1, 2
+
+
+class CVol(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("dims", ctypes.c_int32 * 3), ("format", ctypes.c_int32),
+                ("lo", ctypes.c_float), ("hi", ctypes.c_float)]
+
+
+I3 = ctypes.c_int32 * 3
+
+
+@dataclass
+class Vol:
+    a: np.ndarray          # (Z, Y, X), C-contiguous, dtype DTYPES[fmt]
+    fmt: int
+    lo: float = 0.0
+    hi: float = 1.0
+
+    def c(self) -> CVol:
+        assert self.a.flags["C_CONTIGUOUS"] and self.a.ndim == 3
+        v = CVol()
+        v.data = self.a.ctypes.data
+        v.dims[:] = self.a.shape[::-1]
+        v.format = self.fmt
+        v.lo = self.lo
+        v.hi = self.hi
+        return v
+
+    def copy(self) -> "Vol":
+        return Vol(self.a.copy(), self.fmt, self.lo, self.hi)
+
+
+def empty(dims, fmt, lo=0.0, hi=1.0) -> Vol:
+    """dims = (X, Y, Z) like the reference API."""
+    return Vol(np.zeros((dims[2], dims[1], dims[0]), DTYPES[fmt]), fmt, lo, hi)
+
+
+class _Lib:
+    def __init__(self, path: str, prefix: str, kind: str):
+        self.path, self.prefix, self.kind = path, prefix, kind
+        self.lib = ctypes.CDLL(path)
+        p = ctypes.POINTER(CVol)
+        f = self._f
+        f("map_voxel", None, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, ctypes.c_float, ctypes.c_float])
+        f("unmap_voxel", ctypes.c_float, [ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_float])
+        f("fill_range", ctypes.c_int, [p, I3, I3, ctypes.c_float])
+        f("copy_range", ctypes.c_int, [p, p, I3, I3, I3])
+        f("arith_range", ctypes.c_int, [ctypes.c_int, p, p, p, I3, I3, I3])
+        f("transform_range1", ctypes.c_int, [p, I3, I3, ctypes.c_int])
+        f("transform_range2", ctypes.c_int, [p, p, I3, I3, ctypes.c_int])
+        f("resample", ctypes.c_int, [p, p, ctypes.c_int])
+        if prefix == "vko_":
+            f("resample_window", ctypes.c_int, [p, p, ctypes.c_int, ctypes.c_int32, I3, ctypes.c_int32, I3])
+            f("synth_fill", None, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64])
+
+    def _f(self, name, res, args):
+        fn = getattr(self.lib, self.prefix + name)
+        fn.restype, fn.argtypes = res, args
+        setattr(self, "_" + name, fn)
+
+    # ---- scalar codec
+    def map_voxel(self, value: float, fmt: int, lo=0.0, hi=1.0) -> bytes:
+        b = np.zeros(8, np.uint8)
+        self._map_voxel(b.ctypes.data, value, fmt, lo, hi)
+        return bytes(b[: np.dtype(DTYPES[fmt]).itemsize])
+
+    def unmap_voxel(self, raw: bytes, fmt: int, lo=0.0, hi=1.0) -> float:
+        b = np.frombuffer(bytes(raw) + b"\0" * 8, np.uint8).copy()
+        return float(self._unmap_voxel(b.ctypes.data, fmt, lo, hi))
+
+    # ---- algorithms (in place on the numpy buffers)
+    def fill_range(self, vol: Vol, first, last, value: float):
+        assert self._fill_range(ctypes.byref(vol.c()), I3(*first), I3(*last), value) == 0
+
+    def copy_range(self, dst: Vol, src: Vol, first, last, off=(0, 0, 0)):
+        assert self._copy_range(ctypes.byref(dst.c()), ctypes.byref(src.c()), I3(*first), I3(*last), I3(*off)) == 0
+
+    def arith_range(self, op: int, dst: Vol, s1: Vol, s2: Vol, first, last, off=(0, 0, 0)):
+        assert self._arith_range(op, ctypes.byref(dst.c()), ctypes.byref(s1.c()), ctypes.byref(s2.c()),
+                                 I3(*first), I3(*last), I3(*off)) == 0
+
+    def transform_range1(self, vol: Vol, first, last, op: int):
+        assert self._transform_range1(ctypes.byref(vol.c()), I3(*first), I3(*last), op) == 0
+
+    def transform_range2(self, v1: Vol, v2: Vol, first, last, op: int):
+        assert self._transform_range2(ctypes.byref(v1.c()), ctypes.byref(v2.c()), I3(*first), I3(*last), op) == 0
+
+    def resample(self, dst: Vol, src: Vol, filter: int):
+        assert self._resample(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter) == 0
+
+    def resample_window(self, dst: Vol, src: Vol, filter: int, dz0: int, dst_full, sz0: int, src_full):
+        assert self._resample_window(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter, dz0, I3(*dst_full),
+                                     sz0, I3(*src_full)) == 0
+
+
+def synth(n_or_dims, fmt: int, seed: int, first_voxel: int = 0) -> np.ndarray:
+    """SURVEY.md 8(d) counter-based inputs: element i <- splitmix64(i ^ seed*phi)."""
+    lib = oracle()
+    if isinstance(n_or_dims, (tuple, list)):
+        x, y, z = n_or_dims
+        out = np.empty((z, y, x), DTYPES[fmt])
+    else:
+        out = np.empty(int(n_or_dims), DTYPES[fmt])
+    lib._synth_fill(out.ctypes.data, first_voxel, out.size, fmt, seed)
+    return out
+
+
+def synth_numpy(n: int, fmt: int, seed: int, first_voxel: int = 0) -> np.ndarray:
+    """Vectorised numpy twin of vko_synth_fill (fast enough for 10^9 voxels)."""
+    M = np.uint64(0xFFFFFFFFFFFFFFFF)
+    with np.errstate(over="ignore"):
+        k = np.uint64((seed * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)
+        x = (np.arange(first_voxel, first_voxel + n, dtype=np.uint64) ^ k) + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    _ = M
+    if fmt == FLOAT32:
+        return ((x >> np.uint64(40)).astype(np.float32) * np.float32(2.0 ** -24)).astype(np.float32)
+    return x.astype(DTYPES[fmt])
+
+
+_cache: dict = {}
+
+
+def build(ref: bool = True) -> None:
+    """Build the checkers (building the checker is not using it)."""
+    target = "all" if ref else "oracle"
+    subprocess.run(["make", "-C", HERE, target], check=True, stdout=subprocess.DEVNULL)
+
+
+def oracle() -> _Lib:
+    if "o" not in _cache:
+        path = os.path.join(HERE, "libvkt_oracle.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        _cache["o"] = _Lib(path, "vko_", "port")
+    return _cache["o"]
+
+
+def have_reference() -> bool:
+    return os.path.exists(os.path.join(HERE, "_ref", "libvkt_ref.so"))
+
+
+def reference() -> _Lib:
+    if "r" not in _cache:
+        _cache["r"] = _Lib(os.path.join(HERE, "_ref", "libvkt_ref.so"), "ref_", "reference")
+    return _cache["r"]

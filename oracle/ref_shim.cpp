@@ -1,0 +1,252 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into, imported by or shipped with the product
+// (volkit_b200/).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+// reference legs may load the library this file is built into.
+//
+// Flat extern "C" driver over the UNMODIFIED reference (Kniggi/volkit) serial CPU path.
+// The reference sources are compiled where they lie under /root/reference by oracle/Makefile;
+// this file only *calls* the reference's public C++ API (include/cpp/vkt/*.hpp) so that Python
+// (ctypes) can run the reference on caller-provided byte buffers:
+//
+//   vkt::FillRange      include/cpp/vkt/Fill.hpp        -> src/vkt/Fill.cpp:56-83
+//   vkt::CopyRange      include/cpp/vkt/Copy.hpp        -> src/vkt/Copy.cpp:26-121
+//   vkt::*Range (x10)   include/cpp/vkt/Arithmetic.hpp  -> src/vkt/Arithmetic.cpp:26-714
+//   vkt::TransformRange include/cpp/vkt/Transform.hpp   -> src/vkt/Transform.cpp:26-71
+//   vkt::Resample       include/cpp/vkt/Resample.hpp    -> src/vkt/Resample.cpp:22-31
+//   vkt::MapVoxel/UnmapVoxel include/cpp/vkt/Voxel.hpp  -> src/vkt/Voxel.cpp
+//
+// Every call runs under the reference's default thread policy {CPU, Serial}.
+
+#include <cstdint>
+#include <cstring>
+#include <cstdlib>
+
+#include <vkt/Arithmetic.hpp>
+#include <vkt/Copy.hpp>
+#include <vkt/ExecutionPolicy.hpp>
+#include <vkt/Fill.hpp>
+#include <vkt/Resample.hpp>
+#include <vkt/StructuredVolume.hpp>
+#include <vkt/Transform.hpp>
+#include <vkt/Voxel.hpp>
+
+#include "Transform_serial.hpp" // reference-internal: src/vkt/Transform_serial.hpp (binary overload)
+
+namespace {
+
+// POD volume descriptor shared with the ctypes side (same field order as vktb_vol, include/vktb/backend.h)
+struct RefVol
+{
+    void*   data;
+    int32_t dims[3];
+    int32_t format;    // vkt::DataFormat numeric value
+    float   lo, hi;
+};
+
+// A reference volume that holds a private copy of the caller's bytes.
+struct Staged
+{
+    vkt::StructuredVolume vol;
+    RefVol const*         desc;
+    size_t                bytes;
+
+    explicit Staged(RefVol const* d)
+        : vol(d->dims[0], d->dims[1], d->dims[2], (vkt::DataFormat)d->format, 1.f, 1.f, 1.f, d->lo, d->hi)
+        , desc(d)
+    {
+        bytes = vol.getSizeInBytes();
+        if (bytes) std::memcpy(vol.getData(), d->data, bytes);
+    }
+
+    void writeBack() { if (bytes) std::memcpy(desc->data, vol.getData(), bytes); }
+};
+
+typedef vkt::Error (*ArithFn)(vkt::StructuredVolume&, vkt::StructuredVolume&, vkt::StructuredVolume&,
+                              vkt::Vec3i, vkt::Vec3i, vkt::Vec3i);
+
+ArithFn arithTable(int op)
+{
+    switch (op)
+    {
+    case 0: return (ArithFn)&vkt::SumRange;
+    case 1: return (ArithFn)&vkt::DiffRange;
+    case 2: return (ArithFn)&vkt::ProdRange;
+    case 3: return (ArithFn)&vkt::QuotRange;
+    case 4: return (ArithFn)&vkt::AbsDiffRange;
+    case 5: return (ArithFn)&vkt::SafeSumRange;
+    case 6: return (ArithFn)&vkt::SafeDiffRange;
+    case 7: return (ArithFn)&vkt::SafeProdRange;
+    case 8: return (ArithFn)&vkt::SafeQuotRange;
+    case 9: return (ArithFn)&vkt::SafeAbsDiffRange;
+    }
+    return nullptr;
+}
+
+// ---- Transform ops used by the parity tests (same source text is compiled for the device in
+// volkit_b200/csrc/kernels/transform_ops.cuh; the semantics come from SURVEY.md 8(d) and
+// src/examples/CoreAlgorithms.c:20-24 / src/examples/Arithmetic.cpp:9-21). -----------------
+
+int bytesPerVoxel(vkt::DataFormat f)
+{
+    switch (f)
+    {
+    case vkt::DataFormat::Int8:  case vkt::DataFormat::UInt8:  return 1;
+    case vkt::DataFormat::Int16: case vkt::DataFormat::UInt16: return 2;
+    default: return 4;
+    }
+}
+
+// op 0: bytes[0] ^= (x+y+z)
+void opXorCoord(int32_t x, int32_t y, int32_t z, vkt::VoxelView v)
+{
+    v.bytes[0] ^= (uint8_t)(x + y + z);
+}
+
+// op 1: bitwise invert every byte of the voxel
+void opInvert(int32_t, int32_t, int32_t, vkt::VoxelView v)
+{
+    int n = bytesPerVoxel(v.dataFormat);
+    for (int i = 0; i < n; ++i) v.bytes[i] = (uint8_t)~v.bytes[i];
+}
+
+// op 2: 3-D checkerboard of cell size 8: black cells are zeroed, white cells untouched
+void opChecker8(int32_t x, int32_t y, int32_t z, vkt::VoxelView v)
+{
+    if ((((x >> 3) + (y >> 3) + (z >> 3)) & 1) == 0)
+    {
+        int n = bytesPerVoxel(v.dataFormat);
+        for (int i = 0; i < n; ++i) v.bytes[i] = 0;
+    }
+}
+
+// op 3: threshold through the voxel mapping: value < 0.5*(lo+hi) -> lo else hi
+void opThreshold(int32_t, int32_t, int32_t, vkt::VoxelView v)
+{
+    float val = 0.f;
+    vkt::UnmapVoxel(val, v.bytes, v.dataFormat, v.mappingLo, v.mappingHi);
+    float mid = 0.5f * (v.mappingLo + v.mappingHi);
+    float out = val < mid ? v.mappingLo : v.mappingHi;
+    vkt::MapVoxel(v.bytes, out, v.dataFormat, v.mappingLo, v.mappingHi);
+}
+
+// binary op 0: v1 |= v2; v2 = v1   (bytewise)
+void op2OrAssign(int32_t, int32_t, int32_t, vkt::VoxelView v1, vkt::VoxelView v2)
+{
+    int n = bytesPerVoxel(v1.dataFormat);
+    for (int i = 0; i < n; ++i) { v1.bytes[i] |= v2.bytes[i]; v2.bytes[i] = v1.bytes[i]; }
+}
+
+// binary op 1: swap the two voxels bytewise
+void op2Swap(int32_t, int32_t, int32_t, vkt::VoxelView v1, vkt::VoxelView v2)
+{
+    int n = bytesPerVoxel(v1.dataFormat);
+    for (int i = 0; i < n; ++i) { uint8_t t = v1.bytes[i]; v1.bytes[i] = v2.bytes[i]; v2.bytes[i] = t; }
+}
+
+vkt::TransformUnaryOp unaryTable(int op)
+{
+    switch (op)
+    {
+    case 0: return &opXorCoord;
+    case 1: return &opInvert;
+    case 2: return &opChecker8;
+    case 3: return &opThreshold;
+    }
+    return nullptr;
+}
+
+vkt::TransformBinaryOp binaryTable(int op)
+{
+    switch (op)
+    {
+    case 0: return &op2OrAssign;
+    case 1: return &op2Swap;
+    }
+    return nullptr;
+}
+
+vkt::Vec3i v3(int32_t const* p) { return { p[0], p[1], p[2] }; }
+
+} // namespace
+
+extern "C" {
+
+int ref_abi_version() { return 1; }
+
+void ref_map_voxel(uint8_t* dst, float value, int fmt, float lo, float hi)
+{
+    vkt::MapVoxel(dst, value, (vkt::DataFormat)fmt, lo, hi);
+}
+
+float ref_unmap_voxel(uint8_t const* src, int fmt, float lo, float hi)
+{
+    float v = 0.f;
+    vkt::UnmapVoxel(v, src, (vkt::DataFormat)fmt, lo, hi);
+    return v;
+}
+
+int ref_fill_range(RefVol const* vol, int32_t const* first, int32_t const* last, float value)
+{
+    Staged s(vol);
+    vkt::FillRange(s.vol, v3(first), v3(last), value);
+    s.writeBack();
+    return 0;
+}
+
+int ref_copy_range(RefVol const* dst, RefVol const* src, int32_t const* first, int32_t const* last,
+                   int32_t const* off)
+{
+    Staged d(dst), s(src);
+    vkt::CopyRange(d.vol, s.vol, v3(first), v3(last), v3(off));
+    d.writeBack();
+    return 0;
+}
+
+int ref_arith_range(int op, RefVol const* dst, RefVol const* s1, RefVol const* s2,
+                    int32_t const* first, int32_t const* last, int32_t const* off)
+{
+    ArithFn fn = arithTable(op);
+    if (!fn) return -1;
+    Staged d(dst), a(s1), b(s2);
+    fn(d.vol, a.vol, b.vol, v3(first), v3(last), v3(off));
+    d.writeBack();
+    return 0;
+}
+
+int ref_transform_range1(RefVol const* vol, int32_t const* first, int32_t const* last, int op)
+{
+    vkt::TransformUnaryOp fn = unaryTable(op);
+    if (!fn) return -1;
+    Staged s(vol);
+    vkt::TransformRange(s.vol, v3(first), v3(last), fn);
+    s.writeBack();
+    return 0;
+}
+
+// The reference declares but never defines the C++ binary overloads (include/cpp/vkt/Transform.hpp:30-62);
+// the binary form is only reachable through the C API (src/vkt/Transform.cpp:117-153).
+// so the shim calls the serial body directly (src/vkt/Transform_serial.hpp:53-103), which is what
+// vktTransformRangeSV2 dispatches to under the CPU policy.
+int ref_transform_range2(RefVol const* vol1, RefVol const* vol2, int32_t const* first, int32_t const* last, int op)
+{
+    vkt::TransformBinaryOp fn = binaryTable(op);
+    if (!fn) return -1;
+    Staged a(vol1), b(vol2);
+    vkt::TransformRange_serial(a.vol, b.vol, v3(first), v3(last), fn);
+    a.writeBack();
+    b.writeBack();
+    return 0;
+}
+
+// filter: 0 = Nearest, 1 = Linear (include/cpp/vkt/Resample.hpp:14-18)
+int ref_resample(RefVol const* dst, RefVol const* src, int filter)
+{
+    // Note: under Linear the reference's unclamped hi.x tap reads one voxel past the end of src at
+    // the very last src voxel (StructuredVolumeView.hpp:90-99); the value is multiplied by weight 0.
+    // The read stays inside the malloc chunk (glibc rounds chunks up to 16n+8 bytes).
+    Staged d(dst), s(src);
+    vkt::Resample(d.vol, s.vol, filter ? vkt::FilterMode::Linear : vkt::FilterMode::Nearest);
+    d.writeBack();
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,64 @@
+/* TEST INFRASTRUCTURE ONLY -- see vkt_oracle.c.  Plain-C restatement of the reference's serial
+ * CPU path for the StructuredVolume hot path.  Never linked into or imported by the product. */
+#ifndef VKT_ORACLE_H
+#define VKT_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* numeric values of vkt::DataFormat (reference include/cpp/vkt/common.hpp:53-66) */
+enum {
+    VKO_UNSPECIFIED = 0, VKO_INT8 = 1, VKO_INT16 = 2, VKO_INT32 = 3,
+    VKO_UINT8 = 4, VKO_UINT16 = 5, VKO_UINT32 = 6, VKO_FLOAT32 = 7
+};
+
+/* arithmetic op ids, in the order of reference include/cpp/vkt/Arithmetic.hpp */
+enum {
+    VKO_SUM = 0, VKO_DIFF, VKO_PROD, VKO_QUOT, VKO_ABSDIFF,
+    VKO_SAFESUM, VKO_SAFEDIFF, VKO_SAFEPROD, VKO_SAFEQUOT, VKO_SAFEABSDIFF
+};
+
+/* same field order as vktb_vol (include/vktb/backend.h) and RefVol (oracle/ref_shim.cpp) */
+typedef struct vko_vol {
+    void*   data;
+    int32_t dims[3];
+    int32_t format;
+    float   lo, hi;
+} vko_vol;
+
+int   vko_abi_version(void);
+int   vko_bytes_per_voxel(int format);
+void  vko_map_voxel(uint8_t* dst, float value, int format, float lo, float hi);
+float vko_unmap_voxel(const uint8_t* src, int format, float lo, float hi);
+
+int vko_fill_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], float value);
+int vko_copy_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3],
+                   const int32_t last[3], const int32_t off[3]);
+int vko_arith_range(int op, const vko_vol* dst, const vko_vol* s1, const vko_vol* s2,
+                    const int32_t first[3], const int32_t last[3], const int32_t off[3]);
+int vko_transform_range1(const vko_vol* vol, const int32_t first[3], const int32_t last[3], int op);
+int vko_transform_range2(const vko_vol* v1, const vko_vol* v2, const int32_t first[3],
+                         const int32_t last[3], int op);
+/* filter 0 = Nearest, 1 = Linear (reference-faithful, "mode R"), 2 = true trilinear ("mode T",
+ * a restatement of sampleLinear with float parameters and the six intended clamps) */
+int vko_resample(const vko_vol* dst, const vko_vol* src, int filter);
+/* windowed form used to check z-slab sharding and full-size volumes plane by plane: computes dst
+ * planes [dz0, dz1) of a (virtual) dst volume of dims dst_dims_full from a src window that starts at
+ * global src plane sz0 of a (virtual) src volume of dims src_dims_full; dst->data / src->data point
+ * at the first plane of the window and dst->dims[2] / src->dims[2] hold the window heights. */
+int vko_resample_window(const vko_vol* dst, const vko_vol* src, int filter,
+                        int32_t dz0, const int32_t dst_dims_full[3],
+                        int32_t sz0, const int32_t src_dims_full[3]);
+
+/* synthetic inputs of SURVEY.md 8(d): element i of a volume with seed s gets the low bits of
+ * splitmix64(i ^ s*0x9E3779B97F4A7C15); Float32 gets (h>>40)*2^-24 in [0,1). */
+void vko_synth_fill(void* data, size_t first_voxel, size_t n_voxels, int format, uint64_t seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

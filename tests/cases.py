@@ -1,0 +1,113 @@
+"""Shared case catalogue for the golden fixtures.
+
+Every case is (name, kind, params); inputs are regenerated from seeds (src1 = 1,
+src2 = 2, dst pre-fill = 3) so only the reference's OUTPUT bytes are stored in tests/golden/golden.npz.
+`run_case(lib, case)` runs a case on any implementation exposing the pyoracle._Lib method set (the C
+restatement, the compiled reference, or the CUDA product adapter in tests/gpu_adapter.py).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from oracle import pyoracle as po
+
+U8, U16, U32, F32 = po.UINT8, po.UINT16, po.UINT32, po.FLOAT32
+FMT4 = [U8, U16, U32, F32]
+
+
+def mk(dims, fmt, seed, lo=0.0, hi=1.0):
+    return po.Vol(po.synth(dims, fmt, seed), fmt, lo, hi)
+
+
+def cases():
+    out = []
+    # --- Fill: SURVEY.md F6 table + ranges
+    for fmt in FMT4:
+        for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
+            for value in (0.0, 0.1, 0.5, 0.999, 1.0, 1.5, -0.25, 2999.0):
+                out.append((f"fill/{fmt}/{lo}/{hi}/{value}", "fill",
+                            dict(dims=(13, 7, 5), fmt=fmt, lo=lo, hi=hi, first=(1, 0, 2), last=(12, 7, 4), value=value)))
+    # --- Copy: same-format (bytewise) and converting, dstOffset, clamped src
+    for dfmt in FMT4:
+        for sfmt in FMT4:
+            for smap in ((0.0, 1.0), (-1000.0, 3000.0)):
+                for first, last, off in (((0, 0, 0), (12, 9, 7), (0, 0, 0)), ((1, 2, 1), (11, 8, 6), (8, 8, 8)),
+                                         ((-3, -2, -1), (15, 11, 9), (1, 2, 3))):
+                    out.append((f"copy/{dfmt}/{sfmt}/{smap[0]}/{first}/{off}", "copy",
+                                dict(ddims=(32, 24, 20), sdims=(12, 9, 7), dfmt=dfmt, sfmt=sfmt, smap=smap,
+                                     first=first, last=last, off=off)))
+    # --- Arithmetic: 10 ops x formats x mappings, whole + range/offset
+    combos = [(U16, U16, U16), (U8, U8, U8), (U32, U32, U32), (F32, F32, F32), (U8, U16, F32), (F32, U8, U32),
+              (U16, F32, U8)]
+    for op in range(10):
+        for dfmt, f1, f2 in combos:
+            for dmap in ((0.0, 1.0), (-1000.0, 3000.0)):
+                out.append((f"arith/{op}/{dfmt}/{f1}/{f2}/{dmap[0]}", "arith",
+                            dict(op=op, ddims=(40, 12, 10), sdims=(33, 9, 7), dfmt=dfmt, f1=f1, f2=f2, dmap=dmap,
+                                 s2map=((0.0, 1.0), (-1000.0, 3000.0))[op % 2],
+                                 first=(3, 1, 2), last=(32, 9, 6), off=(8, 3, 4))))
+        out.append((f"arith/{op}/whole", "arith",
+                    dict(op=op, ddims=(37, 11, 6), sdims=(37, 11, 6), dfmt=U16, f1=U16, f2=U16, dmap=(0.0, 1.0),
+                         s2map=(0.0, 1.0), first=(0, 0, 0), last=(37, 11, 6), off=(0, 0, 0))))
+    # --- Transform
+    for fmt in FMT4:
+        for op in range(4):
+            out.append((f"transform1/{fmt}/{op}", "transform1",
+                        dict(dims=(21, 19, 18), fmt=fmt, lo=-1000.0, hi=3000.0, first=(1, 2, 3), last=(20, 18, 17), op=op)))
+        for op in range(2):
+            out.append((f"transform2/{fmt}/{op}", "transform2",
+                        dict(dims=(21, 9, 8), fmt=fmt, first=(1, 0, 1), last=(21, 8, 7), op=op)))
+    # --- Resample: nearest + linear(reference) over down/up/equal/anisotropic dims
+    for sfmt in FMT4:
+        for dfmt in FMT4:
+            for ddims in ((8, 6, 5), (24, 18, 15), (16, 12, 10), (9, 17, 7), (33, 5, 11)):
+                for filt in (po.NEAREST, po.LINEAR):
+                    out.append((f"resample/{sfmt}/{dfmt}/{ddims}/{filt}", "resample",
+                                dict(sdims=(16, 12, 10), ddims=ddims, sfmt=sfmt, dfmt=dfmt, filt=filt,
+                                     smap=(0.0, 1.0), dmap=(-1.0, 2.0))))
+    # --- BASELINE config 1 (CLI pipeline on a 64^3 uint8 volume -> 32^3 uint16)
+    out.append(("cli/config1", "cli1", dict()))
+    return out
+
+
+def run_case(lib, case) -> list[np.ndarray]:
+    """Returns the list of output arrays of the case."""
+    _, kind, p = case
+    if kind == "fill":
+        v = mk(p["dims"], p["fmt"], 3, p["lo"], p["hi"])
+        lib.fill_range(v, p["first"], p["last"], p["value"])
+        return [v.a]
+    if kind == "copy":
+        d = mk(p["ddims"], p["dfmt"], 3)
+        s = mk(p["sdims"], p["sfmt"], 1, *p["smap"])
+        lib.copy_range(d, s, p["first"], p["last"], p["off"])
+        return [d.a]
+    if kind == "arith":
+        d = mk(p["ddims"], p["dfmt"], 3, *p["dmap"])
+        s1 = mk(p["sdims"], p["f1"], 1)
+        s2 = mk(p["sdims"], p["f2"], 2, *p["s2map"])
+        lib.arith_range(p["op"], d, s1, s2, p["first"], p["last"], p["off"])
+        return [d.a]
+    if kind == "transform1":
+        v = mk(p["dims"], p["fmt"], 1, p["lo"], p["hi"])
+        lib.transform_range1(v, p["first"], p["last"], p["op"])
+        return [v.a]
+    if kind == "transform2":
+        a, b = mk(p["dims"], p["fmt"], 1), mk(p["dims"], p["fmt"], 2)
+        lib.transform_range2(a, b, p["first"], p["last"], p["op"])
+        return [a.a, b.a]
+    if kind == "resample":
+        s = mk(p["sdims"], p["sfmt"], 1, *p["smap"])
+        d = mk(p["ddims"], p["dfmt"], 3, *p["dmap"])
+        lib.resample(d, s, p["filt"])
+        return [d.a]
+    if kind == "cli1":
+        # declare-sv 64^3 uint8 | fill 0.1 | fill-range 1 [0,8)^3 | resample --dims 32^3 uint16
+        # (reference src/cli/main.cpp:402-442, 521-574, 701-740; the CLI resamples with Nearest, :734)
+        v = po.empty((64, 64, 64), U8)
+        lib.fill_range(v, (0, 0, 0), (64, 64, 64), 0.1)
+        lib.fill_range(v, (0, 0, 0), (8, 8, 8), 1.0)
+        d = po.empty((32, 32, 32), U16)
+        lib.resample(d, v, po.NEAREST)
+        return [v.a, d.a]
+    raise ValueError(kind)

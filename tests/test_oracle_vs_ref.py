@@ -1,0 +1,148 @@
+"""Pins the C restatement (oracle/vkt_oracle.c) against the UNMODIFIED reference serial path
+(oracle/_ref/libvkt_ref.so, built from /root/reference by oracle/Makefile): byte equality on
+identical seeded inputs for every hot-path function, all four in-scope formats (+Int16)."""
+import itertools
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.needs_ref
+
+FMTS = [po.UINT8, po.UINT16, po.UINT32, po.FLOAT32, po.INT16]
+MAPPINGS = [(0.0, 1.0), (-1000.0, 3000.0)]
+
+
+def mk(dims, fmt, seed, lo=0.0, hi=1.0):
+    return po.Vol(po.synth(dims, fmt, seed), fmt, lo, hi)
+
+
+def same(a: po.Vol, b: po.Vol):
+    return a.a.tobytes() == b.a.tobytes()
+
+
+def test_scalar_codec_sweep():
+    o, r = po.oracle(), po.reference()
+    for lo, hi in MAPPINGS + [(0.25, 0.75)]:
+        for fmt, n in ((po.UINT8, 256), (po.UINT16, 65536), (po.INT16, 65536)):
+            for i in range(0, n, 1 if n == 256 else 17):
+                raw = int(i).to_bytes(2, "little")[: 1 if n == 256 else 2]
+                vo, vr = o.unmap_voxel(raw, fmt, lo, hi), r.unmap_voxel(raw, fmt, lo, hi)
+                assert np.float32(vo).tobytes() == np.float32(vr).tobytes()
+                assert o.map_voxel(vo, fmt, lo, hi) == r.map_voxel(vr, fmt, lo, hi)
+
+
+def test_map_edge_values():
+    o, r = po.oracle(), po.reference()
+    edge = [0.0, -0.0, 0.1, 0.5, 0.999, 1.0, 1.5, -0.25, 2.0, -1.0, 1e-30, -1e-30, 1e10, -1e10, 3e38, -3e38,
+            float("inf"), float("-inf"), float("nan"), 0.99999994, 32767.5 / 65536, 255.0 / 255.999]
+    for fmt in FMTS:
+        for lo, hi in MAPPINGS + [(1.0, 1.0), (1.0, 0.0)]:
+            for v in edge:
+                assert o.map_voxel(v, fmt, lo, hi) == r.map_voxel(v, fmt, lo, hi), (fmt, lo, hi, v)
+
+
+@pytest.mark.parametrize("fmt", FMTS)
+def test_fill(fmt):
+    o, r = po.oracle(), po.reference()
+    for lo, hi in MAPPINGS:
+        for value in (0.1, 1.0, 1.5, -0.25, 2500.0):
+            a, b = mk((9, 7, 5), fmt, 3, lo, hi), mk((9, 7, 5), fmt, 3, lo, hi)
+            o.fill_range(a, (1, 2, 0), (8, 6, 4), value)
+            r.fill_range(b, (1, 2, 0), (8, 6, 4), value)
+            assert same(a, b)
+
+
+@pytest.mark.parametrize("dfmt,sfmt", list(itertools.product(FMTS[:4], FMTS[:4])))
+def test_copy(dfmt, sfmt):
+    o, r = po.oracle(), po.reference()
+    for (dlo, dhi), (slo, shi) in (((0, 1), (0, 1)), ((0, 1), (-1000, 3000))):
+        src = mk((8, 6, 5), sfmt, 1, slo, shi)
+        for first, last, off in (((0, 0, 0), (8, 6, 5), (0, 0, 0)), ((1, 2, 1), (7, 5, 4), (3, 2, 1)),
+                                 ((-2, -1, -3), (10, 8, 7), (1, 1, 1))):
+            a, b = mk((16, 14, 12), dfmt, 3, dlo, dhi), mk((16, 14, 12), dfmt, 3, dlo, dhi)
+            o.copy_range(a, src, first, last, off)
+            r.copy_range(b, src, first, last, off)
+            assert same(a, b)
+
+
+@pytest.mark.parametrize("op", range(10))
+def test_arith(op):
+    o, r = po.oracle(), po.reference()
+    for dfmt, f1, f2 in ((po.UINT16,) * 3, (po.UINT8,) * 3, (po.UINT32,) * 3, (po.FLOAT32,) * 3,
+                         (po.UINT8, po.UINT16, po.FLOAT32), (po.FLOAT32, po.UINT8, po.UINT32), (po.INT16,) * 3):
+        for (dlo, dhi) in MAPPINGS:
+            s1, s2 = mk((11, 6, 5), f1, 1), mk((11, 6, 5), f2, 2, *MAPPINGS[op % 2])
+            a, b = mk((16, 9, 8), dfmt, 3, dlo, dhi), mk((16, 9, 8), dfmt, 3, dlo, dhi)
+            o.arith_range(op, a, s1, s2, (1, 0, 2), (10, 6, 5), (4, 3, 2))
+            r.arith_range(op, b, s1, s2, (1, 0, 2), (10, 6, 5), (4, 3, 2))
+            assert same(a, b), (op, dfmt, f1, f2)
+
+
+def test_arith_exhaustive_u8_pairs():
+    """all 65536 UInt8 x UInt8 pairs for each of the ten ops."""
+    o, r = po.oracle(), po.reference()
+    g = np.arange(256, dtype=np.uint8)
+    A = np.repeat(g, 256).reshape(1, 256, 256).copy()
+    B = np.tile(g, 256).reshape(1, 256, 256).copy()
+    for op in range(10):
+        for lo, hi in MAPPINGS:
+            a, b = po.empty((256, 256, 1), po.UINT8, lo, hi), po.empty((256, 256, 1), po.UINT8, lo, hi)
+            o.arith_range(op, a, po.Vol(A, po.UINT8), po.Vol(B, po.UINT8, lo, hi), (0, 0, 0), (256, 256, 1))
+            r.arith_range(op, b, po.Vol(A, po.UINT8), po.Vol(B, po.UINT8, lo, hi), (0, 0, 0), (256, 256, 1))
+            assert same(a, b), op
+
+
+@pytest.mark.parametrize("fmt", FMTS[:4])
+def test_transform(fmt):
+    o, r = po.oracle(), po.reference()
+    for op in range(4):
+        a, b = mk((20, 19, 18), fmt, 1, -1000, 3000), mk((20, 19, 18), fmt, 1, -1000, 3000)
+        o.transform_range1(a, (1, 2, 3), (19, 18, 17), op)
+        r.transform_range1(b, (1, 2, 3), (19, 18, 17), op)
+        assert same(a, b), op
+    for op in range(2):
+        a1, a2 = mk((9, 8, 7), fmt, 1), mk((9, 8, 7), fmt, 2)
+        b1, b2 = a1.copy(), a2.copy()
+        o.transform_range2(a1, a2, (1, 0, 1), (9, 7, 6), op)
+        r.transform_range2(b1, b2, (1, 0, 1), (9, 7, 6), op)
+        assert same(a1, b1) and same(a2, b2)
+
+
+@pytest.mark.parametrize("sfmt,dfmt", list(itertools.product(FMTS[:4], FMTS[:4])))
+def test_resample(sfmt, dfmt):
+    o, r = po.oracle(), po.reference()
+    src = mk((12, 10, 8), sfmt, 1, 0.0, 1.0)
+    for ddims in ((6, 5, 4), (18, 15, 12), (12, 10, 8), (7, 13, 5), (24, 3, 9)):
+        for filt in (po.NEAREST, po.LINEAR):
+            a, b = po.empty(ddims, dfmt, -1.0, 2.0), po.empty(ddims, dfmt, -1.0, 2.0)
+            o.resample(a, src, filt)
+            r.resample(b, src, filt)
+            assert same(a, b), (ddims, filt)
+
+
+def test_resample_linear_equals_nearest_in_reference():
+    """the reference's Linear mode is numerically nearest-floor."""
+    r = po.reference()
+    src = mk((16, 16, 16), po.UINT16, 1)
+    a, b = po.empty((24, 24, 24), po.UINT16), po.empty((24, 24, 24), po.UINT16)
+    r.resample(a, src, po.NEAREST)
+    r.resample(b, src, po.LINEAR)
+    assert same(a, b)
+
+
+def test_resample_window_matches_whole():
+    o = po.oracle()
+    src = mk((10, 9, 16), po.UINT16, 1)
+    for ddims in ((15, 7, 24), (5, 9, 8)):
+        for filt in (po.NEAREST, po.LINEAR, po.TRILINEAR):
+            whole = po.empty(ddims, po.UINT16)
+            o.resample(whole, src, filt)
+            for dz0, dz1 in ((0, ddims[2] // 2), (ddims[2] // 2, ddims[2])):
+                zs = [int(np.float32(np.float32(z) / np.float32(ddims[2])) * np.float32(16)) for z in (dz0, dz1 - 1)]
+                sz0, sz1 = zs[0], min(zs[1] + 2, 16)
+                win = po.Vol(src.a[sz0:sz1].copy(), po.UINT16)
+                part = po.empty((ddims[0], ddims[1], dz1 - dz0), po.UINT16)
+                o.resample_window(part, win, filt, dz0, ddims, sz0, (10, 9, 16))
+                assert part.a.tobytes() == whole.a[dz0:dz1].tobytes()
