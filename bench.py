@@ -1,0 +1,421 @@
+#!/usr/bin/env python
+"""volkit-b200 benchmark.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size S] [--ops]
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one synthetic batch:
+SafeSum on an S^3 UInt16 volume per GPU (S = 2048 by default: the configuration BASELINE.json's target is
+quoted on; 3 x 16 GiB resident in HBM, far larger than L2, so no L2 flush is needed between iterations).
+N > 1 (torchrun, one process per GPU): every rank owns one S^3 z-slab of a (S, S, N*S) volume -- the ops
+are voxel-independent, so there is no data-path collective; only the timing barrier uses NCCL ("weak" scaling).
+
+  value     whole-job GVoxels/s with inputs resident in HBM (CUDA events on the launching stream, max over ranks)
+  e2e       the same metric through the C-ABI with HOST buffers: pinned H2D of both sources, kernel, D2H of dest
+  roofline  SafeSum kernel: algorithmic bytes (6 B/voxel UInt16) / measured launch duration vs measured HBM peak
+  cpu_baseline  the reference's own serial CPU path (oracle/_ref) on a bounded sample, host cores stated
+  ops       (with --ops, default at N=1) per-op table: Resample 2048^3 -> 1024^3 / 3072^3, Fill, Copy, Transform
+
+--impl reference times the reference's CPU implementation (all host cores, one process per core, each on its
+own sub-volume) on the same metric.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "SafeSum GVoxels/s (UInt16)"
+UNIT = "GVoxels/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=2048, help="edge of the per-GPU UInt16 volume")
+    ap.add_argument("--ops", type=int, default=-1, help="1/0: also time the per-op table (default: on at N=1)")
+    ap.add_argument("--cpu-sample", type=int, default=384, help="edge of the CPU-baseline sub-volume")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ peaks / clocks
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (the recipe's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def _ref_worker(args):
+    """One process = the reference's serial SafeSum on its own edge^3 UInt16 sub-volume."""
+    edge, seed, kind = args
+    from oracle import pyoracle as po
+    lib = po.reference() if kind == "reference" else po.oracle()
+    dims = (edge, edge, edge)
+    a = po.Vol(po.synth_numpy(edge ** 3, po.UINT16, 1 + seed).reshape(edge, edge, edge), po.UINT16)
+    b = po.Vol(po.synth_numpy(edge ** 3, po.UINT16, 2 + seed).reshape(edge, edge, edge), po.UINT16)
+    d = po.empty(dims, po.UINT16)
+    t0 = time.perf_counter()
+    lib.arith_range(po.SAFESUM, d, a, b, (0, 0, 0), dims)
+    return time.perf_counter() - t0
+
+
+def cpu_rate(edge, procs, steps=1, warmup=0):
+    """GVoxels/s of the reference CPU path: `procs` processes, each SafeSum on an edge^3 sub-volume per step."""
+    import multiprocessing as mp
+    from oracle import pyoracle as po
+    kind = "reference" if po.have_reference() else "port"
+    times = []
+    if procs == 1:
+        for s in range(warmup + steps):
+            t = _ref_worker((edge, s, kind))
+            if s >= warmup:
+                times.append(t)
+    else:
+        ctx = mp.get_context("fork")
+        with ctx.Pool(procs) as pool:
+            for s in range(warmup + steps):
+                # workers synthesise their own inputs, then time the op alone; a step lasts as long as its slowest worker
+                ts = pool.map(_ref_worker, [(edge, s * procs + i, kind) for i in range(procs)])
+                if s >= warmup:
+                    times.append(max(ts))
+    sec = float(np.mean(times))
+    return procs * edge ** 3 / sec / 1e9, sec, kind
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    edge = 256
+    val, sec, kind = cpu_rate(edge, cores, steps=max(1, min(args.steps, 5)), warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 arithmetic on u16 voxels", "data": "synthetic",
+        "config": {"workload": f"SafeSum {args.size}^3 UInt16 per GPU", "sample": f"{cores} x {edge}^3 UInt16 per step"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{cores} processes x SafeSum {edge}^3 UInt16 (reference serial path, one process per core)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def torch_synth(torch, n, fmt_bytes, seed, first=0, device="cuda", float32=False):
+    """vko_synth_fill on the GPU (input synthesis only): element i <- splitmix64(i ^ seed*phi)."""
+    def u64(v):
+        v &= 0xFFFFFFFFFFFFFFFF
+        return v - (1 << 64) if v >= (1 << 63) else v
+
+    def lsr(x, k):
+        return (x >> k) & ((1 << (64 - k)) - 1)
+    k = u64(seed * 0x9E3779B97F4A7C15)
+    x = torch.arange(first, first + n, dtype=torch.int64, device=device) ^ k
+    x = x + u64(0x9E3779B97F4A7C15)
+    x = (x ^ lsr(x, 30)) * u64(0xBF58476D1CE4E5B9)
+    x = (x ^ lsr(x, 27)) * u64(0x94D049BB133111EB)
+    x = x ^ lsr(x, 31)
+    if float32:
+        return lsr(x, 40).to(torch.float32) * (2.0 ** -24)
+    if fmt_bytes == 1:
+        return (x & 0xFF).to(torch.uint8)
+    if fmt_bytes == 2:
+        return (x & 0xFFFF).to(torch.int32).to(torch.int16)   # bit pattern of the u16
+    return (x & 0xFFFFFFFF).to(torch.int64).to(torch.int32)
+
+
+def fill_synth(torch, lib, capi, vol, seed, chunk=1 << 27):
+    """Fills a DeviceVolume with the SURVEY.md 8(d) synthetic stream, chunk by chunk."""
+    bpv = capi.BYTES_PER_VOXEL[vol.fmt]
+    n = vol.nbytes // bpv
+    for first in range(0, n, chunk):
+        m = min(chunk, n - first)
+        t = torch_synth(torch, m, bpv, seed, first, float32=(vol.fmt == capi.FLOAT32))
+        capi.check(lib.vktb_memcpy(vol.ptr + first * bpv, t.data_ptr(), m * bpv, capi.D2D), "synth D2D")
+        torch.cuda.current_stream().synchronize()
+        del t
+    torch.cuda.empty_cache()
+
+
+def time_steps(torch, fn, steps, warmup, dist=None):
+    """W warm-ups, then K steps between two CUDA events on the launching stream; max over ranks."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        torch.cuda.synchronize()
+        ms = float(t.item())
+    return ms / steps
+
+
+def check_planes(po, capi, lib, vol_d, seeds, op, size, planes):
+    """Full-size parity through size-independent sampling: a few z-planes vs the oracle on regenerated inputs."""
+    plane = size * size
+    for z in planes:
+        a = po.Vol(po.synth_numpy(plane, po.UINT16, seeds[0], z * plane).reshape(1, size, size), po.UINT16)
+        b = po.Vol(po.synth_numpy(plane, po.UINT16, seeds[1], z * plane).reshape(1, size, size), po.UINT16)
+        ref = po.empty((size, size, 1), po.UINT16)
+        po.oracle().arith_range(op, ref, a, b, (0, 0, 0), (size, size, 1))
+        got = np.empty((1, size, size), np.uint16)
+        capi.check(lib.vktb_memcpy(got.ctypes.data, vol_d.ptr + z * plane * 2, plane * 2, capi.D2H), "plane D2H")
+        if got.tobytes() != ref.a.tobytes():
+            return False
+    return True
+
+
+def mem_available_bytes():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except Exception:
+        pass
+    return 0
+
+
+def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
+    """The call a user makes: host buffers in, host buffer out, through the C-ABI (= what vkt::SafeSum does after
+    ManagedBuffer::migrate): per step pinned H2D of both sources, SafeSum kernel, D2H of the destination."""
+    vol_bytes = size ** 3 * 2
+    host = []
+    for _ in range(3):
+        p = ctypes.c_void_p()
+        capi.check(lib.vktb_host_alloc(ctypes.byref(p), vol_bytes), "vktb_host_alloc")
+        host.append(p.value)
+    # host inputs = the same synthetic volumes (copied down once, outside the timed region)
+    capi.check(lib.vktb_memcpy(host[0], src_a.ptr, vol_bytes, capi.D2H))
+    capi.check(lib.vktb_memcpy(host[1], src_b.ptr, vol_bytes, capi.D2H))
+    z, l = capi.I3(0, 0, 0), capi.I3(size, size, size)
+
+    def step():
+        a, b, d = dv((size,) * 3, capi.UINT16), dv((size,) * 3, capi.UINT16), dv((size,) * 3, capi.UINT16)
+        capi.check(lib.vktb_memcpy(a.ptr, host[0], vol_bytes, capi.H2D))
+        capi.check(lib.vktb_memcpy(b.ptr, host[1], vol_bytes, capi.H2D))
+        capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(d.desc()), ctypes.byref(a.desc()),
+                                        ctypes.byref(b.desc()), z, l, z))
+        capi.check(lib.vktb_memcpy(host[2], d.ptr, vol_bytes, capi.D2H))   # complete on return
+        a.free(); b.free(); d.free()
+
+    ms = time_steps(torch, step, steps, warmup, dist)
+    sample = np.ctypeslib.as_array(ctypes.cast(host[2], ctypes.POINTER(ctypes.c_uint16)), shape=(size * size,)).copy()
+    for h in host:
+        capi.check(lib.vktb_host_free(h))
+    return ms, 2 * vol_bytes, vol_bytes, sample
+
+
+def run_ours(args):
+    import torch
+    from volkit_b200 import capi, launch_count
+    from volkit_b200.device import DeviceVolume
+    from oracle import pyoracle as po   # checker + cpu_baseline leg only
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    lib = capi.load()
+    capi.check(lib.vktb_set_device(local), "vktb_set_device")
+    # kernels run on torch's current stream so torch CUDA events bracket exactly the stream they are launched on
+    capi.check(lib.vktb_set_stream(torch.cuda.current_stream().cuda_stream))
+
+    S = args.size
+    dims = (S, S, S)
+    nvox = S ** 3
+    a, b, d = DeviceVolume(dims, capi.UINT16), DeviceVolume(dims, capi.UINT16), DeviceVolume(dims, capi.UINT16)
+    zoff = rank * S   # this rank's slab of the (S, S, world*S) volume
+    seed_a, seed_b = 1, 2
+    first_voxel = zoff * S * S
+    # synthetic inputs (slab-consistent: voxel index counts across the whole sharded volume)
+    bpv = 2
+    for vol, seed in ((a, seed_a), (b, seed_b)):
+        for f0 in range(0, nvox, 1 << 27):
+            m = min(1 << 27, nvox - f0)
+            t = torch_synth(torch, m, bpv, seed, first_voxel + f0)
+            capi.check(lib.vktb_memcpy(vol.ptr + f0 * bpv, t.data_ptr(), m * bpv, capi.D2D))
+            torch.cuda.synchronize()
+            del t
+    torch.cuda.empty_cache()
+
+    z, l = capi.I3(0, 0, 0), capi.I3(*dims)
+    da, db, dd = a.desc(), b.desc(), d.desc()
+
+    def step():
+        capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z, l, z))
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = launch_count()
+    ms = time_steps(torch, step, args.steps, args.warmup, dist)
+    launches = launch_count() - l0 - args.warmup
+    clocks = sampler.stop() if rank == 0 else {}
+
+    # parity at full size: sampled z-planes vs the oracle on regenerated inputs
+    plane = S * S
+    planes = sorted({0, 1, S // 3, S // 2, S - 1})
+    ok = True
+    for zp in planes:
+        av = po.Vol(po.synth_numpy(plane, po.UINT16, seed_a, first_voxel + zp * plane).reshape(1, S, S), po.UINT16)
+        bv = po.Vol(po.synth_numpy(plane, po.UINT16, seed_b, first_voxel + zp * plane).reshape(1, S, S), po.UINT16)
+        ref = po.empty((S, S, 1), po.UINT16)
+        po.oracle().arith_range(po.SAFESUM, ref, av, bv, (0, 0, 0), (S, S, 1))
+        got = np.empty((1, S, S), np.uint16)
+        capi.check(lib.vktb_memcpy(got.ctypes.data, d.ptr + zp * plane * 2, plane * 2, capi.D2H))
+        ok = ok and got.tobytes() == ref.a.tobytes()
+
+    value = world * nvox / (ms * 1e-3) / 1e9
+    peak, peak_src = measured_peak()
+    alg_bytes = 6.0 * nvox
+    achieved = alg_bytes / (ms * 1e-3) / 1e9
+
+    e2e = None
+    if not args.no_e2e:
+        need = 3 * nvox * 2 + (8 << 30)
+        Se = S
+        while Se > 256 and 3 * Se ** 3 * 2 + (8 << 30) > mem_available_bytes():
+            Se //= 2
+        d.free()
+        if Se != S:
+            a.free(); b.free()
+            a, b = DeviceVolume((Se,) * 3, capi.UINT16), DeviceVolume((Se,) * 3, capi.UINT16)
+            for vol, seed in ((a, seed_a), (b, seed_b)):
+                t = torch_synth(torch, Se ** 3, 2, seed, 0)
+                capi.check(lib.vktb_memcpy(vol.ptr, t.data_ptr(), Se ** 3 * 2, capi.D2D))
+                torch.cuda.synchronize()
+                del t
+        e_steps = max(2, min(args.steps, 4))
+        e_ms, h2d, d2h, _ = run_e2e(torch, lib, capi, DeviceVolume, Se, e_steps, 1, dist, a, b)
+        e2e = {"value": world * Se ** 3 / (e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": e_steps,
+               "workload": f"SafeSum {Se}^3 UInt16 per GPU, pinned host buffers (vktb_host_alloc) -> vktb_memcpy H2D x2 -> "
+                           f"kernel -> vktb_memcpy D2H", "host_mem_limited": Se != S and need > 0}
+
+    ops = None
+    want_ops = args.ops == 1 or (args.ops == -1 and world == 1)
+    if want_ops:
+        a.free(); b.free()
+        try:
+            d.free()
+        except Exception:
+            pass
+        from bench_ops import run_ops
+        ops = run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps)
+
+    cpu = None
+    if rank == 0:
+        edge = args.cpu_sample
+        v, sec, kind = cpu_rate(edge, 1, steps=1, warmup=0)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": kind,
+               "sample": f"SafeSum {edge}^3 UInt16, reference serial path, 1 thread, {sec:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 arithmetic on u16 voxels", "data": "synthetic",
+            "config": {"workload": f"SafeSum {S}^3 UInt16 per GPU (z-slab {rank} of a {S}x{S}x{world * S} volume)",
+                       "l2": "inputs (3 x %.1f GiB) far larger than the 126 MB L2: no flush needed" % (nvox * 2 / 2 ** 30),
+                       "parallelism": f"z-slab x{world}, no data-path collective"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "arithFlatKernel<UInt16,SafeSum>",
+                         "algorithmic_bytes_per_voxel": 6, "frac_of_8TBs_nominal": achieved / 8000.0},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "parity": {"bit_exact_planes": planes, "ok": bool(ok)}, "ops": ops,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

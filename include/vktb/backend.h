@@ -1,0 +1,154 @@
+/* volkit-b200 -- the drop-in boundary.
+ *
+ * C-ABI of libvktb200.so: the B200 (sm_100a) backend for the voxel-parallel StructuredVolume core of
+ * Kniggi/volkit.  Each entry point replaces one internal `*_cuda` backend function (or one Memory
+ * primitive) of the reference; the reference-side shims that bind them are shown in INTEGRATION.md.
+ * File:line citations are relative to the reference tree.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every function returns 0 on success, non-zero on failure and
+ *     leaves a per-thread message retrievable with vktb_last_error(); nothing throws.
+ *   - `vktb_vol.data` is a DEVICE pointer obtained from vktb_alloc() (the algorithms never touch host
+ *     memory and there is no CPU fallback: without a usable GPU every entry point fails loudly).
+ *   - volumes are dense, x fastest: byte offset = ((z*dimX*dimY) + y*dimX + x) * bytesPerVoxel
+ *     (src/vkt/StructuredVolume.cpp:311-317), little endian.
+ *   - algorithms are asynchronous on the backend's per-device compute stream; results are visible to
+ *     the host after the next device-to-host vktb_memcpy() (which orders itself after them) or
+ *     vktb_sync() -- the same contract as the reference, where the D2H cudaMemcpy is the sync point
+ *     (SURVEY.md 3.1).
+ *   - ranges are half open [first,last); an empty range is a no-op.  As in the reference, dst bounds
+ *     are the caller's responsibility (README.md:140).
+ */
+#ifndef VKTB_BACKEND_H
+#define VKTB_BACKEND_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
+
+#define VKTB_ABI_VERSION 1
+
+/* numeric values of vkt::DataFormat / vktDataFormat (include/cpp/vkt/common.hpp:53-66) */
+enum vktb_format {
+    VKTB_UNSPECIFIED = 0, VKTB_INT8 = 1, VKTB_INT16 = 2, VKTB_INT32 = 3,
+    VKTB_UINT8 = 4, VKTB_UINT16 = 5, VKTB_UINT32 = 6, VKTB_FLOAT32 = 7
+};
+
+/* vkt::CopyKind (include/cpp/vkt/Memory.hpp:15-21) */
+enum vktb_copy_kind { VKTB_H2H = 0, VKTB_H2D = 1, VKTB_D2H = 2, VKTB_D2D = 3 };
+
+/* the ten arithmetic ops in the order of include/cpp/vkt/Arithmetic.hpp */
+enum vktb_arith_op {
+    VKTB_SUM = 0, VKTB_DIFF, VKTB_PROD, VKTB_QUOT, VKTB_ABSDIFF,
+    VKTB_SAFESUM, VKTB_SAFEDIFF, VKTB_SAFEPROD, VKTB_SAFEQUOT, VKTB_SAFEABSDIFF
+};
+
+/* vkt::FilterMode (include/cpp/vkt/Resample.hpp:14-18) plus the opt-in true trilinear filter */
+enum vktb_filter {
+    VKTB_NEAREST   = 0,
+    VKTB_LINEAR    = 1,  /* reference-faithful: what StructuredVolumeView::sampleLinear computes */
+    VKTB_TRILINEAR = 2   /* mathematically correct trilinear; NOT what the reference computes */
+};
+
+/* POD twin of StructuredVolumeView (src/vkt/StructuredVolumeView.hpp:19-33, 214-219) */
+typedef struct vktb_vol {
+    void*   data;      /* device pointer */
+    int32_t dims[3];   /* x, y, z */
+    int32_t format;    /* enum vktb_format */
+    float   lo, hi;    /* voxel mapping */
+} vktb_vol;
+
+/* ---- library / device ------------------------------------------------------------------------- */
+int         vktb_abi_version(void);
+const char* vktb_last_error(void);                 /* per-thread, never NULL */
+int         vktb_device_count(int* n);
+int         vktb_set_device(int ordinal);          /* device used by the calling thread (default 0) */
+int         vktb_get_device(int* ordinal);
+/* number of kernels this library has launched so far (all threads); evidence for "gpu_launches" */
+uint64_t    vktb_launch_count(void);
+/* the compute stream (a cudaStream_t) of the calling thread's device; vktb_set_stream(NULL) restores
+ * the backend-owned stream */
+void*       vktb_get_stream(void);
+int         vktb_set_stream(void* cuda_stream);
+int         vktb_sync(void);                       /* waits for compute + copy streams of the device */
+
+/* ---- memory: replaces Allocate_cuda / Free_cuda / cudaMemcpy / MemsetRange_cuda ----------------
+ * src/vkt/Memory_cuda.hpp:16-32, src/vkt/Memory.cpp:40-74, src/vkt/Memory_cuda.cu:15-49 */
+int vktb_alloc(void** ptr, size_t bytes);          /* pooled, stream-ordered device allocation */
+int vktb_free(void* ptr);
+/* Blocking contract of ManagedBuffer::migrate (include/cpp/vkt/ManagedBuffer.hpp:168-198): on return
+ * the SOURCE may be freed or overwritten.  H2D from pageable memory is pipelined through pinned staging
+ * (returns once the last chunk left the source; the DMA tail is ordered before later kernels);
+ * H2D from pinned memory (vktb_host_alloc) is a single DMA.  D2H is complete on return. */
+int vktb_memcpy(void* dst, const void* src, size_t bytes, int copy_kind);
+int vktb_memset_range(void* dst, const void* pattern, size_t dst_bytes, size_t pattern_bytes);
+/* pinned host memory from a reuse pool: what vkt::Allocate hands out under the CPU policy so that
+ * migrate() becomes one full-speed DMA */
+int vktb_host_alloc(void** ptr, size_t bytes);
+int vktb_host_free(void* ptr);
+int vktb_mem_stats(size_t* device_bytes_in_use, size_t* device_bytes_reserved,
+                   size_t* pinned_bytes_in_use, size_t* pinned_bytes_reserved);
+int vktb_trim_pools(void);                         /* give cached device / pinned memory back */
+
+/* ---- algorithms -------------------------------------------------------------------------------- */
+/* FillRange_cuda(StructuredVolumeView, Vec3i, Vec3i, float)  src/vkt/Fill_cuda.hpp:13, Fill_cuda.cu:22-55;
+ * semantics of FillRange_serial, src/vkt/Fill_serial.hpp:20-26 */
+int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], float value);
+
+/* CopyRange_cuda  src/vkt/Copy_cuda.hpp:11-17; semantics of CopyRange_serial, src/vkt/Copy_serial.hpp:13-82:
+ * dst[p - first + off] = src[clamp(p, 0, srcDims-1)], raw bytes if format and mapping agree, else by value */
+int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3],
+                    const int32_t last[3], const int32_t dst_offset[3]);
+
+/* {Sum..SafeAbsDiff}Range_cuda  src/vkt/Arithmetic_cuda.hpp:10-98; semantics of ArithmeticOp,
+ * src/vkt/Arithmetic_serial.hpp:15-45: dst[p + off] = map(f(unmap(s1[p]), unmap(s2[p]))), p absolute */
+int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2,
+                     const int32_t first[3], const int32_t last[3], const int32_t dst_offset[3]);
+
+/* TransformRange_cuda (unary / binary)  src/vkt/Transform_cuda.hpp:12-30 (empty stubs in the reference);
+ * semantics of TransformRange_serial, src/vkt/Transform_serial.hpp:15-103.  A host function pointer cannot
+ * run on the device: `op` is a device-op handle from the registry below. */
+int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op);
+int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int32_t first[3],
+                          const int32_t last[3], int op);
+
+/* Resample_cuda(StructuredVolume&, StructuredVolume&, FilterMode)  src/vkt/Resample_cuda.hpp:12-16;
+ * semantics of Resample_serial, src/vkt/Resample_serial.hpp:26-71 (incl. the equal-dims conversion branch) */
+int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter);
+/* z-slab form for sharded volumes: computes dst planes [dst_z0, dst_z0 + dst->dims[2]) of a volume of
+ * dims dst_full from a src window holding planes [src_z0, src_z0 + src->dims[2]) of a volume of dims
+ * src_full.  vktb_resample_window_src_range() tells which src planes a dst slab needs (incl. the +1 tap). */
+int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter,
+                         int32_t dst_z0, const int32_t dst_full[3],
+                         int32_t src_z0, const int32_t src_full[3]);
+int vktb_resample_window_src_range(int filter, int32_t dst_z0, int32_t dst_z1, int32_t dst_dimz,
+                                   int32_t src_dimz, int32_t* src_z0, int32_t* src_z1);
+
+/* ---- Transform device-op registry --------------------------------------------------------------
+ * Built-in ops are addressed by name; a host TransformUnaryOp / TransformBinaryOp pointer is bound to a
+ * device op once, after which the unchanged vkt::Transform(volume, hostFn) signature resolves it.
+ * Unbound host pointers make Transform fail with InvalidValue under the GPU policy (no CPU fallback). */
+int vktb_unary_op_by_name(const char* name, int* op);     /* "xor_coord", "invert", "checker8", "threshold" */
+int vktb_binary_op_by_name(const char* name, int* op);    /* "or_assign", "swap" */
+int vktb_bind_unary_op(const void* host_fn, int op);
+int vktb_bind_binary_op(const void* host_fn, int op);
+int vktb_lookup_unary_op(const void* host_fn, int* op);   /* non-zero if unbound */
+int vktb_lookup_binary_op(const void* host_fn, int* op);
+
+/* ---- scalar codec on the device (1 thread): used by tests to pin the float/convert emulation ----- */
+int vktb_debug_map_unmap(int format, float lo, float hi, const float* values_dev, uint32_t* mapped_dev,
+                         float* unmapped_dev, size_t n);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* VKTB_BACKEND_H */

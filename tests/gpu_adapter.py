@@ -1,0 +1,72 @@
+"""Runs the case catalogue (tests/cases.py) on the CUDA product THROUGH THE C-ABI: every call uploads the
+numpy inputs with vktb_memcpy, runs one vktb_* algorithm on the device and downloads the outputs.
+Exposes the same method set as oracle.pyoracle._Lib so cases.run_case() works unchanged."""
+from __future__ import annotations
+
+import ctypes
+
+from oracle import pyoracle as po
+from volkit_b200 import capi
+from volkit_b200.device import DeviceVolume
+
+I3 = capi.I3
+
+
+class GpuLib:
+    kind = "cuda"
+
+    def __init__(self):
+        self.lib = capi.load()
+
+    @staticmethod
+    def _up(v: po.Vol) -> DeviceVolume:
+        return DeviceVolume.from_numpy(v.a, v.fmt, v.lo, v.hi)
+
+    @staticmethod
+    def _down(dv: DeviceVolume, v: po.Vol) -> None:
+        v.a[...] = dv.download()
+        dv.free()
+
+    def fill_range(self, vol, first, last, value):
+        d = self._up(vol)
+        capi.check(self.lib.vktb_fill_range(ctypes.byref(d.desc()), I3(*first), I3(*last), value), "fill")
+        self._down(d, vol)
+
+    def copy_range(self, dst, src, first, last, off=(0, 0, 0)):
+        d, s = self._up(dst), self._up(src)
+        capi.check(self.lib.vktb_copy_range(ctypes.byref(d.desc()), ctypes.byref(s.desc()), I3(*first), I3(*last),
+                                            I3(*off)), "copy")
+        self._down(d, dst)
+        s.free()
+
+    def arith_range(self, op, dst, s1, s2, first, last, off=(0, 0, 0)):
+        d, a, b = self._up(dst), self._up(s1), self._up(s2)
+        capi.check(self.lib.vktb_arith_range(op, ctypes.byref(d.desc()), ctypes.byref(a.desc()), ctypes.byref(b.desc()),
+                                             I3(*first), I3(*last), I3(*off)), "arith")
+        self._down(d, dst)
+        a.free(); b.free()
+
+    def transform_range1(self, vol, first, last, op):
+        d = self._up(vol)
+        capi.check(self.lib.vktb_transform_range1(ctypes.byref(d.desc()), I3(*first), I3(*last), op), "transform1")
+        self._down(d, vol)
+
+    def transform_range2(self, v1, v2, first, last, op):
+        a, b = self._up(v1), self._up(v2)
+        capi.check(self.lib.vktb_transform_range2(ctypes.byref(a.desc()), ctypes.byref(b.desc()), I3(*first),
+                                                  I3(*last), op), "transform2")
+        self._down(a, v1)
+        self._down(b, v2)
+
+    def resample(self, dst, src, filt):
+        d, s = self._up(dst), self._up(src)
+        capi.check(self.lib.vktb_resample(ctypes.byref(d.desc()), ctypes.byref(s.desc()), filt), "resample")
+        self._down(d, dst)
+        s.free()
+
+    def resample_window(self, dst, src, filt, dz0, dst_full, sz0, src_full):
+        d, s = self._up(dst), self._up(src)
+        capi.check(self.lib.vktb_resample_window(ctypes.byref(d.desc()), ctypes.byref(s.desc()), filt, dz0,
+                                                 I3(*dst_full), sz0, I3(*src_full)), "resample_window")
+        self._down(d, dst)
+        s.free()

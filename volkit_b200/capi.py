@@ -1,0 +1,106 @@
+"""ctypes binding of the C-ABI (include/vktb/backend.h) -- the boundary the reference's shims bind.
+
+There is no Python or CPU implementation behind this module: if libvktb200.so is missing or no B200
+is usable, calls raise.  Build the library with `python -c "import __graft_entry__ as g; g.build()"`
+or `make -C volkit_b200/csrc`.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libvktb200.so")
+
+# vkt::DataFormat values (reference include/cpp/vkt/common.hpp:53-66)
+INT8, INT16, INT32, UINT8, UINT16, UINT32, FLOAT32 = 1, 2, 3, 4, 5, 6, 7
+H2H, H2D, D2H, D2D = 0, 1, 2, 3
+SUM, DIFF, PROD, QUOT, ABSDIFF, SAFESUM, SAFEDIFF, SAFEPROD, SAFEQUOT, SAFEABSDIFF = range(10)
+NEAREST, LINEAR, TRILINEAR = 0, 1, 2
+BYTES_PER_VOXEL = {INT8: 1, UINT8: 1, INT16: 2, UINT16: 2, INT32: 4, UINT32: 4, FLOAT32: 4}
+
+
+class VktbVol(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("dims", ctypes.c_int32 * 3), ("format", ctypes.c_int32),
+                ("lo", ctypes.c_float), ("hi", ctypes.c_float)]
+
+
+I3 = ctypes.c_int32 * 3
+
+# name -> (restype, argtypes); every symbol include/vktb/backend.h declares
+_P = ctypes.POINTER
+_VP = _P(VktbVol)
+SIGNATURES = {
+    "vktb_abi_version": (ctypes.c_int, []),
+    "vktb_last_error": (ctypes.c_char_p, []),
+    "vktb_device_count": (ctypes.c_int, [_P(ctypes.c_int)]),
+    "vktb_set_device": (ctypes.c_int, [ctypes.c_int]),
+    "vktb_get_device": (ctypes.c_int, [_P(ctypes.c_int)]),
+    "vktb_launch_count": (ctypes.c_uint64, []),
+    "vktb_get_stream": (ctypes.c_void_p, []),
+    "vktb_set_stream": (ctypes.c_int, [ctypes.c_void_p]),
+    "vktb_sync": (ctypes.c_int, []),
+    "vktb_alloc": (ctypes.c_int, [_P(ctypes.c_void_p), ctypes.c_size_t]),
+    "vktb_free": (ctypes.c_int, [ctypes.c_void_p]),
+    "vktb_memcpy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
+    "vktb_memset_range": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t]),
+    "vktb_host_alloc": (ctypes.c_int, [_P(ctypes.c_void_p), ctypes.c_size_t]),
+    "vktb_host_free": (ctypes.c_int, [ctypes.c_void_p]),
+    "vktb_mem_stats": (ctypes.c_int, [_P(ctypes.c_size_t)] * 4),
+    "vktb_trim_pools": (ctypes.c_int, []),
+    "vktb_fill_range": (ctypes.c_int, [_VP, I3, I3, ctypes.c_float]),
+    "vktb_copy_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3]),
+    "vktb_arith_range": (ctypes.c_int, [ctypes.c_int, _VP, _VP, _VP, I3, I3, I3]),
+    "vktb_transform_range1": (ctypes.c_int, [_VP, I3, I3, ctypes.c_int]),
+    "vktb_transform_range2": (ctypes.c_int, [_VP, _VP, I3, I3, ctypes.c_int]),
+    "vktb_resample": (ctypes.c_int, [_VP, _VP, ctypes.c_int]),
+    "vktb_resample_window": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int32, I3, ctypes.c_int32, I3]),
+    "vktb_resample_window_src_range": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                                      ctypes.c_int32, _P(ctypes.c_int32), _P(ctypes.c_int32)]),
+    "vktb_unary_op_by_name": (ctypes.c_int, [ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_binary_op_by_name": (ctypes.c_int, [ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_bind_unary_op": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "vktb_bind_binary_op": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "vktb_lookup_unary_op": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),
+    "vktb_lookup_binary_op": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),
+    "vktb_debug_map_unmap": (ctypes.c_int, [ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
+}
+
+
+class VktbError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Loads libvktb200.so; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VktbError(f"{LIB_PATH} is missing: build it first (make -C volkit_b200/csrc); "
+                            "volkit_b200 has no CPU fallback")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)   # AttributeError if the library does not export the symbol
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().vktb_last_error()
+        raise VktbError(f"{what or 'vktb call'} failed ({rc}): {msg.decode() if msg else '?'}")
+
+
+def vol(ptr: int, dims, fmt: int, lo: float = 0.0, hi: float = 1.0) -> VktbVol:
+    v = VktbVol()
+    v.data = ptr
+    v.dims[:] = dims
+    v.format = fmt
+    v.lo = lo
+    v.hi = hi
+    return v

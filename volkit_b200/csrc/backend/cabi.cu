@@ -1,0 +1,226 @@
+// C-ABI algorithm entry points (include/vktb/backend.h): argument validation, then one launcher call.
+#include "context.hpp"
+
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
+#include "../../../include/vktb/backend.h"
+#include "../kernels/launch.hpp"
+
+using namespace vktb;
+
+namespace {
+
+bool supportedFormat(int f) { return f == F_U8 || f == F_U16 || f == F_U32 || f == F_F32 || f == F_INT16; }
+
+// vktb_vol -> VolDesc; returns false (error set) on bad input
+bool toDesc(const char* fn, const vktb_vol* v, VolDesc& d)
+{
+    if (!v) { fail((std::string(fn) + ": null volume").c_str()); return false; }
+    if (!supportedFormat(v->format)) {
+        // Int8 / Int32 have no case in the reference's MapVoxelImpl/UnmapVoxelImpl (VoxelMapping.hpp:26-95)
+        fail((std::string(fn) + ": unsupported DataFormat (UInt8, UInt16, UInt32, Float32, Int16 only)").c_str());
+        return false;
+    }
+    if (v->dims[0] < 0 || v->dims[1] < 0 || v->dims[2] < 0) { fail((std::string(fn) + ": negative dims").c_str()); return false; }
+    const size_t n = (size_t)v->dims[0] * v->dims[1] * v->dims[2];
+    if (n && !v->data) { fail((std::string(fn) + ": null data pointer").c_str()); return false; }
+    d.data = (uint8_t*)v->data;
+    d.dims[0] = v->dims[0]; d.dims[1] = v->dims[1]; d.dims[2] = v->dims[2];
+    d.format = v->format;
+    d.map = makeMapping(v->lo, v->hi);
+    return true;
+}
+
+int finish(const char* fn, cudaError_t e) { return e == cudaSuccess ? 0 : fail(fn, e); }
+
+// Transform registry
+const char* const kUnaryNames[kNumUnaryOps] = { "xor_coord", "invert", "checker8", "threshold" };
+const char* const kBinaryNames[kNumBinaryOps] = { "or_assign", "swap" };
+std::mutex g_opMutex;
+std::unordered_map<const void*, int> g_unaryBound, g_binaryBound;
+
+} // namespace
+
+extern "C" {
+
+int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], float value)
+{
+    VolDesc v;
+    if (!first || !last) return fail("vktb_fill_range: null range");
+    if (!toDesc("vktb_fill_range", vol, v)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_fill_range", launchFill(c, v, first, last, value));
+}
+
+int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                    const int32_t off[3])
+{
+    VolDesc dv, sv;
+    if (!first || !last || !off) return fail("vktb_copy_range: null range");
+    if (!toDesc("vktb_copy_range", dst, dv) || !toDesc("vktb_copy_range", src, sv)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_copy_range", launchCopy(c, dv, sv, first, last, off));
+}
+
+int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2, const int32_t first[3],
+                     const int32_t last[3], const int32_t off[3])
+{
+    VolDesc dv, av, bv;
+    if (op < 0 || op > VKTB_SAFEABSDIFF) return fail("vktb_arith_range: bad op");
+    if (!first || !last || !off) return fail("vktb_arith_range: null range");
+    if (!toDesc("vktb_arith_range", dst, dv) || !toDesc("vktb_arith_range", s1, av) || !toDesc("vktb_arith_range", s2, bv))
+        return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_arith_range", launchArith(c, op, dv, av, bv, first, last, off));
+}
+
+int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op)
+{
+    VolDesc v;
+    if (op < 0 || op >= kNumUnaryOps) return fail("vktb_transform_range1: unknown device op handle");
+    if (!first || !last) return fail("vktb_transform_range1: null range");
+    if (!toDesc("vktb_transform_range1", vol, v)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_transform_range1", launchTransform1(c, v, first, last, op));
+}
+
+int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int32_t first[3], const int32_t last[3], int op)
+{
+    VolDesc a, b;
+    if (op < 0 || op >= kNumBinaryOps) return fail("vktb_transform_range2: unknown device op handle");
+    if (!first || !last) return fail("vktb_transform_range2: null range");
+    if (!toDesc("vktb_transform_range2", vol1, a) || !toDesc("vktb_transform_range2", vol2, b)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_transform_range2", launchTransform2(c, a, b, first, last, op));
+}
+
+int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter, int32_t dstZ0, const int32_t dstFull[3],
+                         int32_t srcZ0, const int32_t srcFull[3])
+{
+    VolDesc dv, sv;
+    if (filter < 0 || filter > VKTB_TRILINEAR) return fail("vktb_resample: bad filter mode");
+    if (!dstFull || !srcFull) return fail("vktb_resample_window: null dims");
+    if (!toDesc("vktb_resample", dst, dv) || !toDesc("vktb_resample", src, sv)) return -1;
+    if (dv.dims[0] != dstFull[0] || dv.dims[1] != dstFull[1] || sv.dims[0] != srcFull[0] || sv.dims[1] != srcFull[1])
+        return fail("vktb_resample_window: windows must span full x/y extents");
+    if (dstZ0 < 0 || dstZ0 + dv.dims[2] > dstFull[2] || srcZ0 < 0 || srcZ0 + sv.dims[2] > srcFull[2])
+        return fail("vktb_resample_window: window outside the full volume");
+    // the src window must hold every plane the dst slab reads (the extra plane the planner requests for
+    // Linear only carries the weight-0 hi.x spill tap and is optional)
+    if (dv.dims[2] > 0) {
+        int32_t need0, need1;
+        const bool same = dstFull[0] == srcFull[0] && dstFull[1] == srcFull[1] && dstFull[2] == srcFull[2];
+        if (same) { need0 = dstZ0; need1 = dstZ0 + dv.dims[2]; }
+        else vktb_resample_window_src_range(filter == VKTB_LINEAR ? VKTB_TRILINEAR : filter, dstZ0, dstZ0 + dv.dims[2],
+                                            dstFull[2], srcFull[2], &need0, &need1);
+        if (srcZ0 > need0 || srcZ0 + sv.dims[2] < need1)
+            return fail("vktb_resample_window: src window misses planes the dst slab reads");
+    }
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_resample", launchResample(c, dv, sv, filter, dstZ0, dstFull, srcZ0, srcFull));
+}
+
+int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
+{
+    if (!dst || !src) return fail("vktb_resample: null volume");
+    return vktb_resample_window(dst, src, filter, 0, dst->dims, 0, src->dims);
+}
+
+// Host-side slab planner: the reference's own coordinate expression (Resample_serial.hpp:60-62) evaluated in
+// binary32 at the slab's first and last dst plane; it is monotone in z.
+int vktb_resample_window_src_range(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t S, int32_t* sz0, int32_t* sz1)
+{
+    if (!sz0 || !sz1 || D <= 0 || S <= 0 || dz1 <= dz0) return fail("vktb_resample_window_src_range: bad arguments");
+    auto coord = [&](int32_t z) {
+        volatile float q = (float)z / (float)D;    // volatile: one rounding per operation, no contraction
+        volatile float s = q * (float)S;
+        float sv = s;
+        int32_t i = (sv >= -2147483648.0f && sv < 2147483648.0f) ? (int32_t)sv : INT32_MIN;
+        return i;
+    };
+    int32_t lo = coord(dz0), hi = coord(dz1 - 1);
+    lo = lo < 0 ? 0 : (lo > S - 1 ? S - 1 : lo);
+    hi = hi < 0 ? 0 : (hi > S - 1 ? S - 1 : hi);
+    int32_t end = hi + 1;                                   // exclusive
+    if (filter != VKTB_NEAREST) end = hi + 2;               // +1 tap plane
+    if (filter == VKTB_LINEAR) end = hi + 3;                // + the plane the unclamped hi.x tap can spill into
+    if (end > S) end = S;
+    *sz0 = lo; *sz1 = end;
+    return 0;
+}
+
+// ---- Transform registry ----
+int vktb_unary_op_by_name(const char* name, int* op)
+{
+    if (!name || !op) return fail("vktb_unary_op_by_name: null argument");
+    for (int i = 0; i < kNumUnaryOps; ++i) if (!strcmp(name, kUnaryNames[i])) { *op = i; return 0; }
+    return fail("vktb_unary_op_by_name: no such built-in device op");
+}
+
+int vktb_binary_op_by_name(const char* name, int* op)
+{
+    if (!name || !op) return fail("vktb_binary_op_by_name: null argument");
+    for (int i = 0; i < kNumBinaryOps; ++i) if (!strcmp(name, kBinaryNames[i])) { *op = i; return 0; }
+    return fail("vktb_binary_op_by_name: no such built-in device op");
+}
+
+int vktb_bind_unary_op(const void* hostFn, int op)
+{
+    if (!hostFn || op < 0 || op >= kNumUnaryOps) return fail("vktb_bind_unary_op: bad arguments");
+    std::lock_guard<std::mutex> lock(g_opMutex);
+    g_unaryBound[hostFn] = op;
+    return 0;
+}
+
+int vktb_bind_binary_op(const void* hostFn, int op)
+{
+    if (!hostFn || op < 0 || op >= kNumBinaryOps) return fail("vktb_bind_binary_op: bad arguments");
+    std::lock_guard<std::mutex> lock(g_opMutex);
+    g_binaryBound[hostFn] = op;
+    return 0;
+}
+
+int vktb_lookup_unary_op(const void* hostFn, int* op)
+{
+    std::lock_guard<std::mutex> lock(g_opMutex);
+    auto it = g_unaryBound.find(hostFn);
+    if (it == g_unaryBound.end() || !op)
+        return fail("Transform: host function pointer has no device op bound (vktb_bind_unary_op); no CPU fallback on the GPU policy");
+    *op = it->second;
+    return 0;
+}
+
+int vktb_lookup_binary_op(const void* hostFn, int* op)
+{
+    std::lock_guard<std::mutex> lock(g_opMutex);
+    auto it = g_binaryBound.find(hostFn);
+    if (it == g_binaryBound.end() || !op)
+        return fail("Transform: host function pointer has no device op bound (vktb_bind_binary_op); no CPU fallback on the GPU policy");
+    *op = it->second;
+    return 0;
+}
+
+int vktb_debug_map_unmap(int format, float lo, float hi, const float* values, uint32_t* mapped, float* unmapped, size_t n)
+{
+    if (!supportedFormat(format)) return fail("vktb_debug_map_unmap: unsupported format");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_debug_map_unmap", launchDebugCodec(c, format, makeMapping(lo, hi), values, mapped, unmapped, n));
+}
+
+} // extern "C"

@@ -1,0 +1,170 @@
+// Arithmetic family (Sum, Diff, Prod, Quot, AbsDiff and their Safe* twins), device side.
+//
+// Semantics: reference src/vkt/Arithmetic_serial.hpp:15-45 (ArithmeticOp loop) and :47-260 (the ten
+// lambdas): dst[p + off] = map_dst( f( unmap_s1(s1[p]), unmap_s2(s2[p]) ) ), p absolute in [first,last),
+// Safe* = clamp(f, dst.lo, dst.hi) with clamp = max(lo, min(x, hi)) in the reference's operand order.
+//
+// Algorithmic traffic: bpv_s1 + bpv_s2 + bpv_dst bytes per voxel, every byte touched exactly once.
+#pragma once
+
+#include "common.cuh"
+#include "voxel_codec.cuh"
+
+namespace vktb {
+
+template <int OP>
+__device__ __forceinline__ float arithEval(float a, float b, float lo, float hi)
+{
+    float r;
+    switch (OP % 5) {
+    case 0:  r = __fadd_rn(a, b); break;
+    case 1:  r = __fsub_rn(a, b); break;
+    case 2:  r = __fmul_rn(a, b); break;
+    case 3:  r = __fdiv_rn(a, b); break;
+    default: r = fabsf(__fsub_rn(a, b)); break;
+    }
+    return OP >= 5 ? refClamp(r, lo, hi) : r;
+}
+
+struct ArithParams
+{
+    Operand d, a, b;      // dst at (first+off), sources at first
+    Range   g;
+    Mapping md, ma, mb;
+    int     alias;        // a source overlaps dst (in-place use): no non-coherent loads
+};
+
+// Homogeneous formats: one 128-bit vector per operand per chunk.
+template <int F, int OP, bool IDENT>
+__device__ __forceinline__ uint4 arithVec(const uint4& va, const uint4& vb, const Mapping& md,
+                                          const Mapping& ma, const Mapping& mb, const float* lutA, const float* lutB)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+        uint32_t ra = vecGet<BPV>(va, i), rb = vecGet<BPV>(vb, i);
+        float fa, fb;
+        if (F == F_U8) { fa = lutA[ra]; fb = lutB[rb]; }
+        else { fa = unmapVoxel<F, IDENT>(ra, ma); fb = unmapVoxel<F, IDENT>(rb, mb); }
+        float r = arithEval<OP>(fa, fb, md.lo, md.hi);
+        vecSet<BPV>(w, i, mapVoxel<F, IDENT>(r, md));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <int F, int OP, bool IDENT>
+__device__ __forceinline__ uint32_t arithOne(uint32_t ra, uint32_t rb, const Mapping& md, const Mapping& ma,
+                                             const Mapping& mb)
+{
+    float fa = unmapVoxel<F, IDENT>(ra, ma), fb = unmapVoxel<F, IDENT>(rb, mb);
+    return mapVoxel<F, IDENT>(arithEval<OP>(fa, fb, md.lo, md.hi), md);
+}
+
+// ---- flat: the range is one contiguous run of n voxels in all three operands, bases congruent mod 16 ----
+template <int F, int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithFlatKernel(uint8_t* __restrict__ d, const uint8_t* a, const uint8_t* b, size_t n, Mapping md, Mapping ma,
+                Mapping mb, int alias)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    __shared__ float lutA[F == F_U8 ? 256 : 1], lutB[F == F_U8 ? 256 : 1];
+    if (F == F_U8) {
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+            lutA[i] = unmapVoxel<F_U8, IDENT>((uint32_t)i, ma);
+            lutB[i] = unmapVoxel<F_U8, IDENT>((uint32_t)i, mb);
+        }
+        __syncthreads();
+    }
+
+    // scalar head up to the first 16-byte boundary, vector body, scalar tail
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(d) & 15u)) & 15u) / BPV;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) / V;
+    const size_t tail0 = head + nvec * V;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+
+    const uint8_t* av = a + head * BPV;
+    const uint8_t* bv = b + head * BPV;
+    uint8_t* dv = d + head * BPV;
+
+    size_t i = tid;
+    // two vectors per operand in flight per thread
+    for (; i + stride < nvec; i += 2 * stride) {
+        uint4 a0, b0, a1, b1;
+        if (alias) { a0 = ldPlain(av + i * 16); b0 = ldPlain(bv + i * 16);
+                     a1 = ldPlain(av + (i + stride) * 16); b1 = ldPlain(bv + (i + stride) * 16); }
+        else       { a0 = ldStream(av + i * 16); b0 = ldStream(bv + i * 16);
+                     a1 = ldStream(av + (i + stride) * 16); b1 = ldStream(bv + (i + stride) * 16); }
+        stStream(dv + i * 16, arithVec<F, OP, IDENT>(a0, b0, md, ma, mb, lutA, lutB));
+        stStream(dv + (i + stride) * 16, arithVec<F, OP, IDENT>(a1, b1, md, ma, mb, lutA, lutB));
+    }
+    for (; i < nvec; i += stride) {
+        uint4 a0 = alias ? ldPlain(av + i * 16) : ldStream(av + i * 16);
+        uint4 b0 = alias ? ldPlain(bv + i * 16) : ldStream(bv + i * 16);
+        stStream(dv + i * 16, arithVec<F, OP, IDENT>(a0, b0, md, ma, mb, lutA, lutB));
+    }
+    // head + tail voxels (at most 2*(V-1)), one per thread of the first CTA(s)
+    const size_t nEdge = head + (n - tail0);
+    for (size_t e = tid; e < nEdge; e += stride) {
+        size_t k = e < head ? e : tail0 + (e - head);
+        uint32_t r = arithOne<F, OP, IDENT>(loadRaw(a + k * BPV, BPV), loadRaw(b + k * BPV, BPV), md, ma, mb);
+        storeRaw(d + k * BPV, BPV, r);
+    }
+}
+
+// ---- rows: general 3-D range with dstOffset; chunks are cut at 16-byte boundaries of the dst row --------
+template <int F, int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithRowsKernel(ArithParams p)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    forEachRowChunk<V, BPV>(p.g, p.d, [&](int y, int z, int xr, int n, bool full) {
+        uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+        const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
+        const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
+        const bool vec = full && ((reinterpret_cast<uintptr_t>(ap) | reinterpret_cast<uintptr_t>(bp)) & 15u) == 0;
+        if (vec) {
+            uint4 va = p.alias ? ldPlain(ap) : ldStream(ap);
+            uint4 vb = p.alias ? ldPlain(bp) : ldStream(bp);
+            uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+                vecSet<BPV>(w, i, arithOne<F, OP, IDENT>(vecGet<BPV>(va, i), vecGet<BPV>(vb, i), p.md, p.ma, p.mb));
+            stStream(dp, make_uint4(w[0], w[1], w[2], w[3]));
+        } else {
+            for (int i = 0; i < n; ++i) {
+                uint32_t r = arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
+                                                    p.md, p.ma, p.mb);
+                storeRaw(dp + i * BPV, BPV, r);
+            }
+        }
+    });
+}
+
+// ---- generic: any mix of formats (runtime codec), one voxel per thread along x ---------------------------
+template <int OP>
+__global__ void __launch_bounds__(kThreads)
+arithGenericKernel(ArithParams p, int fd, int fa, int fb)
+{
+    const int bd = bytesPerVoxel(fd), ba = bytesPerVoxel(fa), bb = bytesPerVoxel(fb);
+    const long long rows = (long long)p.g.ny * p.g.nz;
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+        const int z = (int)(r / p.g.ny), y = (int)(r - (long long)z * p.g.ny);
+        uint8_t* drow = p.d.base + y * p.d.pitchY + z * p.d.pitchZ;
+        const uint8_t* arow = p.a.base + y * p.a.pitchY + z * p.a.pitchZ;
+        const uint8_t* brow = p.b.base + y * p.b.pitchY + z * p.b.pitchZ;
+        for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < p.g.nx; x += gridDim.x * blockDim.x) {
+            float va = unmapVoxelRt(fa, loadRaw(arow + (long long)x * ba, ba), p.ma);
+            float vb = unmapVoxelRt(fb, loadRaw(brow + (long long)x * bb, bb), p.mb);
+            float rr = arithEval<OP>(va, vb, p.md.lo, p.md.hi);
+            storeRaw(drow + (long long)x * bd, bd, mapVoxelRt(fd, rr, p.md));
+        }
+    }
+}
+
+} // namespace vktb

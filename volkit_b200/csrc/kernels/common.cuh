@@ -1,0 +1,122 @@
+// Shared device helpers: 128-bit streaming loads/stores, range geometry, the row-chunk driver.
+//
+// All in-scope algorithms are HBM-bound byte/float streams; the rules that matter are
+// 128-bit coalesced x-fastest accesses, enough bytes in flight per SM and grids sized in multiples of
+// the SM count.  No tensor cores anywhere.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace vktb {
+
+constexpr int kThreads = 256;   // CTA size of every streaming kernel
+
+// ---- 128-bit global accesses with streaming hints (nothing is re-used: keep L1 clean) -----------------
+__device__ __forceinline__ uint4 ldStream(const void* p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// plain (coherent) 128-bit load: for operands that may alias the destination (in-place arithmetic)
+__device__ __forceinline__ uint4 ldPlain(const void* p)
+{
+    return *reinterpret_cast<const uint4*>(p);
+}
+__device__ __forceinline__ void stStream(void* p, const uint4& v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// ---- element access inside a 16-byte register vector --------------------------------------------------
+// BPV = 1, 2 or 4; i is a compile-time constant after unrolling.
+template <int BPV>
+__device__ __forceinline__ uint32_t vecGet(const uint4& v, int i)
+{
+    const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+    if (BPV == 4) return w[i];
+    if (BPV == 2) return (w[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
+    return (w[i >> 2] >> ((i & 3) * 8)) & 0xffu;
+}
+template <int BPV>
+__device__ __forceinline__ void vecSet(uint32_t (&w)[4], int i, uint32_t e)
+{
+    if (BPV == 4) w[i] = e;
+    else if (BPV == 2) w[i >> 1] |= (e & 0xffffu) << ((i & 1) * 16);
+    else w[i >> 2] |= (e & 0xffu) << ((i & 3) * 8);
+}
+
+// ---- 3-D range geometry ----------------------------------------------------------------------------------
+// One operand of a range operation: `base` addresses the operand's voxel that corresponds to the first
+// voxel of the range; pitches are in BYTES.
+struct Operand
+{
+    uint8_t*  base;
+    long long pitchY;
+    long long pitchZ;
+};
+
+struct Range
+{
+    int nx, ny, nz;   // extents of [first,last)
+    int x0, y0, z0;   // absolute coordinates of the first voxel (ops that see coordinates; copy clamps)
+};
+
+// Launch shape of a rows kernel: blockDim = (tx, 256/tx), grid = (chunk blocks, row blocks).
+struct RowsLaunch { dim3 grid, block; };
+
+inline RowsLaunch rowsLaunch(int nx, long long rows, int vecElems)
+{
+    // +1 chunk: the dst-aligned chunking may split the row's head and tail across two extra chunks
+    int chunks = (nx + vecElems - 1) / vecElems + 1;
+    int tx = 1;
+    while (tx < chunks && tx < kThreads) tx <<= 1;
+    int ty = kThreads / tx;
+    RowsLaunch l;
+    l.block = dim3(tx, ty, 1);
+    long long gy = (rows + ty - 1) / ty;
+    if (gy > 65535) gy = 65535;
+    l.grid = dim3((chunks + tx - 1) / tx, (unsigned)gy, 1);
+    return l;
+}
+
+// The row-chunk driver.  Rows are the (y,z) lines of the range; each thread owns chunks of V consecutive
+// voxels cut at 16-byte boundaries of the DESTINATION row, so full chunks can be stored with one 128-bit
+// store.  body(y, z, xr, n, full) is called with xr = first range-relative x of the chunk, n = valid voxels
+// (n == V && full -> the dst address of xr is 16-byte aligned and the chunk lies fully inside the row).
+template <int V, int BPVD, class Body>
+__device__ __forceinline__ void forEachRowChunk(const Range& g, const Operand& dst, Body body)
+{
+    const long long rows = (long long)g.ny * g.nz;
+    const int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows;
+         r += (long long)gridDim.y * blockDim.y) {
+        const int z = (int)(r / g.ny);
+        const int y = (int)(r - (long long)z * g.ny);
+        const uint8_t* drow = dst.base + y * dst.pitchY + z * dst.pitchZ;
+        const int shift = (int)((reinterpret_cast<uintptr_t>(drow) & 15u) / BPVD);   // voxels into a 16B line
+        int xr = chunk * V - shift;
+        int n = V;
+        if (xr < 0) { n += xr; xr = 0; }
+        if (xr + n > g.nx) n = g.nx - xr;
+        if (n <= 0) continue;
+        body(y, z, xr, n, n == V);
+    }
+}
+
+// Grid for flat (1-D) streaming kernels: enough CTAs to fill every SM several times over, capped so the
+// grid-stride loop amortises the launch; always a multiple of the SM count.
+inline unsigned flatGrid(size_t work, int perCta, int smCount, int ctasPerSm)
+{
+    size_t need = (work + (size_t)perCta - 1) / (size_t)perCta;
+    size_t cap = (size_t)smCount * (size_t)ctasPerSm;
+    if (need >= cap) return (unsigned)cap;
+    size_t g = (need + (size_t)smCount - 1) / (size_t)smCount * (size_t)smCount;   // round up to SM multiple
+    if (g == 0) g = (size_t)smCount;
+    return (unsigned)(g < cap ? g : cap);
+}
+
+} // namespace vktb

@@ -1,0 +1,90 @@
+// Host-side launcher interface between the C-ABI (backend/cabi.cpp) and the kernels (*.cu).
+#pragma once
+
+#include <atomic>
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+#include "voxel_codec.cuh"
+
+namespace vktb {
+
+struct VolDesc
+{
+    uint8_t* data;
+    int      dims[3];
+    int      format;
+    Mapping  map;
+};
+
+struct LaunchCtx
+{
+    cudaStream_t stream;
+    int          smCount;
+};
+
+// Every kernel launch of the library goes through this counter (vktb_launch_count()).
+extern std::atomic<uint64_t> g_launchCount;
+inline void countLaunch() { g_launchCount.fetch_add(1, std::memory_order_relaxed); }
+
+// Host twin of the Mapping preparation (binary32 arithmetic, identical on host and device).
+Mapping makeMapping(float lo, float hi);
+
+// first/last/off are the reference's Vec3i arguments, passed through unchanged.
+cudaError_t launchFill(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], float value);
+cudaError_t launchCopy(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
+                       const int32_t last[3], const int32_t off[3]);
+cudaError_t launchArith(const LaunchCtx&, int op, const VolDesc& dst, const VolDesc& s1, const VolDesc& s2,
+                        const int32_t first[3], const int32_t last[3], const int32_t off[3]);
+cudaError_t launchTransform1(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], int op);
+cudaError_t launchTransform2(const LaunchCtx&, const VolDesc& v1, const VolDesc& v2, const int32_t first[3],
+                             const int32_t last[3], int op);
+cudaError_t launchResample(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, int filter,
+                           int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
+cudaError_t launchConvertFlat(const LaunchCtx&, const VolDesc& dst, uint8_t* d, const VolDesc& src, const uint8_t* s, size_t n);
+cudaError_t launchConvertRows(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
+                              const int32_t last[3], const int32_t off[3]);
+cudaError_t launchMemsetRange(const LaunchCtx&, void* dst, const void* patternDev, size_t dstBytes, size_t patBytes);
+cudaError_t launchDebugCodec(const LaunchCtx&, int format, Mapping m, const float* values, uint32_t* mapped,
+                             float* unmapped, size_t n);
+
+// number of built-in transform ops (transform.cu)
+constexpr int kNumUnaryOps = 4;
+constexpr int kNumBinaryOps = 2;
+
+// 64-bit voxel offset of (x,y,z) in a volume, reference StructuredVolume.cpp:311-317
+inline long long voxelIndex(const VolDesc& v, long long x, long long y, long long z)
+{
+    return (z * v.dims[1] + y) * (long long)v.dims[0] + x;
+}
+
+// ---- geometry helpers shared by the launchers ----
+inline bool overlaps(const VolDesc& a, const VolDesc& b)
+{
+    size_t na = (size_t)a.dims[0] * a.dims[1] * a.dims[2] * bytesPerVoxel(a.format);
+    size_t nb = (size_t)b.dims[0] * b.dims[1] * b.dims[2] * bytesPerVoxel(b.format);
+    return a.data < b.data + nb && b.data < a.data + na;
+}
+
+inline Operand operandAt(const VolDesc& v, long long x, long long y, long long z)
+{
+    const int bpv = bytesPerVoxel(v.format);
+    Operand o;
+    o.base = v.data + voxelIndex(v, x, y, z) * bpv;
+    o.pitchY = (long long)v.dims[0] * bpv;
+    o.pitchZ = (long long)v.dims[0] * v.dims[1] * bpv;
+    return o;
+}
+
+// the range is one contiguous run in volume v
+inline bool contiguous(const VolDesc& v, const Range& g)
+{
+    if (g.ny == 1 && g.nz == 1) return true;
+    if (g.nx != v.dims[0]) return false;
+    return g.nz == 1 || g.ny == v.dims[1];
+}
+
+
+} // namespace vktb
