@@ -31,6 +31,11 @@ __device__ __forceinline__ void stStream(void* p, const uint4& v)
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+__device__ __forceinline__ void stStream32(void* p, uint32_t v)
+{
+    asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
 // ---- element access inside a 16-byte register vector --------------------------------------------------
 // BPV = 1, 2 or 4; i is a compile-time constant after unrolling.
 template <int BPV>

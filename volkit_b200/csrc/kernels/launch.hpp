@@ -43,6 +43,8 @@ cudaError_t launchTransform2(const LaunchCtx&, const VolDesc& v1, const VolDesc&
                              const int32_t last[3], int op);
 cudaError_t launchResample(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, int filter,
                            int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
+cudaError_t launchResampleRowRuns(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
+                                  int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
 cudaError_t launchConvertFlat(const LaunchCtx&, const VolDesc& dst, uint8_t* d, const VolDesc& src, const uint8_t* s, size_t n);
 cudaError_t launchConvertRows(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
                               const int32_t last[3], const int32_t off[3]);

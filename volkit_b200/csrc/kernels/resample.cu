@@ -216,6 +216,12 @@ cudaError_t launchResample(const LaunchCtx& c, const VolDesc& dst, const VolDesc
     int mode = filter == 0 ? MODE_NEAREST : filter == 1 ? MODE_LINEAR8 : MODE_TRILINEAR;
     if (mode == MODE_LINEAR8 && linearIsNearest(src)) mode = MODE_NEAREST;
 
+    if (mode == MODE_NEAREST) {
+        // fast path: TMA row pipeline (resample_rows.cu); falls through when rows are not 16-byte aligned
+        cudaError_t fe = launchResampleRowRuns(c, dst, src, dstZ0, D, srcZ0, S);
+        if (fe != cudaErrorNotSupported) return fe;
+    }
+
     // coordinate tables (stream-ordered scratch)
     const size_t nTab = (size_t)D[0] + D[1] + dzCount;
     int* tab = nullptr;
