@@ -92,6 +92,7 @@ int vktb_memset_range(void* dst, const void* pattern, size_t dst_bytes, size_t p
  * migrate() becomes one full-speed DMA */
 int vktb_host_alloc(void** ptr, size_t bytes);
 int vktb_host_free(void* ptr);
+int vktb_host_owns(const void* ptr);               /* 1 if ptr lies in a live vktb_host_alloc block, else 0 */
 int vktb_mem_stats(size_t* device_bytes_in_use, size_t* device_bytes_reserved,
                    size_t* pinned_bytes_in_use, size_t* pinned_bytes_reserved);
 int vktb_trim_pools(void);                         /* give cached device / pinned memory back */

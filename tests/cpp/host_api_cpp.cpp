@@ -1,0 +1,107 @@
+// Exercises the C++ host mirror (include/vkt/*.hpp) the way the reference's examples do
+// (src/examples/CoreAlgorithms.c, Arithmetic.cpp, ExecutionPolicy.cpp): volumes are created and filled on the CPU,
+// the thread's ExecutionPolicy is switched, algorithms run, results are read back after switching to CPU again.
+// usage: host_api_cpp <cpu|gpu> <dir>      inputs <dir>/a.raw, b.raw (48x40x36 UInt16); outputs <dir>/out_*.raw
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+
+#include <vkt/Arithmetic.hpp>
+#include <vkt/Copy.hpp>
+#include <vkt/ExecutionPolicy.hpp>
+#include <vkt/Fill.hpp>
+#include <vkt/Resample.hpp>
+#include <vkt/StructuredVolume.hpp>
+#include <vkt/Transform.hpp>
+
+using namespace vkt;
+
+static std::string g_dir;
+
+static void load(StructuredVolume& v, const char* name)
+{
+    FILE* f = std::fopen((g_dir + "/" + name).c_str(), "rb");
+    if (!f || std::fread(v.getData(), 1, v.getSizeInBytes(), f) != v.getSizeInBytes()) { std::perror(name); std::exit(2); }
+    std::fclose(f);
+}
+
+static void save(StructuredVolume& v, const char* name)
+{
+    FILE* f = std::fopen((g_dir + "/" + name).c_str(), "wb");
+    std::fwrite(v.getData(), 1, v.getSizeInBytes(), f);   // getData() under the CPU policy migrates back
+    std::fclose(f);
+}
+
+#define CHECK(X) do { if ((X) != NoError) { std::fprintf(stderr, "FAILED: %s\n", #X); return 1; } } while (0)
+
+// the ops of reference src/examples/CoreAlgorithms.c:12-24 (unary: first byte ^= x+y+z; binary: v1 |= v2, v2 = v1)
+static void xorCoord(int32_t x, int32_t y, int32_t z, VoxelView voxel) { voxel.bytes[0] ^= (uint8_t)(x + y + z); }
+static void orAssign(int32_t, int32_t, int32_t, VoxelView v1, VoxelView v2)
+{
+    int n = v1.dataFormat == DataFormat::UInt8 ? 1 : v1.dataFormat == DataFormat::UInt16 ? 2 : 4;
+    for (int i = 0; i < n; ++i) { v1.bytes[i] |= v2.bytes[i]; v2.bytes[i] = v1.bytes[i]; }
+}
+static void unboundOp(int32_t, int32_t, int32_t, VoxelView) {}
+
+int main(int argc, char** argv)
+{
+    if (argc < 3) return 2;
+    const bool gpu = std::strcmp(argv[1], "gpu") == 0;
+    g_dir = argv[2];
+
+    ExecutionPolicy cpu = GetThreadExecutionPolicy();            // default: CPU / Serial
+    if (cpu.device != ExecutionPolicy::Device::CPU) return 3;
+    ExecutionPolicy run = cpu;
+    run.device = gpu ? ExecutionPolicy::Device::GPU : ExecutionPolicy::Device::CPU;
+
+    // policies are per thread and not inherited (reference include/cpp/vkt/ExecutionPolicy.hpp:93-100)
+    SetThreadExecutionPolicy(run);
+    bool childIsDefault = false;
+    std::thread([&] { childIsDefault = GetThreadExecutionPolicy().device == ExecutionPolicy::Device::CPU; }).join();
+    if (!childIsDefault) return 4;
+    SetThreadExecutionPolicy(cpu);
+
+    const int X = 48, Y = 40, Z = 36;
+    StructuredVolume a(X, Y, Z, DataFormat::UInt16), b(X, Y, Z, DataFormat::UInt16);
+    load(a, "a.raw");
+    load(b, "b.raw");
+    StructuredVolume sum(X, Y, Z, DataFormat::UInt16), diff(X, Y, Z, DataFormat::UInt16);
+    StructuredVolume cpy(64, 48, 44, DataFormat::UInt16);
+    StructuredVolume prod(X, Y, Z, DataFormat::Float32, 1.f, 1.f, 1.f, -1000.f, 3000.f);
+
+    SetThreadExecutionPolicy(run);      // deferred: nothing moves until an algorithm touches a volume
+
+    CHECK(Fill(diff, .25f));
+    CHECK(Fill(cpy, .5f));
+    CHECK(SafeSum(sum, a, b));
+    CHECK(SafeDiffRange(diff, a, b, Vec3i{ 3, 5, 7 }, Vec3i{ 47, 38, 33 }, Vec3i{ 1, 2, 3 }));
+    CHECK(Prod(prod, a, b));
+    CHECK(CopyRange(cpy, a, Vec3i{ -3, -2, -1 }, Vec3i{ 51, 42, 37 }, Vec3i{ 1, 2, 3 }));   // clamped src
+
+    StructuredVolume t1(a), t2(b);      // copies are made on the current policy's device
+    if (gpu) {
+        // an unbound host op must fail under the GPU policy instead of running on the CPU
+        if (Transform(t1, unboundOp) != InvalidValue) { std::fprintf(stderr, "unbound op did not fail\n"); return 5; }
+        CHECK(BindDeviceOp(xorCoord, "xor_coord"));
+        CHECK(BindDeviceOp(orAssign, "or_assign"));
+    }
+    CHECK(TransformRange(t1, 1, 2, 3, 47, 39, 35, xorCoord));
+    CHECK(Transform(t1, t2, orAssign));
+
+    StructuredVolume up(72, 60, 54, DataFormat::UInt16), down(24, 20, 18, DataFormat::UInt8, 1.f, 1.f, 1.f, -1.f, 2.f);
+    CHECK(Resample(up, a, FilterMode::Linear));
+    CHECK(Resample(down, a, FilterMode::Nearest));
+
+    // single-voxel accessors work under either policy
+    sum.setValue(1, 2, 3, .75f);
+    float back = sum.getValue(1, 2, 3);
+    if (back < .7499f || back > .7501f) { std::fprintf(stderr, "setValue/getValue round trip: %f\n", back); return 6; }
+
+    SetThreadExecutionPolicy(cpu);
+    save(sum, "out_sum.raw"); save(diff, "out_diff.raw"); save(prod, "out_prod.raw"); save(cpy, "out_cpy.raw");
+    save(t1, "out_t1.raw"); save(t2, "out_t2.raw"); save(up, "out_up.raw"); save(down, "out_down.raw");
+    std::printf("ok\n");
+    return 0;
+}

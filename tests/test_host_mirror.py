@@ -1,0 +1,157 @@
+"""The C++ / C99 host mirror of the reference API (include/vkt, libvkt_b200.so) and the `vkt` CLI, compared with the
+oracle.  The programs under tests/cpp read like the reference's examples; they are compiled here with g++/gcc and run
+under the CPU policy (always) and the GPU policy (-m gpu)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import cases
+from oracle import pyoracle as po
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "volkit_b200", "lib")
+INC = os.path.join(ROOT, "include")
+U8, U16, F32 = po.UINT16 - 1, po.UINT16, po.FLOAT32
+
+
+@pytest.fixture(scope="module")
+def programs(tmp_path_factory):
+    if not os.path.exists(os.path.join(LIB, "libvkt_b200.so")):
+        pytest.fail("volkit_b200/lib/libvkt_b200.so is missing: run __graft_entry__.build()")
+    out = tmp_path_factory.mktemp("hostbin")
+    link = ["-L" + LIB, "-lvkt_b200", "-lvktb200", "-Wl,-rpath," + LIB, "-lpthread"]
+    cpp = str(out / "host_api_cpp")
+    subprocess.run(["g++", "-std=c++14", "-O1", "-I" + INC, os.path.join(ROOT, "tests", "cpp", "host_api_cpp.cpp"),
+                    "-o", cpp] + link, check=True)
+    c = str(out / "host_api_c")
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-D_POSIX_C_SOURCE=200809L", "-O1", "-I" + INC,
+                    os.path.join(ROOT, "tests", "cpp", "host_api_c.c"), "-o", c] + link, check=True)
+    return {"cpp": cpp, "c": c}
+
+
+def raw(path, dims, dtype):
+    return np.fromfile(path, dtype).reshape(dims[2], dims[1], dims[0])
+
+
+def run_cpp(programs, policy, tmp):
+    o = po.oracle()
+    dims = (48, 40, 36)
+    a, b = cases.mk(dims, U16, 1), cases.mk(dims, U16, 2)
+    a.a.tofile(tmp / "a.raw")
+    b.a.tofile(tmp / "b.raw")
+    r = subprocess.run([programs["cpp"], policy, str(tmp)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+
+    full = ((0, 0, 0), dims)
+    # SafeSum whole volume, then one voxel set through setValue(1,2,3, .75)
+    ref = po.empty(dims, U16)
+    o.arith_range(po.SAFESUM, ref, a, b, *full)
+    got = raw(tmp / "out_sum.raw", dims, np.uint16)
+    ref.a[3, 2, 1] = int.from_bytes(o.map_voxel(0.75, U16, 0.0, 1.0), "little")
+    assert got.tobytes() == ref.a.tobytes()
+    # Fill(.25) + SafeDiffRange with dstOffset
+    ref = po.empty(dims, U16)
+    o.fill_range(ref, *full, 0.25)
+    o.arith_range(po.SAFEDIFF, ref, a, b, (3, 5, 7), (47, 38, 33), (1, 2, 3))
+    assert raw(tmp / "out_diff.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    # Prod into Float32 with mapping (-1000, 3000)
+    ref = po.empty(dims, F32, -1000.0, 3000.0)
+    o.arith_range(po.PROD, ref, a, b, *full)
+    assert raw(tmp / "out_prod.raw", dims, np.float32).tobytes() == ref.a.tobytes()
+    # Fill(.5) + CopyRange with clamped src and dstOffset
+    cd = (64, 48, 44)
+    ref = po.empty(cd, U16)
+    o.fill_range(ref, (0, 0, 0), cd, 0.5)
+    o.copy_range(ref, a, (-3, -2, -1), (51, 42, 37), (1, 2, 3))
+    assert raw(tmp / "out_cpy.raw", cd, np.uint16).tobytes() == ref.a.tobytes()
+    # TransformRange unary on a copy of a, then binary with a copy of b
+    t1, t2 = a.copy(), b.copy()
+    o.transform_range1(t1, (1, 2, 3), (47, 39, 35), 0)
+    o.transform_range2(t1, t2, *full, 0)
+    assert raw(tmp / "out_t1.raw", dims, np.uint16).tobytes() == t1.a.tobytes()
+    assert raw(tmp / "out_t2.raw", dims, np.uint16).tobytes() == t2.a.tobytes()
+    # Resample up (Linear) and down (Nearest, UInt8 with mapping (-1, 2))
+    ref = po.empty((72, 60, 54), U16)
+    o.resample(ref, a, po.LINEAR)
+    assert raw(tmp / "out_up.raw", (72, 60, 54), np.uint16).tobytes() == ref.a.tobytes()
+    ref = po.empty((24, 20, 18), U8, -1.0, 2.0)
+    o.resample(ref, a, po.NEAREST)
+    assert raw(tmp / "out_down.raw", (24, 20, 18), np.uint8).tobytes() == ref.a.tobytes()
+
+
+def run_c(programs, policy, tmp):
+    o = po.oracle()
+    r = subprocess.run([programs["c"], policy, str(tmp)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    dims = (40, 32, 24)
+    full = ((0, 0, 0), dims)
+    v, v2 = po.empty(dims, U8), po.empty(dims, U8)
+    o.fill_range(v, *full, 0.1)
+    o.fill_range(v2, *full, 0.3)
+    o.fill_range(v2, (4, 4, 4), (20, 20, 20), 0.9)
+    o.copy_range(v, v2, (10, 4, 2), (34, 28, 20), (0, 0, 0))
+    o.transform_range1(v, (2, 2, 2), (30, 30, 20), 0)
+    v3 = v.copy()
+    o.arith_range(po.SAFESUM, v3, v, v2, *full)
+    o.arith_range(po.ABSDIFF, v2, v, v3, (1, 1, 1), (39, 31, 23), (0, 0, 0))
+    assert raw(tmp / "c_out_volume.raw", dims, np.uint8).tobytes() == v.a.tobytes()
+    assert raw(tmp / "c_out_volume2.raw", dims, np.uint8).tobytes() == v2.a.tobytes()
+    assert raw(tmp / "c_out_volume3.raw", dims, np.uint8).tobytes() == v3.a.tobytes()
+
+
+def cli_pipeline(device):
+    """BASELINE config 1: declare-sv 64^3 uint8 | fill 0.1 | fill-range 1 [0,8)^3 | resample --dims 32^3 uint16."""
+    vkt = os.path.join(LIB, "vkt")
+    env = dict(os.environ, VKT_B200_DEVICE=device)
+    cmd = (f"{vkt} declare-sv --dims 64 64 64 --data-format uint8 | {vkt} fill --value 0.1 | "
+           f"{vkt} fill-range --value 1 --first 0 0 0 --last 8 8 8 | {vkt} resample --dims 32 32 32 --data-format uint16")
+    r = subprocess.run(["bash", "-o", "pipefail", "-c", cmd], capture_output=True, env=env)
+    assert r.returncode == 0, r.stderr
+    out = r.stdout
+    hdr = np.frombuffer(out[:24], np.uint32)
+    assert hdr.tolist() == [1, 0, 32, 32, 32, po.UINT16]
+    assert np.frombuffer(out[24:44], np.float32).tolist() == [1.0, 1.0, 1.0, 0.0, 1.0]
+    case = [c for c in cases.cases() if c[0] == "cli/config1"][0]
+    ref = cases.run_case(po.oracle(), case)[1]
+    assert out[44:] == ref.tobytes()
+
+
+def test_cpp_api_cpu_policy(programs, tmp_path):
+    run_cpp(programs, "cpu", tmp_path)
+
+
+def test_c99_api_cpu_policy(programs, tmp_path):
+    run_c(programs, "cpu", tmp_path)
+
+
+def test_cli_config1_cpu():
+    cli_pipeline("cpu")
+
+
+def test_gpu_policy_fails_loudly_without_gpu(programs, tmp_path):
+    """No CPU fallback: on a machine without a usable B200 the GPU policy must fail, not compute on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    cases.mk((48, 40, 36), U16, 1).a.tofile(tmp_path / "a.raw")
+    cases.mk((48, 40, 36), U16, 2).a.tofile(tmp_path / "b.raw")
+    r = subprocess.run([programs["cpp"], "gpu", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "no usable CUDA device" in r.stderr or "FAILED" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_api_gpu_policy(programs, tmp_path):
+    run_cpp(programs, "gpu", tmp_path)
+
+
+@pytest.mark.gpu
+def test_c99_api_gpu_policy(programs, tmp_path):
+    run_c(programs, "gpu", tmp_path)
+
+
+@pytest.mark.gpu
+def test_cli_config1_gpu():
+    cli_pipeline("gpu")

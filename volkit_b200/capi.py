@@ -46,6 +46,7 @@ SIGNATURES = {
     "vktb_memset_range": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t]),
     "vktb_host_alloc": (ctypes.c_int, [_P(ctypes.c_void_p), ctypes.c_size_t]),
     "vktb_host_free": (ctypes.c_int, [ctypes.c_void_p]),
+    "vktb_host_owns": (ctypes.c_int, [ctypes.c_void_p]),
     "vktb_mem_stats": (ctypes.c_int, [_P(ctypes.c_size_t)] * 4),
     "vktb_trim_pools": (ctypes.c_int, []),
     "vktb_fill_range": (ctypes.c_int, [_VP, I3, I3, ctypes.c_float]),

@@ -416,6 +416,8 @@ int vktb_host_alloc(void** ptr, size_t bytes)
 
 int vktb_host_free(void* ptr) { return pinnedFree(ptr); }
 
+int vktb_host_owns(const void* ptr) { return ptr && pinnedOwns(ptr) ? 1 : 0; }
+
 int vktb_mem_stats(size_t* devInUse, size_t* devReserved, size_t* pinInUse, size_t* pinReserved)
 {
     DeviceCtx* d = currentDevice();

@@ -1,0 +1,203 @@
+// `vkt` command-line tool, hot-path subset: declare-sv | fill | fill-range | resample | dump, piping a structured
+// volume over stdin/stdout in the reference's binary pipe format (reference src/cli/main.cpp:32-88):
+//     u32 magic = 1, u32 assetType = 0, i32 dims[3], u32 dataFormat, f32 dist[3], f32 mapping[2], raw voxels
+// Commands, options, defaults and range checks follow reference src/cli/main.cpp:111-335 (options), :402-442
+// (declare-sv), :521-574 (fill / fill-range), :701-740 (resample, always FilterMode::Nearest), :445-519 (dump).
+//
+// volkit-b200 addition: the execution policy of every stage is chosen with `--device cpu|gpu` or the environment
+// variable VKT_B200_DEVICE (default cpu, as in the reference where the CLI never sets a policy).
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <vkt/ExecutionPolicy.hpp>
+#include <vkt/Fill.hpp>
+#include <vkt/Resample.hpp>
+#include <vkt/StructuredVolume.hpp>
+
+using namespace vkt;
+
+namespace
+{
+struct Header
+{
+    uint32_t magic, assetType;
+    int32_t  dims[3];
+    uint32_t dataFormat;
+    float    dist[3];
+    float    mapping[2];
+};
+static_assert(sizeof(Header) == 44, "pipe header is 44 bytes");
+
+struct Options
+{
+    std::string command;
+    Vec3i dims{ 0, 0, 0 };
+    DataFormat dataFormat = DataFormat::Unspecified;
+    Vec3f dist{ 0.f, 0.f, 0.f };
+    Vec2f mapping{ 0.f, 0.f };
+    Vec3i first{ 0, 0, 0 }, last{ 0, 0, 0 };
+    float value = 0.f;
+    std::string device;
+};
+
+bool fail(const char* msg) { std::fprintf(stderr, "%s\n", msg); return false; }
+
+DataFormat parseFormat(std::string s)
+{
+    std::transform(s.begin(), s.end(), s.begin(), [](unsigned char c) { return (char)std::tolower(c); });
+    static const struct { const char* name; DataFormat f; } table[] = {
+        { "int8", DataFormat::Int8 }, { "int16", DataFormat::Int16 }, { "int32", DataFormat::Int32 },
+        { "uint8", DataFormat::UInt8 }, { "uint16", DataFormat::UInt16 }, { "uint32", DataFormat::UInt32 },
+        { "float32", DataFormat::Float32 } };
+    for (auto& e : table) if (s == e.name) return e.f;
+    return DataFormat::Unspecified;
+}
+
+bool parse(int argc, char** argv, Options& o)
+{
+    if (argc < 2) return fail("Usage: vkt <command> [<args>]");
+    o.command = argv[1];
+    static const char* known[] = { "declare-sv", "dump", "dump-range", "fill", "fill-range", "resample" };
+    if (std::find_if(std::begin(known), std::end(known), [&](const char* k) { return o.command == k; }) == std::end(known)) {
+        std::fprintf(stderr, "Usage: vkt <command> [<args>]\n  Command \"%s\" unknown\n", argv[1]);
+        return false;
+    }
+    auto need = [&](int i, int n, const char* opt) {
+        if (i + n >= argc) { std::fprintf(stderr, "Option %s requires %d argument(s)\n", opt, n); return false; }
+        return true;
+    };
+    for (int i = 2; i < argc; ++i) {
+        std::string opt = argv[i];
+        if (opt == "-df" || opt == "--data-format") { if (!need(i, 1, argv[i])) return false; o.dataFormat = parseFormat(argv[++i]); }
+        else if (opt == "-dims" || opt == "--dims") { if (!need(i, 3, argv[i])) return false; o.dims = { std::atoi(argv[i + 1]), std::atoi(argv[i + 2]), std::atoi(argv[i + 3]) }; i += 3; }
+        else if (opt == "-dist" || opt == "--dist") { if (!need(i, 3, argv[i])) return false; o.dist = { (float)std::atof(argv[i + 1]), (float)std::atof(argv[i + 2]), (float)std::atof(argv[i + 3]) }; i += 3; }
+        else if (opt == "-first" || opt == "--first") { if (!need(i, 3, argv[i])) return false; o.first = { std::atoi(argv[i + 1]), std::atoi(argv[i + 2]), std::atoi(argv[i + 3]) }; i += 3; }
+        else if (opt == "-last" || opt == "--last") { if (!need(i, 3, argv[i])) return false; o.last = { std::atoi(argv[i + 1]), std::atoi(argv[i + 2]), std::atoi(argv[i + 3]) }; i += 3; }
+        else if (opt == "-vm" || opt == "--voxel-mapping") { if (!need(i, 2, argv[i])) return false; o.mapping = { (float)std::atof(argv[i + 1]), (float)std::atof(argv[i + 2]) }; i += 2; }
+        else if (opt == "-v" || opt == "--value") { if (!need(i, 1, argv[i])) return false; o.value = (float)std::atof(argv[++i]); }
+        else if (opt == "--device") { if (!need(i, 1, argv[i])) return false; o.device = argv[++i]; }
+        else { std::fprintf(stderr, "Unknown option %s\n", argv[i]); return false; }
+    }
+    return true;
+}
+
+bool readAll(void* dst, size_t n) { return std::fread(dst, 1, n, stdin) == n; }
+
+// reads header + voxels from stdin into a volume allocated under the CPU policy
+bool readVolume(StructuredVolume& volume)
+{
+    Header h;
+    if (!readAll(&h, sizeof h)) return fail("Cannot read structured volume: short header");
+    if (h.magic != 1u) return fail("Cannot read structured volume, wrong version");
+    if (h.assetType != 0u) return fail("Cannot read structured volume, wrong type");
+    volume = StructuredVolume(h.dims[0], h.dims[1], h.dims[2], (DataFormat)h.dataFormat, h.dist[0], h.dist[1], h.dist[2],
+                              h.mapping[0], h.mapping[1]);
+    if (!readAll(volume.getData(), volume.getSizeInBytes())) return fail("Cannot read structured volume: short data");
+    return true;
+}
+
+// getData() under the CPU policy migrates the result back to the host before it is written
+void writeVolume(StructuredVolume& volume)
+{
+    Header h;
+    h.magic = 1u; h.assetType = 0u;
+    Vec3i d = volume.getDims(); Vec3f s = volume.getDist(); Vec2f m = volume.getVoxelMapping();
+    h.dims[0] = d.x; h.dims[1] = d.y; h.dims[2] = d.z;
+    h.dataFormat = (uint32_t)volume.getDataFormat();
+    h.dist[0] = s.x; h.dist[1] = s.y; h.dist[2] = s.z;
+    h.mapping[0] = m.x; h.mapping[1] = m.y;
+    std::fwrite(&h, 1, sizeof h, stdout);
+    std::fwrite(volume.getData(), 1, volume.getSizeInBytes(), stdout);
+    std::fflush(stdout);
+}
+
+bool checkParams(StructuredVolume& v)
+{
+    Vec3i d = v.getDims(); Vec3f s = v.getDist(); Vec2f m = v.getVoxelMapping();
+    if ((long long)d.x * d.y * d.z < 1) return fail("Invalid dimensions");
+    if (v.getDataFormat() == DataFormat::Unspecified) return fail("Invalid data format");
+    if (s.x * s.y * s.z <= 0.f) return fail("Invalid dist");
+    if (m.y - m.x <= 0.f) return fail("Invalid voxel mapping");
+    return true;
+}
+
+ExecutionPolicy policyFor(const Options& o, bool gpu)
+{
+    ExecutionPolicy ep;
+    (void)o;
+    ep.device = gpu ? ExecutionPolicy::Device::GPU : ExecutionPolicy::Device::CPU;
+    return ep;
+}
+} // namespace
+
+int main(int argc, char** argv)
+{
+    Options o;
+    if (!parse(argc, argv, o)) return EXIT_FAILURE;
+    if (o.device.empty()) { const char* e = std::getenv("VKT_B200_DEVICE"); o.device = e ? e : "cpu"; }
+    const bool gpu = o.device == "gpu" || o.device == "GPU";
+    const ExecutionPolicy cpuPolicy = policyFor(o, false), runPolicy = policyFor(o, gpu);
+
+    if (o.command == "declare-sv") {
+        if ((long long)o.dims.x * o.dims.y * o.dims.z <= 0) { fail("Dims required"); return EXIT_FAILURE; }
+        if (o.dataFormat == DataFormat::Unspecified) { fail("Data format required"); return EXIT_FAILURE; }
+        Vec3f dist = o.dist.x * o.dist.y * o.dist.z <= 0.f ? Vec3f{ 1.f, 1.f, 1.f } : o.dist;
+        Vec2f mapping = o.mapping.y - o.mapping.x <= 0.f ? Vec2f{ 0.f, 1.f } : o.mapping;
+        StructuredVolume volume(o.dims.x, o.dims.y, o.dims.z, o.dataFormat, dist.x, dist.y, dist.z, mapping.x, mapping.y);
+        // the reference emits uninitialised memory here; zeros are as good and reproducible
+        std::memset(volume.getData(), 0, volume.getSizeInBytes());
+        writeVolume(volume);
+    } else if (o.command == "fill" || o.command == "fill-range") {
+        StructuredVolume volume;
+        if (!readVolume(volume) || !checkParams(volume)) return EXIT_FAILURE;
+        const long long range = (long long)(o.last.x - o.first.x) * (o.last.y - o.first.y) * (o.last.z - o.first.z);
+        if (o.command == "fill-range") {
+            if (range <= 0) { fail("Invalid range"); return EXIT_FAILURE; }
+            if (o.first.x < 0 || o.first.y < 0 || o.first.z < 0) { fail("Range underflow"); return EXIT_FAILURE; }
+            Vec3i d = volume.getDims();
+            if (o.last.x > d.x || o.last.y > d.y || o.last.z > d.z) { fail("Range overflow"); return EXIT_FAILURE; }
+        }
+        SetThreadExecutionPolicy(runPolicy);
+        Error e = range > 0 ? FillRange(volume, o.first, o.last, o.value) : Fill(volume, o.value);
+        SetThreadExecutionPolicy(cpuPolicy);
+        if (e != NoError) return EXIT_FAILURE;
+        writeVolume(volume);
+    } else if (o.command == "resample") {
+        StructuredVolume src;
+        if (!readVolume(src)) return EXIT_FAILURE;
+        Vec3i dims = (long long)o.dims.x * o.dims.y * o.dims.z <= 0 ? src.getDims() : o.dims;
+        DataFormat f = o.dataFormat == DataFormat::Unspecified ? src.getDataFormat() : o.dataFormat;
+        Vec3f dist = o.dist.x * o.dist.y * o.dist.z <= 0.f ? src.getDist() : o.dist;
+        Vec2f mapping = o.mapping.y - o.mapping.x <= 0.f ? src.getVoxelMapping() : o.mapping;
+        StructuredVolume dst(dims.x, dims.y, dims.z, f, dist.x, dist.y, dist.z, mapping.x, mapping.y);
+        SetThreadExecutionPolicy(runPolicy);
+        Error e = Resample(dst, src, FilterMode::Nearest);
+        SetThreadExecutionPolicy(cpuPolicy);
+        if (e != NoError) return EXIT_FAILURE;
+        writeVolume(dst);
+    } else {   // dump / dump-range
+        StructuredVolume volume;
+        if (!readVolume(volume)) return EXIT_FAILURE;
+        const long long range = (long long)(o.last.x - o.first.x) * (o.last.y - o.first.y) * (o.last.z - o.first.z);
+        if (o.command == "dump-range" && range <= 0) { fail("Invalid range"); return EXIT_FAILURE; }
+        Vec3i d = volume.getDims(); Vec3f s = volume.getDist(); Vec2f m = volume.getVoxelMapping();
+        std::printf("Object: StructuredVolume\n  dims: (%d,%d,%d)\n  dataFormat: %d\n  dist: (%.1f,%.1f,%.1f)\n  voxelMapping: (%.1f,%.1f)\ndata:\n",
+                    d.x, d.y, d.z, (int)volume.getDataFormat(), s.x, s.y, s.z, m.x, m.y);
+        Vec3i first{ 0, 0, 0 }, last = d;
+        if (range > 0) { first = o.first; last = o.last; }
+        for (int32_t z = first.z; z < last.z; ++z) {
+            std::printf("[%d]\n{\n", z);
+            for (int32_t y = first.y; y < last.y; ++y) {
+                std::printf("  [%d] {", y);
+                for (int32_t x = first.x; x < last.x; ++x) std::printf(x + 1 < last.x ? "%.1f, " : "%.1f", volume.getValue(x, y, z));
+                std::printf("}\n");
+            }
+            std::printf(z + 1 < last.z ? "}\n\n" : "}\n");
+        }
+    }
+    return EXIT_SUCCESS;
+}

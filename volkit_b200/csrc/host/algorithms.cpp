@@ -1,0 +1,252 @@
+// Front functions of the hot-path algorithms: argument normalisation + dispatch on the calling thread's
+// ExecutionPolicy (the reference's VKT_LEGACY_CALL__, src/vkt/Callable.hpp:82-113):
+//     Device::CPU + HostAPI::Serial  -> host::xxx (serial.cpp)
+//     Device::GPU + DeviceAPI::CUDA  -> the C-ABI (include/vktb/backend.h); a failing call returns InvalidValue
+//     anything else                  -> nothing runs (as in the reference), NoError
+// With printPerformance the call is timed and one line is logged in the reference's format (Callable.hpp:23-47).
+#include <chrono>
+#include <cstdio>
+
+#include <vkt/Arithmetic.hpp>
+#include <vkt/Copy.hpp>
+#include <vkt/Fill.hpp>
+#include <vkt/Resample.hpp>
+#include <vkt/StructuredVolume.hpp>
+#include <vkt/Transform.hpp>
+
+#include "backend_link.hpp"
+#include "host_codec.hpp"
+#include "serial.hpp"
+
+namespace vkt
+{
+namespace
+{
+    host::View viewOf(StructuredVolume& v)
+    {
+        host::View w;
+        w.data = v.getData();   // migrates to the host under the CPU policy
+        w.dims = v.getDims();
+        w.format = v.getDataFormat();
+        Vec2f m = v.getVoxelMapping();
+        w.lo = m.x; w.hi = m.y;
+        w.bpv = host::bytesPerVoxel(w.format);
+        return w;
+    }
+
+    // Runs cpu() or gpu() according to the policy; gpu() returns a C-ABI status.
+    template <class Cpu, class Gpu>
+    Error dispatch(char const* name, Cpu cpu, Gpu gpu)
+    {
+        ExecutionPolicy ep = GetThreadExecutionPolicy();
+        typedef std::chrono::steady_clock Clock;
+        if (host::onCpuSerial(ep)) {
+            Clock::time_point t0 = Clock::now();
+            cpu();
+            if (ep.printPerformance)
+                std::printf("Device: CPU (serial), algorithm: %s_serial, time elapsed: %g sec.\n", name,
+                            std::chrono::duration<double>(Clock::now() - t0).count());
+            return NoError;
+        }
+        if (host::onGpu(ep)) {
+            if (ep.printPerformance) vktb_sync();
+            Clock::time_point t0 = Clock::now();
+            if (gpu() != 0) return host::backendError(name);
+            if (ep.printPerformance) {
+                vktb_sync();
+                std::printf("Device: GPU (CUDA), algorithm: %s_cuda, time elapsed: %g sec.\n", name,
+                            std::chrono::duration<double>(Clock::now() - t0).count());
+            }
+            return NoError;
+        }
+        return NoError;
+    }
+
+    void toArray(Vec3i v, int32_t out[3]) { out[0] = v.x; out[1] = v.y; out[2] = v.z; }
+} // namespace
+
+    //---------------------------------------------------------------------------------------------------------
+    // Fill (reference src/vkt/Fill.cpp:32-83)
+    //---------------------------------------------------------------------------------------------------------
+    Error FillRange(StructuredVolume& volume, Vec3i first, Vec3i last, float value)
+    {
+        return dispatch("FillRange",
+            [&] { host::fillRange(viewOf(volume), first, last, value); },
+            [&] {
+                vktb_vol v = host::describe(volume);
+                int32_t f[3], l[3];
+                toArray(first, f); toArray(last, l);
+                return vktb_fill_range(&v, f, l, value);
+            });
+    }
+
+    Error FillRange(StructuredVolume& volume, int32_t firstX, int32_t firstY, int32_t firstZ, int32_t lastX,
+                    int32_t lastY, int32_t lastZ, float value)
+    {
+        return FillRange(volume, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ }, value);
+    }
+
+    Error Fill(StructuredVolume& volume, float value)
+    {
+        return FillRange(volume, Vec3i{ 0, 0, 0 }, volume.getDims(), value);
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Copy (reference src/vkt/Copy.cpp:26-95)
+    //---------------------------------------------------------------------------------------------------------
+    Error CopyRange(StructuredVolume& dst, StructuredVolume& src, Vec3i first, Vec3i last, Vec3i dstOffset)
+    {
+        return dispatch("CopyRange",
+            [&] { host::copyRange(viewOf(dst), viewOf(src), first, last, dstOffset); },
+            [&] {
+                vktb_vol d = host::describe(dst), s = host::describe(src);
+                int32_t f[3], l[3], o[3];
+                toArray(first, f); toArray(last, l); toArray(dstOffset, o);
+                return vktb_copy_range(&d, &s, f, l, o);
+            });
+    }
+
+    Error CopyRange(StructuredVolume& dst, StructuredVolume& src, int32_t firstX, int32_t firstY, int32_t firstZ,
+                    int32_t lastX, int32_t lastY, int32_t lastZ, int32_t dstOffsetX, int32_t dstOffsetY, int32_t dstOffsetZ)
+    {
+        return CopyRange(dst, src, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ },
+                         Vec3i{ dstOffsetX, dstOffsetY, dstOffsetZ });
+    }
+
+    Error Copy(StructuredVolume& dst, StructuredVolume& src)
+    {
+        return CopyRange(dst, src, Vec3i{ 0, 0, 0 }, dst.getDims(), Vec3i{ 0, 0, 0 });   // dst dims: Copy.cpp:32
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Arithmetic (reference src/vkt/Arithmetic.cpp:26-714); op ids = enum vktb_arith_op
+    //---------------------------------------------------------------------------------------------------------
+    static Error arithmetic(char const* name, int op, StructuredVolume& dest, StructuredVolume& source1,
+                            StructuredVolume& source2, Vec3i first, Vec3i last, Vec3i dstOffset)
+    {
+        return dispatch(name,
+            [&] { host::arithRange(op, viewOf(dest), viewOf(source1), viewOf(source2), first, last, dstOffset); },
+            [&] {
+                vktb_vol d = host::describe(dest), a = host::describe(source1), b = host::describe(source2);
+                int32_t f[3], l[3], o[3];
+                toArray(first, f); toArray(last, l); toArray(dstOffset, o);
+                return vktb_arith_range(op, &d, &a, &b, f, l, o);
+            });
+    }
+
+#define VKT_DEFINE_ARITHMETIC_OP__(NAME, OP)                                                                    \
+    Error NAME##Range(StructuredVolume& dest, StructuredVolume& source1, StructuredVolume& source2, Vec3i first, \
+                      Vec3i last, Vec3i dstOffset)                                                              \
+    {                                                                                                           \
+        return arithmetic(#NAME "Range", OP, dest, source1, source2, first, last, dstOffset);                   \
+    }                                                                                                           \
+    Error NAME##Range(StructuredVolume& dest, StructuredVolume& source1, StructuredVolume& source2,             \
+                      int32_t firstX, int32_t firstY, int32_t firstZ, int32_t lastX, int32_t lastY,             \
+                      int32_t lastZ, int32_t dstOffsetX, int32_t dstOffsetY, int32_t dstOffsetZ)                \
+    {                                                                                                           \
+        return arithmetic(#NAME "Range", OP, dest, source1, source2, Vec3i{ firstX, firstY, firstZ },           \
+                          Vec3i{ lastX, lastY, lastZ }, Vec3i{ dstOffsetX, dstOffsetY, dstOffsetZ });           \
+    }                                                                                                           \
+    Error NAME(StructuredVolume& dest, StructuredVolume& source1, StructuredVolume& source2)                    \
+    {                                                                                                           \
+        return arithmetic(#NAME "Range", OP, dest, source1, source2, Vec3i{ 0, 0, 0 }, dest.getDims(),          \
+                          Vec3i{ 0, 0, 0 });                                                                    \
+    }
+
+    VKT_DEFINE_ARITHMETIC_OP__(Sum, VKTB_SUM)
+    VKT_DEFINE_ARITHMETIC_OP__(Diff, VKTB_DIFF)
+    VKT_DEFINE_ARITHMETIC_OP__(Prod, VKTB_PROD)
+    VKT_DEFINE_ARITHMETIC_OP__(Quot, VKTB_QUOT)
+    VKT_DEFINE_ARITHMETIC_OP__(AbsDiff, VKTB_ABSDIFF)
+    VKT_DEFINE_ARITHMETIC_OP__(SafeSum, VKTB_SAFESUM)
+    VKT_DEFINE_ARITHMETIC_OP__(SafeDiff, VKTB_SAFEDIFF)
+    VKT_DEFINE_ARITHMETIC_OP__(SafeProd, VKTB_SAFEPROD)
+    VKT_DEFINE_ARITHMETIC_OP__(SafeQuot, VKTB_SAFEQUOT)
+    VKT_DEFINE_ARITHMETIC_OP__(SafeAbsDiff, VKTB_SAFEABSDIFF)
+#undef VKT_DEFINE_ARITHMETIC_OP__
+
+    //---------------------------------------------------------------------------------------------------------
+    // Transform (reference src/vkt/Transform.cpp:26-71)
+    //---------------------------------------------------------------------------------------------------------
+    Error TransformRange(StructuredVolume& volume, Vec3i first, Vec3i last, TransformUnaryOp unaryOp)
+    {
+        if (!unaryOp) return InvalidValue;
+        return dispatch("TransformRange",
+            [&] { host::transformRange(viewOf(volume), first, last, unaryOp); },
+            [&] {
+                int op = -1;
+                if (vktb_lookup_unary_op((void const*)unaryOp, &op) != 0) return -1;   // unbound: no CPU fallback
+                vktb_vol v = host::describe(volume);
+                int32_t f[3], l[3];
+                toArray(first, f); toArray(last, l);
+                return vktb_transform_range1(&v, f, l, op);
+            });
+    }
+
+    Error TransformRange(StructuredVolume& volume, int32_t firstX, int32_t firstY, int32_t firstZ, int32_t lastX,
+                         int32_t lastY, int32_t lastZ, TransformUnaryOp unaryOp)
+    {
+        return TransformRange(volume, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ }, unaryOp);
+    }
+
+    Error Transform(StructuredVolume& volume, TransformUnaryOp unaryOp)
+    {
+        return TransformRange(volume, Vec3i{ 0, 0, 0 }, volume.getDims(), unaryOp);
+    }
+
+    Error TransformRange(StructuredVolume& volume1, StructuredVolume& volume2, Vec3i first, Vec3i last,
+                         TransformBinaryOp binaryOp)
+    {
+        if (!binaryOp) return InvalidValue;
+        return dispatch("TransformRange",
+            [&] { host::transformRange(viewOf(volume1), viewOf(volume2), first, last, binaryOp); },
+            [&] {
+                int op = -1;
+                if (vktb_lookup_binary_op((void const*)binaryOp, &op) != 0) return -1;
+                vktb_vol a = host::describe(volume1), b = host::describe(volume2);
+                int32_t f[3], l[3];
+                toArray(first, f); toArray(last, l);
+                return vktb_transform_range2(&a, &b, f, l, op);
+            });
+    }
+
+    Error TransformRange(StructuredVolume& volume1, StructuredVolume& volume2, int32_t firstX, int32_t firstY,
+                         int32_t firstZ, int32_t lastX, int32_t lastY, int32_t lastZ, TransformBinaryOp binaryOp)
+    {
+        return TransformRange(volume1, volume2, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ }, binaryOp);
+    }
+
+    Error Transform(StructuredVolume& volume1, StructuredVolume& volume2, TransformBinaryOp binaryOp)
+    {
+        return TransformRange(volume1, volume2, Vec3i{ 0, 0, 0 }, volume1.getDims(), binaryOp);
+    }
+
+    Error BindDeviceOp(TransformUnaryOp hostOp, char const* deviceOpName)
+    {
+        int op = -1;
+        if (vktb_unary_op_by_name(deviceOpName, &op) != 0 || vktb_bind_unary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOp");
+        return NoError;
+    }
+
+    Error BindDeviceOp(TransformBinaryOp hostOp, char const* deviceOpName)
+    {
+        int op = -1;
+        if (vktb_binary_op_by_name(deviceOpName, &op) != 0 || vktb_bind_binary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOp");
+        return NoError;
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Resample (reference src/vkt/Resample.cpp:22-31)
+    //---------------------------------------------------------------------------------------------------------
+    Error Resample(StructuredVolume& dst, StructuredVolume& src, FilterMode fm)
+    {
+        return dispatch("Resample",
+            [&] { host::resample(viewOf(dst), viewOf(src), fm == FilterMode::Linear ? 1 : 0); },
+            [&] {
+                vktb_vol d = host::describe(dst), s = host::describe(src);
+                return vktb_resample(&d, &s, fm == FilterMode::Linear ? VKTB_LINEAR : VKTB_NEAREST);
+            });
+    }
+} // vkt

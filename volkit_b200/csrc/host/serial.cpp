@@ -1,0 +1,144 @@
+#include "serial.hpp"
+
+#include <cmath>
+#include <cstring>
+
+#include "host_codec.hpp"
+
+namespace vkt
+{
+namespace host
+{
+    static inline int clampi(int x, int a, int b) { int m = b < x ? b : x; return a < m ? m : a; }
+
+    // reference src/vkt/Fill_serial.hpp:20-26: every voxel of [first,last) receives map(value)
+    void fillRange(View v, Vec3i first, Vec3i last, float value)
+    {
+        uint8_t raw[8] = {};
+        mapVoxel(raw, value, v.format, v.lo, v.hi);
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y) {
+                uint8_t* row = v.data + v.offset(first.x, y, z);
+                for (int32_t x = first.x; x < last.x; ++x, row += v.bpv) std::memcpy(row, raw, v.bpv);
+            }
+    }
+
+    // reference src/vkt/Copy_serial.hpp:13-82: dst[p - first + off] = src[clamp(p)], bytes iff format and mapping agree
+    void copyRange(View dst, View src, Vec3i first, Vec3i last, Vec3i off)
+    {
+        const bool bytes = dst.format == src.format && dst.lo == src.lo && dst.hi == src.hi;
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    const uint8_t* s = src.data + src.offset(clampi(x, 0, src.dims.x - 1), clampi(y, 0, src.dims.y - 1),
+                                                             clampi(z, 0, src.dims.z - 1));
+                    uint8_t* d = dst.data + dst.offset(x - first.x + off.x, y - first.y + off.y, z - first.z + off.z);
+                    if (bytes) std::memcpy(d, s, dst.bpv);
+                    else mapVoxel(d, unmapVoxel(s, src.format, src.lo, src.hi), dst.format, dst.lo, dst.hi);
+                }
+    }
+
+    // reference src/vkt/Arithmetic_serial.hpp:15-45 (loop) and :47-260 (the ten ops; op ids in header order)
+    void arithRange(int op, View dst, View s1, View s2, Vec3i first, Vec3i last, Vec3i off)
+    {
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    const float a = unmapVoxel(s1.data + s1.offset(x, y, z), s1.format, s1.lo, s1.hi);
+                    const float b = unmapVoxel(s2.data + s2.offset(x, y, z), s2.format, s2.lo, s2.hi);
+                    float r;
+                    switch (op % 5) {
+                    case 0: r = a + b; break;
+                    case 1: r = a - b; break;
+                    case 2: r = a * b; break;
+                    case 3: r = a / b; break;
+                    default: r = std::fabs(a - b); break;
+                    }
+                    if (op >= 5) r = refClamp(r, dst.lo, dst.hi);
+                    mapVoxel(dst.data + dst.offset(x + off.x, y + off.y, z + off.z), r, dst.format, dst.lo, dst.hi);
+                }
+    }
+
+    // reference src/vkt/Transform_serial.hpp:15-50
+    void transformRange(View v, Vec3i first, Vec3i last, TransformUnaryOp op)
+    {
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    uint8_t scratch[8] = {};
+                    uint8_t* p = v.data + v.offset(x, y, z);
+                    std::memcpy(scratch, p, v.bpv);
+                    op(x, y, z, VoxelView{ scratch, v.format, v.lo, v.hi });
+                    std::memcpy(p, scratch, v.bpv);
+                }
+    }
+
+    // reference src/vkt/Transform_serial.hpp:53-103
+    void transformRange(View v1, View v2, Vec3i first, Vec3i last, TransformBinaryOp op)
+    {
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    uint8_t s1[8] = {}, s2[8] = {};
+                    uint8_t* p1 = v1.data + v1.offset(x, y, z);
+                    uint8_t* p2 = v2.data + v2.offset(x, y, z);
+                    std::memcpy(s1, p1, v1.bpv);
+                    std::memcpy(s2, p2, v2.bpv);
+                    op(x, y, z, VoxelView{ s1, v1.format, v1.lo, v1.hi }, VoxelView{ s2, v2.format, v2.lo, v2.hi });
+                    std::memcpy(p1, s1, v1.bpv);
+                    std::memcpy(p2, s2, v2.bpv);
+                }
+    }
+
+    // One tap of the source as a float; linear indices outside the buffer (only reachable through the reference's
+    // unclamped +1 x tap at the very last voxel) read as a zero voxel.
+    static inline float tap(const View& s, long long index)
+    {
+        const long long n = (long long)s.dims.x * s.dims.y * s.dims.z;
+        uint8_t zero[8] = {};
+        const uint8_t* p = (index >= 0 && index < n) ? s.data + (std::size_t)index * s.bpv : zero;
+        return unmapVoxel(p, s.format, s.lo, s.hi);
+    }
+
+    // reference src/vkt/Resample_serial.hpp:26-71 and StructuredVolumeView::sampleLinear
+    // (src/vkt/StructuredVolumeView.hpp:80-119): filter 0 = Nearest, 1 = Linear as the reference computes it (integer
+    // parameters -> fraction 0; lo taps effectively unclamped, hi.y / hi.z clamped, hi.x not)
+    void resample(View dst, View src, int filter)
+    {
+        const Vec3i D = dst.dims, S = src.dims;
+        if (D.x == S.x && D.y == S.y && D.z == S.z) {
+            const std::size_t n = (std::size_t)D.x * D.y * D.z;
+            for (std::size_t i = 0; i < n; ++i)
+                mapVoxel(dst.data + i * dst.bpv, unmapVoxel(src.data + i * src.bpv, src.format, src.lo, src.hi),
+                         dst.format, dst.lo, dst.hi);
+            return;
+        }
+        const long long row = S.x, plane = (long long)S.x * S.y;
+        for (int32_t z = 0; z < D.z; ++z) {
+            const int sz = cvtt32((float)z / (float)D.z * (float)S.z);
+            for (int32_t y = 0; y < D.y; ++y) {
+                const int sy = cvtt32((float)y / (float)D.y * (float)S.y);
+                for (int32_t x = 0; x < D.x; ++x) {
+                    const int sx = cvtt32((float)x / (float)D.x * (float)S.x);
+                    float value;
+                    if (filter == 0) {
+                        value = tap(src, sz * plane + sy * row + sx);
+                    } else {
+                        // lo.x / lo.y clamped, lo.z not; hi.y / hi.z clamped, hi.x not (the reference's typo'd clamps)
+                        const int lx = clampi(sx, 0, S.x - 1), ly = clampi(sy, 0, S.y - 1), lz = sz;
+                        const int hx = sx + 1, hy = clampi(sy + 1, 0, S.y - 1), hz = clampi(sz + 1, 0, S.z - 1);
+                        const float fx = (float)sx - (float)lx, fy = (float)sy - (float)ly, fz = (float)sz - (float)lz;
+                        const float v0 = tap(src, lz * plane + ly * row + lx), v1 = tap(src, lz * plane + ly * row + hx);
+                        const float v2 = tap(src, lz * plane + hy * row + lx), v3 = tap(src, lz * plane + hy * row + hx);
+                        const float v4 = tap(src, hz * plane + ly * row + lx), v5 = tap(src, hz * plane + ly * row + hx);
+                        const float v6 = tap(src, hz * plane + hy * row + lx), v7 = tap(src, hz * plane + hy * row + hx);
+                        value = refLerp(refLerp(refLerp(v0, v1, fx), refLerp(v2, v3, fx), fy),
+                                        refLerp(refLerp(v4, v5, fx), refLerp(v6, v7, fx), fy), fz);
+                    }
+                    mapVoxel(dst.data + dst.offset(x, y, z), value, dst.format, dst.lo, dst.hi);
+                }
+            }
+        }
+    }
+} // host
+} // vkt

@@ -1,0 +1,38 @@
+// Device::CPU / HostAPI::Serial bodies of the hot-path algorithms.  These run only when the calling thread's
+// policy SELECTS the CPU; nothing under Device::GPU ever reaches them (a failing GPU call returns InvalidValue).
+// Semantics follow the reference's serial path (files cited per function in serial.cpp); unlike the reference they
+// work on a raw host view instead of calling migrate() once per voxel.
+#pragma once
+
+#include <cstdint>
+
+#include <vkt/Transform.hpp>
+#include <vkt/common.hpp>
+#include <vkt/linalg.hpp>
+
+namespace vkt
+{
+namespace host
+{
+    struct View
+    {
+        uint8_t*   data;
+        Vec3i      dims;
+        DataFormat format;
+        float      lo, hi;
+        int        bpv;
+
+        std::size_t offset(int32_t x, int32_t y, int32_t z) const
+        {
+            return ((std::size_t)z * dims.x * (std::size_t)dims.y + (std::size_t)y * dims.x + (std::size_t)x) * bpv;
+        }
+    };
+
+    void fillRange(View v, Vec3i first, Vec3i last, float value);
+    void copyRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset);
+    void arithRange(int op, View dst, View s1, View s2, Vec3i first, Vec3i last, Vec3i dstOffset);
+    void transformRange(View v, Vec3i first, Vec3i last, TransformUnaryOp op);
+    void transformRange(View v1, View v2, Vec3i first, Vec3i last, TransformBinaryOp op);
+    void resample(View dst, View src, int filter);
+} // host
+} // vkt
