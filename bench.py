@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--ops", type=int, default=-1, help="1/0: also time the per-op table (default: on at N=1)")
     ap.add_argument("--cpu-sample", type=int, default=384, help="edge of the CPU-baseline sub-volume")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--shard-edge", type=int, default=4096, help="edge of the sharded volumes timed at N > 1")
+    ap.add_argument("--sharded", type=int, default=-1, help="1/0: time the sharded-volume table (default: on at N > 1)")
     return ap.parse_args()
 
 
@@ -389,6 +391,20 @@ def run_ours(args):
         from bench_ops import run_ops
         ops = run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps)
 
+    sharded_ops = None
+    if world > 1 and args.sharded != 0:
+        for v in (a, b, d):
+            try:
+                v.free()
+            except Exception:
+                pass
+        torch.cuda.empty_cache()
+        capi.check(lib.vktb_trim_pools())   # hand the pooled device memory back before torch allocates the slabs
+        from bench_sharded import run_sharded_ops
+        from volkit_b200 import sharded as sharded_mod
+        sharded_ops = run_sharded_ops(torch, dist, lib, capi, sharded_mod.ShardedVolume, sharded_mod, rank, world, peak,
+                                      time_steps, edge=args.shard_edge)
+
     cpu = None
     if rank == 0:
         edge = args.cpu_sample
@@ -408,7 +424,7 @@ def run_ours(args):
                          "traffic": None, "peak_source": peak_src, "kernel": "arithFlatKernel<UInt16,SafeSum>",
                          "algorithmic_bytes_per_voxel": 6, "frac_of_8TBs_nominal": achieved / 8000.0},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "parity": {"bit_exact_planes": planes, "ok": bool(ok)}, "ops": ops,
+            "parity": {"bit_exact_planes": planes, "ok": bool(ok)}, "ops": ops, "ops_sharded": sharded_ops,
         }
         print(json.dumps(line))
     if dist is not None:
@@ -417,10 +433,24 @@ def run_ours(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # exactly ONE JSON line may reach stdout: NCCL / torch chatter ("NCCL version ...") is routed to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    import io
+    capture = io.StringIO()
+    import contextlib
+    with contextlib.redirect_stdout(capture):
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    sys.stdout.flush()
+    lines = [l for l in capture.getvalue().splitlines() if l.startswith("{")]
+    for l in capture.getvalue().splitlines():
+        if not l.startswith("{"):
+            print(l, file=sys.stderr)
+    if lines:
+        os.write(real_stdout, (lines[-1] + "\n").encode())
 
 
 if __name__ == "__main__":

@@ -130,6 +130,10 @@ int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter,
                          int32_t src_z0, const int32_t src_full[3]);
 int vktb_resample_window_src_range(int filter, int32_t dst_z0, int32_t dst_z1, int32_t dst_dimz,
                                    int32_t src_dimz, int32_t* src_z0, int32_t* src_z1);
+/* same with the full dims: drops the extra plane reference-faithful Linear requests for its unclamped +1 x tap
+ * when the x/y maps show that tap can never leave its plane (e.g. exact 2:1 down-sampling) */
+int vktb_resample_window_src_range3(int filter, int32_t dst_z0, int32_t dst_z1, const int32_t dst_full[3],
+                                    const int32_t src_full[3], int32_t* src_z0, int32_t* src_z1);
 
 /* ---- Transform device-op registry --------------------------------------------------------------
  * Built-in ops are addressed by name; a host TransformUnaryOp / TransformBinaryOp pointer is bound to a

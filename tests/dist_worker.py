@@ -1,0 +1,114 @@
+"""One rank of the multi-rank sharding tests.  Spawned by tests/test_sharded_gloo.py (CPU tensors, gloo backend, the
+oracle plugged in as the voxel compute so that the HOST-SIDE logic -- slab ranges, halo plan, point-to-point plane
+exchange, window offsets -- is checked without a GPU) and by tests/test_sharded_gpu.py / bench (CUDA, NCCL, the
+real C-ABI kernels).  Every rank checks its own dst slab against the whole-volume oracle result."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import pyoracle as po  # noqa: E402  (checker)
+from volkit_b200 import capi, sharded  # noqa: E402
+
+CASES = [
+    # (S, D, src fmt, dst fmt, filter)
+    ((20, 12, 17), (30, 18, 23), po.UINT16, po.UINT16, po.NEAREST),
+    ((20, 12, 17), (30, 18, 23), po.FLOAT32, po.FLOAT32, po.LINEAR),
+    ((20, 12, 17), (30, 18, 23), po.UINT16, po.UINT8, po.TRILINEAR),
+    ((16, 8, 32), (8, 4, 16), po.FLOAT32, po.FLOAT32, po.LINEAR),       # exact 2:1 -> planner proves "no halo"
+    ((16, 8, 9), (24, 12, 31), po.UINT8, po.UINT16, po.LINEAR),         # thin src slabs: planes from non-neighbours
+    ((12, 10, 14), (12, 10, 14), po.UINT16, po.FLOAT32, po.NEAREST),    # equal dims: conversion only
+    ((64, 16, 24), (96, 24, 36), po.UINT16, po.UINT16, po.LINEAR),      # 16-byte aligned rows: TMA row pipeline on GPU
+]
+
+
+def np_view(desc, fmt):
+    n = desc.dims[0] * desc.dims[1] * desc.dims[2]
+    dt = np.dtype(po.DTYPES[fmt])
+    buf = (ctypes.c_uint8 * (n * dt.itemsize)).from_address(desc.data)
+    return np.frombuffer(buf, dt).reshape(desc.dims[2], desc.dims[1], desc.dims[0])
+
+
+def oracle_compute(sfmt, dfmt, lo_hi_s, lo_hi_d):
+    o = po.oracle()
+
+    def run(dst_desc, src_desc, filt, dz0, D, sz0, S):
+        d = po.Vol(np_view(dst_desc, dfmt), dfmt, *lo_hi_d)
+        s = po.Vol(np_view(src_desc, sfmt), sfmt, *lo_hi_s)
+        o.resample_window(d, s, filt, dz0, D, sz0, S)
+    return run
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    backend = sys.argv[1]                 # gloo | nccl
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    gpu = backend == "nccl"
+    if gpu:
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+        lib = capi.load()
+        capi.check(lib.vktb_set_device(torch.cuda.current_device()))
+        stream = torch.cuda.Stream()
+        torch.cuda.set_stream(stream)
+        capi.check(lib.vktb_set_stream(stream.cuda_stream))
+    else:
+        dist.init_process_group("gloo")
+        lib = None
+    device = "cuda" if gpu else "cpu"
+    o = po.oracle()
+    total_halo = 0
+    for case_no, (S, D, sfmt, dfmt, filt) in enumerate(CASES):
+        smap, dmap = (0.0, 1.0), (-1.0, 2.0)
+        whole_src = po.Vol(po.synth(S, sfmt, 1), sfmt, *smap)
+        ref = po.empty(D, dfmt, *dmap)
+        o.resample(ref, whole_src, filt)
+
+        # odd cases assemble the window in a fresh buffer, even ones in place (slab allocated with halo room)
+        plan = sharded.halo_plan(filt, D, S, world, lib)
+        halo = sharded.halo_for(plan, S, world, rank) if case_no % 2 == 0 else (0, 0)
+        src = sharded.ShardedVolume(torch, S, sfmt, rank, world, *smap, device=device, halo=halo)
+        dst = sharded.ShardedVolume(torch, D, dfmt, rank, world, *dmap, device=device)
+        mine = np.ascontiguousarray(whole_src.a[src.z0:src.z1]).view(np.uint8).ravel()
+        src.data.copy_(torch.from_numpy(mine.copy()))
+        dst.data.zero_()
+
+        compute = None if gpu else oracle_compute(sfmt, dfmt, smap, dmap)
+        halo = sharded.resample_sharded(dst, src, filt, dist, compute=compute, planner_lib=lib, plan=plan)
+        if gpu:
+            torch.cuda.synchronize()
+        total_halo += halo
+        got = dst.data.cpu().numpy().view(po.DTYPES[dfmt]).reshape(dst.z1 - dst.z0, D[1], D[0])
+        want = ref.a[dst.z0:dst.z1]
+        same = got.tobytes() == want.tobytes()
+        if not same and dfmt == po.FLOAT32:
+            gn, wn = np.isnan(got), np.isnan(want)
+            same = (gn == wn).all() and got[~gn].tobytes() == want[~wn].tobytes()
+        if not same:
+            print(f"rank {rank}: MISMATCH in case {S}->{D} fmt {sfmt}->{dfmt} filter {filt}", flush=True)
+            sys.exit(1)
+        # the planner's "no halo" claim for exact 2:1 down-sampling (SURVEY.md 8(e) caveat)
+        if S == (16, 8, 32) and world == 2 and halo != 0:
+            print(f"rank {rank}: expected no halo for exact 2:1, got {halo} bytes", flush=True)
+            sys.exit(1)
+
+    # elementwise ops need no exchange: slabs tile the volume exactly
+    Z = 23
+    covered = sorted(z for r in range(world) for z in range(*sharded.slab_range(Z, world, r)))
+    assert covered == list(range(Z))
+
+    t = torch.tensor([total_halo], dtype=torch.int64, device=device)
+    dist.all_reduce(t)
+    if rank == 0:
+        print(f"ok world={world} backend={backend} halo_bytes_total={int(t.item())}", flush=True)
+        assert int(t.item()) > 0 or world == 1
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

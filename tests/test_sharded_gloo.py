@@ -1,0 +1,58 @@
+"""Multi-rank sharding logic on CPU: world_size 2 and 3 over gloo (no GPU needed).  See tests/dist_worker.py."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def launch(world, backend):
+    port = free_port()
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), GLOO_SOCKET_IFNAME="lo")
+        procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_worker.py"), backend], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+    assert any("ok world=%d" % world in o for o in outs), outs
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_resample_sharded_gloo(world):
+    launch(world, "gloo")
+
+
+def test_halo_plan_properties():
+    from volkit_b200 import capi, sharded
+    for S, D in (((8, 8, 17), (8, 8, 23)), ((4, 4, 4096), (4, 4, 2048)), ((4, 4, 2048), (4, 4, 3072)), ((4, 4, 9), (4, 4, 31))):
+        for world in (1, 2, 3, 4, 8):
+            for filt in (capi.NEAREST, capi.LINEAR, capi.TRILINEAR):
+                windows, transfers = sharded.halo_plan(filt, D, S, world)
+                for r, (w0, w1) in enumerate(windows):
+                    z0, z1 = sharded.slab_range(S[2], world, r)
+                    got = set(range(max(w0, z0), min(w1, z1)))
+                    for t in transfers:
+                        assert t.src_rank != t.dst_rank
+                        o0, o1 = sharded.slab_range(S[2], world, t.src_rank)
+                        assert o0 <= t.z0 < t.z1 <= o1          # the sender owns what it sends
+                        if t.dst_rank == r:
+                            got |= set(range(t.z0, t.z1))
+                    assert got == set(range(w0, w1)), (S, D, world, filt, r)   # window fully covered, nothing extra
+    # exact 2:1: the 8 taps of dst plane z are src planes 2z and 2z+1 -> never cross a slab boundary
+    _, transfers = sharded.halo_plan(capi.TRILINEAR, (4, 4, 2048), (4, 4, 4096), 8)
+    assert transfers == []
+    # 2:3 up-sampling does cross
+    _, transfers = sharded.halo_plan(capi.TRILINEAR, (4, 4, 3072), (4, 4, 2048), 8)
+    assert len(transfers) == 7 and all(t.z1 - t.z0 == 1 for t in transfers)

@@ -141,26 +141,46 @@ int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
 }
 
 // Host-side slab planner: the reference's own coordinate expression (Resample_serial.hpp:60-62) evaluated in
-// binary32 at the slab's first and last dst plane; it is monotone in z.
-int vktb_resample_window_src_range(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t S, int32_t* sz0, int32_t* sz1)
+// binary32; it is monotone in its argument.
+static int32_t srcCoordHost(int32_t d, int32_t D, int32_t S)
+{
+    volatile float q = (float)d / (float)D;    // volatile: one rounding per operation, no contraction
+    volatile float s = q * (float)S;
+    float sv = s;
+    return (sv >= -2147483648.0f && sv < 2147483648.0f) ? (int32_t)sv : INT32_MIN;
+}
+
+static int planSrcRange(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t S, bool spill, int32_t* sz0, int32_t* sz1)
 {
     if (!sz0 || !sz1 || D <= 0 || S <= 0 || dz1 <= dz0) return fail("vktb_resample_window_src_range: bad arguments");
-    auto coord = [&](int32_t z) {
-        volatile float q = (float)z / (float)D;    // volatile: one rounding per operation, no contraction
-        volatile float s = q * (float)S;
-        float sv = s;
-        int32_t i = (sv >= -2147483648.0f && sv < 2147483648.0f) ? (int32_t)sv : INT32_MIN;
-        return i;
-    };
-    int32_t lo = coord(dz0), hi = coord(dz1 - 1);
+    int32_t lo = srcCoordHost(dz0, D, S), hi = srcCoordHost(dz1 - 1, D, S);
     lo = lo < 0 ? 0 : (lo > S - 1 ? S - 1 : lo);
     hi = hi < 0 ? 0 : (hi > S - 1 ? S - 1 : hi);
     int32_t end = hi + 1;                                   // exclusive
     if (filter != VKTB_NEAREST) end = hi + 2;               // +1 tap plane
-    if (filter == VKTB_LINEAR) end = hi + 3;                // + the plane the unclamped hi.x tap can spill into
+    if (filter == VKTB_LINEAR && spill) end = hi + 3;       // + the plane the unclamped hi.x tap can spill into
     if (end > S) end = S;
     *sz0 = lo; *sz1 = end;
     return 0;
+}
+
+// z-only form: assumes the reference's unclamped hi.x tap (Linear) may spill into the following plane
+int vktb_resample_window_src_range(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t S, int32_t* sz0, int32_t* sz1)
+{
+    return planSrcRange(filter, dz0, dz1, D, S, true, sz0, sz1);
+}
+
+// full-dims form: the spill plane is requested only when it can be read at all -- the last dst column must map to
+// the last src column (hx = Sx leaves the row) and some dst row must tap the last src row (so that the row after
+// it is the first row of the next plane)
+int vktb_resample_window_src_range3(int filter, int32_t dz0, int32_t dz1, const int32_t D[3], const int32_t S[3],
+                                    int32_t* sz0, int32_t* sz1)
+{
+    if (!D || !S) return fail("vktb_resample_window_src_range3: null dims");
+    bool spill = false;
+    if (filter == VKTB_LINEAR && D[0] > 0 && D[1] > 0 && S[0] > 0 && S[1] > 0)
+        spill = srcCoordHost(D[0] - 1, D[0], S[0]) >= S[0] - 1 && srcCoordHost(D[1] - 1, D[1], S[1]) + 1 >= S[1] - 1;
+    return planSrcRange(filter, dz0, dz1, D[2], S[2], spill, sz0, sz1);
 }
 
 // ---- Transform registry ----
