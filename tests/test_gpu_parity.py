@@ -227,6 +227,53 @@ def test_resample_row_pipeline(gpu):
             assert part.a.tobytes() == whole.a[dz0:dz1].tobytes(), (n, g)
 
 
+def test_resample_march_kernel(gpu):
+    """8-tap Resample through the TMA z-march (16-byte aligned src rows): several tiles in x and y, multi-box src bricks
+    (3:1 down-sampling), the reference's unclamped hi.x spill column, NaN / Inf / -0 taps, z-slab windows."""
+    from volkit_b200 import capi
+    o = po.oracle()
+    U8, U16, U32, F32 = po.UINT8, po.UINT16, po.UINT32, po.FLOAT32
+    shapes = [
+        ((200, 70, 40), (300, 100, 64), F32, F32, (0.0, 1.0), (0.0, 1.0), (po.LINEAR, po.TRILINEAR)),
+        ((256, 64, 48), (128, 32, 24), F32, F32, (0.0, 1.0), (0.0, 1.0), (po.LINEAR, po.TRILINEAR)),    # exact 2:1
+        ((264, 50, 30), (88, 20, 12), U16, U16, (0.0, 1.0), (-1.0, 2.0), (po.TRILINEAR,)),              # 3:1, 2 boxes in x
+        ((768, 20, 10), (256, 7, 5), U8, U8, (0.0, 1.0), (0.0, 1.0), (po.TRILINEAR,)),                   # 3:1 UInt8, 4 boxes
+        ((64, 40, 24), (200, 130, 70), U16, U8, (-1000.0, 3000.0), (0.0, 1.0), (po.TRILINEAR,)),        # 3x up, converting
+        ((64, 33, 17), (36, 50, 40), F32, U16, (0.0, 1.0), (0.0, 1.0), (po.LINEAR, po.TRILINEAR)),      # mixed per axis
+        ((48, 20, 12), (64, 30, 18), U32, F32, (0.0, 1.0), (0.0, 1.0), (po.TRILINEAR,)),
+    ]
+    for S, D, sfmt, dfmt, smap, dmap, filters in shapes:
+        src = cases.mk(S, sfmt, 1, *smap)
+        if sfmt == F32:
+            flat = src.a.ravel()
+            flat[::211] = np.nan
+            flat[3::173] = np.inf
+            flat[5::97] = -0.0
+            flat[-1] = np.nan          # the tap the unclamped hi.x reads at the very last voxel's row end
+        for filt in filters:
+            a, b = cases.mk(D, dfmt, 3, *dmap), cases.mk(D, dfmt, 3, *dmap)
+            o.resample(a, src, filt)
+            gpu.resample(b, src, filt)
+            assert same_bits(b.a, a.a), (S, D, sfmt, dfmt, filt)
+    # z-slab windows, Float32 Linear (8 taps) and true trilinear
+    S, D = (64, 30, 32), (96, 45, 48)
+    src = cases.mk(S, F32, 1)
+    src.a.ravel()[::101] = np.inf
+    for filt in (po.LINEAR, po.TRILINEAR):
+        whole = po.empty(D, F32)
+        o.resample(whole, src, filt)
+        for n in (2, 3):
+            for g in range(n):
+                dz0, dz1 = g * D[2] // n, (g + 1) * D[2] // n
+                a, b = ctypes.c_int32(), ctypes.c_int32()
+                capi.check(gpu.lib.vktb_resample_window_src_range3(filt, dz0, dz1, capi.I3(*D), capi.I3(*S), ctypes.byref(a),
+                                                                   ctypes.byref(b)))
+                win = po.Vol(src.a[a.value:b.value].copy(), F32)
+                part = po.empty((D[0], D[1], dz1 - dz0), F32)
+                gpu.resample_window(part, win, filt, dz0, D, a.value, S)
+                assert same_bits(part.a, whole.a[dz0:dz1]), (filt, n, g)
+
+
 def test_empty_and_degenerate_ranges(gpu):
     v = cases.mk((9, 7, 5), po.UINT16, 3)
     before = v.a.copy()

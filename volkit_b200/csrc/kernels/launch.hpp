@@ -45,6 +45,8 @@ cudaError_t launchResample(const LaunchCtx&, const VolDesc& dst, const VolDesc& 
                            int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
 cudaError_t launchResampleRowRuns(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
                                   int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
+cudaError_t launchResampleMarch(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, int mode /*1 Linear8, 2 trilinear*/,
+                                int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
 cudaError_t launchConvertFlat(const LaunchCtx&, const VolDesc& dst, uint8_t* d, const VolDesc& src, const uint8_t* s, size_t n);
 cudaError_t launchConvertRows(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
                               const int32_t last[3], const int32_t off[3]);

@@ -220,6 +220,10 @@ cudaError_t launchResample(const LaunchCtx& c, const VolDesc& dst, const VolDesc
         // fast path: TMA row pipeline (resample_rows.cu); falls through when rows are not 16-byte aligned
         cudaError_t fe = launchResampleRowRuns(c, dst, src, dstZ0, D, srcZ0, S);
         if (fe != cudaErrorNotSupported) return fe;
+    } else {
+        // 8-tap modes: TMA z-march (resample_march.cu); falls through when the operands do not qualify
+        cudaError_t fe = launchResampleMarch(c, dst, src, mode, dstZ0, D, srcZ0, S);
+        if (fe != cudaErrorNotSupported) return fe;
     }
 
     // coordinate tables (stream-ordered scratch)

@@ -1,0 +1,427 @@
+// Resample, 8-tap modes, as a z-marching brick kernel with TMA 3-D tile staging.
+//
+//   MODE_LINEAR8    reference-faithful FilterMode::Linear for sources whose taps cannot be proven finite (Float32):
+//                   StructuredVolumeView::sampleLinear, reference src/vkt/StructuredVolumeView.hpp:80-119, called with
+//                   truncated coordinates (src/vkt/Resample_serial.hpp:55-69): all 8 taps run through the lerp chain with
+//                   fraction 0, hi.x is NOT clamped, lo.z is NOT clamped (the reference's typo'd clamps).
+//   MODE_TRILINEAR  the opt-in mathematically correct filter (float coordinates, six clamps); not what the reference
+//                   computes.
+//
+// One CTA owns a dst (x,y) tile of 64 32-bit words x BY rows and marches through the dst planes.  The src planes it
+// needs (lo/hi plane of every dst plane, monotone in z) are streamed through a ring of kRing shared-memory slots; each
+// slot holds the src brick [xOrigin, +bxS) x [yOrigin, +byS) of one plane, fetched with cp.async.bulk.tensor.3d
+// (SASS UTMALDG) against a CUtensorMap of the src window (out-of-bounds elements arrive as zeros and are never tapped).
+// Warp 0 issues the loads kRing-2 planes ahead; full[]/empty[] mbarriers hand slots between the TMA unit and the eight
+// consumer warps, so there is no CTA-wide barrier in the march.  Every src plane tile is read from L2/HBM once per CTA
+// and re-used for all dst planes that tap it (~1.5 planes at 2:3 up-sampling, both z taps at 2:1 down-sampling).
+//
+// Thread mapping: lane-consecutive dst words along x (conflict-free or 2-way shared-memory taps for ratios <= 2, one
+// full 128-byte line per warp store), four rows per pass.  Per-thread tap offsets and x fractions live in registers,
+// the tile's row offsets / y fractions in a small shared table.
+//
+// Algorithmic traffic: Sx*Sy*Sz*bpv_src (every src voxel is tapped when the ratio is <= 2) + Dx*Dy*Dz*bpv_dst.
+#include <cstdlib>
+
+#include <cuda.h>
+
+#include "common.cuh"
+#include "launch.hpp"
+#include "tma.cuh"
+#include "voxel_codec.cuh"
+
+namespace vktb {
+
+namespace {
+
+constexpr int kMarchThreads = 256;
+constexpr int kLanesX = 64;     // threads along x: one 32-bit dst word each
+constexpr int kRowsY = kMarchThreads / kLanesX;
+constexpr int kMaxBY = 32;      // dst rows per tile (8 passes of kRowsY)
+constexpr int kRing = 4;        // src plane slots
+constexpr int kMaxBox = 256;    // TMA box extent limit per dimension
+constexpr int kMaxBoxesX = 4;
+constexpr int kHdr = 4;
+
+enum { M_LINEAR8 = 1, M_TRILINEAR = 2 };
+
+struct AxisEntry { int lo, hi; float fr; };
+
+// lo / hi tap and fraction of dst index d on one axis (axis: 0 x, 1 y, 2 z)
+__device__ __forceinline__ AxisEntry axisEntry(int d, int D, int S, int mode, int axis)
+{
+    const float s = __fmul_rn(__fdiv_rn(__int2float_rn(d), __int2float_rn(D)), __int2float_rn(S));
+    const int l = (int)x86Cvtt32(s);
+    AxisEntry e;
+    if (mode == M_TRILINEAR) {
+        e.lo = min(max(l, 0), S - 1);
+        e.hi = min(max((int)x86Cvtt32(__fadd_rn(s, 1.f)), 0), S - 1);
+        e.fr = __fsub_rn(s, __int2float_rn(e.lo));
+    } else {
+        const int cl = min(max(l, 0), S - 1);
+        e.lo = axis == 2 ? l : cl;                                   // lo.z is never clamped
+        e.hi = axis == 0 ? l + 1 : min(max(l + 1, 0), S - 1);        // hi.x is never clamped
+        e.fr = __fsub_rn(__int2float_rn(l), __int2float_rn(axis == 2 ? l : cl));
+    }
+    return e;
+}
+
+// Table layout (ints; fractions bit-cast): hdr[4] = {nSeq}; x: lo[Dx] hi[Dx] fr[Dx]; y: lo[Dy] hi[Dy] fr[Dy];
+// z: lo[dz] hi[dz] fr[dz] seqLo[dz] seqHi[dz]; planeOf[szCount]; mark[szCount]; rank[szCount]
+__global__ void __launch_bounds__(1024)
+marchPlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz0, int Dz, int Sz, int srcZ0, int szCount, int mode)
+{
+    __shared__ int scan[1024];
+    const int t = threadIdx.x;
+    int* X = tab + kHdr;
+    int* Y = X + 3 * Dx;
+    int* Z = Y + 3 * Dy;
+    if (blockIdx.x < 2) {
+        const int n = blockIdx.x == 0 ? Dx : Dy, S = blockIdx.x == 0 ? Sx : Sy;
+        int* A = blockIdx.x == 0 ? X : Y;
+        for (int i = t; i < n; i += 1024) {
+            const AxisEntry e = axisEntry(i, n, S, mode, blockIdx.x);
+            A[i] = e.lo; A[n + i] = e.hi; A[2 * n + i] = __float_as_int(e.fr);
+        }
+        return;
+    }
+    int* seqLo = Z + 3 * dzCount;
+    int* seqHi = seqLo + dzCount;
+    int* planeOf = seqHi + dzCount;
+    int* mark = planeOf + szCount;
+    int* rank = mark + szCount;
+    for (int i = t; i < szCount; i += 1024) mark[i] = 0;
+    __syncthreads();
+    for (int i = t; i < dzCount; i += 1024) {
+        const AxisEntry e = axisEntry(dz0 + i, Dz, Sz, mode, 2);
+        Z[i] = e.lo; Z[dzCount + i] = e.hi; Z[2 * dzCount + i] = __float_as_int(e.fr);
+        const int a = e.lo - srcZ0, b = e.hi - srcZ0;
+        if (a >= 0 && a < szCount) mark[a] = 1;
+        if (b >= 0 && b < szCount) mark[b] = 1;
+    }
+    __syncthreads();
+    const int seg = (szCount + 1023) / 1024;
+    const int i0 = min(szCount, t * seg), i1 = min(szCount, i0 + seg);
+    int cnt = 0;
+    for (int i = i0; i < i1; ++i) cnt += mark[i];
+    scan[t] = cnt;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = t >= o ? scan[t - o] : 0;
+        __syncthreads();
+        scan[t] += v;
+        __syncthreads();
+    }
+    int k = scan[t] - cnt;
+    for (int i = i0; i < i1; ++i) {
+        rank[i] = k;
+        if (mark[i]) { planeOf[k] = i; ++k; }
+    }
+    if (t == 1023) tab[0] = scan[1023];
+    __syncthreads();
+    for (int i = t; i < dzCount; i += 1024) {
+        const int a = min(max(Z[i] - srcZ0, 0), szCount - 1), b = min(max(Z[dzCount + i] - srcZ0, 0), szCount - 1);
+        seqLo[i] = rank[a];
+        seqHi[i] = rank[b];
+    }
+}
+
+struct MarchParams
+{
+    uint8_t*       d;       // dst window base
+    const uint8_t* s;       // src window base (spill tap only)
+    int Dx, Dy, dzCount;
+    int Sx, Sy, szCount;
+    int BXv, BY, tilesX;    // dst tile: BXv voxels (= 64 words) x BY rows
+    int bxS, byS, nBoxX;    // src brick: nBoxX boxes of bxS x byS elements per plane
+    int slotBytes;
+    const int* tab;
+    Mapping md, ms;
+};
+
+template <int B> struct ElemT;
+template <> struct ElemT<1> { typedef uint8_t type; };
+template <> struct ElemT<2> { typedef uint16_t type; };
+template <> struct ElemT<4> { typedef uint32_t type; };
+
+template <int FS, int FD, int MODE>
+__global__ void __launch_bounds__(kMarchThreads)
+resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
+{
+    constexpr int BS = bytesPerVoxel(FS), BD = bytesPerVoxel(FD);
+    constexpr int VW = 4 / BD;   // dst voxels per 32-bit word
+    typedef typename ElemT<BS>::type SrcT;
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full[kRing], empty[kRing];
+    __shared__ int rowLoOff[kMaxBY], rowHiOff[kMaxBY], rowLoId[kMaxBY], rowHiId[kMaxBY];
+    __shared__ float rowFr[kMaxBY];
+
+    const int t = threadIdx.x, lx = t % kLanesX, ty = t / kLanesX;
+    const int* X = p.tab + kHdr;
+    const int* Y = X + 3 * p.Dx;
+    const int* Z = Y + 3 * p.Dy;
+    const int* seqLoT = Z + 3 * p.dzCount;
+    const int* seqHiT = seqLoT + p.dzCount;
+    const int* planeOf = seqHiT + p.dzCount;
+    const int nSeq = p.tab[0];
+
+    const int tileX = blockIdx.x % p.tilesX, tileY = blockIdx.x / p.tilesX;
+    const int x0 = tileX * p.BXv, y0 = tileY * p.BY;
+    const int h = min(p.BY, p.Dy - y0);
+    // the innermost TMA coordinate must address a 16-byte aligned element (found the hard way: misaligned box
+    // origins raise an illegal-instruction fault)
+    const int xOrigin = X[x0] & ~(16 / BS - 1), yOrigin = Y[y0];
+    const int boxElems = p.bxS * p.byS;
+
+    // this thread's dst word: voxels x0 + lx*VW + i
+    const int xw = x0 + lx * VW;
+    const bool active = xw < p.Dx;
+    int oLo[VW], oHi[VW];
+    float fx[VW];
+    bool spill[VW];
+    bool anySpill = false;
+#pragma unroll
+    for (int i = 0; i < VW; ++i) {
+        oLo[i] = oHi[i] = 0; fx[i] = 0.f; spill[i] = false;
+        if (active) {
+            const int x = xw + i;
+            const int a = X[x] - xOrigin, b = X[p.Dx + x] - xOrigin;
+            oLo[i] = (a / p.bxS) * boxElems + a % p.bxS;
+            spill[i] = MODE == M_LINEAR8 && X[p.Dx + x] >= p.Sx;   // the unclamped +1 tap leaves the row
+            oHi[i] = spill[i] ? oLo[i] : (b / p.bxS) * boxElems + b % p.bxS;
+            fx[i] = __int_as_float(X[2 * p.Dx + x]);
+            anySpill |= spill[i];
+        }
+    }
+    for (int r = t; r < h; r += kMarchThreads) {
+        const int y = y0 + r;
+        rowLoId[r] = Y[y]; rowHiId[r] = Y[p.Dy + y];
+        rowLoOff[r] = (Y[y] - yOrigin) * p.bxS;
+        rowHiOff[r] = (Y[p.Dy + y] - yOrigin) * p.bxS;
+        rowFr[r] = __int_as_float(Y[2 * p.Dy + y]);
+    }
+    if (t == 0) {
+        for (int i = 0; i < kRing; ++i) { mbarInit(smemAddr(&full[i]), 1); mbarInit(smemAddr(&empty[i]), kMarchThreads / 32); }
+        fenceBarrierInit();
+    }
+    __syncthreads();
+
+    const long long dstRowPitch = (long long)p.Dx * BD;
+    const long long dstPlanePitch = dstRowPitch * p.Dy;
+    const long long srcCount = (long long)p.Sx * p.Sy * p.szCount;   // voxels in the src window
+    const uint32_t slotTx = (uint32_t)(p.nBoxX * boxElems * BS);
+
+    // one tap as a float; `spilled`: the reference's hi.x tap at the last column reads linear index + 1, i.e. the first
+    // voxel of the next row / plane, or nothing (zero voxel) past the end of the buffer
+    auto tapF = [&](const uint8_t* slot, int off) -> float {
+        return unmapVoxel<FS, false>((uint32_t)reinterpret_cast<const SrcT*>(slot)[off], p.ms);
+    };
+    auto spillF = [&](int plane, int row) -> float {
+        const long long idx = ((long long)plane * p.Sy + row) * p.Sx + p.Sx;
+        const uint32_t raw = idx < srcCount ? (uint32_t)reinterpret_cast<const SrcT*>(p.s)[idx] : 0u;
+        return unmapVoxel<FS, false>(raw, p.ms);
+    };
+
+    int issued = 0, released = 0, prevLo = -1, prevHi = -1;
+    uint32_t outWord[kMaxBY / kRowsY];
+#pragma unroll
+    for (int i = 0; i < kMaxBY / kRowsY; ++i) outWord[i] = 0u;
+
+    for (int zi = 0; zi < p.dzCount; ++zi) {
+        const int sLo = seqLoT[zi], sHi = seqHiT[zi];
+        if (t < 32) {
+            const int want = min(nSeq, sLo + kRing);
+            while (issued < want) {
+                const int slot = issued % kRing;
+                if (issued >= kRing) mbarWait(smemAddr(&empty[slot]), (uint32_t)(((issued / kRing) & 1) ^ 1));
+                if (t == 0) {
+                    const uint32_t bar = smemAddr(&full[slot]);
+                    mbarArriveExpectTx(bar, slotTx);
+                    const int plane = planeOf[issued];
+                    for (int kb = 0; kb < p.nBoxX; ++kb)
+                        tensorLoad3d(smemAddr(smem + slot * p.slotBytes + kb * boxElems * BS), &tmap,
+                                     xOrigin + kb * p.bxS, yOrigin, plane, bar);
+                }
+                __syncwarp();
+                ++issued;
+            }
+        }
+        mbarWait(smemAddr(&full[sLo % kRing]), (uint32_t)((sLo / kRing) & 1));
+        mbarWait(smemAddr(&full[sHi % kRing]), (uint32_t)((sHi / kRing) & 1));
+
+        // reference-faithful Linear: fractions are all zero, so dst planes tapping the same src planes are identical
+        const bool reuse = MODE == M_LINEAR8 && sLo == prevLo && sHi == prevHi;
+        prevLo = sLo; prevHi = sHi;
+        const uint8_t* slotLo = smem + (sLo % kRing) * p.slotBytes;
+        const uint8_t* slotHi = smem + (sHi % kRing) * p.slotBytes;
+        const float fz = __int_as_float(Z[2 * p.dzCount + zi]);
+        if (active) {
+#pragma unroll
+            for (int pass = 0; pass < kMaxBY / kRowsY; ++pass) {
+                const int r = ty + pass * kRowsY;
+                if (r >= h) break;
+                if (!reuse) {
+                    const int rl = rowLoOff[r], rh = rowHiOff[r];
+                    const float fy = rowFr[r];
+                    uint32_t word = 0u;
+#pragma unroll
+                    for (int i = 0; i < VW; ++i) {
+                        float v0 = tapF(slotLo, rl + oLo[i]), v2 = tapF(slotLo, rh + oLo[i]);
+                        float v4 = tapF(slotHi, rl + oLo[i]), v6 = tapF(slotHi, rh + oLo[i]);
+                        float v1, v3, v5, v7;
+                        if (anySpill && spill[i]) {
+                            const int pl = planeOf[sLo], ph = planeOf[sHi];
+                            v1 = spillF(pl, rowLoId[r]); v3 = spillF(pl, rowHiId[r]);
+                            v5 = spillF(ph, rowLoId[r]); v7 = spillF(ph, rowHiId[r]);
+                        } else {
+                            v1 = tapF(slotLo, rl + oHi[i]); v3 = tapF(slotLo, rh + oHi[i]);
+                            v5 = tapF(slotHi, rl + oHi[i]); v7 = tapF(slotHi, rh + oHi[i]);
+                        }
+                        const float f = refLerp(refLerp(refLerp(v0, v1, fx[i]), refLerp(v2, v3, fx[i]), fy),
+                                                refLerp(refLerp(v4, v5, fx[i]), refLerp(v6, v7, fx[i]), fy), fz);
+                        const uint32_t e = mapVoxel<FD, false>(f, p.md);
+                        word |= (BD == 4) ? e : (e & ((1u << (8 * (BD & 3))) - 1u)) << (8 * BD * i);
+                    }
+                    outWord[pass] = word;
+                }
+                stStream32(p.d + (long long)zi * dstPlanePitch + (long long)(y0 + r) * dstRowPitch + (long long)xw * BD,
+                           outWord[pass]);
+            }
+        }
+        // hand back the planes no later dst plane taps
+        const int nextLo = zi + 1 < p.dzCount ? seqLoT[zi + 1] : nSeq;
+        __syncwarp();
+        if ((t & 31) == 0)
+            for (; released < nextLo; ++released) mbarArrive(smemAddr(&empty[released % kRing]));
+        released = max(released, nextLo);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// libcuda is never linked: the driver entry point is fetched through the runtime
+EncodeTiledFn encodeTiled()
+{
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+template <int FS, int FD, int MODE>
+cudaError_t launchMarch(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid)
+{
+    auto kern = resampleMarchKernel<FS, FD, MODE>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, kMarchThreads, smemBytes, c.stream>>>(tm, p);
+    countLaunch();
+    return cudaGetLastError();
+}
+
+template <int FS, int FD>
+cudaError_t launchMarchMode(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid, int mode)
+{
+    return mode == M_LINEAR8 ? launchMarch<FS, FD, M_LINEAR8>(c, tm, p, smemBytes, grid)
+                             : launchMarch<FS, FD, M_TRILINEAR>(c, tm, p, smemBytes, grid);
+}
+
+template <int FS>
+cudaError_t launchMarchDst(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid,
+                           int fd, int mode)
+{
+    switch (fd) {
+    case F_U8:  return launchMarchMode<FS, F_U8>(c, tm, p, smemBytes, grid, mode);
+    case F_U16: return launchMarchMode<FS, F_U16>(c, tm, p, smemBytes, grid, mode);
+    case F_U32: return launchMarchMode<FS, F_U32>(c, tm, p, smemBytes, grid, mode);
+    case F_F32: return launchMarchMode<FS, F_F32>(c, tm, p, smemBytes, grid, mode);
+    }
+    return cudaErrorNotSupported;
+}
+
+} // namespace
+
+// 8-tap resample (mode 1 = reference-faithful Linear, 2 = true trilinear) through the TMA z-march.  Returns
+// cudaErrorNotSupported when the operands do not qualify; the caller then uses the direct-gather kernel.
+cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, int mode,
+                                int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3])
+{
+    const int bs = bytesPerVoxel(src.format), bd = bytesPerVoxel(dst.format);
+    const int dzCount = dst.dims[2], szCount = src.dims[2];
+    auto plain = [](int f) { return f == F_U8 || f == F_U16 || f == F_U32 || f == F_F32; };
+    if (!plain(src.format) || !plain(dst.format)) return cudaErrorNotSupported;
+    if (getenv("VKTB_RS_NO_MARCH")) return cudaErrorNotSupported;
+    // TMA: 16-byte aligned base and strides; dst rows are written as 32-bit words
+    if ((reinterpret_cast<uintptr_t>(src.data) & 15u) || ((long long)S[0] * bs) % 16) return cudaErrorNotSupported;
+    if ((reinterpret_cast<uintptr_t>(dst.data) & 3u) || ((long long)D[0] * bd) % 4) return cudaErrorNotSupported;
+    for (int a = 0; a < 3; ++a) if (D[a] > (1 << 24) || S[a] > (1 << 24)) return cudaErrorNotSupported;
+    EncodeTiledFn encode = encodeTiled();
+    if (!encode) return cudaErrorNotSupported;
+
+    MarchParams p;
+    p.d = dst.data; p.s = src.data;
+    p.Dx = D[0]; p.Dy = D[1]; p.dzCount = dzCount;
+    p.Sx = S[0]; p.Sy = S[1]; p.szCount = szCount;
+    p.md = dst.map; p.ms = src.map;
+    p.BXv = kLanesX * (4 / bd);
+    p.tilesX = (D[0] + p.BXv - 1) / p.BXv;
+    // src brick extents: floor(tile * S / D) + 3 covers lo .. hi of the tile (hi may be lo + 2 after rounding)
+    const int gran = 16 / bs;
+    const long long spanX = (long long)p.BXv * S[0] / D[0] + 3 + (gran - 1);   // + the origin's round-down to 16 bytes
+    if (spanX <= kMaxBox) { p.nBoxX = 1; p.bxS = (int)((spanX + gran - 1) / gran * gran); if (p.bxS > kMaxBox) p.bxS = kMaxBox; }
+    else { p.nBoxX = (int)((spanX + kMaxBox - 1) / kMaxBox); p.bxS = kMaxBox; }
+    if (p.nBoxX > kMaxBoxesX) return cudaErrorNotSupported;
+    int BY = kMaxBY;
+    long long byS = 0, slot = 0;
+    for (; BY >= kRowsY; BY /= 2) {
+        byS = (long long)BY * S[1] / D[1] + 3;
+        slot = ((long long)p.nBoxX * p.bxS * byS * bs + 127) / 128 * 128;
+        if (byS <= kMaxBox && slot <= 20 * 1024) break;
+    }
+    if (BY < kRowsY) return cudaErrorNotSupported;
+    p.BY = BY; p.byS = (int)byS; p.slotBytes = (int)slot;
+    const int tilesY = (D[1] + BY - 1) / BY;
+    const size_t smemBytes = (size_t)kRing * slot;
+
+    CUtensorMap tm;
+    const cuuint64_t gdim[3] = { (cuuint64_t)S[0], (cuuint64_t)S[1], (cuuint64_t)szCount };
+    const cuuint64_t gstr[2] = { (cuuint64_t)S[0] * bs, (cuuint64_t)S[0] * S[1] * bs };
+    const cuuint32_t box[3] = { (cuuint32_t)p.bxS, (cuuint32_t)p.byS, 1u };
+    const cuuint32_t estr[3] = { 1u, 1u, 1u };
+    const CUtensorMapDataType dt = bs == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : bs == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16
+                                                                                      : CU_TENSOR_MAP_DATA_TYPE_UINT32;
+    if (encode(&tm, dt, 3, const_cast<uint8_t*>(src.data), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorNotSupported;
+
+    const size_t nTab = kHdr + 3 * (size_t)D[0] + 3 * (size_t)D[1] + 5 * (size_t)dzCount + 3 * (size_t)szCount;
+    int* tab = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&tab, nTab * sizeof(int), c.stream);
+    if (e != cudaSuccess) return e;
+    p.tab = tab;
+    marchPlanKernel<<<3, 1024, 0, c.stream>>>(tab, D[0], S[0], D[1], S[1], dzCount, dstZ0, D[2], S[2], srcZ0, szCount, mode);
+    countLaunch();
+
+    const unsigned grid = (unsigned)(p.tilesX * tilesY);
+    switch (src.format) {
+    case F_U8:  e = launchMarchDst<F_U8>(c, tm, p, smemBytes, grid, dst.format, mode); break;
+    case F_U16: e = launchMarchDst<F_U16>(c, tm, p, smemBytes, grid, dst.format, mode); break;
+    case F_U32: e = launchMarchDst<F_U32>(c, tm, p, smemBytes, grid, dst.format, mode); break;
+    case F_F32: e = launchMarchDst<F_F32>(c, tm, p, smemBytes, grid, dst.format, mode); break;
+    default: e = cudaErrorNotSupported;
+    }
+    cudaFreeAsync(tab, c.stream);
+    return e;
+}
+
+} // namespace vktb
