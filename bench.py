@@ -253,8 +253,10 @@ def mem_available_bytes():
 
 
 def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
-    """The call a user makes: host buffers in, host buffer out, through the C-ABI (= what vkt::SafeSum does after
-    ManagedBuffer::migrate): per step pinned H2D of both sources, SafeSum kernel, D2H of the destination."""
+    """The call a user makes with HOST buffers, through the C-ABI.  Two forms are timed on the same pinned buffers:
+      streamed  vktb_hosted_arith_range: z-slabs, upload / kernel / download overlapped (the product's e2e path)
+      serial    what vkt::SafeSum does after ManagedBuffer::migrate(): whole-buffer H2D x2, kernel, whole-buffer D2H
+    Returns (streamed ms, serial ms, h2d bytes, d2h bytes, sample of the streamed result, sample of the serial)."""
     vol_bytes = size ** 3 * 2
     host = []
     for _ in range(3):
@@ -265,8 +267,12 @@ def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
     capi.check(lib.vktb_memcpy(host[0], src_a.ptr, vol_bytes, capi.D2H))
     capi.check(lib.vktb_memcpy(host[1], src_b.ptr, vol_bytes, capi.D2H))
     z, l = capi.I3(0, 0, 0), capi.I3(size, size, size)
+    hv = [capi.vol(h, (size,) * 3, capi.UINT16) for h in host]
 
-    def step():
+    def grab():
+        return np.ctypeslib.as_array(ctypes.cast(host[2], ctypes.POINTER(ctypes.c_uint16)), shape=(size * size,)).copy()
+
+    def step_serial():
         a, b, d = dv((size,) * 3, capi.UINT16), dv((size,) * 3, capi.UINT16), dv((size,) * 3, capi.UINT16)
         capi.check(lib.vktb_memcpy(a.ptr, host[0], vol_bytes, capi.H2D))
         capi.check(lib.vktb_memcpy(b.ptr, host[1], vol_bytes, capi.H2D))
@@ -275,11 +281,18 @@ def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
         capi.check(lib.vktb_memcpy(host[2], d.ptr, vol_bytes, capi.D2H))   # complete on return
         a.free(); b.free(); d.free()
 
-    ms = time_steps(torch, step, steps, warmup, dist)
-    sample = np.ctypeslib.as_array(ctypes.cast(host[2], ctypes.POINTER(ctypes.c_uint16)), shape=(size * size,)).copy()
+    def step_streamed():
+        capi.check(lib.vktb_hosted_arith_range(capi.SAFESUM, ctypes.byref(hv[2]), ctypes.byref(hv[0]),
+                                               ctypes.byref(hv[1]), z, l, z), "vktb_hosted_arith_range")
+
+    ms_serial = time_steps(torch, step_serial, max(1, steps // 2), warmup, dist)
+    sample_serial = grab()
+    ctypes.memset(host[2], 0, size * size * 2)
+    ms = time_steps(torch, step_streamed, steps, warmup, dist)
+    sample = grab()
     for h in host:
         capi.check(lib.vktb_host_free(h))
-    return ms, 2 * vol_bytes, vol_bytes, sample
+    return ms, ms_serial, 2 * vol_bytes, vol_bytes, sample, sample_serial
 
 
 def run_ours(args):
@@ -374,11 +387,18 @@ def run_ours(args):
                 torch.cuda.synchronize()
                 del t
         e_steps = max(2, min(args.steps, 4))
-        e_ms, h2d, d2h, _ = run_e2e(torch, lib, capi, DeviceVolume, Se, e_steps, 1, dist, a, b)
+        e_ms, e_ms_serial, h2d, d2h, smp, smp_serial = run_e2e(torch, lib, capi, DeviceVolume, Se, e_steps, 1, dist, a, b)
+        if smp.tobytes() != smp_serial.tobytes():
+            raise SystemExit("bench: streamed and serial end-to-end results differ")
         e2e = {"value": world * Se ** 3 / (e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": e_steps,
-               "workload": f"SafeSum {Se}^3 UInt16 per GPU, pinned host buffers (vktb_host_alloc) -> vktb_memcpy H2D x2 -> "
-                           f"kernel -> vktb_memcpy D2H", "host_mem_limited": Se != S and need > 0}
+               "workload": f"SafeSum {Se}^3 UInt16 per GPU, pinned host buffers (vktb_host_alloc) -> "
+                           f"vktb_hosted_arith_range (z-slabs: H2D x2 | kernel | D2H overlapped)",
+               "serial_migrate_value": world * Se ** 3 / (e_ms_serial * 1e-3) / 1e9,
+               "serial_migrate_ms": e_ms_serial,
+               "serial_migrate_workload": "vktb_memcpy H2D x2 -> vktb_arith_range -> vktb_memcpy D2H (whole buffers, "
+                                          "what ManagedBuffer::migrate() does)",
+               "host_mem_limited": Se != S and need > 0}
 
     ops = None
     want_ops = args.ops == 1 or (args.ops == -1 and world == 1)

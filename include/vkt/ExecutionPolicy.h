@@ -23,6 +23,11 @@ typedef struct
 VKTAPI void vktSetThreadExecutionPolicy(vktExecutionPolicy_t policy);
 VKTAPI vktExecutionPolicy_t vktGetThreadExecutionPolicy(void);
 
+/* volkit-b200 extension: stream host-resident volumes through the GPU in z-slabs instead of migrating them
+ * (see vkt::SetHostStreaming in ExecutionPolicy.hpp) */
+VKTAPI void vktSetHostStreaming(vktBool_t enabled);
+VKTAPI vktBool_t vktGetHostStreaming(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,4 +24,12 @@ namespace vkt
 
     VKTAPI void SetThreadExecutionPolicy(ExecutionPolicy policy);
     VKTAPI ExecutionPolicy GetThreadExecutionPolicy();
+
+    // volkit-b200 extension (per thread, default off or VKT_B200_STREAMING=1): under Device::GPU, algorithms whose
+    // volumes all still live on the host do not migrate() them; they stream z-slabs through the B200 (upload, kernel
+    // and download overlapped, vktb_hosted_* in vktb/backend.h) and leave the volumes -- and the result -- on the
+    // host.  Same voxels as the migrating call; volumes larger than device memory work.  Covers the arithmetic
+    // family, unary Transform and Resample; other calls, and calls with a device-resident volume, migrate as usual.
+    VKTAPI void SetHostStreaming(bool enabled);
+    VKTAPI bool GetHostStreaming();
 } // vkt

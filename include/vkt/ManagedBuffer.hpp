@@ -96,6 +96,10 @@ namespace vkt
             data_ = moved;
         }
 
+        // volkit-b200 extension: where the bytes live right now, and the pointer WITHOUT migrating
+        bool residesOnHost() const { return lastAllocationPolicy_.device == ExecutionPolicy::Device::CPU; }
+        T* dataInPlace() { return data_; }
+
     protected:
         void allocate(std::size_t size)
         {

@@ -135,6 +135,19 @@ int vktb_resample_window_src_range(int filter, int32_t dst_z0, int32_t dst_z1, i
 int vktb_resample_window_src_range3(int filter, int32_t dst_z0, int32_t dst_z1, const int32_t dst_full[3],
                                     const int32_t src_full[3], int32_t* src_z0, int32_t* src_z1);
 
+/* ---- Host-resident volumes, streamed ---------------------------------------------------------------
+ * Same semantics and results as the entry points above, but every vktb_vol.data is a HOST pointer (pinned:
+ * vktb_host_alloc or cudaHostRegister; pageable memory works without overlap).  The range is cut into z-slabs and
+ * upload, kernel and download of consecutive slabs overlap on two copy engines (PCIe is full duplex), instead of
+ * the three serial whole-buffer phases of ManagedBuffer::migrate() (include/cpp/vkt/ManagedBuffer.hpp:168-198)
+ * -> kernel -> migrate() back.  Volumes larger than device memory are fine; the volumes stay on the host and
+ * the result is complete in host memory on return.  The range must lie inside all volumes; dst may be one of
+ * the sources (in place, offset 0) but must not overlap them otherwise. */
+int vktb_hosted_arith_range(int op, const vktb_vol* dst, const vktb_vol* src1, const vktb_vol* src2,
+                            const int32_t first[3], const int32_t last[3], const int32_t dst_offset[3]);
+int vktb_hosted_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op);
+int vktb_hosted_resample(const vktb_vol* dst, const vktb_vol* src, int filter);
+
 /* ---- Transform device-op registry --------------------------------------------------------------
  * Built-in ops are addressed by name; a host TransformUnaryOp / TransformBinaryOp pointer is bound to a
  * device op once, after which the unchanged vkt::Transform(volume, hostFn) signature resolves it.

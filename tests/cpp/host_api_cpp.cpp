@@ -1,7 +1,7 @@
 // Exercises the C++ host mirror (include/vkt/*.hpp) the way the reference's examples do
 // (src/examples/CoreAlgorithms.c, Arithmetic.cpp, ExecutionPolicy.cpp): volumes are created and filled on the CPU,
 // the thread's ExecutionPolicy is switched, algorithms run, results are read back after switching to CPU again.
-// usage: host_api_cpp <cpu|gpu> <dir>      inputs <dir>/a.raw, b.raw (48x40x36 UInt16); outputs <dir>/out_*.raw
+// usage: host_api_cpp <cpu|gpu|gpu-stream> <dir>      inputs <dir>/a.raw, b.raw (48x40x36 UInt16); outputs <dir>/out_*.raw
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -48,7 +48,8 @@ static void unboundOp(int32_t, int32_t, int32_t, VoxelView) {}
 int main(int argc, char** argv)
 {
     if (argc < 3) return 2;
-    const bool gpu = std::strcmp(argv[1], "gpu") == 0;
+    const bool stream = std::strcmp(argv[1], "gpu-stream") == 0;    // GPU policy + host streaming extension
+    const bool gpu = stream || std::strcmp(argv[1], "gpu") == 0;
     g_dir = argv[2];
 
     ExecutionPolicy cpu = GetThreadExecutionPolicy();            // default: CPU / Serial
@@ -72,6 +73,31 @@ int main(int argc, char** argv)
     StructuredVolume prod(X, Y, Z, DataFormat::Float32, 1.f, 1.f, 1.f, -1000.f, 3000.f);
 
     SetThreadExecutionPolicy(run);      // deferred: nothing moves until an algorithm touches a volume
+
+    if (stream) {
+        // host streaming: volumes that all live on the host are streamed through the GPU in z-slabs and STAY on the
+        // host; the voxels are those of the migrating call (saved as out_s_*.raw, compared with the same references)
+        if (GetHostStreaming()) return 7;                  // off by default
+        SetHostStreaming(true);
+        SetThreadExecutionPolicy(cpu);                     // volumes are allocated where the policy says: on the host
+        StructuredVolume ssum(X, Y, Z, DataFormat::UInt16), sup(72, 60, 54, DataFormat::UInt16);
+        StructuredVolume st(a);                            // host copy of a
+        SetThreadExecutionPolicy(run);
+        CHECK(BindDeviceOp(xorCoord, "xor_coord"));
+        CHECK(SafeSum(ssum, a, b));
+        CHECK(Resample(sup, a, FilterMode::Linear));
+        CHECK(TransformRange(st, 1, 2, 3, 47, 39, 35, xorCoord));
+        if (!ssum.residesOnHost() || !sup.residesOnHost() || !st.residesOnHost() || !a.residesOnHost() || !b.residesOnHost()) {
+            std::fprintf(stderr, "host streaming migrated a volume\n");
+            return 8;
+        }
+        SetThreadExecutionPolicy(cpu);
+        save(ssum, "out_s_sum.raw"); save(sup, "out_s_up.raw"); save(st, "out_s_t.raw");
+        SetThreadExecutionPolicy(run);
+        // a call with a device-resident volume migrates as usual, streaming on or off
+        CHECK(Fill(ssum, .5f));
+        if (ssum.residesOnHost()) return 9;
+    }
 
     CHECK(Fill(diff, .25f));
     CHECK(Fill(cpy, .5f));

@@ -70,3 +70,52 @@ class GpuLib:
                                                  I3(*dst_full), sz0, I3(*src_full)), "resample_window")
         self._down(d, dst)
         s.free()
+
+
+class HostedLib:
+    """The vktb_hosted_* entry points: inputs live in pinned host memory (vktb_host_alloc), the library streams
+    z-slabs through the device.  Same method names as GpuLib for the three algorithms it covers."""
+    kind = "cuda-hosted"
+
+    def __init__(self):
+        self.lib = capi.load()
+
+    def _pin(self, v: po.Vol):
+        import numpy as np
+        p = ctypes.c_void_p()
+        n = max(1, v.a.nbytes)
+        capi.check(self.lib.vktb_host_alloc(ctypes.byref(p), n), "vktb_host_alloc")
+        view = np.ctypeslib.as_array(ctypes.cast(p.value, ctypes.POINTER(ctypes.c_uint8)), shape=(n,))
+        view[:v.a.nbytes] = np.frombuffer(v.a.tobytes(), dtype=np.uint8)
+        x, y, z = v.a.shape[2], v.a.shape[1], v.a.shape[0]
+        return p, view, capi.vol(p.value, (x, y, z), v.fmt, v.lo, v.hi)
+
+    def _unpin(self, pinned, v: po.Vol, write_back: bool):
+        import numpy as np
+        p, view, _ = pinned
+        if write_back:
+            v.a[...] = np.frombuffer(view[:v.a.nbytes].tobytes(), dtype=v.a.dtype).reshape(v.a.shape)
+        capi.check(self.lib.vktb_host_free(p), "vktb_host_free")
+
+    def arith_range(self, op, dst, s1, s2, first, last, off=(0, 0, 0)):
+        d = self._pin(dst)
+        a = d if s1 is dst else self._pin(s1)
+        b = d if s2 is dst else (a if s2 is s1 else self._pin(s2))
+        capi.check(self.lib.vktb_hosted_arith_range(op, ctypes.byref(d[2]), ctypes.byref(a[2]), ctypes.byref(b[2]),
+                                                    I3(*first), I3(*last), I3(*off)), "hosted arith")
+        if b is not d and b is not a:
+            self._unpin(b, s2, False)
+        if a is not d:
+            self._unpin(a, s1, False)
+        self._unpin(d, dst, True)
+
+    def transform_range1(self, vol, first, last, op):
+        d = self._pin(vol)
+        capi.check(self.lib.vktb_hosted_transform_range1(ctypes.byref(d[2]), I3(*first), I3(*last), op), "hosted transform1")
+        self._unpin(d, vol, True)
+
+    def resample(self, dst, src, filt):
+        d, s = self._pin(dst), self._pin(src)
+        capi.check(self.lib.vktb_hosted_resample(ctypes.byref(d[2]), ctypes.byref(s[2]), filt), "hosted resample")
+        self._unpin(s, src, False)
+        self._unpin(d, dst, True)

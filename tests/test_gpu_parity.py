@@ -99,6 +99,33 @@ def test_arith_exhaustive_u8_pairs(gpu):
             assert a.a.tobytes() == b.a.tobytes(), (op, lo, hi)
 
 
+def test_arith_u8_pair_table_stream(gpu):
+    """UInt8 streams of >= 2^24 voxels take the 64 KiB pair-table kernel: all ten ops, two mappings, in-place use, and an
+    unaligned contiguous range (scalar head / tail)."""
+    o = po.oracle()
+    dims = (512, 256, 128)
+    s1, s2 = cases.mk(dims, po.UINT8, 1), cases.mk(dims, po.UINT8, 2, -1000.0, 3000.0)
+    for op in range(10):
+        lo, hi = ((0.0, 1.0), (-1000.0, 3000.0))[op % 2]
+        a, b = po.empty(dims, po.UINT8, lo, hi), po.empty(dims, po.UINT8, lo, hi)
+        o.arith_range(op, a, s1, s2, (0, 0, 0), dims)
+        gpu.arith_range(op, b, s1, s2, (0, 0, 0), dims)
+        assert a.a.tobytes() == b.a.tobytes(), op
+    # identity mappings everywhere (the IDENT template), dst aliasing source 1
+    t2 = cases.mk(dims, po.UINT8, 2)
+    a, b = s1.copy(), s1.copy()
+    o.arith_range(po.SAFESUM, a, a, t2, (0, 0, 0), dims)
+    gpu.arith_range(po.SAFESUM, b, b, t2, (0, 0, 0), dims)
+    assert a.a.tobytes() == b.a.tobytes()
+    # one long row: contiguous but starting at an odd byte -> scalar head and tail around the vector body
+    long = (dims[0] * dims[1] * dims[2], 1, 1)
+    r1, r2 = po.Vol(s1.a.reshape(1, 1, -1), po.UINT8), po.Vol(t2.a.reshape(1, 1, -1), po.UINT8)
+    a, b = po.empty(long, po.UINT8), po.empty(long, po.UINT8)
+    o.arith_range(po.SAFEDIFF, a, r1, r2, (3, 0, 0), (long[0] - 5, 1, 1))
+    gpu.arith_range(po.SAFEDIFF, b, r1, r2, (3, 0, 0), (long[0] - 5, 1, 1))
+    assert a.a.tobytes() == b.a.tobytes()
+
+
 def test_arith_u16_edge_pairs(gpu):
     """2^16-stride sweep + all edge pairs of UInt16 x UInt16 for each op."""
     o = po.oracle()
@@ -136,6 +163,23 @@ def test_config2_256cube(gpu, fmt):
     o.arith_range(po.SAFESUM, a, s1, s2, (3, 5, 7), (255, 254, 253), (1, 2, 3))
     gpu.arith_range(po.SAFESUM, b, s1, s2, (3, 5, 7), (255, 254, 253), (1, 2, 3))
     assert same_bits(b.a, a.a)
+
+
+def test_transform_flat_and_rows(gpu):
+    """Transform over contiguous ranges (flat stream kernel: whole volumes, whole planes, part of one plane) and over
+    boxed ranges (row kernel); odd row lengths make vectors straddle rows and misalign the range start."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        for dims in ((67, 13, 9), (64, 32, 8), (5, 3, 2), (1, 1, 1), (1, 7, 300)):
+            X, Y, Z = dims
+            ranges = [((0, 0, 0), dims), ((0, 0, Z // 2), dims), ((0, Y // 3, Z - 1), (X, Y, Z)),
+                      ((0, 0, 0), (X, Y, max(1, Z - 1))), ((X // 2, 0, 0), dims), ((0, 1 % Y, 0), (X, Y, Z))]
+            for first, last in ranges:
+                for op in range(4):
+                    a, b = cases.mk(dims, fmt, 5), cases.mk(dims, fmt, 5)
+                    o.transform_range1(a, first, last, op)
+                    gpu.transform_range1(b, first, last, op)
+                    assert same_bits(b.a, a.a), (fmt, dims, first, last, op)
 
 
 def test_resample_shapes(gpu):
@@ -272,6 +316,72 @@ def test_resample_march_kernel(gpu):
                 part = po.empty((D[0], D[1], dz1 - dz0), F32)
                 gpu.resample_window(part, win, filt, dz0, D, a.value, S)
                 assert same_bits(part.a, whole.a[dz0:dz1]), (filt, n, g)
+
+
+@pytest.fixture()
+def hosted(monkeypatch):
+    from gpu_adapter import HostedLib
+    monkeypatch.setenv("VKTB_HOSTED_SLAB_KB", "24")     # a few planes per slab: every call runs many pipeline stages
+    return HostedLib()
+
+
+def test_hosted_arith_streams_slabs(gpu, hosted):
+    """Host-resident volumes streamed through the device in z-slabs give the bytes of the whole-volume call."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        dims = (48, 40, 37)
+        s1, s2 = cases.mk(dims, fmt, 1), cases.mk(dims, fmt, 2)
+        for op in (po.SAFESUM, po.DIFF, po.SAFEPROD):
+            a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
+            o.arith_range(op, a, s1, s2, (0, 0, 0), dims)
+            hosted.arith_range(op, b, s1, s2, (0, 0, 0), dims)
+            assert same_bits(b.a, a.a), (fmt, op)
+        # sub-box with a dst offset: the untouched dst voxels of every plane must survive the round trip
+        a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
+        o.arith_range(po.SAFESUM, a, s1, s2, (3, 5, 7), (40, 33, 30), (2, 1, 4))
+        hosted.arith_range(po.SAFESUM, b, s1, s2, (3, 5, 7), (40, 33, 30), (2, 1, 4))
+        assert same_bits(b.a, a.a), fmt
+        # in place: dst is source 1
+        a, b = s1.copy(), s1.copy()
+        o.arith_range(po.SAFEDIFF, a, a, s2, (0, 0, 0), dims)
+        hosted.arith_range(po.SAFEDIFF, b, b, s2, (0, 0, 0), dims)
+        assert same_bits(b.a, a.a), fmt
+    # mixed formats, non-default mappings
+    d1, d2 = po.empty((32, 24, 20), po.UINT16, -1.0, 3.0), po.empty((32, 24, 20), po.UINT16, -1.0, 3.0)
+    s1, s2 = cases.mk((32, 24, 20), po.UINT8, 1), cases.mk((32, 24, 20), po.FLOAT32, 2)
+    o.arith_range(po.SAFEPROD, d1, s1, s2, (0, 0, 0), (32, 24, 20))
+    hosted.arith_range(po.SAFEPROD, d2, s1, s2, (0, 0, 0), (32, 24, 20))
+    assert same_bits(d2.a, d1.a)
+
+
+def test_hosted_transform_and_resample(gpu, hosted):
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        dims = (40, 24, 50)
+        for first, last in (((0, 0, 0), dims), ((3, 2, 5), (37, 20, 41))):
+            for op in range(4):
+                a, b = cases.mk(dims, fmt, 5), cases.mk(dims, fmt, 5)
+                o.transform_range1(a, first, last, op)     # ops read absolute z: slabs must not renumber planes
+                hosted.transform_range1(b, first, last, op)
+                assert same_bits(b.a, a.a), (fmt, first, op)
+    for sfmt, dfmt in ((po.UINT16, po.UINT16), (po.FLOAT32, po.FLOAT32), (po.UINT8, po.UINT16)):
+        src = cases.mk((64, 48, 40), sfmt, 1)
+        for ddims in ((32, 24, 20), (96, 72, 60), (50, 37, 53), (64, 48, 40)):
+            for filt in (po.NEAREST, po.LINEAR, po.TRILINEAR):
+                a, b = po.empty(ddims, dfmt, -1.0, 2.0), po.empty(ddims, dfmt, -1.0, 2.0)
+                o.resample(a, src, filt)
+                hosted.resample(b, src, filt)
+                assert same_bits(b.a, a.a), (sfmt, dfmt, ddims, filt)
+
+
+def test_hosted_rejects_bad_calls(gpu, hosted):
+    from volkit_b200 import capi
+    v = cases.mk((16, 16, 16), po.UINT8, 1)
+    with pytest.raises(RuntimeError):
+        hosted.arith_range(po.SUM, v, v, v, (0, 0, 0), (16, 16, 17))        # range outside the volumes
+    with pytest.raises(RuntimeError):
+        hosted.arith_range(po.SUM, v, v, v, (0, 0, 0), (16, 16, 8), (0, 0, 8))   # in place with an offset
+    assert capi.load().vktb_last_error()
 
 
 def test_empty_and_degenerate_ranges(gpu):

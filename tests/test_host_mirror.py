@@ -79,6 +79,17 @@ def run_cpp(programs, policy, tmp):
     ref = po.empty((24, 20, 18), U8, -1.0, 2.0)
     o.resample(ref, a, po.NEAREST)
     assert raw(tmp / "out_down.raw", (24, 20, 18), np.uint8).tobytes() == ref.a.tobytes()
+    if policy == "gpu-stream":
+        # the host-streaming prelude: same voxels as the migrating calls
+        ref = po.empty(dims, U16)
+        o.arith_range(po.SAFESUM, ref, a, b, *full)
+        assert raw(tmp / "out_s_sum.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+        ref = po.empty((72, 60, 54), U16)
+        o.resample(ref, a, po.LINEAR)
+        assert raw(tmp / "out_s_up.raw", (72, 60, 54), np.uint16).tobytes() == ref.a.tobytes()
+        t = a.copy()
+        o.transform_range1(t, (1, 2, 3), (47, 39, 35), 0)
+        assert raw(tmp / "out_s_t.raw", dims, np.uint16).tobytes() == t.a.tobytes()
 
 
 def run_c(programs, policy, tmp):
@@ -145,6 +156,12 @@ def test_gpu_policy_fails_loudly_without_gpu(programs, tmp_path):
 @pytest.mark.gpu
 def test_cpp_api_gpu_policy(programs, tmp_path):
     run_cpp(programs, "gpu", tmp_path)
+
+
+@pytest.mark.gpu
+def test_cpp_api_gpu_policy_host_streaming(programs, tmp_path, monkeypatch):
+    monkeypatch.setenv("VKTB_HOSTED_SLAB_KB", "16")      # several slabs even on the 48x40x36 test volumes
+    run_cpp(programs, "gpu-stream", tmp_path)
 
 
 @pytest.mark.gpu

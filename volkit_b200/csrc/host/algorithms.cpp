@@ -63,6 +63,11 @@ namespace
     }
 
     void toArray(Vec3i v, int32_t out[3]) { out[0] = v.x; out[1] = v.y; out[2] = v.z; }
+
+    // host streaming (SetHostStreaming): taken when every volume of the call still lives on the host
+    bool streamed(StructuredVolume& a) { return GetHostStreaming() && a.residesOnHost(); }
+    bool streamed(StructuredVolume& a, StructuredVolume& b) { return streamed(a) && b.residesOnHost(); }
+    bool streamed(StructuredVolume& a, StructuredVolume& b, StructuredVolume& c) { return streamed(a, b) && c.residesOnHost(); }
 } // namespace
 
     //---------------------------------------------------------------------------------------------------------
@@ -127,9 +132,14 @@ namespace
         return dispatch(name,
             [&] { host::arithRange(op, viewOf(dest), viewOf(source1), viewOf(source2), first, last, dstOffset); },
             [&] {
-                vktb_vol d = host::describe(dest), a = host::describe(source1), b = host::describe(source2);
                 int32_t f[3], l[3], o[3];
                 toArray(first, f); toArray(last, l); toArray(dstOffset, o);
+                if (streamed(dest, source1, source2)) {
+                    vktb_vol d = host::describeInPlace(dest), a = host::describeInPlace(source1),
+                             b = host::describeInPlace(source2);
+                    return vktb_hosted_arith_range(op, &d, &a, &b, f, l, o);
+                }
+                vktb_vol d = host::describe(dest), a = host::describe(source1), b = host::describe(source2);
                 return vktb_arith_range(op, &d, &a, &b, f, l, o);
             });
     }
@@ -176,9 +186,13 @@ namespace
             [&] {
                 int op = -1;
                 if (vktb_lookup_unary_op((void const*)unaryOp, &op) != 0) return -1;   // unbound: no CPU fallback
-                vktb_vol v = host::describe(volume);
                 int32_t f[3], l[3];
                 toArray(first, f); toArray(last, l);
+                if (streamed(volume)) {
+                    vktb_vol v = host::describeInPlace(volume);
+                    return vktb_hosted_transform_range1(&v, f, l, op);
+                }
+                vktb_vol v = host::describe(volume);
                 return vktb_transform_range1(&v, f, l, op);
             });
     }
@@ -245,8 +259,13 @@ namespace
         return dispatch("Resample",
             [&] { host::resample(viewOf(dst), viewOf(src), fm == FilterMode::Linear ? 1 : 0); },
             [&] {
+                const int filter = fm == FilterMode::Linear ? VKTB_LINEAR : VKTB_NEAREST;
+                if (streamed(dst, src)) {
+                    vktb_vol d = host::describeInPlace(dst), s = host::describeInPlace(src);
+                    return vktb_hosted_resample(&d, &s, filter);
+                }
                 vktb_vol d = host::describe(dst), s = host::describe(src);
-                return vktb_resample(&d, &s, fm == FilterMode::Linear ? VKTB_LINEAR : VKTB_NEAREST);
+                return vktb_resample(&d, &s, filter);
             });
     }
 } // vkt

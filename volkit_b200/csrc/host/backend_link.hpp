@@ -40,5 +40,18 @@ namespace host
         d.lo = m.x; d.hi = m.y;
         return d;
     }
+
+    // descriptor of a host-resident volume as it lies (no migration): input of the vktb_hosted_* calls
+    inline vktb_vol describeInPlace(StructuredVolume& v)
+    {
+        vktb_vol d;
+        d.data = v.dataInPlace();
+        Vec3i dims = v.getDims();
+        d.dims[0] = dims.x; d.dims[1] = dims.y; d.dims[2] = dims.z;
+        d.format = (int32_t)v.getDataFormat();
+        Vec2f m = v.getVoxelMapping();
+        d.lo = m.x; d.hi = m.y;
+        return d;
+    }
 } // host
 } // vkt

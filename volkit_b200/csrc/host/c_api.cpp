@@ -46,6 +46,9 @@ void vktSetThreadExecutionPolicy(vktExecutionPolicy_t policy)
     vkt::SetThreadExecutionPolicy(ep);
 }
 
+void vktSetHostStreaming(vktBool_t enabled) { vkt::SetHostStreaming(enabled != 0); }
+vktBool_t vktGetHostStreaming(void) { return vkt::GetHostStreaming() ? 1 : 0; }
+
 vktExecutionPolicy_t vktGetThreadExecutionPolicy(void)
 {
     vkt::ExecutionPolicy ep = vkt::GetThreadExecutionPolicy();

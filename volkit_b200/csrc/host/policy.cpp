@@ -1,5 +1,6 @@
 // ExecutionPolicy + ManagedResource registry (reference src/vkt/ExecutionPolicy.cpp:17-36,
 // src/vkt/ManagedResource.cpp:16-41).
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -14,6 +15,19 @@ namespace vkt
 
     void SetThreadExecutionPolicy(ExecutionPolicy policy) { t_policy = policy; }
     ExecutionPolicy GetThreadExecutionPolicy() { return t_policy; }
+
+    // host streaming (volkit-b200 extension): -1 = not set on this thread, take the environment's default
+    static thread_local int t_streaming = -1;
+
+    void SetHostStreaming(bool enabled) { t_streaming = enabled ? 1 : 0; }
+    bool GetHostStreaming()
+    {
+        if (t_streaming < 0) {
+            char const* e = std::getenv("VKT_B200_STREAMING");
+            t_streaming = (e && e[0] == '1') ? 1 : 0;
+        }
+        return t_streaming == 1;
+    }
 
     static std::mutex g_resourceMutex;
     static std::unordered_map<ResourceHandle, ManagedResource> g_resources;

@@ -6,6 +6,9 @@ namespace vktb {
 
 namespace {
 
+// below this the table build (65536 entries per CTA) is not worth it
+constexpr size_t kPairTableMinVoxels = (size_t)1 << 24;
+
 struct ArithPlan
 {
     ArithParams p;
@@ -21,7 +24,21 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
 {
     constexpr int BPV = bytesPerVoxel(F);
     constexpr int V = 16 / BPV;
+    if constexpr (F == F_U8) {
+        if (pl.flat && pl.n >= kPairTableMinVoxels) {
+            // big UInt8 streams: 64 KiB pair table per CTA, 3 CTAs per SM (persistent)
+            auto kern = arithPairTableKernel<OP, IDENT>;
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPairTableBytes);
+            if (e != cudaSuccess) return e;
+            unsigned grid = flatGrid(pl.n / V + 1, kThreads * 2, c.smCount, 3);
+            kern<<<grid, kThreads, kPairTableBytes, c.stream>>>(pl.p.d.base, pl.p.a.base, pl.p.b.base, pl.n, pl.p.md,
+                                                                 pl.p.ma, pl.p.mb, pl.p.alias);
+            countLaunch();
+            return cudaGetLastError();
+        }
+    }
     if (pl.flat) {
+
         // 2 vectors/thread/iteration, up to 8 CTAs per SM resident
         unsigned grid = flatGrid(pl.n / V + 1, kThreads * 2, c.smCount, 8);
         arithFlatKernel<F, OP, IDENT><<<grid, kThreads, 0, c.stream>>>(

@@ -116,6 +116,86 @@ arithFlatKernel(uint8_t* __restrict__ d, const uint8_t* a, const uint8_t* b, siz
     }
 }
 
+// ---- flat, UInt8 x UInt8 -> UInt8 through a 64 KiB pair table ------------------------------------------------------
+// result[a][b] = map(f(unmap(a), unmap(b))) is built once per CTA in shared memory with the exact codec above; the
+// stream then costs one byte-wide table load per voxel instead of two float look-ups plus ~14 arithmetic
+// instructions (the per-operand tables of arithFlatKernel made UInt8 shared-memory bound at ~57 % of the HBM
+// roofline; ncu: profiles/r01_notes.md).  Persistent grid, so the table is built 148 * k times per launch.
+constexpr int kPairTableBytes = 65536;
+
+template <int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithPairTableKernel(uint8_t* __restrict__ d, const uint8_t* a, const uint8_t* b, size_t n, Mapping md, Mapping ma,
+                     Mapping mb, int alias)
+{
+    extern __shared__ __align__(16) uint8_t pairTab[];
+    __shared__ float lutB[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) lutB[i] = unmapVoxel<F_U8, IDENT>((uint32_t)i, mb);
+    __syncthreads();
+    // thread t builds row a = t (blockDim.x == 256): 256 entries, written as 64 words
+    {
+        const float fa = unmapVoxel<F_U8, IDENT>((uint32_t)threadIdx.x, ma);
+        uint32_t* row = reinterpret_cast<uint32_t*>(pairTab + threadIdx.x * 256);
+        for (int w = 0; w < 64; ++w) {
+            // rotate the word order per thread: conflict-free shared-memory stores
+            const int ww = (w + threadIdx.x) & 63;
+            uint32_t word = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                word |= (mapVoxel<F_U8, IDENT>(arithEval<OP>(fa, lutB[ww * 4 + k], md.lo, md.hi), md) & 0xffu) << (8 * k);
+            row[ww] = word;
+        }
+    }
+    __syncthreads();
+
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(d) & 15u)) & 15u);
+    if (head > n) head = n;
+    const size_t nvec = (n - head) / 16;
+    const size_t tail0 = head + nvec * 16;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const uint8_t* av = a + head;
+    const uint8_t* bv = b + head;
+    uint8_t* dv = d + head;
+
+    auto lookup = [&](const uint4& va, const uint4& vb) -> uint4 {
+        const uint32_t wa[4] = { va.x, va.y, va.z, va.w }, wb[4] = { vb.x, vb.y, vb.z, vb.w };
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t ia = (wa[q] >> (8 * k)) & 0xffu, ib = (wb[q] >> (8 * k)) & 0xffu;
+                r |= (uint32_t)pairTab[ia * 256u + ib] << (8 * k);
+            }
+            w[q] = r;
+        }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    };
+
+    size_t i = tid;
+    for (; i + stride < nvec; i += 2 * stride) {
+        uint4 a0, b0, a1, b1;
+        if (alias) { a0 = ldPlain(av + i * 16); b0 = ldPlain(bv + i * 16);
+                     a1 = ldPlain(av + (i + stride) * 16); b1 = ldPlain(bv + (i + stride) * 16); }
+        else       { a0 = ldStream(av + i * 16); b0 = ldStream(bv + i * 16);
+                     a1 = ldStream(av + (i + stride) * 16); b1 = ldStream(bv + (i + stride) * 16); }
+        stStream(dv + i * 16, lookup(a0, b0));
+        stStream(dv + (i + stride) * 16, lookup(a1, b1));
+    }
+    for (; i < nvec; i += stride) {
+        uint4 a0 = alias ? ldPlain(av + i * 16) : ldStream(av + i * 16);
+        uint4 b0 = alias ? ldPlain(bv + i * 16) : ldStream(bv + i * 16);
+        stStream(dv + i * 16, lookup(a0, b0));
+    }
+    const size_t nEdge = head + (n - tail0);
+    for (size_t e = tid; e < nEdge; e += stride) {
+        size_t k = e < head ? e : tail0 + (e - head);
+        d[k] = pairTab[(uint32_t)a[k] * 256u + b[k]];
+    }
+}
+
 // ---- rows: general 3-D range with dstOffset; chunks are cut at 16-byte boundaries of the dst row --------
 template <int F, int OP, bool IDENT>
 __global__ void __launch_bounds__(kThreads)

@@ -97,9 +97,10 @@ __device__ __forceinline__ void forEachRowChunk(const Range& g, const Operand& d
 {
     const long long rows = (long long)g.ny * g.nz;
     const int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool small = rows < 0x7fffffffLL;   // 32-bit row arithmetic (the 64-bit division is a ~100-instruction call)
     for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows;
          r += (long long)gridDim.y * blockDim.y) {
-        const int z = (int)(r / g.ny);
+        const int z = small ? (int)((unsigned)r / (unsigned)g.ny) : (int)(r / g.ny);
         const int y = (int)(r - (long long)z * g.ny);
         const uint8_t* drow = dst.base + y * dst.pitchY + z * dst.pitchZ;
         const int shift = (int)((reinterpret_cast<uintptr_t>(drow) & 15u) / BPVD);   // voxels into a 16B line

@@ -30,6 +30,33 @@ __device__ __forceinline__ uint32_t unaryOp(int x, int y, int z, uint32_t raw, i
     return mapVoxelRt(fmt, val < mid ? m.lo : m.hi, m);
 }
 
+// Whole-vector form of an op for 16 bytes of ONE row starting at (x, y, z): ops that are byte-parallel get a
+// few SIMD-in-word instructions instead of a per-voxel extract/compute/insert chain.
+template <int BPV, int OP>
+__device__ __forceinline__ uint4 unaryOpVec(int x, int y, int z, const uint4& in, int fmt, uint32_t mask, const Mapping& m)
+{
+    constexpr int V = 16 / BPV;
+    const uint32_t iw[4] = { in.x, in.y, in.z, in.w };
+    uint32_t w[4] = { 0u, 0u, 0u, 0u };
+    if constexpr (OP == 0) {
+        const uint32_t s = (uint32_t)(x + y + z);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if constexpr (BPV == 1) w[k] = iw[k] ^ __vadd4(((s + 4u * k) & 0xffu) * 0x01010101u, 0x03020100u);
+            else if constexpr (BPV == 2) w[k] = iw[k] ^ (((s + 2u * k) & 0xffu) | (((s + 2u * k + 1u) & 0xffu) << 16));
+            else w[k] = iw[k] ^ ((s + k) & 0xffu);
+        }
+    } else if constexpr (OP == 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) w[k] = ~iw[k];
+    } else {
+#pragma unroll
+        for (int i = 0; i < V; ++i)
+            vecSet<BPV>(w, i, unaryOp<OP>(x + i, y, z, vecGet<BPV>(in, i), fmt, mask, m));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 struct T1Params { Operand v; Range g; Mapping m; int fmt; };
 
 template <int BPV, int OP>
@@ -42,17 +69,76 @@ transform1Kernel(T1Params p)
         uint8_t* dp = p.v.base + y * p.v.pitchY + z * p.v.pitchZ + (long long)xr * BPV;
         const int ax = p.g.x0 + xr, ay = p.g.y0 + y, az = p.g.z0 + z;
         if (full) {
-            uint4 in = ldPlain(dp);
-            uint32_t w[4] = { 0u, 0u, 0u, 0u };
-#pragma unroll
-            for (int i = 0; i < V; ++i)
-                vecSet<BPV>(w, i, unaryOp<OP>(ax + i, ay, az, vecGet<BPV>(in, i), p.fmt, mask, p.m));
-            stStream(dp, make_uint4(w[0], w[1], w[2], w[3]));
+            stStream(dp, unaryOpVec<BPV, OP>(ax, ay, az, ldPlain(dp), p.fmt, mask, p.m));
         } else {
             for (int i = 0; i < n; ++i)
                 storeRaw(dp + i * BPV, BPV, unaryOp<OP>(ax + i, ay, az, loadRaw(dp + i * BPV, BPV), p.fmt, mask, p.m));
         }
     });
+}
+
+// Contiguous ranges (whole volumes, whole planes): flat grid-stride stream, four 128-bit vectors in flight per thread.
+// The op still sees absolute coordinates: they are rebuilt from the linear voxel index with 32-bit arithmetic.
+template <int BPV, int OP>
+__global__ void __launch_bounds__(kThreads)
+transform1FlatKernel(uint8_t* __restrict__ d, size_t n, int nx, int ny, int x0, int y0, int z0, Mapping m, int fmt)
+{
+    constexpr int V = 16 / BPV;
+    constexpr uint32_t mask = BPV == 4 ? 0xffffffffu : (1u << (BPV * 8)) - 1u;
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(d) & 15u)) & 15u) / BPV;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) / V;
+    const size_t tail0 = head + nvec * V;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    uint8_t* dv = d + head * BPV;
+
+    // coordinates advance with the grid stride by add-with-carry: one 64-bit division pair per thread, none per vector
+    struct Coord { int x, y, z; };
+    auto coordOf = [&](size_t v) {
+        const size_t row = v / (unsigned)nx, zr = row / (unsigned)ny;
+        return Coord{ (int)(v - row * (unsigned)nx), (int)(row - zr * (unsigned)ny), (int)zr };
+    };
+    const Coord step = coordOf(stride * V);
+    auto advance = [&](Coord& c) {
+        c.x += step.x; if (c.x >= nx) { c.x -= nx; ++c.y; }
+        c.y += step.y; if (c.y >= ny) { c.y -= ny; ++c.z; }
+        c.z += step.z;
+    };
+    auto apply = [&](size_t vec, Coord c, const uint4& in) {
+        if (c.x + V <= nx) {            // the whole vector lies in one row
+            stStream(dv + vec * 16, unaryOpVec<BPV, OP>(x0 + c.x, y0 + c.y, z0 + c.z, in, fmt, mask, m));
+            return;
+        }
+        uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+        for (int i = 0; i < V; ++i) {   // the vector wraps into the next row(s)
+            vecSet<BPV>(w, i, unaryOp<OP>(x0 + c.x, y0 + c.y, z0 + c.z, vecGet<BPV>(in, i), fmt, mask, m));
+            if (++c.x == nx) { c.x = 0; if (++c.y == ny) { c.y = 0; ++c.z; } }
+        }
+        stStream(dv + vec * 16, make_uint4(w[0], w[1], w[2], w[3]));
+    };
+
+    size_t i = tid;
+    Coord c = coordOf(head + tid * V);
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        const uint4 v0 = ldPlain(dv + i * 16), v1 = ldPlain(dv + (i + stride) * 16);
+        const uint4 v2 = ldPlain(dv + (i + 2 * stride) * 16), v3 = ldPlain(dv + (i + 3 * stride) * 16);
+        apply(i, c, v0); advance(c);
+        apply(i + stride, c, v1); advance(c);
+        apply(i + 2 * stride, c, v2); advance(c);
+        apply(i + 3 * stride, c, v3); advance(c);
+    }
+    for (; i < nvec; i += stride) { apply(i, c, ldPlain(dv + i * 16)); advance(c); }
+    const size_t nEdge = head + (n - tail0);
+    for (size_t e = tid; e < nEdge; e += stride) {
+        const size_t k = e < head ? e : tail0 + (e - head);
+        const size_t row = k / (unsigned)nx;
+        const int x = (int)(k - row * (unsigned)nx);
+        const size_t zr = row / (unsigned)ny;
+        const int y = (int)(row - zr * (unsigned)ny), z = (int)zr;
+        storeRaw(d + k * BPV, BPV, unaryOp<OP>(x0 + x, y0 + y, z0 + z, loadRaw(d + k * BPV, BPV), fmt, mask, m));
+    }
 }
 
 // binary ops act on bytesPerVoxel(volume1.format) bytes of both scratch buffers (mask1)
@@ -115,8 +201,23 @@ transform2GenericKernel(T2Params p)
 }
 
 template <int BPV>
-cudaError_t launchT1(const LaunchCtx& c, const T1Params& p, int op)
+cudaError_t launchT1(const LaunchCtx& c, const T1Params& p, int op, bool flat)
 {
+    if (flat) {
+        const size_t n = (size_t)p.g.nx * p.g.ny * p.g.nz;
+        const unsigned grid = flatGrid(n * BPV / 16 + 1, kThreads * 4, c.smCount, 8);
+#define VKTB_T1_FLAT(OP) transform1FlatKernel<BPV, OP><<<grid, kThreads, 0, c.stream>>>(p.v.base, n, p.g.nx, p.g.ny, p.g.x0, p.g.y0, p.g.z0, p.m, p.fmt)
+        switch (op) {
+        case 0: VKTB_T1_FLAT(0); break;
+        case 1: VKTB_T1_FLAT(1); break;
+        case 2: VKTB_T1_FLAT(2); break;
+        case 3: VKTB_T1_FLAT(3); break;
+        default: return cudaErrorInvalidValue;
+        }
+#undef VKTB_T1_FLAT
+        countLaunch();
+        return cudaGetLastError();
+    }
     RowsLaunch l = rowsLaunch(p.g.nx, (long long)p.g.ny * p.g.nz, 16 / BPV);
     switch (op) {
     case 0: transform1Kernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p); break;
@@ -155,10 +256,13 @@ cudaError_t launchTransform1(const LaunchCtx& c, const VolDesc& vol, const int32
     if (!makeRange(p.g, first, last)) return cudaSuccess;
     p.v = operandAt(vol, first[0], first[1], first[2]);
     p.m = vol.map; p.fmt = vol.format;
+    // whole rows of whole planes (or a single plane): one contiguous run, 32-bit indexable
+    const bool flat = contiguous(vol, p.g) && p.g.nx == vol.dims[0] && (p.g.nz == 1 || p.g.ny == vol.dims[1])
+                   && (long long)p.g.nx * p.g.ny * p.g.nz < (1LL << 40);
     switch (bytesPerVoxel(vol.format)) {
-    case 1: return launchT1<1>(c, p, op);
-    case 2: return launchT1<2>(c, p, op);
-    case 4: return launchT1<4>(c, p, op);
+    case 1: return launchT1<1>(c, p, op, flat);
+    case 2: return launchT1<2>(c, p, op, flat);
+    case 4: return launchT1<4>(c, p, op, flat);
     }
     return cudaErrorInvalidValue;
 }
