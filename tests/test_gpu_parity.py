@@ -158,6 +158,24 @@ def test_config2_256cube(gpu, fmt):
     o.copy_range(a, s1, (0, 0, 0), (248, 248, 248), (8, 8, 8))
     gpu.copy_range(b, s1, (0, 0, 0), (248, 248, 248), (8, 8, 8))
     assert a.a.tobytes() == b.a.tobytes()
+    # src and dst rows in the same non-zero 16-byte phase (uniform-phase row kernel, partial head and tail chunks)
+    a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
+    o.copy_range(a, s1, (9, 5, 7), (254, 250, 251), (1, 2, 3))
+    gpu.copy_range(b, s1, (9, 5, 7), (254, 250, 251), (1, 2, 3))
+    assert a.a.tobytes() == b.a.tobytes()
+    a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
+    o.arith_range(po.SAFEDIFF, a, s1, s2, (3, 5, 7), (255, 254, 253), (8, 1, 2))
+    gpu.arith_range(po.SAFEDIFF, b, s1, s2, (3, 5, 7), (255, 254, 253), (8, 1, 2))
+    assert same_bits(b.a, a.a)
+    t1, t2, u1, u2 = cases.mk(dims, fmt, 4), cases.mk(dims, fmt, 5), cases.mk(dims, fmt, 4), cases.mk(dims, fmt, 5)
+    for op in (0, 1):
+        o.transform_range2(t1, t2, (3, 5, 7), (255, 254, 253), op)
+        gpu.transform_range2(u1, u2, (3, 5, 7), (255, 254, 253), op)
+        assert same_bits(u1.a, t1.a) and same_bits(u2.a, t2.a), op
+    for op in range(4):
+        o.transform_range1(t1, (5, 1, 2), (250, 255, 250), op)
+        gpu.transform_range1(u1, (5, 1, 2), (250, 255, 250), op)
+        assert same_bits(u1.a, t1.a), op
     # range with odd offsets (unaligned rows) and in-place use
     a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
     o.arith_range(po.SAFESUM, a, s1, s2, (3, 5, 7), (255, 254, 253), (1, 2, 3))

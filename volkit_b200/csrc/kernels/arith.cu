@@ -45,7 +45,16 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
             pl.p.d.base, pl.p.a.base, pl.p.b.base, pl.n, pl.p.md, pl.p.ma, pl.p.mb, pl.p.alias);
     } else {
         RowsLaunch l = rowsLaunch(pl.p.g.nx, (long long)pl.p.g.ny * pl.p.g.nz, V);
-        arithRowsKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p);
+        const ArithParams& q = pl.p;
+        const uintptr_t phase = reinterpret_cast<uintptr_t>(q.d.base) & 15u;
+        const bool uniform = ((q.d.pitchY | q.d.pitchZ | q.a.pitchY | q.a.pitchZ | q.b.pitchY | q.b.pitchZ) & 15) == 0
+                          && phase == (reinterpret_cast<uintptr_t>(q.a.base) & 15u)
+                          && phase == (reinterpret_cast<uintptr_t>(q.b.base) & 15u)
+                          && (long long)q.g.ny * q.g.nz < 0x7fffffffLL;
+        if (uniform)
+            arithRowsUniformKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p, (int)(phase / bytesPerVoxel(F)));
+        else
+            arithRowsKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p);
     }
     countLaunch();
     return cudaGetLastError();

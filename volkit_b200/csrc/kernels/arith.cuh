@@ -226,6 +226,41 @@ arithRowsKernel(ArithParams p)
     });
 }
 
+// ---- rows, every row of all three operands in the same 16-byte phase: two rows (four loads) in flight ----
+struct ArithPair { uint4 a, b; };
+
+template <int F, int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithRowsUniformKernel(ArithParams p, int shift)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    forEachRowChunkUniform<V, 2, ArithPair>(p.g, shift,
+        [&](int y, int z, int xr) {
+            const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
+            const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
+            ArithPair q;
+            if (p.alias) { q.a = ldPlain(ap); q.b = ldPlain(bp); }
+            else         { q.a = ldStream(ap); q.b = ldStream(bp); }
+            return q;
+        },
+        [&](int y, int z, int xr, const ArithPair& q) {
+            uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+                vecSet<BPV>(w, i, arithOne<F, OP, IDENT>(vecGet<BPV>(q.a, i), vecGet<BPV>(q.b, i), p.md, p.ma, p.mb));
+            stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, make_uint4(w[0], w[1], w[2], w[3]));
+        },
+        [&](int y, int z, int xr, int n) {
+            uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+            const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
+            const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
+            for (int i = 0; i < n; ++i)
+                storeRaw(dp + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
+                                                                  p.md, p.ma, p.mb));
+        });
+}
+
 // ---- generic: any mix of formats (runtime codec), one voxel per thread along x ---------------------------
 template <int OP>
 __global__ void __launch_bounds__(kThreads)

@@ -113,6 +113,53 @@ __device__ __forceinline__ void forEachRowChunk(const Range& g, const Operand& d
     }
 }
 
+// The row-chunk driver for ranges whose rows all share one 16-byte phase (every pitch of every operand is a
+// multiple of 16 and the operands are congruent mod 16; the launcher checks): the thread's chunk [xr, xr + n) is the
+// same in every row, rows advance by add-with-carry instead of a division, and full chunks run U rows at a time --
+// U independent 128-bit loads per operand in flight before the first store (a single row per iteration leaves a
+// copy with 16 B in flight per thread, ~80 % of the HBM roofline; ncu: profiles/r01_rows_notes.md).
+//   load(y, z, xr) -> Regs        reads the chunk's vectors (no stores)
+//   store(y, z, xr, regs)         computes and stores one full chunk
+//   edge(y, z, xr, n)             scalar path for the row's partial head / tail chunk
+// rows < 2^31 (launcher).
+template <int V, int U, class Regs, class Load, class Store, class Edge>
+__device__ __forceinline__ void forEachRowChunkUniform(const Range& g, int shift, Load load, Store store, Edge edge)
+{
+    const int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    int xr = chunk * V - shift, n = V;
+    if (xr < 0) { n += xr; xr = 0; }
+    if (xr + n > g.nx) n = g.nx - xr;
+    if (n <= 0) return;
+    const unsigned rows = (unsigned)g.ny * (unsigned)g.nz;
+    const unsigned S = gridDim.y * blockDim.y;
+    unsigned r = blockIdx.y * blockDim.y + threadIdx.y;
+    if (r >= rows) return;
+    int z = (int)(r / (unsigned)g.ny), y = (int)(r - (unsigned)z * (unsigned)g.ny);
+    const int sz = (int)(S / (unsigned)g.ny), sy = (int)(S - (unsigned)sz * (unsigned)g.ny);
+    auto next = [&] { y += sy; z += sz; if (y >= g.ny) { y -= g.ny; ++z; } };
+    const bool full = n == V;
+    for (; (unsigned long long)r + (unsigned long long)(U - 1) * S < rows; r += U * S) {
+        int ys[U], zs[U];
+        Regs q[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            ys[u] = y; zs[u] = z;
+            if (full) q[u] = load(y, z, xr);
+            next();
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (full) store(ys[u], zs[u], xr, q[u]);
+            else edge(ys[u], zs[u], xr, n);
+        }
+    }
+    for (; r < rows; r += S) {
+        if (full) { Regs q = load(y, z, xr); store(y, z, xr, q); }
+        else edge(y, z, xr, n);
+        next();
+    }
+}
+
 // Grid for flat (1-D) streaming kernels: enough CTAs to fill every SM several times over, capped so the
 // grid-stride loop amortises the launch; always a multiple of the SM count.
 inline unsigned flatGrid(size_t work, int perCta, int smCount, int ctasPerSm)

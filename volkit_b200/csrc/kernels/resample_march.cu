@@ -66,9 +66,11 @@ __device__ __forceinline__ AxisEntry axisEntry(int d, int D, int S, int mode, in
 }
 
 // Table layout (ints; fractions bit-cast): hdr[4] = {nSeq}; x: lo[Dx] hi[Dx] fr[Dx]; y: lo[Dy] hi[Dy] fr[Dy];
-// z: lo[dz] hi[dz] fr[dz] seqLo[dz] seqHi[dz]; planeOf[szCount]; mark[szCount]; rank[szCount]
+// z: lo[dz] hi[dz] fr[dz] seqLo[dz] seqHi[dz]; planeOf[szCount]; mark[szCount]; rank[szCount];
+// zpack[dz] = int4 {seqLo, seqHi, fr, -} at zpackOff (16-byte aligned)
 __global__ void __launch_bounds__(1024)
-marchPlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz0, int Dz, int Sz, int srcZ0, int szCount, int mode)
+marchPlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz0, int Dz, int Sz, int srcZ0, int szCount, int mode,
+                int zpackOff)
 {
     __shared__ int scan[1024];
     const int t = threadIdx.x;
@@ -122,6 +124,8 @@ marchPlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz0, 
         const int a = min(max(Z[i] - srcZ0, 0), szCount - 1), b = min(max(Z[dzCount + i] - srcZ0, 0), szCount - 1);
         seqLo[i] = rank[a];
         seqHi[i] = rank[b];
+        // everything the march needs per dst plane in one 16-byte record
+        reinterpret_cast<int4*>(tab + zpackOff)[i] = make_int4(rank[a], rank[b], Z[2 * dzCount + i], 0);
     }
 }
 
@@ -134,6 +138,8 @@ struct MarchParams
     int BXv, BY, tilesX;    // dst tile: BXv voxels (= 64 words) x BY rows
     int bxS, byS, nBoxX;    // src brick: nBoxX boxes of bxS x byS elements per plane
     int slotBytes;
+    int spillOff;           // byte offset of the spill column (byS rows x 16 bytes) inside a slot
+    int zpackOff;           // int offset of the int4 per-plane records in tab
     const int* tab;
     Mapping md, ms;
 };
@@ -143,17 +149,35 @@ template <> struct ElemT<1> { typedef uint8_t type; };
 template <> struct ElemT<2> { typedef uint16_t type; };
 template <> struct ElemT<4> { typedef uint32_t type; };
 
-template <int FS, int FD, int MODE>
+// dst voxels per thread and row: one 64-bit store for 2- and 4-byte voxels, one 32-bit store for bytes
+__host__ __device__ constexpr int marchVoxelsPerThread(int bd) { return bd == 1 ? 4 : 8 / bd; }
+// row passes per thread (tile height = passes * kRowsY): bounded so that both register planes (2 * passes * voxels
+// floats) leave room for two CTAs per SM
+__host__ __device__ constexpr int marchPasses(int bd) { return bd == 4 ? kMaxBY / kRowsY : kMaxBY / kRowsY / 2; }
+
+template <int BYTES> __device__ __forceinline__ void marchStore(uint8_t* p, uint32_t w0, uint32_t w1);
+template <> __device__ __forceinline__ void marchStore<4>(uint8_t* p, uint32_t w0, uint32_t)
+{
+    asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" :: "l"(p), "r"(w0));
+}
+template <> __device__ __forceinline__ void marchStore<8>(uint8_t* p, uint32_t w0, uint32_t w1)
+{
+    asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(w0), "r"(w1));
+}
+
+template <int FS, int FD, int MODE, bool IDENT>
 __global__ void __launch_bounds__(kMarchThreads)
-resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
+resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapSpill, MarchParams p)
 {
     constexpr int BS = bytesPerVoxel(FS), BD = bytesPerVoxel(FD);
-    constexpr int VW = 4 / BD;   // dst voxels per 32-bit word
+    constexpr int VPT = marchVoxelsPerThread(BD);
+    constexpr int SB = VPT * BD;             // bytes per store
+    constexpr int NPASS = marchPasses(BD);
+    constexpr int NP = NPASS * VPT;
     typedef typename ElemT<BS>::type SrcT;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[kRing], empty[kRing];
-    __shared__ int rowLoOff[kMaxBY], rowHiOff[kMaxBY], rowLoId[kMaxBY], rowHiId[kMaxBY];
-    __shared__ float rowFr[kMaxBY];
+    __shared__ int4 rowInfo[kMaxBY];         // {lo row byte offset in the brick, hi row byte offset, y fraction, lo | hi << 16 brick rows}
 
     const int t = threadIdx.x, lx = t % kLanesX, ty = t / kLanesX;
     const int* X = p.tab + kHdr;
@@ -162,9 +186,12 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
     const int* seqLoT = Z + 3 * p.dzCount;
     const int* seqHiT = seqLoT + p.dzCount;
     const int* planeOf = seqHiT + p.dzCount;
+    const int4* zpack = reinterpret_cast<const int4*>(p.tab + p.zpackOff);
     const int nSeq = p.tab[0];
 
-    const int tileX = blockIdx.x % p.tilesX, tileY = blockIdx.x / p.tilesX;
+    // x tiles in descending order: the tile holding the last columns (extra spill pass in reference-faithful Linear) is
+    // the slowest and starts first instead of forming the tail of the launch
+    const int tileX = p.tilesX - 1 - (int)(blockIdx.x % p.tilesX), tileY = blockIdx.x / p.tilesX;
     const int x0 = tileX * p.BXv, y0 = tileY * p.BY;
     const int h = min(p.BY, p.Dy - y0);
     // the innermost TMA coordinate must address a 16-byte aligned element (found the hard way: misaligned box
@@ -172,32 +199,32 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
     const int xOrigin = X[x0] & ~(16 / BS - 1), yOrigin = Y[y0];
     const int boxElems = p.bxS * p.byS;
 
-    // this thread's dst word: voxels x0 + lx*VW + i
-    const int xw = x0 + lx * VW;
-    const bool active = xw < p.Dx;
-    int oLo[VW], oHi[VW];
-    float fx[VW];
-    bool spill[VW];
+    // this thread's dst voxels: x0 + lx*VPT + i in rows y0 + ty + pass*kRowsY
+    const int xw = x0 + lx * VPT;
+    const bool active = xw < p.Dx;           // Dx is a multiple of VPT (launcher)
+    const int nPass = active ? max(0, (h - ty + kRowsY - 1) / kRowsY) : 0;
+    int oLo[VPT], oHi[VPT];                  // byte offsets of the x taps inside a brick row
+    float fx[VPT], gx[VPT];                  // x fraction and 1 - fraction
+    bool spill[VPT];
     bool anySpill = false;
 #pragma unroll
-    for (int i = 0; i < VW; ++i) {
+    for (int i = 0; i < VPT; ++i) {
         oLo[i] = oHi[i] = 0; fx[i] = 0.f; spill[i] = false;
         if (active) {
             const int x = xw + i;
             const int a = X[x] - xOrigin, b = X[p.Dx + x] - xOrigin;
-            oLo[i] = (a / p.bxS) * boxElems + a % p.bxS;
+            oLo[i] = ((a / p.bxS) * boxElems + a % p.bxS) * BS;
             spill[i] = MODE == M_LINEAR8 && X[p.Dx + x] >= p.Sx;   // the unclamped +1 tap leaves the row
-            oHi[i] = spill[i] ? oLo[i] : (b / p.bxS) * boxElems + b % p.bxS;
+            oHi[i] = spill[i] ? oLo[i] : ((b / p.bxS) * boxElems + b % p.bxS) * BS;
             fx[i] = __int_as_float(X[2 * p.Dx + x]);
             anySpill |= spill[i];
         }
+        gx[i] = __fsub_rn(1.0f, fx[i]);
     }
     for (int r = t; r < h; r += kMarchThreads) {
         const int y = y0 + r;
-        rowLoId[r] = Y[y]; rowHiId[r] = Y[p.Dy + y];
-        rowLoOff[r] = (Y[y] - yOrigin) * p.bxS;
-        rowHiOff[r] = (Y[p.Dy + y] - yOrigin) * p.bxS;
-        rowFr[r] = __int_as_float(Y[2 * p.Dy + y]);
+        rowInfo[r] = make_int4((Y[y] - yOrigin) * p.bxS * BS, (Y[p.Dy + y] - yOrigin) * p.bxS * BS, Y[2 * p.Dy + y],
+                               (Y[y] - yOrigin) | ((Y[p.Dy + y] - yOrigin) << 16));
     }
     if (t == 0) {
         for (int i = 0; i < kRing; ++i) { mbarInit(smemAddr(&full[i]), 1); mbarInit(smemAddr(&empty[i]), kMarchThreads / 32); }
@@ -207,28 +234,93 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
 
     const long long dstRowPitch = (long long)p.Dx * BD;
     const long long dstPlanePitch = dstRowPitch * p.Dy;
-    const long long srcCount = (long long)p.Sx * p.Sy * p.szCount;   // voxels in the src window
-    const uint32_t slotTx = (uint32_t)(p.nBoxX * boxElems * BS);
+    const long long rowStep = dstRowPitch * kRowsY;
+    // the reference's unclamped hi.x tap of the last column reads linear index + 1: column 0 of the NEXT row (the next
+    // plane's first row after the last row; nothing, i.e. a zero voxel, past the end of the window).  The tile that
+    // holds those columns stages that column with a second, 2-D tensor map over the window flattened to rows
+    // (16 bytes x byS rows starting one row below the brick; out-of-bounds rows arrive as zeros).
+    const bool tileSpill = MODE == M_LINEAR8 && X[p.Dx + min(p.Dx, x0 + p.BXv) - 1] >= p.Sx;
+    const uint32_t slotTx = (uint32_t)(p.nBoxX * boxElems * BS) + (tileSpill ? (uint32_t)p.byS * 16u : 0u);
+    const Mapping ms = p.ms, md = p.md;
 
-    // one tap as a float; `spilled`: the reference's hi.x tap at the last column reads linear index + 1, i.e. the first
-    // voxel of the next row / plane, or nothing (zero voxel) past the end of the buffer
-    auto tapF = [&](const uint8_t* slot, int off) -> float {
-        return unmapVoxel<FS, false>((uint32_t)reinterpret_cast<const SrcT*>(slot)[off], p.ms);
+    auto tapF = [&](const uint8_t* row, int off) -> float {
+        return unmapVoxel<FS, IDENT>((uint32_t)*reinterpret_cast<const SrcT*>(row + off), ms);
     };
-    auto spillF = [&](int plane, int row) -> float {
-        const long long idx = ((long long)plane * p.Sy + row) * p.Sx + p.Sx;
-        const uint32_t raw = idx < srcCount ? (uint32_t)reinterpret_cast<const SrcT*>(p.s)[idx] : 0u;
-        return unmapVoxel<FS, false>(raw, p.ms);
-    };
+    // the reference's hi.x tap at the last column reads linear index + 1, i.e. the first voxel of the next row /
+    // plane, or nothing (zero voxel) past the end of the buffer
+    // lerp with the complement precomputed: (1-x)*a + x*b, each operation rounded on its own (refLerp)
+    auto lerp = [](float a, float b, float x, float g) { return __fadd_rn(__fmul_rn(g, a), __fmul_rn(x, b)); };
 
-    int issued = 0, released = 0, prevLo = -1, prevHi = -1;
-    uint32_t outWord[kMaxBY / kRowsY];
+    // ---- the march ----------------------------------------------------------------------------------------------
+    // The reference nests its lerps x -> y -> z (StructuredVolumeView.hpp:112-118), so the chain factors exactly:
+    //     P(s, y, x) = lerp_y(lerp_x(v[lx,ly,s], v[hx,ly,s]), lerp_x(v[lx,hy,s], v[hx,hy,s]))     per src plane s
+    //     out(z, y, x) = map(lerp_z(P(lz), P(hz)))
+    // with every intermediate a binary32 value either way.  A thread owns the same (x, y) positions in every dst
+    // plane, so the two P planes it needs stay in its REGISTERS: each src plane goes through the 4-tap x/y stage
+    // once per tile (not once per dst plane that taps it), the slot is handed back to the TMA unit right after, and a
+    // dst plane costs one lerp, one map and a share of one store per voxel.
+    float Plo[NP], Phi[NP];
 #pragma unroll
-    for (int i = 0; i < kMaxBY / kRowsY; ++i) outWord[i] = 0u;
+    for (int i = 0; i < NP; ++i) Plo[i] = Phi[i] = 0.f;
 
-    for (int zi = 0; zi < p.dzCount; ++zi) {
-        const int sLo = seqLoT[zi], sHi = seqHiT[zi];
+    auto stageXY = [&](float (&P)[NP], int k) {
+        const int slotId = k % kRing;
+        mbarWait(smemAddr(&full[slotId]), (uint32_t)((k / kRing) & 1));
+        const uint8_t* slot = smem + slotId * p.slotBytes;
+        // branch-free hot path: a spilled hi.x tap is read as its lo tap here and patched below
+#pragma unroll
+        for (int pass = 0; pass < NPASS; ++pass) {
+            if (pass < nPass) {
+                const int4 ri = rowInfo[ty + pass * kRowsY];
+                const uint8_t* rowLo = slot + ri.x;
+                const uint8_t* rowHi = slot + ri.y;
+                const float fy = __int_as_float(ri.z), gy = __fsub_rn(1.0f, fy);
+#pragma unroll
+                for (int i = 0; i < VPT; ++i) {
+                    const float v0 = tapF(rowLo, oLo[i]), v1 = tapF(rowLo, oHi[i]);
+                    const float v2 = tapF(rowHi, oLo[i]), v3 = tapF(rowHi, oHi[i]);
+                    P[pass * VPT + i] = lerp(lerp(v0, v1, fx[i], gx[i]), lerp(v2, v3, fx[i], gx[i]), fy, gy);
+                }
+            }
+        }
+        if (anySpill) {   // only the lanes holding the last columns, only reference-faithful Linear
+            const uint8_t* col = slot + p.spillOff;
+#pragma unroll
+            for (int pass = 0; pass < NPASS; ++pass) {
+                if (pass < nPass) {
+                    const int4 ri = rowInfo[ty + pass * kRowsY];
+                    const float fy = __int_as_float(ri.z), gy = __fsub_rn(1.0f, fy);
+                    const float v1 = tapF(col, (ri.w & 0xffff) * 16), v3 = tapF(col, (ri.w >> 16) * 16);
+#pragma unroll
+                    for (int i = 0; i < VPT; ++i) {
+                        if (spill[i]) {
+                            const float v0 = tapF(slot + ri.x, oLo[i]), v2 = tapF(slot + ri.y, oLo[i]);
+                            P[pass * VPT + i] = lerp(lerp(v0, v1, fx[i], gx[i]), lerp(v2, v3, fx[i], gx[i]), fy, gy);
+                        }
+                    }
+                }
+            }
+        }
+        // this warp is done with the slot
+        __syncwarp();
+        if ((t & 31) == 0) mbarArrive(smemAddr(&empty[slotId]));
+    };
+
+    int issued = 0, curLo = -1, curHi = -1, prevLo = -1, prevHi = -1;
+    uint32_t outWord[NPASS * (SB / 4)];
+#pragma unroll
+    for (int i = 0; i < NPASS * (SB / 4); ++i) outWord[i] = 0u;
+    uint8_t* dz = p.d + (long long)(y0 + ty) * dstRowPitch + (long long)xw * BD;   // this thread's first row, plane zi
+
+    int nextPlane = (t == 0 && nSeq > 0) ? planeOf[0] : 0;
+    int4 zNext = zpack[0];       // per-plane record, fetched one plane ahead (an L2 round trip otherwise stalls every plane)
+    for (int zi = 0; zi < p.dzCount; ++zi, dz += dstPlanePitch) {
+        const int4 zc = zNext;
+        if (zi + 1 < p.dzCount) zNext = zpack[zi + 1];
+        const int sLo = zc.x, sHi = zc.y;
         if (t < 32) {
+            // warp 0 keeps the TMA unit kRing planes ahead of its own position; the slots it re-arms belong to planes
+            // below sLo, which this warp has staged already, so the wait below only ever waits for OTHER warps
             const int want = min(nSeq, sLo + kRing);
             while (issued < want) {
                 const int slot = issued % kRing;
@@ -236,63 +328,65 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, MarchParams p)
                 if (t == 0) {
                     const uint32_t bar = smemAddr(&full[slot]);
                     mbarArriveExpectTx(bar, slotTx);
-                    const int plane = planeOf[issued];
+                    const int plane = nextPlane;
+                    if (issued + 1 < nSeq) nextPlane = planeOf[issued + 1];   // fetched before it is needed
                     for (int kb = 0; kb < p.nBoxX; ++kb)
                         tensorLoad3d(smemAddr(smem + slot * p.slotBytes + kb * boxElems * BS), &tmap,
                                      xOrigin + kb * p.bxS, yOrigin, plane, bar);
+                    if (tileSpill)
+                        tensorLoad2d(smemAddr(smem + slot * p.slotBytes + p.spillOff), &tmapSpill, 0,
+                                     plane * p.Sy + yOrigin + 1, bar);
                 }
                 __syncwarp();
                 ++issued;
             }
         }
-        mbarWait(smemAddr(&full[sLo % kRing]), (uint32_t)((sLo / kRing) & 1));
-        mbarWait(smemAddr(&full[sHi % kRing]), (uint32_t)((sHi / kRing) & 1));
+        // bring the register planes to (sLo, sHi): the sequence is monotone, so a plane is staged exactly once and in
+        // sequence order (lo first), or inherited from the other register set
+        if (sLo != curLo) {
+            if (sLo == curHi) {
+#pragma unroll
+                for (int i = 0; i < NP; ++i) Plo[i] = Phi[i];
+            } else {
+                stageXY(Plo, sLo);
+            }
+            curLo = sLo;
+        }
+        if (sHi != curHi) {
+            if (sHi == curLo) {
+#pragma unroll
+                for (int i = 0; i < NP; ++i) Phi[i] = Plo[i];
+            } else {
+                stageXY(Phi, sHi);
+            }
+            curHi = sHi;
+        }
 
         // reference-faithful Linear: fractions are all zero, so dst planes tapping the same src planes are identical
         const bool reuse = MODE == M_LINEAR8 && sLo == prevLo && sHi == prevHi;
         prevLo = sLo; prevHi = sHi;
-        const uint8_t* slotLo = smem + (sLo % kRing) * p.slotBytes;
-        const uint8_t* slotHi = smem + (sHi % kRing) * p.slotBytes;
-        const float fz = __int_as_float(Z[2 * p.dzCount + zi]);
-        if (active) {
+        if (!reuse) {
+            const float fz = __int_as_float(zc.z), gz = __fsub_rn(1.0f, fz);
 #pragma unroll
-            for (int pass = 0; pass < kMaxBY / kRowsY; ++pass) {
-                const int r = ty + pass * kRowsY;
-                if (r >= h) break;
-                if (!reuse) {
-                    const int rl = rowLoOff[r], rh = rowHiOff[r];
-                    const float fy = rowFr[r];
-                    uint32_t word = 0u;
+            for (int pass = 0; pass < NPASS; ++pass) {
+                uint32_t w[2] = { 0u, 0u };
 #pragma unroll
-                    for (int i = 0; i < VW; ++i) {
-                        float v0 = tapF(slotLo, rl + oLo[i]), v2 = tapF(slotLo, rh + oLo[i]);
-                        float v4 = tapF(slotHi, rl + oLo[i]), v6 = tapF(slotHi, rh + oLo[i]);
-                        float v1, v3, v5, v7;
-                        if (anySpill && spill[i]) {
-                            const int pl = planeOf[sLo], ph = planeOf[sHi];
-                            v1 = spillF(pl, rowLoId[r]); v3 = spillF(pl, rowHiId[r]);
-                            v5 = spillF(ph, rowLoId[r]); v7 = spillF(ph, rowHiId[r]);
-                        } else {
-                            v1 = tapF(slotLo, rl + oHi[i]); v3 = tapF(slotLo, rh + oHi[i]);
-                            v5 = tapF(slotHi, rl + oHi[i]); v7 = tapF(slotHi, rh + oHi[i]);
-                        }
-                        const float f = refLerp(refLerp(refLerp(v0, v1, fx[i]), refLerp(v2, v3, fx[i]), fy),
-                                                refLerp(refLerp(v4, v5, fx[i]), refLerp(v6, v7, fx[i]), fy), fz);
-                        const uint32_t e = mapVoxel<FD, false>(f, p.md);
-                        word |= (BD == 4) ? e : (e & ((1u << (8 * (BD & 3))) - 1u)) << (8 * BD * i);
-                    }
-                    outWord[pass] = word;
+                for (int i = 0; i < VPT; ++i) {
+                    const uint32_t e = mapVoxel<FD, IDENT>(lerp(Plo[pass * VPT + i], Phi[pass * VPT + i], fz, gz), md);
+                    if (BD == 4) w[i] = e;
+                    else if (BD == 2) w[i >> 1] |= (e & 0xffffu) << (16 * (i & 1));
+                    else w[0] |= (e & 0xffu) << (8 * i);
                 }
-                stStream32(p.d + (long long)zi * dstPlanePitch + (long long)(y0 + r) * dstRowPitch + (long long)xw * BD,
-                           outWord[pass]);
+                outWord[pass * (SB / 4)] = w[0];
+                if (SB == 8) outWord[pass * (SB / 4) + SB / 8] = w[1];
             }
         }
-        // hand back the planes no later dst plane taps
-        const int nextLo = zi + 1 < p.dzCount ? seqLoT[zi + 1] : nSeq;
-        __syncwarp();
-        if ((t & 31) == 0)
-            for (; released < nextLo; ++released) mbarArrive(smemAddr(&empty[released % kRing]));
-        released = max(released, nextLo);
+        uint8_t* q = dz;
+#pragma unroll
+        for (int pass = 0; pass < NPASS; ++pass) {
+            if (pass < nPass) marchStore<SB>(q, outWord[pass * (SB / 4)], outWord[pass * (SB / 4) + SB / 8]);
+            q += rowStep;
+        }
     }
 }
 
@@ -318,26 +412,30 @@ EncodeTiledFn encodeTiled()
     return fn;
 }
 
-template <int FS, int FD, int MODE>
-cudaError_t launchMarch(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid)
+template <int FS, int FD, int MODE, bool IDENT>
+cudaError_t launchMarch(const LaunchCtx& c, const CUtensorMap* tm, const MarchParams& p, size_t smemBytes, unsigned grid)
 {
-    auto kern = resampleMarchKernel<FS, FD, MODE>;
+    auto kern = resampleMarchKernel<FS, FD, MODE, IDENT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
     if (e != cudaSuccess) return e;
-    kern<<<grid, kMarchThreads, smemBytes, c.stream>>>(tm, p);
+    kern<<<grid, kMarchThreads, smemBytes, c.stream>>>(tm[0], tm[1], p);
     countLaunch();
     return cudaGetLastError();
 }
 
 template <int FS, int FD>
-cudaError_t launchMarchMode(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid, int mode)
+cudaError_t launchMarchMode(const LaunchCtx& c, const CUtensorMap* tm, const MarchParams& p, size_t smemBytes, unsigned grid, int mode)
 {
-    return mode == M_LINEAR8 ? launchMarch<FS, FD, M_LINEAR8>(c, tm, p, smemBytes, grid)
-                             : launchMarch<FS, FD, M_TRILINEAR>(c, tm, p, smemBytes, grid);
+    // default (0,1) mappings on both sides drop the mapping arithmetic from the codec
+    if (p.ms.identity && p.md.identity)
+        return mode == M_LINEAR8 ? launchMarch<FS, FD, M_LINEAR8, true>(c, tm, p, smemBytes, grid)
+                                 : launchMarch<FS, FD, M_TRILINEAR, true>(c, tm, p, smemBytes, grid);
+    return mode == M_LINEAR8 ? launchMarch<FS, FD, M_LINEAR8, false>(c, tm, p, smemBytes, grid)
+                             : launchMarch<FS, FD, M_TRILINEAR, false>(c, tm, p, smemBytes, grid);
 }
 
 template <int FS>
-cudaError_t launchMarchDst(const LaunchCtx& c, const CUtensorMap& tm, const MarchParams& p, size_t smemBytes, unsigned grid,
+cudaError_t launchMarchDst(const LaunchCtx& c, const CUtensorMap* tm, const MarchParams& p, size_t smemBytes, unsigned grid,
                            int fd, int mode)
 {
     switch (fd) {
@@ -361,9 +459,10 @@ cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const Vo
     auto plain = [](int f) { return f == F_U8 || f == F_U16 || f == F_U32 || f == F_F32; };
     if (!plain(src.format) || !plain(dst.format)) return cudaErrorNotSupported;
     if (getenv("VKTB_RS_NO_MARCH")) return cudaErrorNotSupported;
-    // TMA: 16-byte aligned base and strides; dst rows are written as 32-bit words
+    // TMA: 16-byte aligned base and strides; dst rows are written as 32- or 64-bit words
     if ((reinterpret_cast<uintptr_t>(src.data) & 15u) || ((long long)S[0] * bs) % 16) return cudaErrorNotSupported;
-    if ((reinterpret_cast<uintptr_t>(dst.data) & 3u) || ((long long)D[0] * bd) % 4) return cudaErrorNotSupported;
+    const int storeBytes = marchVoxelsPerThread(bd) * bd;
+    if ((reinterpret_cast<uintptr_t>(dst.data) % storeBytes) || ((long long)D[0] * bd) % storeBytes) return cudaErrorNotSupported;
     for (int a = 0; a < 3; ++a) if (D[a] > (1 << 24) || S[a] > (1 << 24)) return cudaErrorNotSupported;
     EncodeTiledFn encode = encodeTiled();
     if (!encode) return cudaErrorNotSupported;
@@ -373,7 +472,7 @@ cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const Vo
     p.Dx = D[0]; p.Dy = D[1]; p.dzCount = dzCount;
     p.Sx = S[0]; p.Sy = S[1]; p.szCount = szCount;
     p.md = dst.map; p.ms = src.map;
-    p.BXv = kLanesX * (4 / bd);
+    p.BXv = kLanesX * marchVoxelsPerThread(bd);
     p.tilesX = (D[0] + p.BXv - 1) / p.BXv;
     // src brick extents: floor(tile * S / D) + 3 covers lo .. hi of the tile (hi may be lo + 2 after rounding)
     const int gran = 16 / bs;
@@ -381,35 +480,47 @@ cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const Vo
     if (spanX <= kMaxBox) { p.nBoxX = 1; p.bxS = (int)((spanX + gran - 1) / gran * gran); if (p.bxS > kMaxBox) p.bxS = kMaxBox; }
     else { p.nBoxX = (int)((spanX + kMaxBox - 1) / kMaxBox); p.bxS = kMaxBox; }
     if (p.nBoxX > kMaxBoxesX) return cudaErrorNotSupported;
-    int BY = kMaxBY;
-    long long byS = 0, slot = 0;
+    int BY = marchPasses(bd) * kRowsY;
+    long long byS = 0, slot = 0, spillOff = 0;
     for (; BY >= kRowsY; BY /= 2) {
         byS = (long long)BY * S[1] / D[1] + 3;
-        slot = ((long long)p.nBoxX * p.bxS * byS * bs + 127) / 128 * 128;
+        spillOff = ((long long)p.nBoxX * p.bxS * byS * bs + 127) / 128 * 128;
+        slot = (spillOff + byS * 16 + 127) / 128 * 128;
         if (byS <= kMaxBox && slot <= 20 * 1024) break;
     }
     if (BY < kRowsY) return cudaErrorNotSupported;
-    p.BY = BY; p.byS = (int)byS; p.slotBytes = (int)slot;
+    p.BY = BY; p.byS = (int)byS; p.slotBytes = (int)slot; p.spillOff = (int)spillOff;
     const int tilesY = (D[1] + BY - 1) / BY;
     const size_t smemBytes = (size_t)kRing * slot;
 
-    CUtensorMap tm;
+    CUtensorMap tm[2];
     const cuuint64_t gdim[3] = { (cuuint64_t)S[0], (cuuint64_t)S[1], (cuuint64_t)szCount };
     const cuuint64_t gstr[2] = { (cuuint64_t)S[0] * bs, (cuuint64_t)S[0] * S[1] * bs };
     const cuuint32_t box[3] = { (cuuint32_t)p.bxS, (cuuint32_t)p.byS, 1u };
     const cuuint32_t estr[3] = { 1u, 1u, 1u };
     const CUtensorMapDataType dt = bs == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : bs == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16
                                                                                       : CU_TENSOR_MAP_DATA_TYPE_UINT32;
-    if (encode(&tm, dt, 3, const_cast<uint8_t*>(src.data), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    if (encode(&tm[0], dt, 3, const_cast<uint8_t*>(src.data), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return cudaErrorNotSupported;
+    // the spill column: the window as Sy*szCount rows, boxes of 16 bytes x byS rows
+    const cuuint64_t gdim2[2] = { (cuuint64_t)S[0], (cuuint64_t)S[1] * (cuuint64_t)szCount };
+    const cuuint32_t box2[2] = { (cuuint32_t)(16 / bs), (cuuint32_t)p.byS };
+    if ((cuuint64_t)S[1] * (cuuint64_t)szCount > 0x7fffffffull ||
+        encode(&tm[1], dt, 2, const_cast<uint8_t*>(src.data), gdim2, gstr, box2, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorNotSupported;
 
-    const size_t nTab = kHdr + 3 * (size_t)D[0] + 3 * (size_t)D[1] + 5 * (size_t)dzCount + 3 * (size_t)szCount;
+    const size_t nBase = kHdr + 3 * (size_t)D[0] + 3 * (size_t)D[1] + 5 * (size_t)dzCount + 3 * (size_t)szCount;
+    const size_t zpackOff = (nBase + 3) / 4 * 4;
+    if (zpackOff > 0x7fffffff) return cudaErrorNotSupported;
+    const size_t nTab = zpackOff + 4 * (size_t)dzCount;
+    p.zpackOff = (int)zpackOff;
     int* tab = nullptr;
     cudaError_t e = cudaMallocAsync((void**)&tab, nTab * sizeof(int), c.stream);
     if (e != cudaSuccess) return e;
     p.tab = tab;
-    marchPlanKernel<<<3, 1024, 0, c.stream>>>(tab, D[0], S[0], D[1], S[1], dzCount, dstZ0, D[2], S[2], srcZ0, szCount, mode);
+    marchPlanKernel<<<3, 1024, 0, c.stream>>>(tab, D[0], S[0], D[1], S[1], dzCount, dstZ0, D[2], S[2], srcZ0, szCount, mode, p.zpackOff);
     countLaunch();
 
     const unsigned grid = (unsigned)(p.tilesX * tilesY);

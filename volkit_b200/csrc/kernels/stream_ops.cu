@@ -138,6 +138,24 @@ copyRowsKernel(CopyParams p)
     });
 }
 
+// bytewise copy of a box whose rows share one 16-byte phase in dst and src and need no clamping
+template <int BPV>
+__global__ void __launch_bounds__(kThreads)
+copyRowsUniformKernel(CopyParams p, int shift)
+{
+    constexpr int V = 16 / BPV;
+    const uint8_t* s0 = p.s + (((long long)p.g.z0 * p.sy + p.g.y0) * (long long)p.sx + p.g.x0) * BPV;
+    const long long spy = (long long)p.sx * BPV, spz = spy * p.sy;
+    forEachRowChunkUniform<V, 4, uint4>(p.g, shift,
+        [&](int y, int z, int xr) { return ldStream(s0 + y * spy + z * spz + (long long)xr * BPV); },
+        [&](int y, int z, int xr, const uint4& q) { stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, q); },
+        [&](int y, int z, int xr, int n) {
+            const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
+            uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+            for (int i = 0; i < n; ++i) storeRaw(dp + i * BPV, BPV, loadRaw(sp + i * BPV, BPV));
+        });
+}
+
 // ---------------------------------------------------------------- Copy (by value) ------------------------
 // generic: runtime formats, one voxel per thread along x, clamped src
 __global__ void __launch_bounds__(kThreads)
@@ -324,7 +342,18 @@ cudaError_t launchCopy(const LaunchCtx& c, const VolDesc& dst, const VolDesc& sr
             copyFlatKernel<<<grid, kThreads, 0, c.stream>>>(p.d.base, s0, n * bd);
         } else {
             RowsLaunch l = rowsLaunch(g.nx, (long long)g.ny * g.nz, 16 / bd);
-            if (bd == 1) copyRowsKernel<1><<<l.grid, l.block, 0, c.stream>>>(p);
+            // all rows in one 16-byte phase, src == dst phase, nothing to clamp: several rows in flight per thread
+            const long long spy = (long long)src.dims[0] * bs, spz = spy * src.dims[1];
+            const bool uniform = inside && (p.d.pitchY % 16) == 0 && (p.d.pitchZ % 16) == 0 && (spy % 16) == 0 && (spz % 16) == 0
+                              && ((reinterpret_cast<uintptr_t>(p.d.base) ^ reinterpret_cast<uintptr_t>(s0)) & 15u) == 0
+                              && (long long)g.ny * g.nz < 0x7fffffffLL;
+            if (uniform) {
+                const int shift = (int)((reinterpret_cast<uintptr_t>(p.d.base) & 15u) / bd);
+                if (bd == 1) copyRowsUniformKernel<1><<<l.grid, l.block, 0, c.stream>>>(p, shift);
+                else if (bd == 2) copyRowsUniformKernel<2><<<l.grid, l.block, 0, c.stream>>>(p, shift);
+                else copyRowsUniformKernel<4><<<l.grid, l.block, 0, c.stream>>>(p, shift);
+            }
+            else if (bd == 1) copyRowsKernel<1><<<l.grid, l.block, 0, c.stream>>>(p);
             else if (bd == 2) copyRowsKernel<2><<<l.grid, l.block, 0, c.stream>>>(p);
             else copyRowsKernel<4><<<l.grid, l.block, 0, c.stream>>>(p);
         }

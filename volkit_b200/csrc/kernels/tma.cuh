@@ -80,11 +80,17 @@ __device__ __forceinline__ void bulkWaitAll()
     asm volatile("cp.async.bulk.wait_group %0;" :: "n"(N) : "memory");
 }
 
-// ---- 3-D tensor-map tile load (box of a dense x-fastest volume; out-of-bounds elements read as zero) ------
+// ---- tensor-map tile loads (box of a dense x-fastest volume; out-of-bounds elements read as zero) ---------
 __device__ __forceinline__ void tensorLoad3d(uint32_t dstSmem, const void* tensorMap, int x, int y, int z, uint32_t bar)
 {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  :: "r"(dstSmem), "l"(tensorMap), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tensorLoad2d(uint32_t dstSmem, const void* tensorMap, int x, int y, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dstSmem), "l"(tensorMap), "r"(x), "r"(y), "r"(bar) : "memory");
 }
 
 } // namespace vktb

@@ -77,6 +77,27 @@ transform1Kernel(T1Params p)
     });
 }
 
+// boxed range whose rows share one 16-byte phase: four rows in flight per thread
+template <int BPV, int OP>
+__global__ void __launch_bounds__(kThreads)
+transform1UniformKernel(T1Params p, int shift)
+{
+    constexpr int V = 16 / BPV;
+    constexpr uint32_t mask = BPV == 4 ? 0xffffffffu : (1u << (BPV * 8)) - 1u;
+    forEachRowChunkUniform<V, 4, uint4>(p.g, shift,
+        [&](int y, int z, int xr) { return ldPlain(p.v.base + y * p.v.pitchY + z * p.v.pitchZ + (long long)xr * BPV); },
+        [&](int y, int z, int xr, const uint4& q) {
+            stStream(p.v.base + y * p.v.pitchY + z * p.v.pitchZ + (long long)xr * BPV,
+                     unaryOpVec<BPV, OP>(p.g.x0 + xr, p.g.y0 + y, p.g.z0 + z, q, p.fmt, mask, p.m));
+        },
+        [&](int y, int z, int xr, int n) {
+            uint8_t* dp = p.v.base + y * p.v.pitchY + z * p.v.pitchZ + (long long)xr * BPV;
+            for (int i = 0; i < n; ++i)
+                storeRaw(dp + i * BPV, BPV, unaryOp<OP>(p.g.x0 + xr + i, p.g.y0 + y, p.g.z0 + z, loadRaw(dp + i * BPV, BPV),
+                                                       p.fmt, mask, p.m));
+        });
+}
+
 // Contiguous ranges (whole volumes, whole planes): flat grid-stride stream, four 128-bit vectors in flight per thread.
 // The op still sees absolute coordinates: they are rebuilt from the linear voxel index with 32-bit arithmetic.
 template <int BPV, int OP>
@@ -181,6 +202,44 @@ transform2Kernel(T2Params p)
     });
 }
 
+struct VecPair { uint4 a, b; };
+
+// both volumes' rows in one 16-byte phase: two rows (four loads) in flight per thread
+template <int BPV, int OP>
+__global__ void __launch_bounds__(kThreads)
+transform2UniformKernel(T2Params p, int shift)
+{
+    constexpr int V = 16 / BPV;
+    constexpr uint32_t mask = BPV == 4 ? 0xffffffffu : (1u << (BPV * 8)) - 1u;
+    forEachRowChunkUniform<V, 2, VecPair>(p.g, shift,
+        [&](int y, int z, int xr) {
+            VecPair q;
+            q.a = ldPlain(p.v1.base + y * p.v1.pitchY + z * p.v1.pitchZ + (long long)xr * BPV);
+            q.b = ldPlain(p.v2.base + y * p.v2.pitchY + z * p.v2.pitchZ + (long long)xr * BPV);
+            return q;
+        },
+        [&](int y, int z, int xr, const VecPair& q) {
+            uint32_t w1[4] = { 0u, 0u, 0u, 0u }, w2[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                uint32_t a = vecGet<BPV>(q.a, i), b = vecGet<BPV>(q.b, i);
+                binaryOp<OP>(a, b, mask);
+                vecSet<BPV>(w1, i, a); vecSet<BPV>(w2, i, b);
+            }
+            stStream(p.v1.base + y * p.v1.pitchY + z * p.v1.pitchZ + (long long)xr * BPV, make_uint4(w1[0], w1[1], w1[2], w1[3]));
+            stStream(p.v2.base + y * p.v2.pitchY + z * p.v2.pitchZ + (long long)xr * BPV, make_uint4(w2[0], w2[1], w2[2], w2[3]));
+        },
+        [&](int y, int z, int xr, int n) {
+            uint8_t* p1 = p.v1.base + y * p.v1.pitchY + z * p.v1.pitchZ + (long long)xr * BPV;
+            uint8_t* p2 = p.v2.base + y * p.v2.pitchY + z * p.v2.pitchZ + (long long)xr * BPV;
+            for (int i = 0; i < n; ++i) {
+                uint32_t a = loadRaw(p1 + i * BPV, BPV), b = loadRaw(p2 + i * BPV, BPV);
+                binaryOp<OP>(a, b, mask);
+                storeRaw(p1 + i * BPV, BPV, a); storeRaw(p2 + i * BPV, BPV, b);
+            }
+        });
+}
+
 // mixed bytes-per-voxel: one voxel per thread
 template <int OP>
 __global__ void __launch_bounds__(kThreads)
@@ -219,6 +278,18 @@ cudaError_t launchT1(const LaunchCtx& c, const T1Params& p, int op, bool flat)
         return cudaGetLastError();
     }
     RowsLaunch l = rowsLaunch(p.g.nx, (long long)p.g.ny * p.g.nz, 16 / BPV);
+    if (((p.v.pitchY | p.v.pitchZ) & 15) == 0 && (long long)p.g.ny * p.g.nz < 0x7fffffffLL) {
+        const int shift = (int)((reinterpret_cast<uintptr_t>(p.v.base) & 15u) / BPV);
+        switch (op) {
+        case 0: transform1UniformKernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p, shift); break;
+        case 1: transform1UniformKernel<BPV, 1><<<l.grid, l.block, 0, c.stream>>>(p, shift); break;
+        case 2: transform1UniformKernel<BPV, 2><<<l.grid, l.block, 0, c.stream>>>(p, shift); break;
+        case 3: transform1UniformKernel<BPV, 3><<<l.grid, l.block, 0, c.stream>>>(p, shift); break;
+        default: return cudaErrorInvalidValue;
+        }
+        countLaunch();
+        return cudaGetLastError();
+    }
     switch (op) {
     case 0: transform1Kernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p); break;
     case 1: transform1Kernel<BPV, 1><<<l.grid, l.block, 0, c.stream>>>(p); break;
@@ -234,9 +305,18 @@ template <int BPV>
 cudaError_t launchT2(const LaunchCtx& c, const T2Params& p, int op)
 {
     RowsLaunch l = rowsLaunch(p.g.nx, (long long)p.g.ny * p.g.nz, 16 / BPV);
-    if (op == 0) transform2Kernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p);
-    else if (op == 1) transform2Kernel<BPV, 1><<<l.grid, l.block, 0, c.stream>>>(p);
-    else return cudaErrorInvalidValue;
+    const uintptr_t phase = reinterpret_cast<uintptr_t>(p.v1.base) & 15u;
+    const bool uniform = ((p.v1.pitchY | p.v1.pitchZ | p.v2.pitchY | p.v2.pitchZ) & 15) == 0
+                      && phase == (reinterpret_cast<uintptr_t>(p.v2.base) & 15u) && p.v1.base != p.v2.base
+                      && (long long)p.g.ny * p.g.nz < 0x7fffffffLL;
+    if (op != 0 && op != 1) return cudaErrorInvalidValue;
+    if (uniform) {
+        const int shift = (int)(phase / BPV);
+        if (op == 0) transform2UniformKernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p, shift);
+        else transform2UniformKernel<BPV, 1><<<l.grid, l.block, 0, c.stream>>>(p, shift);
+    }
+    else if (op == 0) transform2Kernel<BPV, 0><<<l.grid, l.block, 0, c.stream>>>(p);
+    else transform2Kernel<BPV, 1><<<l.grid, l.block, 0, c.stream>>>(p);
     countLaunch();
     return cudaGetLastError();
 }

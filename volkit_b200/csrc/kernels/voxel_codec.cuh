@@ -84,14 +84,22 @@ __device__ __forceinline__ uint32_t mapVoxel(float value, const Mapping& m)
     return 0u;
 }
 
+// Exact uint -> float for values below 2^23 without the conversion pipe: OR the value into the mantissa of 2^23
+// and subtract 2^23 (both steps exact).  I2F runs at a fraction of the FP32 rate and the integer kernels convert
+// two to eight voxels per output voxel.
+__device__ __forceinline__ float smallUintToFloat(uint32_t v)
+{
+    return __fsub_rn(__uint_as_float(0x4B000000u | v), 8388608.0f);
+}
+
 // ---- unmap: raw -> float ----------------------------------------------------------------------------
 template <int F, bool IDENT>
 __device__ __forceinline__ float unmapVoxel(uint32_t raw, const Mapping& m)
 {
     if (F == F_F32) return __uint_as_float(raw);   // raw bits, mapping NOT applied (VoxelMapping.hpp:163-178)
     float t;
-    if (F == F_U8)         t = __fdiv_rn(__uint2float_rn(raw & 0xffu), 255.999f);
-    else if (F == F_U16)   t = __fmul_rn(__uint2float_rn(raw & 0xffffu), 1.52587890625e-05f);
+    if (F == F_U8)         t = __fdiv_rn(smallUintToFloat(raw & 0xffu), 255.999f);
+    else if (F == F_U16)   t = __fmul_rn(smallUintToFloat(raw & 0xffffu), 1.52587890625e-05f);
     else if (F == F_INT16) t = __fmul_rn(__fadd_rn(__int2float_rn((int)(short)(raw & 0xffffu)), 32767.f), 1.52587890625e-05f);
     else if (F == F_U32)   t = __fmul_rn(__uint2float_rn(raw), 2.3283064365386962890625e-10f);
     else return 0.f;
