@@ -189,9 +189,12 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     const int4* zpack = reinterpret_cast<const int4*>(p.tab + p.zpackOff);
     const int nSeq = p.tab[0];
 
-    // x tiles in descending order: the tile holding the last columns (extra spill pass in reference-faithful Linear) is
-    // the slowest and starts first instead of forming the tail of the launch
-    const int tileX = p.tilesX - 1 - (int)(blockIdx.x % p.tilesX), tileY = blockIdx.x / p.tilesX;
+    // the tiles holding the last columns run an extra spill pass in reference-faithful Linear: they are the slowest,
+    // so they take the first block indices (all of them start in the first wave) instead of forming the launch's tail
+    const int tilesY = gridDim.x / p.tilesX;
+    int tileX, tileY;
+    if ((int)blockIdx.x < tilesY) { tileX = p.tilesX - 1; tileY = blockIdx.x; }
+    else { const int b = blockIdx.x - tilesY; tileX = b % (p.tilesX - 1); tileY = b / (p.tilesX - 1); }
     const int x0 = tileX * p.BXv, y0 = tileY * p.BY;
     const int h = min(p.BY, p.Dy - y0);
     // the innermost TMA coordinate must address a 16-byte aligned element (found the hard way: misaligned box

@@ -91,6 +91,12 @@ __device__ __forceinline__ float smallUintToFloat(uint32_t v)
 {
     return __fsub_rn(__uint_as_float(0x4B000000u | v), 8388608.0f);
 }
+// v * 2^-16 for v < 2^16 the same way: 128.0f has an ulp of 2^-16, so 128 + v*2^-16 is the bit pattern
+// 0x43000000 | v and the subtraction is exact -- equal to float(v) / 65535.999f (= float(v) * 2^-16, also exact).
+__device__ __forceinline__ float u16ToUnit(uint32_t v)
+{
+    return __fsub_rn(__uint_as_float(0x43000000u | v), 128.0f);
+}
 
 // ---- unmap: raw -> float ----------------------------------------------------------------------------
 template <int F, bool IDENT>
@@ -99,7 +105,7 @@ __device__ __forceinline__ float unmapVoxel(uint32_t raw, const Mapping& m)
     if (F == F_F32) return __uint_as_float(raw);   // raw bits, mapping NOT applied (VoxelMapping.hpp:163-178)
     float t;
     if (F == F_U8)         t = __fdiv_rn(smallUintToFloat(raw & 0xffu), 255.999f);
-    else if (F == F_U16)   t = __fmul_rn(smallUintToFloat(raw & 0xffffu), 1.52587890625e-05f);
+    else if (F == F_U16)   t = u16ToUnit(raw & 0xffffu);
     else if (F == F_INT16) t = __fmul_rn(__fadd_rn(__int2float_rn((int)(short)(raw & 0xffffu)), 32767.f), 1.52587890625e-05f);
     else if (F == F_U32)   t = __fmul_rn(__uint2float_rn(raw), 2.3283064365386962890625e-10f);
     else return 0.f;
