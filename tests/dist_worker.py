@@ -97,6 +97,54 @@ def main():
             print(f"rank {rank}: expected no halo for exact 2:1, got {halo} bytes", flush=True)
             sys.exit(1)
 
+    # *Range calls with a z offset / clamped Copy: dst slab <- window of src planes (same plane transfers)
+    def fill_slab(vol, whole):
+        part = np.ascontiguousarray(whole.a[vol.z0:vol.z1]).view(np.uint8).ravel()
+        vol.data.copy_(torch.from_numpy(part.copy()))
+
+    def check_slab(vol, ref, what):
+        got = vol.data.cpu().numpy().view(po.DTYPES[vol.fmt]).reshape(vol.z1 - vol.z0, vol.dims[1], vol.dims[0])
+        if got.tobytes() != ref.a[vol.z0:vol.z1].tobytes():
+            print(f"rank {rank}: MISMATCH in {what}", flush=True)
+            sys.exit(1)
+
+    def as_vol(desc, fmt, lo_hi=(0.0, 1.0)):
+        return po.Vol(np_view(desc, fmt), fmt, *lo_hi)
+
+    fmt = po.UINT16
+    Sd, Dd = (24, 10, 19), (28, 14, 26)
+    whole_a, whole_b = po.Vol(po.synth(Sd, fmt, 1), fmt), po.Vol(po.synth(Sd, fmt, 2), fmt)
+    for first, last, off in (((-3, -2, -4), (22, 9, 23), (1, 2, 2)),     # clamped on both z ends
+                             ((2, 1, 3), (20, 8, 17), (5, 4, 9)),         # interior, large z offset
+                             ((0, 0, 0), (24, 10, 19), (0, 0, 0))):       # congruent part: no transfers at all
+        whole_d = po.Vol(po.synth(Dd, fmt, 3), fmt)
+        ref = whole_d.copy()
+        o.copy_range(ref, whole_a, first, last, off)
+        a = sharded.ShardedVolume(torch, Sd, fmt, rank, world, device=device)
+        d = sharded.ShardedVolume(torch, Dd, fmt, rank, world, device=device)
+        fill_slab(a, whole_a); fill_slab(d, whole_d)
+        compute = None if gpu else (lambda dd, sd, f, l, of: o.copy_range(as_vol(dd, fmt), as_vol(sd, fmt), f, l, of))
+        total_halo += sharded.copy_range_sharded(d, a, first, last, off, dist, compute=compute)
+        if gpu:
+            torch.cuda.synchronize()
+        check_slab(d, ref, f"CopyRange {first} {last} {off}")
+    for op, first, last, off in ((po.SAFESUM, (1, 2, 3), (23, 9, 18), (4, 3, 7)),
+                                 (po.DIFF, (0, 0, 0), (24, 10, 19), (2, 1, 0)),        # no z offset: no transfers
+                                 (po.SAFEPROD, (0, 0, 5), (24, 10, 6), (0, 0, 20))):   # a single plane far away
+        whole_d = po.Vol(po.synth(Dd, fmt, 3), fmt)
+        ref = whole_d.copy()
+        o.arith_range(op, ref, whole_a, whole_b, first, last, off)
+        a = sharded.ShardedVolume(torch, Sd, fmt, rank, world, device=device)
+        b = sharded.ShardedVolume(torch, Sd, fmt, rank, world, device=device)
+        d = sharded.ShardedVolume(torch, Dd, fmt, rank, world, device=device)
+        fill_slab(a, whole_a); fill_slab(b, whole_b); fill_slab(d, whole_d)
+        compute = None if gpu else (lambda op_, dd, ad, bd, f, l, of:
+                                    o.arith_range(op_, as_vol(dd, fmt), as_vol(ad, fmt), as_vol(bd, fmt), f, l, of))
+        total_halo += sharded.arith_range_sharded(op, d, a, b, first, last, off, dist, compute=compute)
+        if gpu:
+            torch.cuda.synchronize()
+        check_slab(d, ref, f"arith {op} {first} {last} {off}")
+
     # elementwise ops need no exchange: slabs tile the volume exactly
     Z = 23
     covered = sorted(z for r in range(world) for z in range(*sharded.slab_range(Z, world, r)))

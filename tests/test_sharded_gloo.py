@@ -56,3 +56,40 @@ def test_halo_plan_properties():
     # 2:3 up-sampling does cross
     _, transfers = sharded.halo_plan(capi.TRILINEAR, (4, 4, 3072), (4, 4, 2048), 8)
     assert len(transfers) == 7 and all(t.z1 - t.z0 == 1 for t in transfers)
+
+
+def test_range_plan_properties():
+    """Every p.z of the range is computed by exactly one rank, whose window holds the (clamped) src plane it reads;
+    transfers only carry planes their sender owns; a congruent call (no z shift) moves nothing."""
+    from volkit_b200 import sharded
+    for kind in ("arith", "copy"):
+        for Sz, Dz, first, last, off in ((19, 26, 3, 17, 7), (19, 26, 0, 19, 0), (64, 64, 0, 64, 0), (9, 40, 2, 8, 31),
+                                         (19, 26, -4, 23, 2)):
+            if kind == "arith" and (first < 0 or last > Sz):
+                continue
+            for world in (1, 2, 3, 4, 8):
+                windows, sub, transfers = sharded.range_plan(kind, first, last, off, Dz, Sz, world)
+                owner = {}
+                for r, (pz0, pz1) in enumerate(sub):
+                    dz0, dz1 = sharded.slab_range(Dz, world, r)
+                    for pz in range(pz0, pz1):
+                        assert pz not in owner
+                        owner[pz] = r
+                        dplane = pz + off if kind == "arith" else pz - first + off
+                        assert dz0 <= dplane < dz1
+                        splane = pz if kind == "arith" else min(max(pz, 0), Sz - 1)
+                        assert windows[r][0] <= splane < windows[r][1]
+                want = [pz for pz in range(first, last) if 0 <= (pz + off if kind == "arith" else pz - first + off) < Dz]
+                assert sorted(owner) == want
+                for t in transfers:
+                    o0, o1 = sharded.slab_range(Sz, world, t.src_rank)
+                    assert t.src_rank != t.dst_rank and o0 <= t.z0 < t.z1 <= o1
+                for r, (w0, w1) in enumerate(windows):
+                    z0, z1 = sharded.slab_range(Sz, world, r)
+                    got = set(range(max(w0, z0), min(w1, z1)))
+                    for t in transfers:
+                        if t.dst_rank == r:
+                            got |= set(range(t.z0, t.z1))
+                    assert got == set(range(w0, w1))
+                if Sz == Dz and off == 0 and first == 0:
+                    assert transfers == []

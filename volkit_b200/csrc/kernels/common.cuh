@@ -117,7 +117,7 @@ __device__ __forceinline__ void forEachRowChunk(const Range& g, const Operand& d
 // multiple of 16 and the operands are congruent mod 16; the launcher checks): the thread's chunk [xr, xr + n) is the
 // same in every row, rows advance by add-with-carry instead of a division, and full chunks run U rows at a time --
 // U independent 128-bit loads per operand in flight before the first store (a single row per iteration leaves a
-// copy with 16 B in flight per thread, ~80 % of the HBM roofline; ncu: profiles/r01_rows_notes.md).
+// copy with 16 B in flight per thread, ~80 % of the HBM roofline; ncu: profiles/r01_notes.md).
 //   load(y, z, xr) -> Regs        reads the chunk's vectors (no stores)
 //   store(y, z, xr, regs)         computes and stores one full chunk
 //   edge(y, z, xr, n)             scalar path for the row's partial head / tail chunk

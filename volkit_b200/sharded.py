@@ -175,3 +175,95 @@ def resample_sharded(dst: ShardedVolume, src: ShardedVolume, filt: int, dist, co
         sdesc = capi.vol(buf.data_ptr(), (S[0], S[1], window[1] - window[0]), src.fmt, src.lo, src.hi)
         (compute or _cabi_resample_window)(dst.desc(), sdesc, filt, dst.z0, D, w0, S)
     return received
+
+
+# ---- *Range calls whose dst planes come from other src planes (z offset, clamped Copy) ------------------------------
+#
+# Reference semantics: arithmetic writes dst[p + off] = f(s1[p], s2[p]) for absolute p in
+# [first, last) (Arithmetic_serial.hpp:15-45); Copy writes dst[p - first + off] = src[clamp(p, 0, dims-1)]
+# (Copy_serial.hpp:13-82).  Sharded by DST slab: a rank runs the sub-range of p.z whose dst planes it owns on a window of
+# the src planes that sub-range reads; planes it does not own arrive by the same point-to-point transfers Resample uses.
+
+def range_plan(kind: str, first_z: int, last_z: int, off_z: int, dst_dimz: int, src_dimz: int, world: int):
+    """(windows, subranges, transfers): per rank the src planes [w0, w1) it needs, the p.z sub-range [pz0, pz1) it
+    computes, and the plane transfers.  kind = "arith" (dst plane = p.z + off_z, no clamp) or "copy"
+    (dst plane = p.z - first_z + off_z, src plane clamped to [0, src_dimz - 1])."""
+    assert kind in ("arith", "copy")
+    shift = off_z if kind == "arith" else off_z - first_z
+    windows, subranges, transfers = [], [], []
+    for r in range(world):
+        dz0, dz1 = slab_range(dst_dimz, world, r)
+        pz0, pz1 = max(first_z, dz0 - shift), min(last_z, dz1 - shift)
+        if pz1 <= pz0:
+            windows.append((0, 0))
+            subranges.append((0, 0))
+            continue
+        if kind == "arith":
+            assert 0 <= pz0 and pz1 <= src_dimz, "arithmetic range outside the source volumes"
+            need = (pz0, pz1)
+        else:
+            need = (min(max(pz0, 0), src_dimz - 1), min(max(pz1 - 1, 0), src_dimz - 1) + 1)
+        windows.append(need)
+        subranges.append((pz0, pz1))
+        for o in range(world):
+            if o == r:
+                continue
+            oz0, oz1 = slab_range(src_dimz, world, o)
+            a, b = max(need[0], oz0), min(need[1], oz1)
+            if a < b:
+                transfers.append(Transfer(o, r, a, b))
+    return windows, subranges, transfers
+
+
+def _window_desc(vol: ShardedVolume, buf, window):
+    return capi.vol(buf.data_ptr(), (vol.dims[0], vol.dims[1], window[1] - window[0]), vol.fmt, vol.lo, vol.hi)
+
+
+def _cabi_copy_range(dst_desc, src_desc, first, last, off):
+    lib = capi.load()
+    capi.check(lib.vktb_copy_range(ctypes.byref(dst_desc), ctypes.byref(src_desc), capi.I3(*first), capi.I3(*last),
+                                   capi.I3(*off)), "vktb_copy_range")
+
+
+def _cabi_arith_range(op, dst_desc, a_desc, b_desc, first, last, off):
+    lib = capi.load()
+    capi.check(lib.vktb_arith_range(op, ctypes.byref(dst_desc), ctypes.byref(a_desc), ctypes.byref(b_desc),
+                                    capi.I3(*first), capi.I3(*last), capi.I3(*off)), "vktb_arith_range")
+
+
+def copy_range_sharded(dst: ShardedVolume, src: ShardedVolume, first, last, off, dist, compute=None) -> int:
+    """dst slab <- CopyRange(src, first, last, off) with the reference's clamped src indexing.  Returns the halo
+    bytes this rank received."""
+    assert dst.storage.data_ptr() != src.storage.data_ptr(), "sharded CopyRange needs distinct volumes"
+    windows, sub, transfers = range_plan("copy", first[2], last[2], off[2], dst.dims[2], src.dims[2], dst.world)
+    window = windows[dst.rank]
+    buf = gather_window(src, window, transfers, dist)
+    pz0, pz1 = sub[dst.rank]
+    if pz1 > pz0:
+        w0 = window[0]
+        f = (first[0], first[1], pz0 - w0)             # may be negative: clamps to the window's first plane = plane 0
+        l = (last[0], last[1], pz1 - w0)
+        o = (off[0], off[1], pz0 - first[2] + off[2] - dst.z0)
+        (compute or _cabi_copy_range)(dst.desc(), _window_desc(src, buf, window), f, l, o)
+    return sum((t.z1 - t.z0) * src.plane_bytes for t in transfers if t.dst_rank == dst.rank)
+
+
+def arith_range_sharded(op: int, dst: ShardedVolume, s1: ShardedVolume, s2: ShardedVolume, first, last, off, dist,
+                        compute=None) -> int:
+    """dst slab <- op(s1, s2) over [first, last) written at + off.  With off[2] == 0 and congruent volumes no plane
+    moves.  Returns the halo bytes this rank received."""
+    assert s1.dims[2] == s2.dims[2], "sources of a sharded arithmetic call must have the same number of planes"
+    assert dst.storage.data_ptr() not in (s1.storage.data_ptr(), s2.storage.data_ptr()) or off[2] == 0
+    windows, sub, transfers = range_plan("arith", first[2], last[2], off[2], dst.dims[2], s1.dims[2], dst.world)
+    window = windows[dst.rank]
+    buf1 = gather_window(s1, window, transfers, dist)
+    buf2 = buf1 if s2 is s1 else gather_window(s2, window, transfers, dist)
+    pz0, pz1 = sub[dst.rank]
+    if pz1 > pz0:
+        f = (first[0], first[1], 0)                    # the windows start at plane pz0
+        l = (last[0], last[1], pz1 - pz0)
+        o = (off[0], off[1], pz0 + off[2] - dst.z0)
+        (compute or _cabi_arith_range)(op, dst.desc(), _window_desc(s1, buf1, window), _window_desc(s2, buf2, window),
+                                       f, l, o)
+    recv = sum((t.z1 - t.z0) for t in transfers if t.dst_rank == dst.rank)
+    return recv * (s1.plane_bytes + (0 if s2 is s1 else s2.plane_bytes))
