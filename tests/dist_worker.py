@@ -114,7 +114,7 @@ def main():
     fmt = po.UINT16
     Sd, Dd = (24, 10, 19), (28, 14, 26)
     whole_a, whole_b = po.Vol(po.synth(Sd, fmt, 1), fmt), po.Vol(po.synth(Sd, fmt, 2), fmt)
-    for first, last, off in (((-3, -2, -4), (22, 9, 23), (1, 2, 2)),     # clamped on both z ends
+    for first, last, off in (((-3, -2, -4), (22, 9, 20), (1, 2, 2)),     # clamped on both z ends (24 planes land in dst planes 2..25)
                              ((2, 1, 3), (20, 8, 17), (5, 4, 9)),         # interior, large z offset
                              ((0, 0, 0), (24, 10, 19), (0, 0, 0))):       # congruent part: no transfers at all
         whole_d = po.Vol(po.synth(Dd, fmt, 3), fmt)
