@@ -252,6 +252,16 @@ def mem_available_bytes():
     return 0
 
 
+def recorded_traffic(kernel, size):
+    """DRAM bytes per launch of `kernel` at this size from a committed `ncu --set full` capture (profiles/traffic.json),
+    or (None, None): the bench itself never runs under a profiler."""
+    try:
+        e = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel][str(size)]
+        return int(e["bytes"]), e["source"]
+    except Exception:
+        return None, None
+
+
 def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
     """The call a user makes with HOST buffers, through the C-ABI.  Two forms are timed on the same pinned buffers:
       streamed  vktb_hosted_arith_range: z-slabs, upload / kernel / download overlapped (the product's e2e path)
@@ -369,6 +379,7 @@ def run_ours(args):
     value = world * nvox / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
     alg_bytes = 6.0 * nvox
+    traffic, traffic_src = recorded_traffic("arithFlatKernel<UInt16,SafeSum>", S)
     achieved = alg_bytes / (ms * 1e-3) / 1e9
 
     e2e = None
@@ -441,7 +452,8 @@ def run_ours(args):
                        "l2": "inputs (3 x %.1f GiB) far larger than the 126 MB L2: no flush needed" % (nvox * 2 / 2 ** 30),
                        "parallelism": f"z-slab x{world}, no data-path collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "arithFlatKernel<UInt16,SafeSum>",
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "kernel": "arithFlatKernel<UInt16,SafeSum>",
                          "algorithmic_bytes_per_voxel": 6, "frac_of_8TBs_nominal": achieved / 8000.0},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "parity": {"bit_exact_planes": planes, "ok": bool(ok)}, "ops": ops, "ops_sharded": sharded_ops,

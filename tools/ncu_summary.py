@@ -34,14 +34,18 @@ def launches(path):
         a[0] += 1
         a[1] += to_ns(row[vi], row[ui])
     tot = sum(a[1] for a in agg.values())
-    ours = sum(a[1] for k, a in agg.items() if "vktb::" in k)
+    # this library's kernels are the only CamelCase "...Kernel" names in the process (torch's end in "_kernel");
+    # ncu prints anonymous-namespace kernels without the vktb:: prefix
+    is_ours = lambda k: "vktb::" in k or re.search(r"[a-z0-9]Kernel\b", k) is not None  # noqa: E731
+    ours = sum(a[1] for k, a in agg.items() if is_ours(k))
     print(f"# ncu launch list: {path}\n")
     print("`ncu --metrics gpu__time_duration.sum --clock-control none` (cold-cache, serialised: compare SHARES, not absolutes)\n")
     print(f"total {tot / 1e6:.3f} ms over {sum(a[0] for a in agg.values())} launches; vktb:: kernels {ours / 1e6:.3f} ms "
-          f"({100 * ours / tot:.1f} %), the rest is torch input synthesis outside the timed regions\n")
+          f"({100 * ours / tot:.1f} %); anything else is torch input synthesis outside the timed regions (excluded when the "
+          f"capture was filtered with -k regex:Kernel)\n")
     print("| launches | total ms | avg ms | share | share of vktb | kernel |\n|---:|---:|---:|---:|---:|---|")
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        mine = "vktb::" in k
+        mine = is_ours(k)
         print(f"| {a[0]} | {a[1] / 1e6:.3f} | {a[1] / a[0] / 1e6:.4f} | {100 * a[1] / tot:.1f} % | "
               f"{(f'{100 * a[1] / ours:.1f} %') if mine else '-'} | `{k[:120]}` |")
 
