@@ -32,8 +32,9 @@ def run_sharded_ops(torch, dist, lib, capi, ShardedVolume, sharded, rank, world,
     # ---- config 4: edge^3 UInt8, Fill / Transform / SafeSum, z-slab sharded, no communication -------------------
     E = edge
     dims = (E, E, E)
-    a = ShardedVolume(torch, dims, capi.UINT8, rank, world)
-    b = ShardedVolume(torch, dims, capi.UINT8, rank, world)
+    ZOFF = 8                                         # z offset of the sharded SumRange line below
+    a = ShardedVolume(torch, dims, capi.UINT8, rank, world, halo=(ZOFF, 0))   # room for the planes that line pulls in
+    b = ShardedVolume(torch, dims, capi.UINT8, rank, world, halo=(ZOFF, 0))
     d = ShardedVolume(torch, dims, capi.UINT8, rank, world)
     first = a.z0 * E * E
     synth_into(a.data, 1, 1, first)
@@ -46,6 +47,17 @@ def run_sharded_ops(torch, dist, lib, capi, ShardedVolume, sharded, rank, world,
     record(f"Transform xor_coord {tag}", n, 2 * n, lambda: capi.check(lib.vktb_transform_range1(ctypes.byref(dd), z3, l3, 0)))
     record(f"SafeSum {tag}", n, 3 * n,
            lambda: capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z3, l3, z3)))
+    # *Range with a z offset: dst plane z reads src plane z - 8 -> 8 planes per source cross every slab boundary
+    nr = E * E * (E - ZOFF)
+    got = [0]
+
+    def sum_range():
+        got[0] = sharded.arith_range_sharded(capi.SUM, d, a, b, (0, 0, 0), (E, E, E - ZOFF), (0, 0, ZOFF), dist)
+
+    record(f"SumRange dstOffset (0,0,{ZOFF}) {tag}", nr, 3 * nr, sum_range)
+    t = torch.tensor([got[0]], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t) if dist is not None else None
+    out[f"SumRange dstOffset (0,0,{ZOFF}) {tag}"]["halo_bytes_all_ranks"] = int(t.item())
     del a, b, d
     torch.cuda.empty_cache()
 
