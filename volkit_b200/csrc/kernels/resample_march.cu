@@ -481,7 +481,11 @@ cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const Vo
     const int gran = 16 / bs;
     const long long spanX = (long long)p.BXv * S[0] / D[0] + 3 + (gran - 1);   // + the origin's round-down to 16 bytes
     if (spanX <= kMaxBox) { p.nBoxX = 1; p.bxS = (int)((spanX + gran - 1) / gran * gran); if (p.bxS > kMaxBox) p.bxS = kMaxBox; }
-    else { p.nBoxX = (int)((spanX + kMaxBox - 1) / kMaxBox); p.bxS = kMaxBox; }
+    else { p.nBoxX = (int)((spanX + kMaxBox - 1) / kMaxBox); p.bxS = kMaxBox; }   // whole boxes: 128-byte aligned smem dst
+    // Measured (profiles/r01_notes.md): splitting the span into evenly sized boxes makes 2:1 down-sampling of Float32
+    // fit the slot budget, but there the march runs at 2.3 ms against 1.06 ms for the direct gather (no plane is
+    // re-used and the taps need no conversion, so the per-plane hand-off is pure latency); Float32 down-sampling
+    // therefore stays on the gather kernel -- the slot budget below rejects it.
     if (p.nBoxX > kMaxBoxesX) return cudaErrorNotSupported;
     int BY = marchPasses(bd) * kRowsY;
     long long byS = 0, slot = 0, spillOff = 0;
