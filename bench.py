@@ -386,8 +386,14 @@ def run_ours(args):
     if not args.no_e2e:
         need = 3 * nvox * 2 + (8 << 30)
         Se = S
-        while Se > 256 and 3 * Se ** 3 * 2 + (8 << 30) > mem_available_bytes():
-            Se //= 2
+        # every rank of the box pins its own three host volumes at the same time: share what is available
+        host_budget = mem_available_bytes() // world
+        if dist is not None:
+            tb = torch.tensor([host_budget], dtype=torch.int64, device="cuda")
+            dist.all_reduce(tb, op=dist.ReduceOp.MIN)      # same edge on every rank
+            host_budget = int(tb.item())
+        while Se > 256 and 3 * Se ** 3 * 2 + (8 << 30) > host_budget:
+            Se = max(256, (Se * 7 // 8) // 64 * 64)         # shrink the edge in ~12 % steps
         d.free()
         if Se != S:
             a.free(); b.free()
