@@ -52,6 +52,15 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
            lambda: capi.check(lib.vktb_arith_range(capi.SAFEPROD, ctypes.byref(gd), ctypes.byref(gm), ctypes.byref(db), z3, l3, z3)))
     record(f"Transform xor_coord {S}^3 UInt16", n, 4 * n,
            lambda: capi.check(lib.vktb_transform_range1(ctypes.byref(dd), z3, l3, 0)))
+    # Flip (each visited voxel and its partner are read and written once) and Histogram (one read pass)
+    for axis, name in ((0, "X"), (1, "Y (mirrors y and z, as the reference)")):
+        record(f"Flip {name} {S}^3 UInt16", n, 4 * (n if S % 2 == 0 else n - S * S),
+               lambda: capi.check(lib.vktb_flip_range(ctypes.byref(dd), ctypes.byref(da), z3, l3, z3, axis)))
+    bins = ctypes.c_void_p()
+    capi.check(lib.vktb_alloc(ctypes.byref(bins), 256 * 8))
+    record(f"Histogram 256 bins {S}^3 UInt16", n, 2 * n,
+           lambda: capi.check(lib.vktb_histogram_range(ctypes.byref(da), z3, l3, bins, 256, None)))
+    capi.check(lib.vktb_free(bins))
     b.free(); d.free()
 
     # ---- Resample S^3 -> (S/2)^3 and -> (3S/2)^3, UInt16 (BASELINE config 3)

@@ -7,4 +7,6 @@ typedef struct { float x, y, z; } vktVec3f_t;
 typedef struct { int x, y, z; } vktVec3i_t;
 typedef struct { vktVec3f_t min, max; } vktBox3f_t;
 
+typedef enum { vktAxisX, vktAxisY, vktAxisZ } vktAxis;   /* reference include/c/vkt/linalg.h:94-99 */
+
 #endif

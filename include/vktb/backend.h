@@ -135,6 +135,23 @@ int vktb_resample_window_src_range(int filter, int32_t dst_z0, int32_t dst_z1, i
 int vktb_resample_window_src_range3(int filter, int32_t dst_z0, int32_t dst_z1, const int32_t dst_full[3],
                                     const int32_t src_full[3], int32_t* src_z0, int32_t* src_z1);
 
+/* ---- Flip and Histogram ----------------------------------------------------------
+ * FlipRange_cuda(StructuredVolume& dest, StructuredVolume& source, Vec3i first, Vec3i last, Vec3i dstOffset, Axis)
+ * (src/vkt/Flip_cuda.hpp:11-18); semantics of FlipRange_serial AS WRITTEN (src/vkt/Flip_serial.hpp:11-63): loops
+ * over [0, last-first) halved on the axis, partner index last-1-i, z mirrored when axis == Y (so Y mirrors y and z,
+ * Z mirrors nothing), raw bytes exchanged crosswise at + dst_offset.  axis 0/1/2 = vkt::Axis X/Y/Z.  dest may be
+ * source (in place, dst_offset 0).  Both volumes must have the same bytes per voxel. */
+int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                    const int32_t dst_offset[3], int axis);
+/* ComputeHistogramRange_cuda(StructuredVolume&, Histogram&, Vec3i first, Vec3i last)
+ * (src/vkt/Histogram_cuda.hpp:12-17); semantics of ComputeHistogramRange_serial (src/vkt/Histogram_serial.hpp:18-51):
+ * bins (DEVICE pointer, num_bins 64-bit counters = Histogram::getBinCounts() under the GPU policy) are zeroed, then
+ * bin (size_t)((value - lo) * (num_bins / (hi - lo))) is incremented per voxel, binary32 arithmetic.  Voxels whose
+ * index falls outside [0, num_bins) -- where the reference writes out of bounds -- are dropped; their number is
+ * returned through dropped_host when it is not NULL (this makes the call synchronous). */
+int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
+                         size_t num_bins, uint64_t* dropped_host);
+
 /* ---- Host-resident volumes, streamed ---------------------------------------------------------------
  * Same semantics and results as the entry points above, but every vktb_vol.data is a HOST pointer (pinned:
  * vktb_host_alloc or cudaHostRegister; pageable memory works without overlap).  The range is cut into z-slabs and

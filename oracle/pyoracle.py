@@ -82,6 +82,8 @@ class _Lib:
         f("transform_range1", ctypes.c_int, [p, I3, I3, ctypes.c_int])
         f("transform_range2", ctypes.c_int, [p, p, I3, I3, ctypes.c_int])
         f("resample", ctypes.c_int, [p, p, ctypes.c_int])
+        f("flip_range", ctypes.c_int, [p, p, I3, I3, I3, ctypes.c_int])
+        f("histogram_range", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p])
         if prefix == "vko_":
             f("resample_window", ctypes.c_int, [p, p, ctypes.c_int, ctypes.c_int32, I3, ctypes.c_int32, I3])
             f("synth_fill", None, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64])
@@ -120,6 +122,18 @@ class _Lib:
 
     def resample(self, dst: Vol, src: Vol, filter: int):
         assert self._resample(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter) == 0
+
+    def flip_range(self, dst: Vol, src: Vol, first, last, off=(0, 0, 0), axis: int = 0):
+        """src may be dst itself (in place)"""
+        assert self._flip_range(ctypes.byref(dst.c()), ctypes.byref(src.c()), I3(*first), I3(*last), I3(*off), axis) == 0
+
+    def histogram_range(self, vol: Vol, first, last, num_bins: int):
+        """(bins as uint64 array, voxels dropped because their bin index fell outside [0, num_bins))"""
+        bins = np.zeros(num_bins, np.uint64)
+        dropped = np.zeros(1, np.uint64)
+        assert self._histogram_range(ctypes.byref(vol.c()), I3(*first), I3(*last), bins.ctypes.data, num_bins,
+                                     dropped.ctypes.data) == 0
+        return bins, int(dropped[0])
 
     def resample_window(self, dst: Vol, src: Vol, filter: int, dz0: int, dst_full, sz0: int, src_full):
         assert self._resample_window(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter, dz0, I3(*dst_full),

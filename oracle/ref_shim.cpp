@@ -24,6 +24,8 @@
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Flip.hpp>
+#include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -246,6 +248,38 @@ int ref_resample(RefVol const* dst, RefVol const* src, int filter)
     Staged d(dst), s(src);
     vkt::Resample(d.vol, s.vol, filter ? vkt::FilterMode::Linear : vkt::FilterMode::Nearest);
     d.writeBack();
+    return 0;
+}
+
+// vkt::FlipRange (include/cpp/vkt/Flip.hpp -> src/vkt/Flip.cpp:94-104).  Same data pointer for dst and src = the
+// in-place call on ONE volume object.
+int ref_flip_range(RefVol const* dst, RefVol const* src, int32_t const* first, int32_t const* last,
+                   int32_t const* off, int axis)
+{
+    if (axis < 0 || axis > 2) return -1;
+    if (dst->data == src->data) {
+        Staged v(dst);
+        vkt::FlipRange(v.vol, v.vol, v3(first), v3(last), v3(off), (vkt::Axis)axis);
+        v.writeBack();
+        return 0;
+    }
+    Staged d(dst), s(src);
+    vkt::FlipRange(d.vol, s.vol, v3(first), v3(last), v3(off), (vkt::Axis)axis);
+    d.writeBack();
+    return 0;
+}
+
+// vkt::ComputeHistogramRange (include/cpp/vkt/Histogram.hpp -> src/vkt/Histogram.cpp:60-91).  The caller must keep
+// every voxel's bin inside [0, num_bins): the reference writes out of bounds otherwise.
+int ref_histogram_range(RefVol const* vol, int32_t const* first, int32_t const* last, uint64_t* bins, size_t numBins,
+                        uint64_t* dropped)
+{
+    Staged v(vol);
+    vkt::Histogram h(numBins);
+    vkt::ComputeHistogramRange(v.vol, h, v3(first), v3(last));
+    std::size_t* c = h.getBinCounts();
+    for (size_t i = 0; i < numBins; ++i) bins[i] = (uint64_t)c[i];
+    if (dropped) *dropped = 0;
     return 0;
 }
 

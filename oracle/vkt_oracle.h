@@ -54,6 +54,13 @@ int vko_resample_window(const vko_vol* dst, const vko_vol* src, int filter,
                         int32_t dz0, const int32_t dst_dims_full[3],
                         int32_t sz0, const int32_t src_dims_full[3]);
 
+/* axis 0/1/2 = vkt::Axis X/Y/Z; restated as written, see vkt_oracle.c */
+int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
+                   const int32_t off[3], int axis);
+/* bins[num_bins] (zeroed first); voxels whose bin index falls outside [0, num_bins) are counted in *dropped */
+int vko_histogram_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
+                        size_t num_bins, uint64_t* dropped);
+
 /* synthetic inputs of SURVEY.md 8(d): element i of a volume with seed s gets the low bits of
  * splitmix64(i ^ s*0x9E3779B97F4A7C15); Float32 gets (h>>40)*2^-24 in [0,1). */
 void vko_synth_fill(void* data, size_t first_voxel, size_t n_voxels, int format, uint64_t seed);

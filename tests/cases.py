@@ -65,6 +65,24 @@ def cases():
                     out.append((f"resample/{sfmt}/{dfmt}/{ddims}/{filt}", "resample",
                                 dict(sdims=(16, 12, 10), ddims=ddims, sfmt=sfmt, dfmt=dfmt, filt=filt,
                                      smap=(0.0, 1.0), dmap=(-1.0, 2.0))))
+    # --- Flip: all three axes (Y mirrors y and z, Z mirrors nothing -- as the reference is
+    # written), whole volume / range that ignores `first` / dstOffset, and in place
+    for fmt in (U8, U16, F32):
+        for axis in range(3):
+            out.append((f"flip/{fmt}/{axis}/whole", "flip",
+                        dict(sdims=(22, 9, 8), ddims=(22, 9, 8), fmt=fmt, first=(0, 0, 0), last=(22, 9, 8), off=(0, 0, 0),
+                             axis=axis, inplace=False)))
+            out.append((f"flip/{fmt}/{axis}/range", "flip",
+                        dict(sdims=(22, 9, 8), ddims=(25, 12, 10), fmt=fmt, first=(3, 1, 2), last=(20, 8, 7), off=(2, 3, 1),
+                             axis=axis, inplace=False)))
+            out.append((f"flip/{fmt}/{axis}/inplace", "flip",
+                        dict(sdims=(16, 9, 8), ddims=(16, 9, 8), fmt=fmt, first=(0, 0, 0), last=(16, 9, 8), off=(0, 0, 0),
+                             axis=axis, inplace=True)))
+    # --- Histogram: bins as uint64
+    for fmt, lo, hi in ((U8, 0.0, 1.0), (U16, 0.0, 1.0), (U16, -1000.0, 3000.0), (U32, 0.0, 1.0), (F32, 0.0, 1.0)):
+        for nb in (7, 256, 5000):
+            out.append((f"hist/{fmt}/{lo}/{nb}", "hist",
+                        dict(dims=(31, 14, 9), fmt=fmt, lo=lo, hi=hi, first=(1, 0, 2), last=(30, 13, 9), bins=nb)))
     # --- BASELINE config 1 (CLI pipeline on a 64^3 uint8 volume -> 32^3 uint16)
     out.append(("cli/config1", "cli1", dict()))
     return out
@@ -101,6 +119,19 @@ def run_case(lib, case) -> list[np.ndarray]:
         d = mk(p["ddims"], p["dfmt"], 3, *p["dmap"])
         lib.resample(d, s, p["filt"])
         return [d.a]
+    if kind == "flip":
+        s = mk(p["sdims"], p["fmt"], 1)
+        if p["inplace"]:
+            lib.flip_range(s, s, p["first"], p["last"], p["off"], p["axis"])
+            return [s.a]
+        d = mk(p["ddims"], p["fmt"], 3)
+        lib.flip_range(d, s, p["first"], p["last"], p["off"], p["axis"])
+        return [d.a]
+    if kind == "hist":
+        v = mk(p["dims"], p["fmt"], 1, p["lo"], p["hi"])
+        bins, dropped = lib.histogram_range(v, p["first"], p["last"], p["bins"])
+        assert dropped == 0, "case must stay inside the reference's defined behaviour"
+        return [bins]
     if kind == "cli1":
         # declare-sv 64^3 uint8 | fill 0.1 | fill-range 1 [0,8)^3 | resample --dims 32^3 uint16
         # (reference src/cli/main.cpp:402-442, 521-574, 701-740; the CLI resamples with Nearest, :734)

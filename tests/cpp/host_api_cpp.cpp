@@ -12,6 +12,8 @@
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Flip.hpp>
+#include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -120,6 +122,16 @@ int main(int argc, char** argv)
     CHECK(Resample(up, a, FilterMode::Linear));
     CHECK(Resample(down, a, FilterMode::Nearest));
 
+    // Flip (as the reference is written: Axis::Y mirrors y and z, Axis::Z mirrors nothing) and Histogram
+    StructuredVolume fx(X, Y, Z, DataFormat::UInt16), fy(64, 48, 44, DataFormat::UInt16), fz(a);
+    CHECK(Fill(fx, 0.f));
+    CHECK(Fill(fy, .5f));
+    CHECK(Flip(fx, a, Axis::X));
+    CHECK(FlipRange(fy, a, Vec3i{ 2, 1, 3 }, Vec3i{ 46, 39, 35 }, Vec3i{ 5, 4, 3 }, Axis::Y));
+    CHECK(Flip(fz, fz, Axis::Z));                       // in place
+    Histogram hist(300);
+    CHECK(ComputeHistogramRange(a, hist, 1, 2, 3, 47, 39, 35));
+
     // single-voxel accessors work under either policy
     sum.setValue(1, 2, 3, .75f);
     float back = sum.getValue(1, 2, 3);
@@ -128,6 +140,12 @@ int main(int argc, char** argv)
     SetThreadExecutionPolicy(cpu);
     save(sum, "out_sum.raw"); save(diff, "out_diff.raw"); save(prod, "out_prod.raw"); save(cpy, "out_cpy.raw");
     save(t1, "out_t1.raw"); save(t2, "out_t2.raw"); save(up, "out_up.raw"); save(down, "out_down.raw");
+    save(fx, "out_fx.raw"); save(fy, "out_fy.raw"); save(fz, "out_fz.raw");
+    {
+        FILE* f = std::fopen((g_dir + "/out_hist.raw").c_str(), "wb");
+        std::fwrite(hist.getBinCounts(), sizeof(std::size_t), hist.getNumBins(), f);   // migrates the bins back
+        std::fclose(f);
+    }
     std::printf("ok\n");
     return 0;
 }

@@ -64,6 +64,29 @@ class GpuLib:
         self._down(d, dst)
         s.free()
 
+    def flip_range(self, dst, src, first, last, off=(0, 0, 0), axis=0):
+        d = self._up(dst)
+        s = d if src is dst else self._up(src)
+        capi.check(self.lib.vktb_flip_range(ctypes.byref(d.desc()), ctypes.byref(s.desc()), I3(*first), I3(*last),
+                                            I3(*off), axis), "flip")
+        if s is not d:
+            s.free()
+        self._down(d, dst)
+
+    def histogram_range(self, vol, first, last, num_bins):
+        import numpy as np
+        v = self._up(vol)
+        bins = ctypes.c_void_p()
+        capi.check(self.lib.vktb_alloc(ctypes.byref(bins), num_bins * 8), "alloc bins")
+        dropped = ctypes.c_uint64(0)
+        capi.check(self.lib.vktb_histogram_range(ctypes.byref(v.desc()), I3(*first), I3(*last), bins, num_bins,
+                                                 ctypes.byref(dropped)), "histogram")
+        out = np.zeros(num_bins, np.uint64)
+        capi.check(self.lib.vktb_memcpy(out.ctypes.data, bins, num_bins * 8, capi.D2H), "download bins")
+        capi.check(self.lib.vktb_free(bins))
+        v.free()
+        return out, int(dropped.value)
+
     def resample_window(self, dst, src, filt, dz0, dst_full, sz0, src_full):
         d, s = self._up(dst), self._up(src)
         capi.check(self.lib.vktb_resample_window(ctypes.byref(d.desc()), ctypes.byref(s.desc()), filt, dz0,

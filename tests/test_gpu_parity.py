@@ -402,6 +402,51 @@ def test_hosted_rejects_bad_calls(gpu, hosted):
     assert capi.load().vktb_last_error()
 
 
+def test_flip_kernels(gpu):
+    """Pair kernel (X axis, unaligned rows) and the 128-bit row-swap kernel (Y / Z with 16-byte aligned rows)."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        for dims, first, last, off, ddims in (((128, 40, 24), (0, 0, 0), (128, 40, 24), (0, 0, 0), (128, 40, 24)),
+                                              ((128, 40, 24), (16, 3, 2), (112, 37, 21), (16, 2, 1), (160, 48, 30)),
+                                              ((67, 21, 10), (1, 2, 3), (66, 20, 9), (3, 1, 2), (80, 30, 20))):
+            for axis in range(3):
+                src = cases.mk(dims, fmt, 1)
+                a, b = cases.mk(ddims, fmt, 3), cases.mk(ddims, fmt, 3)
+                o.flip_range(a, src, first, last, off, axis)
+                gpu.flip_range(b, src, first, last, off, axis)
+                assert a.a.tobytes() == b.a.tobytes(), (fmt, dims, axis)
+                if dims == ddims:
+                    a, b = src.copy(), src.copy()
+                    o.flip_range(a, a, first, last, off, axis)
+                    gpu.flip_range(b, b, first, last, off, axis)
+                    assert a.a.tobytes() == b.a.tobytes(), ("in place", fmt, axis)
+    with pytest.raises(RuntimeError):
+        gpu.flip_range(cases.mk((8, 8, 8), po.UINT16, 1), cases.mk((8, 8, 8), po.UINT8, 1), (0, 0, 0), (8, 8, 8))
+
+
+def test_histogram_kernels(gpu):
+    """Shared-memory counters (bins fit in shared memory) and global atomics (they do not); dropped voxels."""
+    o = po.oracle()
+    for fmt, lo, hi in ((po.UINT8, 0.0, 1.0), (po.UINT16, 0.0, 1.0), (po.UINT16, -1000.0, 3000.0), (po.UINT32, 0.0, 1.0),
+                        (po.FLOAT32, 0.0, 1.0)):
+        v = cases.mk((200, 60, 33), fmt, 7, lo, hi)
+        for first, last in (((0, 0, 0), (200, 60, 33)), ((3, 5, 7), (199, 58, 30))):
+            for nb in (1, 64, 256, 4096, 24576, 100000):
+                ref, rd = o.histogram_range(v, first, last, nb)
+                got, gd = gpu.histogram_range(v, first, last, nb)
+                assert rd == gd == 0 and got.tobytes() == ref.tobytes(), (fmt, lo, first, nb)
+    # Float32 voxels outside the mapping, NaN and Inf: the reference indexes out of bounds, both sides drop and count
+    v = cases.mk((64, 32, 16), po.FLOAT32, 3, 0.25, 0.75)
+    flat = v.a.ravel()
+    flat[::101] = np.nan
+    flat[5::97] = np.inf
+    flat[7::89] = -3.0
+    ref, rd = o.histogram_range(v, (0, 0, 0), (64, 32, 16), 128)
+    got, gd = gpu.histogram_range(v, (0, 0, 0), (64, 32, 16), 128)
+    assert rd == gd and rd > 0 and got.tobytes() == ref.tobytes()
+    assert int(got.sum()) + gd == 64 * 32 * 16
+
+
 def test_empty_and_degenerate_ranges(gpu):
     v = cases.mk((9, 7, 5), po.UINT16, 3)
     before = v.a.copy()

@@ -79,6 +79,19 @@ def run_cpp(programs, policy, tmp):
     ref = po.empty((24, 20, 18), U8, -1.0, 2.0)
     o.resample(ref, a, po.NEAREST)
     assert raw(tmp / "out_down.raw", (24, 20, 18), np.uint8).tobytes() == ref.a.tobytes()
+    # Flip along X (whole), Y (range + offset into a 64x48x44 volume filled with .5), Z in place; histogram of a range
+    ref = po.empty(dims, U16)
+    o.flip_range(ref, a, (0, 0, 0), dims, (0, 0, 0), 0)
+    assert raw(tmp / "out_fx.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    ref = po.empty(cd, U16)
+    o.fill_range(ref, (0, 0, 0), cd, 0.5)
+    o.flip_range(ref, a, (2, 1, 3), (46, 39, 35), (5, 4, 3), 1)
+    assert raw(tmp / "out_fy.raw", cd, np.uint16).tobytes() == ref.a.tobytes()
+    ref = a.copy()
+    o.flip_range(ref, ref, (0, 0, 0), dims, (0, 0, 0), 2)
+    assert raw(tmp / "out_fz.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    bins, dropped = o.histogram_range(a, (1, 2, 3), (47, 39, 35), 300)
+    assert dropped == 0 and np.fromfile(tmp / "out_hist.raw", np.uint64).tobytes() == bins.tobytes()
     if policy == "gpu-stream":
         # the host-streaming prelude: same voxels as the migrating calls
         ref = po.empty(dims, U16)

@@ -122,6 +122,48 @@ def test_resample(sfmt, dfmt):
             assert same(a, b), (ddims, filt)
 
 
+@pytest.mark.parametrize("fmt", FMTS[:4])
+def test_flip(fmt):
+    """the restatement keeps the reference's quirks: `first` ignored, z mirrored on Axis::Y, nothing mirrored on Axis::Z"""
+    o, r = po.oracle(), po.reference()
+    for dims, ddims, first, last, off in (((9, 7, 6), (9, 7, 6), (0, 0, 0), (9, 7, 6), (0, 0, 0)),
+                                          ((12, 10, 8), (14, 13, 10), (2, 0, 1), (9, 7, 6), (1, 2, 1)),
+                                          ((8, 8, 8), (8, 8, 8), (1, 1, 1), (8, 8, 8), (0, 0, 0))):
+        for axis in range(3):
+            src = mk(dims, fmt, 1)
+            a, b = mk(ddims, fmt, 3), mk(ddims, fmt, 3)
+            o.flip_range(a, src, first, last, off, axis)
+            r.flip_range(b, src, first, last, off, axis)
+            assert a.a.tobytes() == b.a.tobytes(), (dims, axis)
+            if off == (0, 0, 0) and dims == ddims:
+                a, b = src.copy(), src.copy()
+                o.flip_range(a, a, first, last, off, axis)
+                r.flip_range(b, b, first, last, off, axis)
+                assert a.a.tobytes() == b.a.tobytes(), ("in place", dims, axis)
+    # the documented quirks, literally
+    v = po.Vol(np.arange(4 * 3 * 2, dtype=np.uint8).reshape(2, 3, 4), po.UINT8)
+    d = po.empty((4, 3, 2), po.UINT8)
+    r.flip_range(d, v, (0, 0, 0), (4, 3, 2), (0, 0, 0), 2)               # Axis::Z: lower half copied, nothing mirrored
+    assert d.a[0].tobytes() == v.a[0].tobytes() and not d.a[1].any()
+    d = po.empty((4, 3, 2), po.UINT8)
+    r.flip_range(d, v, (0, 0, 0), (4, 3, 2), (0, 0, 0), 1)               # Axis::Y: y and z mirrored together
+    assert d.a[1, 2, 0] == v.a[0, 0, 0] and d.a[0, 0, 0] == v.a[1, 2, 0]
+
+
+@pytest.mark.parametrize("fmt", FMTS[:4])
+def test_histogram(fmt):
+    o, r = po.oracle(), po.reference()
+    for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
+        if fmt == po.FLOAT32 and lo != 0.0:
+            continue                                   # Float32 voxels are not mapped on read: they would leave the bins
+        v = mk((25, 12, 10), fmt, 2, lo, hi)
+        for nb in (1, 16, 256, 4099):
+            ha, dropped = o.histogram_range(v, (1, 2, 3), (24, 11, 9), nb)
+            hb, _ = r.histogram_range(v, (1, 2, 3), (24, 11, 9), nb)
+            assert dropped == 0 and ha.tobytes() == hb.tobytes(), (lo, nb)
+            assert int(ha.sum()) == 23 * 9 * 6
+
+
 def test_resample_linear_equals_nearest_in_reference():
     """the reference's Linear mode is numerically nearest-floor."""
     r = po.reference()

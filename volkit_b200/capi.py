@@ -60,6 +60,8 @@ SIGNATURES = {
                                                       ctypes.c_int32, _P(ctypes.c_int32), _P(ctypes.c_int32)]),
     "vktb_resample_window_src_range3": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, I3, I3,
                                                        _P(ctypes.c_int32), _P(ctypes.c_int32)]),
+    "vktb_flip_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3, ctypes.c_int]),
+    "vktb_histogram_range": (ctypes.c_int, [_VP, I3, I3, ctypes.c_void_p, ctypes.c_size_t, _P(ctypes.c_uint64)]),
     "vktb_hosted_arith_range": (ctypes.c_int, [ctypes.c_int, _VP, _VP, _VP, I3, I3, I3]),
     "vktb_hosted_transform_range1": (ctypes.c_int, [_VP, I3, I3, ctypes.c_int]),
     "vktb_hosted_resample": (ctypes.c_int, [_VP, _VP, ctypes.c_int]),

@@ -140,6 +140,46 @@ int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
     return vktb_resample_window(dst, src, filter, 0, dst->dims, 0, src->dims);
 }
 
+int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                    const int32_t off[3], int axis)
+{
+    VolDesc dv, sv;
+    if (axis < 0 || axis > 2) return fail("vktb_flip_range: bad axis");
+    if (!first || !last || !off) return fail("vktb_flip_range: null range");
+    if (!toDesc("vktb_flip_range", dst, dv) || !toDesc("vktb_flip_range", src, sv)) return -1;
+    if (bytesPerVoxel(dv.format) != bytesPerVoxel(sv.format))
+        return fail("vktb_flip_range: dest and source must have the same bytes per voxel (raw bytes are exchanged)");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_flip_range", launchFlip(c, dv, sv, first, last, off, axis));
+}
+
+int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
+                         size_t numBins, uint64_t* droppedHost)
+{
+    VolDesc v;
+    if (!first || !last || !bins) return fail("vktb_histogram_range: null argument");
+    if (numBins == 0 || numBins > ((size_t)1 << 24)) return fail("vktb_histogram_range: numBins must be in [1, 2^24]");
+    if (!toDesc("vktb_histogram_range", vol, v)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    cudaStream_t s = currentStream(d);
+    LaunchCtx c{ s, d->smCount };
+    unsigned long long* dropped = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&dropped, sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return fail("vktb_histogram_range", e);
+    e = launchHistogram(c, v, first, last, reinterpret_cast<unsigned long long*>(bins), numBins, dropped);
+    if (e == cudaSuccess && droppedHost) {
+        unsigned long long h = 0;
+        e = cudaMemcpyAsync(&h, dropped, sizeof(h), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        *droppedHost = h;
+    }
+    cudaFreeAsync(dropped, s);
+    return finish("vktb_histogram_range", e);
+}
+
 // Host-side slab planner: the reference's own coordinate expression (Resample_serial.hpp:60-62) evaluated in
 // binary32; it is monotone in its argument.
 static int32_t srcCoordHost(int32_t d, int32_t D, int32_t S)

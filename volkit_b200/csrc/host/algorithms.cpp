@@ -10,6 +10,8 @@
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Flip.hpp>
+#include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -267,5 +269,78 @@ namespace
                 vktb_vol d = host::describe(dst), s = host::describe(src);
                 return vktb_resample(&d, &s, filter);
             });
+    }
+    //---------------------------------------------------------------------------------------------------------
+    // Flip (reference src/vkt/Flip.cpp:26-117)
+    //---------------------------------------------------------------------------------------------------------
+    Error FlipRange(StructuredVolume& dest, StructuredVolume& source, Vec3i first, Vec3i last, Vec3i dstOffset, Axis axis)
+    {
+        if (dest.getBytesPerVoxel() != source.getBytesPerVoxel()) return InvalidValue;
+        return dispatch("FlipRange",
+            [&] { host::flipRange(viewOf(dest), viewOf(source), first, last, dstOffset, (int)axis); },
+            [&] {
+                vktb_vol d = host::describe(dest), s = host::describe(source);
+                int32_t f[3], l[3], o[3];
+                toArray(first, f); toArray(last, l); toArray(dstOffset, o);
+                return vktb_flip_range(&d, &s, f, l, o, (int)axis);
+            });
+    }
+
+    Error FlipRange(StructuredVolume& dest, StructuredVolume& source, Vec3i first, Vec3i last, Axis axis)
+    {
+        return FlipRange(dest, source, first, last, Vec3i{ 0, 0, 0 }, axis);
+    }
+
+    Error FlipRange(StructuredVolume& dest, StructuredVolume& source, int32_t firstX, int32_t firstY, int32_t firstZ,
+                    int32_t lastX, int32_t lastY, int32_t lastZ, Axis axis)
+    {
+        return FlipRange(dest, source, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ }, Vec3i{ 0, 0, 0 }, axis);
+    }
+
+    Error FlipRange(StructuredVolume& dest, StructuredVolume& source, int32_t firstX, int32_t firstY, int32_t firstZ,
+                    int32_t lastX, int32_t lastY, int32_t lastZ, int32_t dstOffsetX, int32_t dstOffsetY, int32_t dstOffsetZ,
+                    Axis axis)
+    {
+        return FlipRange(dest, source, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ },
+                         Vec3i{ dstOffsetX, dstOffsetY, dstOffsetZ }, axis);
+    }
+
+    Error Flip(StructuredVolume& dest, StructuredVolume& source, Axis axis)
+    {
+        return FlipRange(dest, source, Vec3i{ 0, 0, 0 }, dest.getDims(), Vec3i{ 0, 0, 0 }, axis);   // dest dims: Flip.cpp:28-36
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Histogram (reference src/vkt/Histogram.cpp:23-84)
+    //---------------------------------------------------------------------------------------------------------
+    Histogram::Histogram(std::size_t numBins) { resize(numBins); }
+    std::size_t Histogram::getNumBins() const { return size_; }
+    std::size_t* Histogram::getBinCounts() { migrate(); return data_; }
+
+    Error ComputeHistogramRange(StructuredVolume& volume, Histogram& histogram, Vec3i first, Vec3i last)
+    {
+        static_assert(sizeof(std::size_t) == sizeof(uint64_t), "bins are 64-bit counters");
+        return dispatch("ComputeHistogramRange",
+            [&] {
+                host::View v = viewOf(volume);
+                host::histogramRange(v, first, last, histogram.getBinCounts(), histogram.getNumBins());
+            },
+            [&] {
+                vktb_vol v = host::describe(volume);
+                int32_t f[3], l[3];
+                toArray(first, f); toArray(last, l);
+                return vktb_histogram_range(&v, f, l, (uint64_t*)histogram.getBinCounts(), histogram.getNumBins(), nullptr);
+            });
+    }
+
+    Error ComputeHistogramRange(StructuredVolume& volume, Histogram& histogram, int32_t firstX, int32_t firstY,
+                                int32_t firstZ, int32_t lastX, int32_t lastY, int32_t lastZ)
+    {
+        return ComputeHistogramRange(volume, histogram, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ });
+    }
+
+    Error ComputeHistogram(StructuredVolume& volume, Histogram& histogram)
+    {
+        return ComputeHistogramRange(volume, histogram, Vec3i{ 0, 0, 0 }, volume.getDims());
     }
 } // vkt

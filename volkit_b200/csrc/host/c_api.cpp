@@ -4,6 +4,7 @@
 #include <vkt/Copy.h>
 #include <vkt/ExecutionPolicy.h>
 #include <vkt/Fill.h>
+#include <vkt/Flip.h>
 #include <vkt/Memory.h>
 #include <vkt/Resample.h>
 #include <vkt/StructuredVolume.h>
@@ -14,6 +15,7 @@
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Flip.hpp>
 #include <vkt/Memory.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
@@ -129,6 +131,17 @@ vktError vktCopyRangeSV(vktStructuredVolume dst, vktStructuredVolume src, int32_
                         int32_t ly, int32_t lz, int32_t ox, int32_t oy, int32_t oz)
 {
     return (vktError)vkt::CopyRange(dst->volume, src->volume, fx, fy, fz, lx, ly, lz, ox, oy, oz);
+}
+
+//--- Flip (reference src/vkt/Flip.cpp:127-167) -------------------------------------------------------------------
+vktError vktFlipSV(vktStructuredVolume dest, vktStructuredVolume source, vktAxis axis)
+{
+    return (vktError)vkt::Flip(dest->volume, source->volume, (vkt::Axis)axis);
+}
+vktError vktFlipRangeSV(vktStructuredVolume dest, vktStructuredVolume source, int32_t fx, int32_t fy, int32_t fz, int32_t lx,
+                        int32_t ly, int32_t lz, int32_t ox, int32_t oy, int32_t oz, vktAxis axis)
+{
+    return (vktError)vkt::FlipRange(dest->volume, source->volume, fx, fy, fz, lx, ly, lz, ox, oy, oz, (vkt::Axis)axis);
 }
 
 //--- Arithmetic ------------------------------------------------------------------------------------------------

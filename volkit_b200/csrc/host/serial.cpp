@@ -140,5 +140,38 @@ namespace host
             }
         }
     }
+    // reference src/vkt/Flip_serial.hpp:11-63, as written (first ignored, z mirrored on Axis::Y, Axis::Z mirrors nothing)
+    void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i off, int axis)
+    {
+        int32_t rx = last.x - first.x, ry = last.y - first.y, rz = last.z - first.z;
+        if (axis == 0) rx >>= 1; else if (axis == 1) ry >>= 1; else rz >>= 1;
+        for (int32_t z = 0; z < rz; ++z)
+            for (int32_t y = 0; y < ry; ++y)
+                for (int32_t x = 0; x < rx; ++x) {
+                    const int32_t xx = axis == 0 ? last.x - 1 - x : x;
+                    const int32_t yy = axis == 1 ? last.y - 1 - y : y;
+                    const int32_t zz = axis == 1 ? last.z - 1 - z : z;
+                    uint8_t v1[8], v2[8];
+                    std::memcpy(v1, src.data + src.offset(x, y, z), src.bpv);
+                    std::memcpy(v2, src.data + src.offset(xx, yy, zz), src.bpv);
+                    std::memcpy(dst.data + dst.offset(off.x + x, off.y + y, off.z + z), v2, dst.bpv);
+                    std::memcpy(dst.data + dst.offset(off.x + xx, off.y + yy, off.z + zz), v1, dst.bpv);
+                }
+    }
+
+    // reference src/vkt/Histogram_serial.hpp:18-51; indices outside [0, numBins) are skipped (the reference's UB)
+    void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins)
+    {
+        for (std::size_t i = 0; i < numBins; ++i) bins[i] = 0;
+        const float scale = (float)numBins / (vol.hi - vol.lo);
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    const float val = unmapVoxel(vol.data + vol.offset(x, y, z), vol.format, vol.lo, vol.hi);
+                    const float b = (val - vol.lo) * scale;
+                    if (b >= 0.0f && b < (float)numBins) bins[(std::size_t)b]++;
+                    else if (b > -1.0f && b < 0.0f) bins[0]++;
+                }
+    }
 } // host
 } // vkt

@@ -34,5 +34,7 @@ namespace host
     void transformRange(View v, Vec3i first, Vec3i last, TransformUnaryOp op);
     void transformRange(View v1, View v2, Vec3i first, Vec3i last, TransformBinaryOp op);
     void resample(View dst, View src, int filter);
+    void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset, int axis);
+    void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins);
 } // host
 } // vkt
