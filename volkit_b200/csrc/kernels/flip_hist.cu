@@ -76,12 +76,54 @@ flipRowsVecKernel(FlipParams p, int vecsPerRow)
     }
 }
 
+// 16 bytes with their BPV-sized elements in reverse order
+template <int BPV>
+__device__ __forceinline__ uint4 reverseElems(const uint4& v)
+{
+    if (BPV == 4) return make_uint4(v.w, v.z, v.y, v.x);
+    const unsigned sel = BPV == 2 ? 0x1032u : 0x0123u;
+    return make_uint4(__byte_perm(v.w, 0u, sel), __byte_perm(v.z, 0u, sel), __byte_perm(v.y, 0u, sel), __byte_perm(v.x, 0u, sel));
+}
+
+// x mirrored, row starts / pitches / last.x * bpv multiples of 16 bytes: a 16-byte chunk of visited voxels and the
+// 16-byte chunk of their partners are exchanged with their elements reversed; the (rx mod V) voxels next to the
+// middle go through the scalar path
+template <int BPV>
+__global__ void __launch_bounds__(kThreads)
+flipXVecKernel(FlipParams p, int vecsPerRow)
+{
+    constexpr int V = 16 / BPV;
+    const long long rows = (long long)p.ry * p.rz;
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+        const int z = (int)(r / p.ry), y = (int)(r - (long long)z * p.ry);
+        const uint8_t* srow = p.s + y * p.sPitchY + z * p.sPitchZ;
+        uint8_t* drow = p.d + y * p.dPitchY + z * p.dPitchZ;
+        for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < vecsPerRow; v += gridDim.x * blockDim.x) {
+            const long long lo = (long long)v * 16;                              // voxels x = v*V .. v*V + V-1
+            const long long hi = ((long long)p.lx + 1 - (long long)(v + 1) * V) * BPV;   // partners lx - x, ascending
+            const uint4 a = ldPlain(srow + lo), b = ldPlain(srow + hi);
+            stStream(drow + lo, reverseElems<BPV>(b));
+            stStream(drow + hi, reverseElems<BPV>(a));
+        }
+        for (int x = vecsPerRow * V + blockIdx.x * blockDim.x + threadIdx.x; x < p.rx; x += gridDim.x * blockDim.x) {
+            const int xx = p.lx - x;
+            const uint32_t v1 = loadRaw(srow + (long long)x * BPV, BPV), v2 = loadRaw(srow + (long long)xx * BPV, BPV);
+            storeRaw(drow + (long long)x * BPV, BPV, v2);
+            storeRaw(drow + (long long)xx * BPV, BPV, v1);
+        }
+    }
+}
+
 template <int BPV>
 cudaError_t launchFlipBpv(const LaunchCtx& c, const FlipParams& p, int axis, bool vec)
 {
     const long long rows = (long long)p.ry * p.rz;
     const unsigned gy = (unsigned)(rows > 65535 ? 65535 : rows);
-    if (vec) {
+    if (vec && axis == 0) {
+        const int vecs = (int)((long long)p.rx * BPV / 16);
+        dim3 grid((unsigned)((vecs + kThreads) / kThreads), gy, 1);
+        flipXVecKernel<BPV><<<grid, kThreads, 0, c.stream>>>(p, vecs);
+    } else if (vec) {
         const int vecs = (int)((long long)p.rx * BPV / 16);
         dim3 grid((unsigned)((vecs + kThreads - 1) / kThreads), gy, 1);
         if (axis == 1) flipRowsVecKernel<1><<<grid, kThreads, 0, c.stream>>>(p, vecs);
@@ -106,88 +148,139 @@ struct HistParams
     int format;
     Mapping m;
     float scale;             // (float)numBins / (hi - lo), binary32 (host)
-    float binsF;             // (float)numBins
     unsigned long long* bins;
     unsigned long long* dropped;
     unsigned numBins;
+    size_t n;                // voxels of the range
+    int flat;                // the range is one contiguous run
 };
 
+// bin index of an unmapped value, or -1 where the reference would write out of bounds.  cvt.rzi saturates and
+// truncates toward zero like the (size_t) cast does for in-range values: b in (-1, 0) -> 0, b <= -1 -> negative,
+// b >= numBins -> >= numBins; NaN converts to 0 and is rejected separately.
+template <int F>
 __device__ __forceinline__ int histBin(float val, const HistParams& p)
 {
     const float b = __fmul_rn(__fsub_rn(val, p.m.lo), p.scale);
-    if (b >= 0.0f && b < p.binsF) return (int)b;          // truncation toward zero, as the (size_t) cast
-    if (b > -1.0f && b < 0.0f) return 0;
-    return -1;                                            // the reference would write out of bounds (NaN included)
+    const int i = __float2int_rz(b);
+    if (b != b) return -1;                                // Float32 NaN voxels, or a degenerate mapping (hi == lo)
+    return (unsigned)i < p.numBins ? i : -1;
 }
 
-template <int F, bool SHARED>
+// SHARED: per-CTA 32-bit counters in shared memory, REPL copies of every bin laid out as sh[bin * REPL + lane % REPL].
+// With REPL = 32 lane l only ever touches bank l: no bank conflicts and no same-address serialisation inside a warp
+// whatever the data looks like (a warp of equal voxels would otherwise serialise 32-fold).
+// FLAT: the range is one contiguous run of p.n voxels (grid-stride over 128-bit vectors, four in flight); otherwise
+// one CTA walks rows.
+template <int F, bool IDENT, bool SHARED, bool FLAT>
 __global__ void __launch_bounds__(kThreads)
-histogramKernel(HistParams p)
+histogramKernel(HistParams p, int replShift)
 {
     constexpr int BPV = bytesPerVoxel(F);
     constexpr int V = 16 / BPV;
     extern __shared__ uint32_t sh[];
+    const unsigned nCounters = p.numBins << replShift;
+    const unsigned myCopy = threadIdx.x & ((1u << replShift) - 1u);
     if (SHARED) {
-        for (unsigned i = threadIdx.x; i < p.numBins; i += blockDim.x) sh[i] = 0u;
+        for (unsigned i = threadIdx.x; i < nCounters; i += blockDim.x) sh[i] = 0u;
         __syncthreads();
     }
     unsigned drops = 0;
     auto count = [&](uint32_t raw) {
-        const int b = histBin(unmapVoxel<F, false>(raw, p.m), p);
+        const int b = histBin<F>(unmapVoxel<F, IDENT>(raw, p.m), p);
         if (b < 0) { ++drops; return; }
-        if (SHARED) atomicAdd(&sh[b], 1u);
+        if (SHARED) atomicAdd(&sh[((unsigned)b << replShift) + myCopy], 1u);
         else atomicAdd(&p.bins[b], 1ull);
     };
-    const long long rows = (long long)p.ny * p.nz;
-    for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
-        const int z = (int)(r / p.ny), y = (int)(r - (long long)z * p.ny);
-        const uint8_t* row = p.s + y * p.pitchY + z * p.pitchZ;
-        // scalar head up to the first 16-byte boundary, 128-bit body, scalar tail
-        int head = (int)(((16u - (reinterpret_cast<uintptr_t>(row) & 15u)) & 15u) / BPV);
-        if (head > p.nx) head = p.nx;
-        const int nvec = (p.nx - head) / V;
-        const int tail0 = head + nvec * V;
-        const uint8_t* body = row + (long long)head * BPV;
-        for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
-            const uint4 q = ldStream(body + v * 16LL);
+    auto countVec = [&](const uint4& q) {
 #pragma unroll
-            for (int i = 0; i < V; ++i) count(vecGet<BPV>(q, i));
+        for (int i = 0; i < V; ++i) count(vecGet<BPV>(q, i));
+    };
+    if (FLAT) {
+        const size_t n = p.n;
+        size_t head = ((16u - (reinterpret_cast<uintptr_t>(p.s) & 15u)) & 15u) / BPV;
+        if (head > n) head = n;
+        const size_t nvec = (n - head) / V, tail0 = head + nvec * V;
+        const uint8_t* body = p.s + head * BPV;
+        const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+        size_t i = tid;
+        for (; i + 3 * stride < nvec; i += 4 * stride) {
+            const uint4 q0 = ldStream(body + i * 16), q1 = ldStream(body + (i + stride) * 16);
+            const uint4 q2 = ldStream(body + (i + 2 * stride) * 16), q3 = ldStream(body + (i + 3 * stride) * 16);
+            countVec(q0); countVec(q1); countVec(q2); countVec(q3);
         }
-        const int nEdge = head + (p.nx - tail0);
-        for (int e = threadIdx.x; e < nEdge; e += blockDim.x) {
-            const int x = e < head ? e : tail0 + (e - head);
-            count(loadRaw(row + (long long)x * BPV, BPV));
+        for (; i < nvec; i += stride) countVec(ldStream(body + i * 16));
+        const size_t nEdge = head + (n - tail0);
+        for (size_t e = tid; e < nEdge; e += stride) {
+            const size_t k = e < head ? e : tail0 + (e - head);
+            count(loadRaw(p.s + k * BPV, BPV));
+        }
+    } else {
+        const long long rows = (long long)p.ny * p.nz;
+        for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+            const int z = (int)(r / p.ny), y = (int)(r - (long long)z * p.ny);
+            const uint8_t* row = p.s + y * p.pitchY + z * p.pitchZ;
+            // scalar head up to the first 16-byte boundary, 128-bit body (two vectors in flight), scalar tail
+            int head = (int)(((16u - (reinterpret_cast<uintptr_t>(row) & 15u)) & 15u) / BPV);
+            if (head > p.nx) head = p.nx;
+            const int nvec = (p.nx - head) / V;
+            const int tail0 = head + nvec * V;
+            const uint8_t* body = row + (long long)head * BPV;
+            int v = threadIdx.x;
+            for (; v + (int)blockDim.x < nvec; v += 2 * blockDim.x) {
+                const uint4 q0 = ldStream(body + v * 16LL), q1 = ldStream(body + (v + (int)blockDim.x) * 16LL);
+                countVec(q0); countVec(q1);
+            }
+            for (; v < nvec; v += blockDim.x) countVec(ldStream(body + v * 16LL));
+            const int nEdge = head + (p.nx - tail0);
+            for (int e = threadIdx.x; e < nEdge; e += blockDim.x) {
+                const int x = e < head ? e : tail0 + (e - head);
+                count(loadRaw(row + (long long)x * BPV, BPV));
+            }
         }
     }
     if (drops) atomicAdd(p.dropped, (unsigned long long)drops);
     if (SHARED) {
         __syncthreads();
-        for (unsigned i = threadIdx.x; i < p.numBins; i += blockDim.x)
-            if (sh[i]) atomicAdd(&p.bins[i], (unsigned long long)sh[i]);
+        for (unsigned i = threadIdx.x; i < p.numBins; i += blockDim.x) {
+            unsigned long long sum = 0;
+            for (unsigned k = 0; k < (1u << replShift); ++k) sum += sh[(i << replShift) + ((k + i) & ((1u << replShift) - 1u))];
+            if (sum) atomicAdd(&p.bins[i], sum);
+        }
     }
+}
+
+template <int F, bool IDENT, bool SHARED>
+cudaError_t launchHistK(const LaunchCtx& c, const HistParams& p, unsigned grid, size_t shBytes, int replShift)
+{
+    auto k = p.flat ? histogramKernel<F, IDENT, SHARED, true> : histogramKernel<F, IDENT, SHARED, false>;
+    if (shBytes > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shBytes);
+        if (e != cudaSuccess) return e;
+    }
+    k<<<grid, kThreads, shBytes, c.stream>>>(p, replShift);
+    countLaunch();
+    return cudaGetLastError();
 }
 
 template <int F>
 cudaError_t launchHistF(const LaunchCtx& c, const HistParams& p)
 {
     const long long rows = (long long)p.ny * p.nz;
+    constexpr size_t kMaxShared = 96 * 1024;
+    const bool shared = (size_t)p.numBins * 4 <= kMaxShared;
+    // as many copies per bin as fit in 32 KiB (so several CTAs stay resident), at most one per lane
+    int replShift = 0;
+    while (shared && replShift < 5 && ((size_t)p.numBins * 4 << (replShift + 1)) <= 32 * 1024) ++replShift;
+    const size_t shBytes = shared ? ((size_t)p.numBins * 4 << replShift) : 0;
     // persistent: a few CTAs per SM, every CTA flushes its shared counters once
-    long long grid = (long long)c.smCount * 8;
-    if (grid > rows) grid = rows;
-    const size_t shBytes = (size_t)p.numBins * 4;
-    const bool shared = shBytes <= 96 * 1024;
-    if (shared) {
-        auto k = histogramKernel<F, true>;
-        if (shBytes > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shBytes);
-            if (e != cudaSuccess) return e;
-        }
-        k<<<(unsigned)grid, kThreads, shBytes, c.stream>>>(p);
-    } else {
-        histogramKernel<F, false><<<(unsigned)grid, kThreads, 0, c.stream>>>(p);
-    }
-    countLaunch();
-    return cudaGetLastError();
+    long long grid = (long long)c.smCount * 6;
+    if (!p.flat && grid > rows) grid = rows;
+    const bool ident = p.m.identity != 0;
+    if (shared) return ident ? launchHistK<F, true, true>(c, p, (unsigned)grid, shBytes, replShift)
+                             : launchHistK<F, false, true>(c, p, (unsigned)grid, shBytes, replShift);
+    return ident ? launchHistK<F, true, false>(c, p, (unsigned)grid, 0, 0)
+                 : launchHistK<F, false, false>(c, p, (unsigned)grid, 0, 0);
 }
 
 } // namespace
@@ -206,9 +299,12 @@ cudaError_t launchFlip(const LaunchCtx& c, const VolDesc& dst, const VolDesc& sr
     p.dPitchY = (long long)dst.dims[0] * bpv; p.dPitchZ = p.dPitchY * dst.dims[1];
     p.s = src.data;
     p.d = dst.data + voxelIndex(dst, off[0], off[1], off[2]) * bpv;
-    const bool vec = axis != 0 && ((long long)p.rx * bpv) % 16 == 0
-                  && ((reinterpret_cast<uintptr_t>(p.s) | reinterpret_cast<uintptr_t>(p.d)) & 15u) == 0
-                  && ((p.sPitchY | p.sPitchZ | p.dPitchY | p.dPitchZ) & 15) == 0;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(p.s) | reinterpret_cast<uintptr_t>(p.d)) & 15u) == 0
+                      && ((p.sPitchY | p.sPitchZ | p.dPitchY | p.dPitchZ) & 15) == 0;
+    // rows swap whole (x not mirrored) when the row length is a multiple of 16 bytes; mirrored x needs the partner
+    // chunks [last.x - (v+1)V, last.x - vV) on 16-byte boundaries too
+    const bool vec = aligned && (axis != 0 ? ((long long)p.rx * bpv) % 16 == 0
+                                           : ((long long)last[0] * bpv) % 16 == 0 && (long long)p.rx * bpv >= 16);
     switch (bpv) {
     case 1: return launchFlipBpv<1>(c, p, axis, vec);
     case 2: return launchFlipBpv<2>(c, p, axis, vec);
@@ -237,8 +333,10 @@ cudaError_t launchHistogram(const LaunchCtx& c, const VolDesc& vol, const int32_
         volatile float scale = (float)numBins / range;
         p.scale = scale;
     }
-    p.binsF = (float)numBins;
     p.bins = bins; p.dropped = droppedDev; p.numBins = (unsigned)numBins;
+    p.n = (size_t)p.nx * p.ny * p.nz;
+    Range g; g.nx = p.nx; g.ny = p.ny; g.nz = p.nz; g.x0 = first[0]; g.y0 = first[1]; g.z0 = first[2];
+    p.flat = contiguous(vol, g) ? 1 : 0;
     switch (vol.format) {
     case F_U8:    return launchHistF<F_U8>(c, p);
     case F_U16:   return launchHistF<F_U16>(c, p);
