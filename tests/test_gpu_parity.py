@@ -435,6 +435,19 @@ def test_histogram_kernels(gpu):
                 ref, rd = o.histogram_range(v, first, last, nb)
                 got, gd = gpu.histogram_range(v, first, last, nb)
                 assert rd == gd == 0 and got.tobytes() == ref.tobytes(), (fmt, lo, first, nb)
+    # contiguous runs of >= 2^20 voxels (flat path); odd row length + plane offset misalign the run's start; a constant
+    # volume sends every voxel to one bin
+    for fmt, lo, hi in ((po.UINT8, 0.0, 1.0), (po.UINT16, 0.0, 1.0), (po.UINT16, -1000.0, 3000.0), (po.FLOAT32, 0.0, 1.0)):
+        v = cases.mk((251, 130, 41), fmt, 9, lo, hi)
+        for first, last in (((0, 0, 0), (251, 130, 41)), ((0, 0, 3), (251, 130, 40))):
+            for nb in (1, 100, 256):
+                ref, rd = o.histogram_range(v, first, last, nb)
+                got, gd = gpu.histogram_range(v, first, last, nb)
+                assert rd == gd == 0 and got.tobytes() == ref.tobytes(), ("flat", fmt, lo, first, nb)
+    v = po.Vol(np.full((64, 128, 256), 40000, np.uint16), po.UINT16)
+    ref, _ = o.histogram_range(v, (0, 0, 0), (256, 128, 64), 256)
+    got, _ = gpu.histogram_range(v, (0, 0, 0), (256, 128, 64), 256)
+    assert got.tobytes() == ref.tobytes() and int(got.max()) == 256 * 128 * 64
     # Float32 voxels outside the mapping, NaN and Inf: the reference indexes out of bounds, both sides drop and count
     v = cases.mk((64, 32, 16), po.FLOAT32, 3, 0.25, 0.75)
     flat = v.a.ravel()
