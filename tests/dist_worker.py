@@ -145,6 +145,26 @@ def main():
             torch.cuda.synchronize()
         check_slab(d, ref, f"arith {op} {first} {last} {off}")
 
+    # Histogram: per-rank bins + one SUM all-reduce (the only collective on the path)
+    for hfmt, lo, hi in ((po.UINT16, 0.0, 1.0), (po.UINT8, -1.0, 2.0)):
+        whole = po.Vol(po.synth((33, 12, 21), hfmt, 4), hfmt, lo, hi)
+        hv = sharded.ShardedVolume(torch, (33, 12, 21), hfmt, rank, world, lo, hi, device=device)
+        fill_slab(hv, whole)
+        for first, last, nb in (((0, 0, 0), (33, 12, 21), 256), ((2, 1, 5), (30, 11, 17), 37)):
+            ref_bins, dropped = o.histogram_range(whole, first, last, nb)
+            assert dropped == 0
+
+            def cpu_hist(desc, f, l, bins_ptr, n):
+                b, _ = o.histogram_range(as_vol(desc, hfmt, (lo, hi)), f, l, n)
+                ctypes.memmove(bins_ptr, b.ctypes.data, n * 8)
+
+            got = sharded.histogram_sharded(hv, first, last, nb, dist, compute=None if gpu else cpu_hist)
+            if gpu:
+                torch.cuda.synchronize()
+            if got.cpu().numpy().astype(np.uint64).tobytes() != ref_bins.tobytes():
+                print(f"rank {rank}: MISMATCH in histogram {hfmt} {first} {last} {nb}", flush=True)
+                sys.exit(1)
+
     # elementwise ops need no exchange: slabs tile the volume exactly
     Z = 23
     covered = sorted(z for r in range(world) for z in range(*sharded.slab_range(Z, world, r)))

@@ -267,3 +267,27 @@ def arith_range_sharded(op: int, dst: ShardedVolume, s1: ShardedVolume, s2: Shar
                                        f, l, o)
     recv = sum((t.z1 - t.z0) for t in transfers if t.dst_rank == dst.rank)
     return recv * (s1.plane_bytes + (0 if s2 is s1 else s2.plane_bytes))
+
+
+# ---- Histogram of a sharded volume: the one real exchange step of the path -- a SUM all-reduce of the bins -------------
+
+def _cabi_histogram_range(vol_desc, first, last, bins_ptr, num_bins):
+    lib = capi.load()
+    capi.check(lib.vktb_histogram_range(ctypes.byref(vol_desc), capi.I3(*first), capi.I3(*last), bins_ptr, num_bins, None),
+               "vktb_histogram_range")
+
+
+def histogram_sharded(vol: ShardedVolume, first, last, num_bins: int, dist, compute=None):
+    """ComputeHistogramRange (reference src/vkt/Histogram_serial.hpp:18-51) of a z-slab sharded volume: every rank
+    counts the planes of [first, last) it owns into its own 64-bit bins (int64 tensor on the volume's device), then
+    one all-reduce (NCCL on GPUs, SUM) gives every rank the global histogram.  Returns the bins tensor."""
+    torch = vol.torch
+    bins = torch.zeros(num_bins, dtype=torch.int64, device=vol.storage.device)
+    z0, z1 = max(first[2], vol.z0), min(last[2], vol.z1)
+    if z1 > z0 and last[0] > first[0] and last[1] > first[1]:
+        f = (first[0], first[1], z0 - vol.z0)
+        l = (last[0], last[1], z1 - vol.z0)
+        (compute or _cabi_histogram_range)(vol.desc(), f, l, bins.data_ptr(), num_bins)
+    if dist is not None and vol.world > 1:
+        dist.all_reduce(bins, op=dist.ReduceOp.SUM)
+    return bins
