@@ -57,3 +57,16 @@ def test_synth_numpy_twin():
         a = po.synth(1000, fmt, 7, first_voxel=123)
         b = po.synth_numpy(1000, fmt, 7, first_voxel=123)
         assert a.tobytes() == b.tobytes()
+
+
+def test_u8_identity_round_trip():
+    """map(unmap(v)) == v for every UInt8 and UInt16 value under the default mapping: the one-tap Resample kernels move
+    raw voxels for these formats instead of running them through the codec."""
+    libs = [po.oracle()] + ([po.reference()] if po.have_reference() else [])
+    for lib in libs:
+        for v in range(256):
+            raw = bytes([v])
+            assert lib.map_voxel(lib.unmap_voxel(raw, po.UINT8), po.UINT8) == raw, v
+        for v in list(range(0, 65536, 257)) + [1, 2, 65534, 65535, 32767, 32768]:
+            raw = int(v).to_bytes(2, "little")
+            assert lib.map_voxel(lib.unmap_voxel(raw, po.UINT16), po.UINT16) == raw, v

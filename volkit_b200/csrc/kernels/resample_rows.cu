@@ -301,8 +301,12 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     int R = (int)(16384 / srcRow);
     if (R < 1) R = 1;
     if (R > 8) R = 8;
+    // measured (profiles/r01_notes.md: sweeps over rows x stages x grid, repeated on one box): up-sampling runs best with
+    // 2 rows per item and 2 stages (small CTAs, 8 resident per SM); down-sampling with one 16 KiB item and 3 stages
+    const bool up = D[0] > S[0];
+    if (up && R > 2) R = 2;
     p.R = envInt("VKTB_RS_ROWS", R, 1, 8);
-    p.stages = envInt("VKTB_RS_STAGES", 3, 2, kMaxStages);
+    p.stages = envInt("VKTB_RS_STAGES", up ? 2 : 3, 2, kMaxStages);
     const size_t smemBytes = (size_t)p.stages * p.R * srcRow;
 
     // plan tables: header, x map, y runs, z runs
@@ -330,6 +334,10 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     if (src.format == dst.format && identity && src.format == F_U16) {
         // unmap: raw * 2^-16 (exact); map: t * 65536 (exact), truncation of an integer-valued float: raw -> raw
         e = launchRowRun<F_U16, F_U16, true>(c, p, smemBytes, grid);
+    } else if (src.format == dst.format && identity && src.format == F_U8) {
+        // (uint8)(float(v) / 255.999f * 255.999f) == v for all 256 values (checked exhaustively by
+        // tests/test_golden_oracle.py::test_u8_identity_round_trip against the reference build): raw -> raw
+        e = launchRowRun<F_U8, F_U8, true>(c, p, smemBytes, grid);
     } else if (src.format == dst.format && identity && src.format == F_F32) {
         // unmap: raw bits; map: (v - +0) / 1 == v (NaN payloads survive, as on x86)
         e = launchRowRun<F_F32, F_F32, true>(c, p, smemBytes, grid);
