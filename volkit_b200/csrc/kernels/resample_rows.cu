@@ -169,6 +169,13 @@ resampleRowRunKernel(RowRunParams p)
         for (int i = 0; i < S; ++i) { mbarInit(smemAddr(&full[i]), 1); mbarInit(smemAddr(&empty[i]), kRowThreads / 32); }
         fenceBarrierInit();
     }
+    // one tap: the dst voxel is a pure function of the src voxel -- for byte sources that function is a 256-entry
+    // table, built here with the exact codec (the UInt8 unmap is an IEEE division per voxel otherwise)
+    constexpr bool kTable = FS == F_U8 && !MOVE;
+    __shared__ uint32_t convTab[kTable ? 256 : 1];
+    if (kTable)
+        for (int i = t; i < 256; i += kRowThreads)
+            convTab[i] = mapVoxel<FD, false>(unmapVoxel<FS, false>((uint32_t)i, p.ms), p.md);
     __syncthreads();
 
     const long long srcRowPitch = (long long)p.Sx * BS;
@@ -224,7 +231,7 @@ resampleRowRunKernel(RowRunParams p)
                     for (int i = 0; i < V; ++i) {
                         const uint32_t off = (rel[c][i / 2] >> ((i & 1) * 16)) & 0xffffu;
                         const uint32_t raw = (uint32_t)*reinterpret_cast<const SrcT*>(srow + off);
-                        vecSet<BD>(out, i, MOVE ? raw : mapVoxel<FD, false>(unmapVoxel<FS, false>(raw, p.ms), p.md));
+                        vecSet<BD>(out, i, MOVE ? raw : kTable ? convTab[raw & 0xffu] : mapVoxel<FD, false>(unmapVoxel<FS, false>(raw, p.ms), p.md));
                     }
                     const uint4 v = make_uint4(out[0], out[1], out[2], out[3]);
                     uint8_t* dcol = p.d + (long long)x0 * BD + (long long)q * 16;
