@@ -227,6 +227,32 @@ def test_resample_float_specials_linear(gpu):
         assert same_bits(b.a, a.a), ddims
 
 
+def test_resample_halve_x_kernel(gpu):
+    """8-tap modes with an exact 2:1 x map (coalesced four-row gather): every format, y / z ratios of any kind,
+    Float32 specials, and a dst width whose x map is NOT exact (falls back to the other kernels)."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.UINT32, po.FLOAT32):
+        src = cases.mk((96, 40, 24), fmt, 1)
+        if fmt == po.FLOAT32:
+            flat = src.a.ravel()
+            flat[::53] = np.nan
+            flat[7::71] = np.inf
+            flat[3::67] = -0.0
+        for ddims in ((48, 20, 12), (48, 60, 36), (48, 33, 7), (48, 40, 24)):
+            for filt in (po.LINEAR, po.TRILINEAR):
+                a, b = po.empty(ddims, fmt, -1.0, 2.0), po.empty(ddims, fmt, -1.0, 2.0)
+                o.resample(a, src, filt)
+                gpu.resample(b, src, filt)
+                assert same_bits(b.a, a.a), (fmt, ddims, filt)
+    # 2:1 with a width for which (x / float(Dx)) * Sx dips below 2x somewhere: the host check must reject it
+    for Dx in (16, 24, 40, 56, 80, 176):
+        src = cases.mk((2 * Dx, 6, 5), po.FLOAT32, 2)
+        a, b = po.empty((Dx, 3, 5), po.FLOAT32), po.empty((Dx, 3, 5), po.FLOAT32)
+        o.resample(a, src, po.LINEAR)
+        gpu.resample(b, src, po.LINEAR)
+        assert same_bits(b.a, a.a), Dx
+
+
 def test_resample_zslab_windows(gpu):
     """z-slab sharding on one device ("virtual ranks"): slabs computed one by one equal the whole."""
     from volkit_b200 import capi

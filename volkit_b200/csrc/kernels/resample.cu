@@ -149,6 +149,94 @@ resampleKernel(RsParams p)
     }
 }
 
+// 8-tap modes when the x map is exactly lo = 2x, hi = 2x + 1 (2:1 down-sampling in x; the launcher verifies the whole
+// map on the host): the 2V x taps of V consecutive dst voxels are 32 consecutive bytes of the src row, so the 8 taps
+// come from 4 rows x 2 coalesced 128-bit loads, all eight in flight before the first use.  Same formats on both
+// sides (same bytes per voxel).  hi.x = 2x + 1 <= Sx - 1: the reference's unclamped tap never leaves the row here.
+template <int F, int MODE>
+__global__ void __launch_bounds__(kThreads)
+resampleHalveXKernel(RsParams p)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    const int chunks = p.Dx / V;                      // Dx is a multiple of V (launcher)
+    const long long rows = (long long)p.Dy * p.dzCount;
+    const long long rowPitch = (long long)p.Sx * BPV, planePitch = rowPitch * p.Sy;
+    // byte voxels unmap through a 256-entry table (exact codec) instead of an IEEE division per tap
+    __shared__ float lut[F == F_U8 ? 256 : 1];
+    if (F == F_U8) {
+        for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < 256; i += blockDim.x * blockDim.y)
+            lut[i] = unmapVoxel<F_U8, false>((uint32_t)i, p.ms);
+        __syncthreads();
+    }
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= chunks) return;
+    const int x0 = c * V;
+    float fx[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) fx[i] = MODE == MODE_TRILINEAR ? p.xfr[x0 + i] : 0.f;   // Linear: float(lo) - float(lo)
+
+    for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows; r += (long long)gridDim.y * blockDim.y) {
+        const int zz = (int)(r / p.Dy), y = (int)(r - (long long)zz * p.Dy);
+        const int sy = p.ymap[y], sz = p.zmap[zz];
+        int hy, hz; float fy, fz;
+        if (MODE == MODE_LINEAR8) {
+            hy = min(max(sy + 1, 0), p.Sy - 1); hz = min(max(sz + 1, 0), p.Sz - 1);
+            fy = __fsub_rn(__int2float_rn(sy), __int2float_rn(min(max(sy, 0), p.Sy - 1)));
+            fz = __fsub_rn(__int2float_rn(sz), __int2float_rn(sz));
+        } else {
+            hy = p.yhi[y]; hz = p.zhi[zz];
+            fy = p.yfr[y]; fz = p.zfr[zz];
+        }
+        const uint8_t* b00 = p.s + (long long)(sz - p.sz0) * planePitch + (long long)sy * rowPitch + (long long)x0 * 2 * BPV;
+        const uint8_t* b10 = p.s + (long long)(sz - p.sz0) * planePitch + (long long)hy * rowPitch + (long long)x0 * 2 * BPV;
+        const uint8_t* b01 = p.s + (long long)(hz - p.sz0) * planePitch + (long long)sy * rowPitch + (long long)x0 * 2 * BPV;
+        const uint8_t* b11 = p.s + (long long)(hz - p.sz0) * planePitch + (long long)hy * rowPitch + (long long)x0 * 2 * BPV;
+        const uint4 q00a = ldStream(b00), q00b = ldStream(b00 + 16), q10a = ldStream(b10), q10b = ldStream(b10 + 16);
+        const uint4 q01a = ldStream(b01), q01b = ldStream(b01 + 16), q11a = ldStream(b11), q11b = ldStream(b11 + 16);
+        uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            // voxels 2i and 2i+1 of the 2V staged ones: first half of them in the a vector, second half in b
+            auto pick = [&](const uint4& a, const uint4& b, int k) {
+                const uint32_t raw = k < V ? vecGet<BPV>(a, k) : vecGet<BPV>(b, k - V);
+                return F == F_U8 ? lut[raw] : unmapVoxel<F, false>(raw, p.ms);
+            };
+            const float v0 = pick(q00a, q00b, 2 * i), v1 = pick(q00a, q00b, 2 * i + 1);
+            const float v2 = pick(q10a, q10b, 2 * i), v3 = pick(q10a, q10b, 2 * i + 1);
+            const float v4 = pick(q01a, q01b, 2 * i), v5 = pick(q01a, q01b, 2 * i + 1);
+            const float v6 = pick(q11a, q11b, 2 * i), v7 = pick(q11a, q11b, 2 * i + 1);
+            const float f = refLerp(refLerp(refLerp(v0, v1, fx[i]), refLerp(v2, v3, fx[i]), fy),
+                                    refLerp(refLerp(v4, v5, fx[i]), refLerp(v6, v7, fx[i]), fy), fz);
+            vecSet<BPV>(w, i, mapVoxel<F, false>(f, p.md));
+        }
+        stStream(p.d + (r * p.Dx + x0) * BPV, make_uint4(w[0], w[1], w[2], w[3]));
+    }
+}
+
+template <int F>
+cudaError_t launchHalveX(const LaunchCtx& c, const RsParams& p, int mode)
+{
+    RowsLaunch l = rowsLaunch(p.Dx, (long long)p.Dy * p.dzCount, 16 / bytesPerVoxel(F));
+    if (mode == MODE_LINEAR8) resampleHalveXKernel<F, MODE_LINEAR8><<<l.grid, l.block, 0, c.stream>>>(p);
+    else resampleHalveXKernel<F, MODE_TRILINEAR><<<l.grid, l.block, 0, c.stream>>>(p);
+    countLaunch();
+    return cudaGetLastError();
+}
+
+// the reference's x coordinate expression (Resample_serial.hpp:60), one rounding per operation, on the host
+bool xMapIsExactHalving(int Dx, int Sx)
+{
+    if (Sx != 2 * Dx || Dx > (1 << 20)) return false;
+    for (int x = 0; x < Dx; ++x) {
+        volatile float q = (float)x / (float)Dx;
+        volatile float sxf = q * (float)Sx;
+        const float sv = sxf;
+        if ((int)sv != 2 * x || (int)(sv + 1.f) != 2 * x + 1) return false;
+    }
+    return true;
+}
+
 template <int FS, int FD>
 cudaError_t launchMode(const LaunchCtx& c, const RsParams& p, int mode)
 {
@@ -220,7 +308,14 @@ cudaError_t launchResample(const LaunchCtx& c, const VolDesc& dst, const VolDesc
         // fast path: TMA row pipeline (resample_rows.cu); falls through when rows are not 16-byte aligned
         cudaError_t fe = launchResampleRowRuns(c, dst, src, dstZ0, D, srcZ0, S);
         if (fe != cudaErrorNotSupported) return fe;
-    } else {
+    }
+    // 8-tap modes, exact 2:1 in x, same format, 16-byte aligned rows: coalesced 4-row gather (below)
+    const int bd = bytesPerVoxel(dst.format);
+    const bool halveX = mode != MODE_NEAREST && src.format == dst.format && src.format != F_INT16
+                     && (D[0] * bd) % 16 == 0 && ((long long)S[0] * bs) % 16 == 0
+                     && ((reinterpret_cast<uintptr_t>(src.data) | reinterpret_cast<uintptr_t>(dst.data)) & 15u) == 0
+                     && xMapIsExactHalving(D[0], S[0]);
+    if (mode != MODE_NEAREST && !halveX) {
         // 8-tap modes: TMA z-march (resample_march.cu); falls through when the operands do not qualify
         cudaError_t fe = launchResampleMarch(c, dst, src, mode, dstZ0, D, srcZ0, S);
         if (fe != cudaErrorNotSupported) return fe;
@@ -248,6 +343,17 @@ cudaError_t launchResample(const LaunchCtx& c, const VolDesc& dst, const VolDesc
     coordTableKernel<<<(dzCount + 255) / 256, 256, 0, c.stream>>>(tab + oz, hiTab + oz, frTab + oz, D[2], S[2], dstZ0, dzCount, tri);
     countLaunch(); countLaunch(); countLaunch();
 
+    if (halveX) {
+        switch (src.format) {
+        case F_U8:  e = launchHalveX<F_U8>(c, p, mode); break;
+        case F_U16: e = launchHalveX<F_U16>(c, p, mode); break;
+        case F_U32: e = launchHalveX<F_U32>(c, p, mode); break;
+        case F_F32: e = launchHalveX<F_F32>(c, p, mode); break;
+        default: e = cudaErrorInvalidValue;
+        }
+        cudaFreeAsync(tab, c.stream);
+        return e;
+    }
     switch (src.format) {
     case F_U8:  e = launchDst<F_U8>(c, p, dst.format, mode); break;
     case F_U16: e = launchDst<F_U16>(c, p, dst.format, mode); break;
