@@ -486,6 +486,46 @@ def test_histogram_kernels(gpu):
     assert int(got.sum()) + gd == 64 * 32 * 16
 
 
+def test_cabi_from_many_threads(gpu):
+    """The C-ABI may be called from any thread (SURVEY 8(b) threading): four host threads run different algorithms on
+    their own volumes at the same time (ctypes releases the GIL during the calls); every result must equal the oracle's."""
+    import threading
+    o = po.oracle()
+    dims = (96, 64, 48)
+    errors = []
+
+    def worker(k):
+        try:
+            for rep in range(6):
+                fmt = (po.UINT8, po.UINT16, po.FLOAT32, po.UINT16)[k]
+                s1, s2 = cases.mk(dims, fmt, 10 + k), cases.mk(dims, fmt, 20 + k)
+                a, b = cases.mk(dims, fmt, 3), cases.mk(dims, fmt, 3)
+                if k == 0:
+                    o.arith_range(po.SAFESUM, a, s1, s2, (0, 0, 0), dims)
+                    gpu.arith_range(po.SAFESUM, b, s1, s2, (0, 0, 0), dims)
+                elif k == 1:
+                    o.copy_range(a, s1, (-2, 1, 3), (90, 60, 40), (1, 2, 3))
+                    gpu.copy_range(b, s1, (-2, 1, 3), (90, 60, 40), (1, 2, 3))
+                elif k == 2:
+                    a, b = po.empty((144, 96, 72), fmt), po.empty((144, 96, 72), fmt)
+                    o.resample(a, s1, po.LINEAR)
+                    gpu.resample(b, s1, po.LINEAR)
+                else:
+                    o.transform_range1(a, (1, 2, 3), (95, 60, 40), rep % 4)
+                    gpu.transform_range1(b, (1, 2, 3), (95, 60, 40), rep % 4)
+                if not same_bits(b.a, a.a):
+                    errors.append((k, rep))
+        except Exception as e:                      # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+
+
 def test_empty_and_degenerate_ranges(gpu):
     v = cases.mk((9, 7, 5), po.UINT16, 3)
     before = v.a.copy()
