@@ -46,6 +46,13 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
     record(f"SumRange {m}^3 UInt16 dstOffset (8,8,8)", m ** 3, 6 * m ** 3,
            lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z3,
                                                    capi.I3(m, m, m), capi.I3(8, 8, 8))))
+    # sources at another 16-byte phase than the destination (funnel-shifted loads)
+    record(f"CopyRange {m}^3 UInt16 first (1,1,1) dstOffset (0,0,0)", m ** 3, 4 * m ** 3,
+           lambda: capi.check(lib.vktb_copy_range(ctypes.byref(dd), ctypes.byref(da), capi.I3(1, 1, 1),
+                                                  capi.I3(m + 1, m + 1, m + 1), z3)))
+    record(f"SumRange {m}^3 UInt16 dstOffset (1,2,3)", m ** 3, 6 * m ** 3,
+           lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z3,
+                                                   capi.I3(m, m, m), capi.I3(1, 2, 3))))
     gm = capi.vol(a.ptr, (S, S, S), capi.UINT16, -1000.0, 3000.0)
     gd = capi.vol(d.ptr, (S, S, S), capi.UINT16, -1000.0, 3000.0)
     record(f"SafeProd {S}^3 UInt16 mapping (-1000,3000)", n, 6 * n,
@@ -56,6 +63,28 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
     for axis, name in ((0, "X"), (1, "Y (mirrors y and z, as the reference)")):
         record(f"Flip {name} {S}^3 UInt16", n, 4 * (n if S % 2 == 0 else n - S * S),
                lambda: capi.check(lib.vktb_flip_range(ctypes.byref(dd), ctypes.byref(da), z3, l3, z3, axis)))
+    # BrickDecompose: 64^3 bricks, halo 1 on every side, all bricks in ONE launch
+    bs, halo = 64, 1
+    nb = (S + bs - 1) // bs
+    edge = lambda i: halo + min(bs, S - i * bs) + halo
+    bricks, firsts, lasts, total = [], [], [], 0
+    for z in range(nb):
+        for y in range(nb):
+            for x in range(nb):
+                bd = (edge(x), edge(y), edge(z))
+                bricks.append((total, bd))
+                firsts += [x * bs - halo, y * bs - halo, z * bs - halo]
+                lasts += [min((x + 1) * bs, S) + halo, min((y + 1) * bs, S) + halo, min((z + 1) * bs, S) + halo]
+                total += bd[0] * bd[1] * bd[2]
+    pool = ctypes.c_void_p()
+    capi.check(lib.vktb_alloc(ctypes.byref(pool), total * 2))
+    descs = (capi.VktbVol * len(bricks))(*[capi.vol(pool.value + 2 * o, bd, capi.UINT16, 0.0, 1.0) for o, bd in bricks])
+    i32 = lambda v: (ctypes.c_int32 * len(v))(*v)
+    bf, bl, bo = i32(firsts), i32(lasts), i32([0] * len(firsts))
+    record(f"BrickDecompose {S}^3 UInt16 -> {len(bricks)} bricks of {bs}^3 + halo {halo}", total, 4 * total,
+           lambda: capi.check(lib.vktb_copy_range_batch(len(bricks), descs, ctypes.byref(da), bf, bl, bo)),
+           "one launch for all bricks; voxels = brick voxels incl. halos, alg_bytes = 2 bpv per brick voxel")
+    capi.check(lib.vktb_free(pool))
     bins = ctypes.c_void_p()
     capi.check(lib.vktb_alloc(ctypes.byref(bins), 256 * 8))
     record(f"Histogram 256 bins {S}^3 UInt16", n, 2 * n,

@@ -107,6 +107,14 @@ int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t l
 int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3],
                     const int32_t last[3], const int32_t dst_offset[3]);
 
+/* BrickDecompose_cuda(Array3D<StructuredVolume>&, StructuredVolume&, Vec3i brickSize, Vec3i haloNeg, Vec3i haloPos)
+ * (src/vkt/Decompose_cuda.hpp:16-22; semantics of BrickDecompose_serial, src/vkt/Decompose_serial.hpp:15-48: one
+ * CopyRange(dest[index], source, first, last) per brick).  n CopyRange calls from ONE source in a single launch:
+ * box i copies [firsts[3i..], lasts[3i..]) of src into dsts[i] at offs[3i..], src indices clamped as in
+ * vktb_copy_range.  Boxes whose format or mapping differs from the source's are converted one launch each. */
+int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts,
+                          const int32_t* lasts, const int32_t* offs);
+
 /* {Sum..SafeAbsDiff}Range_cuda  src/vkt/Arithmetic_cuda.hpp:10-98; semantics of ArithmeticOp,
  * src/vkt/Arithmetic_serial.hpp:15-45: dst[p + off] = map(f(unmap(s1[p]), unmap(s2[p]))), p absolute */
 int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2,

@@ -84,6 +84,9 @@ class _Lib:
         f("resample", ctypes.c_int, [p, p, ctypes.c_int])
         f("flip_range", ctypes.c_int, [p, p, I3, I3, I3, ctypes.c_int])
         f("histogram_range", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p])
+        i32p = ctypes.POINTER(ctypes.c_int32)
+        f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
+        f("brick_decompose", ctypes.c_int, [p, I3, I3, I3, ctypes.c_void_p, ctypes.c_size_t])
         if prefix == "vko_":
             f("resample_window", ctypes.c_int, [p, p, ctypes.c_int, ctypes.c_int32, I3, ctypes.c_int32, I3])
             f("synth_fill", None, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64])
@@ -134,6 +137,29 @@ class _Lib:
         assert self._histogram_range(ctypes.byref(vol.c()), I3(*first), I3(*last), bins.ctypes.data, num_bins,
                                      dropped.ctypes.data) == 0
         return bins, int(dropped[0])
+
+    def brick_layout(self, sdims, brick, halo_neg=(0, 0, 0), halo_pos=(0, 0, 0)):
+        """BrickDecomposeResize: (num_bricks (x, y, z), [brick dims (x, y, z), ...] in x-fastest brick order)"""
+        nb = I3()
+        self._brick_layout(I3(*sdims), I3(*brick), I3(*halo_neg), I3(*halo_pos), nb, None)
+        n = nb[0] * nb[1] * nb[2]
+        dims = (ctypes.c_int32 * (3 * n))()
+        self._brick_layout(I3(*sdims), I3(*brick), I3(*halo_neg), I3(*halo_pos), nb, dims)
+        return tuple(nb), [tuple(dims[3 * i: 3 * i + 3]) for i in range(n)]
+
+    def brick_decompose(self, src: Vol, brick, halo_neg=(0, 0, 0), halo_pos=(0, 0, 0)):
+        """BrickDecomposeResize + BrickDecompose: the bricks as a list of (Z, Y, X) arrays, x-fastest brick order"""
+        sdims = src.a.shape[::-1]
+        _, dims = self.brick_layout(sdims, brick, halo_neg, halo_pos)
+        out = np.zeros(sum(d[0] * d[1] * d[2] for d in dims), DTYPES[src.fmt])
+        assert self._brick_decompose(ctypes.byref(src.c()), I3(*brick), I3(*halo_neg), I3(*halo_pos), out.ctypes.data,
+                                     out.nbytes) == 0
+        bricks, at = [], 0
+        for d in dims:
+            n = d[0] * d[1] * d[2]
+            bricks.append(out[at: at + n].reshape(d[2], d[1], d[0]))
+            at += n
+        return bricks
 
     def resample_window(self, dst: Vol, src: Vol, filter: int, dz0: int, dst_full, sz0: int, src_full):
         assert self._resample_window(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter, dz0, I3(*dst_full),

@@ -22,6 +22,9 @@
 
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
+#include <vkt/Decompose.hpp>
+#include <vkt/Decompose.h>
+#include <vkt/StructuredVolume.h>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
 #include <vkt/Flip.hpp>
@@ -31,6 +34,7 @@
 #include <vkt/Transform.hpp>
 #include <vkt/Voxel.hpp>
 
+#include "StructuredVolume_impl.hpp" // reference-internal: the struct behind the C handle
 #include "Transform_serial.hpp" // reference-internal: src/vkt/Transform_serial.hpp (binary overload)
 
 namespace {
@@ -280,6 +284,78 @@ int ref_histogram_range(RefVol const* vol, int32_t const* first, int32_t const* 
     std::size_t* c = h.getBinCounts();
     for (size_t i = 0; i < numBins; ++i) bins[i] = (uint64_t)c[i];
     if (dropped) *dropped = 0;
+    return 0;
+}
+
+// vktBrickDecomposeResizeSV + vktBrickDecomposeSV (include/c/vkt/Decompose.h -> src/vkt/Decompose.cpp:152-256 ->
+// BrickDecomposeC_serial, src/vkt/Decompose_serial.hpp:50-88).  The C entry points are used because the C++
+// BrickDecomposeResize move-assigns volumes onto the malloc'ed, never-constructed elements of Array3D (its
+// ManagedBuffer hands out raw bytes): whether that frees garbage depends on the heap's history.  The C array holds
+// plain handles, so the same loops run without that hazard.
+struct CSource
+{
+    vktStructuredVolume h;
+    explicit CSource(RefVol const* d)
+    {
+        vktStructuredVolumeCreate(&h, d->dims[0], d->dims[1], d->dims[2], (vktDataFormat)d->format, 1.f, 1.f, 1.f,
+                                  d->lo, d->hi);
+        size_t bytes = h->volume.getSizeInBytes();   // the C accessors are declared but not defined by the reference
+        if (bytes && d->data) std::memcpy(h->volume.getData(), d->data, bytes);
+    }
+    ~CSource() { vktStructuredVolumeDestroy(h); }
+};
+
+struct CBricks
+{
+    vktArray3D_vktStructuredVolume arr;
+    CBricks(vktStructuredVolume source, int32_t const* b, int32_t const* n, int32_t const* p)
+    {
+        vktArray3D_vktStructuredVolume_CreateEmpty(&arr);
+        vktBrickDecomposeResizeSV(arr, source, b[0], b[1], b[2], n[0], n[1], n[2], p[0], p[1], p[2]);
+    }
+    ~CBricks()
+    {
+        size_t n = vktArray3D_vktStructuredVolume_NumElements(arr);
+        vktStructuredVolume* v = vktArray3D_vktStructuredVolume_Data(arr);
+        for (size_t i = 0; i < n; ++i) vktStructuredVolumeDestroy(v[i]);
+        vktArray3D_vktStructuredVolume_Destroy(arr);
+    }
+};
+
+size_t ref_brick_layout(int32_t const* srcDims, int32_t const* brick, int32_t const* haloNeg, int32_t const* haloPos,
+                        int32_t* numBricks, int32_t* brickDims)
+{
+    RefVol d = { nullptr, { srcDims[0], srcDims[1], srcDims[2] }, (int32_t)vkt::DataFormat::UInt8, 0.f, 1.f };
+    CSource source(&d);
+    CBricks bricks(source.h, brick, haloNeg, haloPos);
+    vktVec3i_t nb = vktArray3D_vktStructuredVolume_Dims(bricks.arr);
+    numBricks[0] = nb.x; numBricks[1] = nb.y; numBricks[2] = nb.z;
+    size_t n = vktArray3D_vktStructuredVolume_NumElements(bricks.arr), total = 0;
+    vktStructuredVolume* v = vktArray3D_vktStructuredVolume_Data(bricks.arr);
+    for (size_t i = 0; i < n; ++i) {
+        vkt::Vec3i bd = v[i]->volume.getDims();
+        if (brickDims) { brickDims[3 * i] = bd.x; brickDims[3 * i + 1] = bd.y; brickDims[3 * i + 2] = bd.z; }
+        total += (size_t)bd.x * (size_t)bd.y * (size_t)bd.z;
+    }
+    return total;
+}
+
+int ref_brick_decompose(RefVol const* src, int32_t const* brick, int32_t const* haloNeg, int32_t const* haloPos,
+                        uint8_t* out, size_t outBytes)
+{
+    CSource source(src);
+    CBricks bricks(source.h, brick, haloNeg, haloPos);
+    vktBrickDecomposeSV(bricks.arr, source.h, brick[0], brick[1], brick[2], haloNeg[0], haloNeg[1], haloNeg[2],
+                        haloPos[0], haloPos[1], haloPos[2]);
+    size_t n = vktArray3D_vktStructuredVolume_NumElements(bricks.arr), total = 0;
+    vktStructuredVolume* v = vktArray3D_vktStructuredVolume_Data(bricks.arr);
+    for (size_t i = 0; i < n; ++i) total += v[i]->volume.getSizeInBytes();
+    if (total != outBytes) return -2;
+    for (size_t i = 0; i < n; ++i) {
+        size_t bytes = v[i]->volume.getSizeInBytes();
+        std::memcpy(out, v[i]->volume.getData(), bytes);
+        out += bytes;
+    }
     return 0;
 }
 

@@ -61,6 +61,13 @@ int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3
 int vko_histogram_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                         size_t num_bins, uint64_t* dropped);
 
+/* BrickDecomposeResize's layout (num_bricks[3]; brick_dims = 3 ints per brick in x-fastest brick order, may be
+ * NULL) -> total voxels of all bricks; vko_brick_decompose writes the bricks back to back into out */
+size_t vko_brick_layout(const int32_t src_dims[3], const int32_t brick[3], const int32_t halo_neg[3],
+                        const int32_t halo_pos[3], int32_t num_bricks[3], int32_t* brick_dims);
+int vko_brick_decompose(const vko_vol* src, const int32_t brick[3], const int32_t halo_neg[3],
+                        const int32_t halo_pos[3], uint8_t* out, size_t out_bytes);
+
 /* synthetic inputs of SURVEY.md 8(d): element i of a volume with seed s gets the low bits of
  * splitmix64(i ^ s*0x9E3779B97F4A7C15); Float32 gets (h>>40)*2^-24 in [0,1). */
 void vko_synth_fill(void* data, size_t first_voxel, size_t n_voxels, int format, uint64_t seed);

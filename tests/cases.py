@@ -15,6 +15,12 @@ U8, U16, U32, F32 = po.UINT8, po.UINT16, po.UINT32, po.FLOAT32
 FMT4 = [U8, U16, U32, F32]
 
 
+# (source dims, brick size, halo neg, halo pos) for BrickDecompose
+BRICK_CASES = [((16, 12, 10), (8, 4, 5), (0, 0, 0), (0, 0, 0)), ((17, 13, 9), (8, 8, 8), (0, 0, 0), (0, 0, 0)),
+               ((17, 13, 9), (5, 6, 4), (1, 1, 1), (1, 1, 1)), ((20, 7, 6), (7, 7, 7), (2, 0, 1), (0, 3, 1)),
+               ((9, 9, 9), (16, 16, 16), (1, 2, 3), (3, 2, 1)), ((12, 1, 5), (4, 1, 2), (0, 0, 0), (1, 0, 0))]
+
+
 def mk(dims, fmt, seed, lo=0.0, hi=1.0):
     return po.Vol(po.synth(dims, fmt, seed), fmt, lo, hi)
 

@@ -7,6 +7,7 @@
 
 #include <vkt/Arithmetic.h>
 #include <vkt/Copy.h>
+#include <vkt/Decompose.h>
 #include <vkt/ExecutionPolicy.h>
 #include <vkt/Fill.h>
 #include <vkt/Resample.h>
@@ -53,8 +54,27 @@ int main(int argc, char** argv)
     vktStructuredVolumeCreateCopy(&volume3, volume);
     VKT_SAFE_CALL(vktSafeSumSV(volume3, volume, volume2));
     VKT_SAFE_CALL(vktAbsDiffRangeSV(volume2, volume, volume3, 1, 1, 1, 39, 31, 23, 0, 0, 0));
+    /* BrickDecompose as in reference src/examples/Decompose.c: 16^3 bricks, halo 1 on every side */
+    vktArray3D_vktStructuredVolume decomp;
+    vktArray3D_vktStructuredVolume_CreateEmpty(&decomp);
+    VKT_SAFE_CALL(vktBrickDecomposeResizeSV(decomp, volume3, 16, 16, 16, 1, 1, 1, 1, 1, 1));
+    VKT_SAFE_CALL(vktBrickDecomposeSV(decomp, volume3, 16, 16, 16, 1, 1, 1, 1, 1, 1));
     vktSetThreadExecutionPolicy(cpu);
 
+    {
+        char path[1024];
+        snprintf(path, sizeof path, "%s/%s", argv[2], "c_out_bricks.raw");
+        FILE* f = fopen(path, "wb");
+        vktVec3i_t nb = vktArray3D_vktStructuredVolume_Dims(decomp);
+        if (nb.x != 3 || nb.y != 2 || nb.z != 2 || vktArray3D_vktStructuredVolume_NumElements(decomp) != 12) return 3;
+        for (vktStructuredVolume* b = vktArray3D_vktStructuredVolume_Begin(decomp);
+             b != vktArray3D_vktStructuredVolume_End(decomp); ++b) {
+            fwrite(vktStructuredVolumeGetData(*b), 1, vktStructuredVolumeGetSizeInBytes(*b), f);
+            vktStructuredVolumeDestroy(*b);
+        }
+        fclose(f);
+        vktArray3D_vktStructuredVolume_Destroy(decomp);
+    }
     save(volume, argv[2], "c_out_volume.raw");
     save(volume2, argv[2], "c_out_volume2.raw");
     save(volume3, argv[2], "c_out_volume3.raw");

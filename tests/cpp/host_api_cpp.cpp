@@ -12,6 +12,7 @@
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Decompose.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
@@ -132,6 +133,12 @@ int main(int argc, char** argv)
     Histogram hist(300);
     CHECK(ComputeHistogramRange(a, hist, 1, 2, 3, 47, 39, 35));
 
+    // BrickDecompose: 20x16x16 bricks with halos (-1,-2,0)/(2,1,1): 3x3x3 bricks, the far ones cropped
+    Array3D<StructuredVolume> bricks;
+    CHECK(BrickDecomposeResize(bricks, a, Vec3i{ 20, 16, 16 }, Vec3i{ 1, 2, 0 }, Vec3i{ 2, 1, 1 }));
+    if (bricks.dims().x != 3 || bricks.dims().y != 3 || bricks.dims().z != 3) return 10;
+    CHECK(BrickDecompose(bricks, a, Vec3i{ 20, 16, 16 }, Vec3i{ 1, 2, 0 }, Vec3i{ 2, 1, 1 }));
+
     // single-voxel accessors work under either policy
     sum.setValue(1, 2, 3, .75f);
     float back = sum.getValue(1, 2, 3);
@@ -144,6 +151,11 @@ int main(int argc, char** argv)
     {
         FILE* f = std::fopen((g_dir + "/out_hist.raw").c_str(), "wb");
         std::fwrite(hist.getBinCounts(), sizeof(std::size_t), hist.getNumBins(), f);   // migrates the bins back
+        std::fclose(f);
+    }
+    {
+        FILE* f = std::fopen((g_dir + "/out_bricks.raw").c_str(), "wb");
+        for (StructuredVolume& b : bricks) std::fwrite(b.getData(), 1, b.getSizeInBytes(), f);
         std::fclose(f);
     }
     std::printf("ok\n");

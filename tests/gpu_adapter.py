@@ -39,6 +39,34 @@ class GpuLib:
         self._down(d, dst)
         s.free()
 
+    def copy_range_batch(self, dsts, src, firsts, lasts, offs):
+        """n CopyRange calls from one source in ONE vktb_copy_range_batch launch; dsts are updated in place"""
+        n = len(dsts)
+        s = self._up(src)
+        dv = [self._up(d) for d in dsts]
+        descs = (capi.VktbVol * n)(*[d.desc() for d in dv])
+        flat = lambda t: (ctypes.c_int32 * (3 * n))(*[c for v in t for c in v])
+        capi.check(self.lib.vktb_copy_range_batch(n, descs, ctypes.byref(s.desc()), flat(firsts), flat(lasts), flat(offs)),
+                   "copy batch")
+        for d, v in zip(dv, dsts):
+            self._down(d, v)
+        s.free()
+
+    def brick_decompose(self, src, brick, halo_neg=(0, 0, 0), halo_pos=(0, 0, 0), prefill_seed=None):
+        """BrickDecomposeResize's layout (host logic, taken from the oracle) + one batched launch for all bricks"""
+        sdims = src.a.shape[::-1]
+        nb, dims = po.oracle().brick_layout(sdims, brick, halo_neg, halo_pos)
+        bricks = [po.Vol(po.synth(d, src.fmt, 7 + i), src.fmt, src.lo, src.hi) for i, d in enumerate(dims)]
+        firsts, lasts = [], []
+        for z in range(nb[2]):
+            for y in range(nb[1]):
+                for x in range(nb[0]):
+                    f = [i * b for i, b in zip((x, y, z), brick)]
+                    lasts.append(tuple(min(f_ + b, d) + p for f_, b, d, p in zip(f, brick, sdims, halo_pos)))
+                    firsts.append(tuple(f_ - n_ for f_, n_ in zip(f, halo_neg)))
+        self.copy_range_batch(bricks, src, firsts, lasts, [(0, 0, 0)] * len(bricks))
+        return [b.a for b in bricks]
+
     def arith_range(self, op, dst, s1, s2, first, last, off=(0, 0, 0)):
         d, a, b = self._up(dst), self._up(s1), self._up(s2)
         capi.check(self.lib.vktb_arith_range(op, ctypes.byref(d.desc()), ctypes.byref(a.desc()), ctypes.byref(b.desc()),

@@ -183,6 +183,69 @@ def test_config2_256cube(gpu, fmt):
     assert same_bits(b.a, a.a)
 
 
+def test_range_ops_shifted_rows(gpu):
+    """*Range calls whose source rows sit at another 16-byte phase than the destination rows (funnel-shifted 128-bit
+    loads): pitches that are / are not multiples of 16 bytes, ranges that end on the very last voxel of the source
+    (the one chunk whose second vector would leave the buffer), clamped Copy borders, in-place use."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.UINT32, po.FLOAT32):
+        for sdims, ddims in (((64, 16, 8), (96, 24, 12)), ((67, 13, 9), (83, 21, 15)), ((48, 5, 4), (48, 5, 4))):
+            s1, s2 = cases.mk(sdims, fmt, 1), cases.mk(sdims, fmt, 2)
+            X, Y, Z = sdims
+            for first, last, off in (((0, 0, 0), sdims, (0, 0, 0)), ((1, 0, 0), sdims, (0, 0, 0)),
+                                     ((3, 1, 2), sdims, (2, 3, 1)), ((5, 2, 1), (X - 1, Y, Z), (7, 0, 2)),
+                                     ((0, 0, 0), (X - 3, Y - 1, Z), (13, 1, 0))):
+                fits = all(l + f_ - f_ + o_ <= d for f_, l, o_, d in zip(first, last, off, ddims))
+                if not fits or any(f_ + o_ < 0 for f_, o_ in zip(first, off)):
+                    continue
+                a, b = cases.mk(ddims, fmt, 3), cases.mk(ddims, fmt, 3)
+                for op in (po.SAFESUM, po.DIFF):
+                    o.arith_range(op, a, s1, s2, first, last, off)
+                    gpu.arith_range(op, b, s1, s2, first, last, off)
+                    assert same_bits(b.a, a.a), (fmt, sdims, first, last, off, op)
+                a, b = cases.mk(ddims, fmt, 3), cases.mk(ddims, fmt, 3)
+                cl = tuple(l - f_ for f_, l in zip(first, last))   # Copy writes dst[p - first + off]
+                if all(c + o_ <= d for c, o_, d in zip(cl, off, ddims)):
+                    o.copy_range(a, s1, first, last, off)
+                    gpu.copy_range(b, s1, first, last, off)
+                    assert a.a.tobytes() == b.a.tobytes(), (fmt, sdims, first, last, off)
+            # clamped borders: first < 0 and last > dims, dst offset at an odd phase
+            a, b = cases.mk(ddims, fmt, 3), cases.mk(ddims, fmt, 3)
+            first, last = (-3, -1, -2), (X + 2, Y + 1, Z + 1)
+            if all(l - f_ + 1 <= d for f_, l, d in zip(first, last, ddims)):
+                o.copy_range(a, s1, first, last, (1, 0, 0))
+                gpu.copy_range(b, s1, first, last, (1, 0, 0))
+                assert a.a.tobytes() == b.a.tobytes(), (fmt, sdims, "clamped")
+
+
+def test_brick_decompose_batch(gpu):
+    """BrickDecompose as one vktb_copy_range_batch launch: cropped border bricks, halos clamped at the volume border,
+    brick rows at every 16-byte phase; plus a batch that mixes bytewise and converting boxes and empty boxes."""
+    o = po.oracle()
+    extra = [((130, 70, 33), (64, 32, 16), (1, 1, 1), (1, 1, 1)), ((96, 64, 40), (32, 32, 32), (0, 0, 0), (0, 0, 0)),
+             ((200, 9, 5), (67, 4, 2), (3, 0, 1), (2, 2, 0))]
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        for sdims, brick, neg, pos in cases.BRICK_CASES + extra:
+            v = cases.mk(sdims, fmt, 3, -1000.0, 3000.0)
+            want = o.brick_decompose(v, brick, neg, pos)
+            got = gpu.brick_decompose(v, brick, neg, pos)
+            assert len(want) == len(got)
+            for i, (a, b) in enumerate(zip(want, got)):
+                assert a.shape == b.shape and a.tobytes() == b.tobytes(), (fmt, sdims, brick, neg, pos, i)
+    # mixed batch: same-format boxes (batched), a converting box (own launch), an empty box, a dst offset
+    src = cases.mk((40, 20, 12), po.UINT16, 1)
+    specs = [(po.UINT16, (24, 12, 8), (3, 2, 1), (23, 12, 8), (1, 0, 0)), (po.UINT8, (24, 12, 8), (0, 0, 0), (24, 12, 8), (0, 0, 0)),
+             (po.UINT16, (8, 8, 8), (5, 5, 5), (5, 9, 9), (0, 0, 0)), (po.UINT16, (50, 25, 14), (-4, -2, -1), (44, 22, 13), (1, 1, 0)),
+             (po.FLOAT32, (10, 10, 10), (30, 10, 2), (40, 20, 12), (0, 0, 0))]
+    want = [cases.mk(d, f, 9 + i) for i, (f, d, *_r) in enumerate(specs)]
+    got = [w.copy() for w in want]
+    for w, (_f, _d, first, last, off) in zip(want, specs):
+        o.copy_range(w, src, first, last, off)
+    gpu.copy_range_batch(got, src, [s[2] for s in specs], [s[3] for s in specs], [s[4] for s in specs])
+    for i, (w, g) in enumerate(zip(want, got)):
+        assert same_bits(g.a, w.a), i
+
+
 def test_transform_flat_and_rows(gpu):
     """Transform over contiguous ranges (flat stream kernel: whole volumes, whole planes, part of one plane) and over
     boxed ranges (row kernel); odd row lengths make vectors straddle rows and misalign the range start."""

@@ -92,6 +92,8 @@ def run_cpp(programs, policy, tmp):
     assert raw(tmp / "out_fz.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     bins, dropped = o.histogram_range(a, (1, 2, 3), (47, 39, 35), 300)
     assert dropped == 0 and np.fromfile(tmp / "out_hist.raw", np.uint64).tobytes() == bins.tobytes()
+    want = b"".join(x.tobytes() for x in o.brick_decompose(a, (20, 16, 16), (1, 2, 0), (2, 1, 1)))
+    assert (tmp / "out_bricks.raw").read_bytes() == want
     if policy == "gpu-stream":
         # the host-streaming prelude: same voxels as the migrating calls
         ref = po.empty(dims, U16)
@@ -123,6 +125,8 @@ def run_c(programs, policy, tmp):
     assert raw(tmp / "c_out_volume.raw", dims, np.uint8).tobytes() == v.a.tobytes()
     assert raw(tmp / "c_out_volume2.raw", dims, np.uint8).tobytes() == v2.a.tobytes()
     assert raw(tmp / "c_out_volume3.raw", dims, np.uint8).tobytes() == v3.a.tobytes()
+    want = b"".join(x.tobytes() for x in o.brick_decompose(v3, (16, 16, 16), (1, 1, 1), (1, 1, 1)))
+    assert (tmp / "c_out_bricks.raw").read_bytes() == want
 
 
 def cli_pipeline(device):

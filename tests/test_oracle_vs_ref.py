@@ -6,6 +6,8 @@ import itertools
 import numpy as np
 import pytest
 
+import cases
+
 from oracle import pyoracle as po
 
 pytestmark = pytest.mark.needs_ref
@@ -162,6 +164,23 @@ def test_histogram(fmt):
             hb, _ = r.histogram_range(v, (1, 2, 3), (24, 11, 9), nb)
             assert dropped == 0 and ha.tobytes() == hb.tobytes(), (lo, nb)
             assert int(ha.sum()) == 23 * 9 * 6
+
+
+@pytest.mark.parametrize("fmt", FMTS[:4])
+def test_brick_decompose(fmt):
+    """BrickDecomposeResize's brick grid and BrickDecompose's contents (halo voxels clamped at the volume border)."""
+    o, r = po.oracle(), po.reference()
+    for sdims, brick, neg, pos in cases.BRICK_CASES:
+        assert o.brick_layout(sdims, brick, neg, pos) == r.brick_layout(sdims, brick, neg, pos), (sdims, brick)
+        v = mk(sdims, fmt, 3, -1000.0, 3000.0)
+        a, b = o.brick_decompose(v, brick, neg, pos), r.brick_decompose(v, brick, neg, pos)
+        assert len(a) == len(b)
+        for i, (x, y) in enumerate(zip(a, b)):
+            assert x.shape == y.shape and x.tobytes() == y.tobytes(), (sdims, brick, neg, pos, i)
+    # without halos the bricks tile the volume exactly
+    v = mk((16, 12, 10), fmt, 3)
+    bricks = o.brick_decompose(v, (8, 4, 5))
+    assert np.array_equal(bricks[0], v.a[:5, :4, :8]) and np.array_equal(bricks[-1], v.a[5:, 8:, 8:])
 
 
 def test_resample_linear_equals_nearest_in_reference():

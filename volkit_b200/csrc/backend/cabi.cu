@@ -1,6 +1,7 @@
 // C-ABI algorithm entry points (include/vktb/backend.h): argument validation, then one launcher call.
 #include "context.hpp"
 
+#include <vector>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -66,6 +67,23 @@ int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
     return finish("vktb_copy_range", launchCopy(c, dv, sv, first, last, off));
+}
+
+int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts, const int32_t* lasts,
+                          const int32_t* offs)
+{
+    if (n < 0) return fail("vktb_copy_range_batch: negative count");
+    if (n == 0) return 0;
+    if (!dsts || !firsts || !lasts || !offs) return fail("vktb_copy_range_batch: null argument");
+    VolDesc sv;
+    if (!toDesc("vktb_copy_range_batch", src, sv)) return -1;
+    std::vector<VolDesc> dv((size_t)n);
+    for (int i = 0; i < n; ++i)
+        if (!toDesc("vktb_copy_range_batch", dsts + i, dv[(size_t)i])) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_copy_range_batch", launchCopyBatch(c, n, dv.data(), sv, firsts, lasts, offs));
 }
 
 int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2, const int32_t first[3],

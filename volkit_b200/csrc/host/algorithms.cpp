@@ -6,9 +6,11 @@
 // With printPerformance the call is timed and one line is logged in the reference's format (Callable.hpp:23-47).
 #include <chrono>
 #include <cstdio>
+#include <vector>
 
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
+#include <vkt/Decompose.hpp>
 #include <vkt/Fill.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
@@ -270,6 +272,87 @@ namespace
                 return vktb_resample(&d, &s, filter);
             });
     }
+    //---------------------------------------------------------------------------------------------------------
+    // BrickDecompose (reference src/vkt/Decompose.cpp:22-150, Decompose_serial.hpp:15-48)
+    //---------------------------------------------------------------------------------------------------------
+    Error host::brickDecompose(StructuredVolume* const* bricks, Vec3i nb, StructuredVolume& source, Vec3i brickSize,
+                               Vec3i haloNeg, Vec3i haloPos)
+    {
+        const std::size_t n = nb.x * std::size_t(nb.y) * nb.z;
+        const Vec3i sd = source.getDims();
+        std::vector<int32_t> firsts(3 * n), lasts(3 * n), offs(3 * n, 0);
+        std::size_t i = 0;
+        for (int z = 0; z < nb.z; ++z)
+            for (int y = 0; y < nb.y; ++y)
+                for (int x = 0; x < nb.x; ++x, ++i) {
+                    const int idx[3] = { x, y, z }, bs[3] = { brickSize.x, brickSize.y, brickSize.z };
+                    const int dim[3] = { sd.x, sd.y, sd.z }, neg[3] = { haloNeg.x, haloNeg.y, haloNeg.z };
+                    const int pos[3] = { haloPos.x, haloPos.y, haloPos.z };
+                    for (int a = 0; a < 3; ++a) {
+                        const int f = idx[a] * bs[a];
+                        firsts[3 * i + a] = f - neg[a];
+                        lasts[3 * i + a] = (f + bs[a] < dim[a] ? f + bs[a] : dim[a]) + pos[a];
+                    }
+                }
+        auto v3 = [](int32_t const* p) { return Vec3i{ p[0], p[1], p[2] }; };
+        return dispatch("BrickDecompose",
+            [&] {
+                host::View s = viewOf(source);
+                for (std::size_t k = 0; k < n; ++k)
+                    host::copyRange(viewOf(*bricks[k]), s, v3(&firsts[3 * k]), v3(&lasts[3 * k]), Vec3i{ 0, 0, 0 });
+            },
+            [&] {
+                // every brick and the source on the device first, then one launch for all boxes
+                std::vector<vktb_vol> d(n);
+                for (std::size_t k = 0; k < n; ++k) d[k] = host::describe(*bricks[k]);
+                vktb_vol s = host::describe(source);
+                return vktb_copy_range_batch((int)n, d.data(), &s, firsts.data(), lasts.data(), offs.data());
+            });
+    }
+
+    Error BrickDecompose(Array3D<StructuredVolume>& dest, StructuredVolume& source, Vec3i brickSize, Vec3i haloSizeNeg,
+                         Vec3i haloSizePos)
+    {
+        std::vector<StructuredVolume*> bricks(dest.numElements());
+        for (std::size_t i = 0; i < bricks.size(); ++i) bricks[i] = dest.data() + i;
+        return host::brickDecompose(bricks.data(), dest.dims(), source, brickSize, haloSizeNeg, haloSizePos);
+    }
+
+    Error BrickDecompose(Array3D<StructuredVolume>& dest, StructuredVolume& source, int32_t brickSizeX, int32_t brickSizeY,
+                         int32_t brickSizeZ, int32_t haloSizeNegX, int32_t haloSizeNegY, int32_t haloSizeNegZ,
+                         int32_t haloSizePosX, int32_t haloSizePosY, int32_t haloSizePosZ)
+    {
+        return BrickDecompose(dest, source, Vec3i{ brickSizeX, brickSizeY, brickSizeZ },
+                              Vec3i{ haloSizeNegX, haloSizeNegY, haloSizeNegZ }, Vec3i{ haloSizePosX, haloSizePosY, haloSizePosZ });
+    }
+
+    Error BrickDecomposeResize(Array3D<StructuredVolume>& dest, StructuredVolume& source, Vec3i brickSize,
+                               Vec3i haloSizeNeg, Vec3i haloSizePos)
+    {
+        if (brickSize.x <= 0 || brickSize.y <= 0 || brickSize.z <= 0) return InvalidValue;
+        const Vec3i sd = source.getDims(), nb = host::brickCount(sd, brickSize);
+        const Vec3f dist = source.getDist();
+        const Vec2f m = source.getVoxelMapping();
+        dest = Array3D<StructuredVolume>(nb);
+        for (int z = 0; z < nb.z; ++z)
+            for (int y = 0; y < nb.y; ++y)
+                for (int x = 0; x < nb.x; ++x) {
+                    const Vec3i d = host::brickDims(sd, brickSize, haloSizeNeg, haloSizePos, Vec3i{ x, y, z });
+                    dest[Vec3i{ x, y, z }] = StructuredVolume(d.x, d.y, d.z, source.getDataFormat(), dist.x, dist.y, dist.z,
+                                                              m.x, m.y);
+                }
+        return NoError;
+    }
+
+    Error BrickDecomposeResize(Array3D<StructuredVolume>& dest, StructuredVolume& source, int32_t brickSizeX,
+                               int32_t brickSizeY, int32_t brickSizeZ, int32_t haloSizeNegX, int32_t haloSizeNegY,
+                               int32_t haloSizeNegZ, int32_t haloSizePosX, int32_t haloSizePosY, int32_t haloSizePosZ)
+    {
+        return BrickDecomposeResize(dest, source, Vec3i{ brickSizeX, brickSizeY, brickSizeZ },
+                                    Vec3i{ haloSizeNegX, haloSizeNegY, haloSizeNegZ },
+                                    Vec3i{ haloSizePosX, haloSizePosY, haloSizePosZ });
+    }
+
     //---------------------------------------------------------------------------------------------------------
     // Flip (reference src/vkt/Flip.cpp:26-117)
     //---------------------------------------------------------------------------------------------------------

@@ -1,7 +1,9 @@
 // C99 API over the C++ host mirror (reference: the "C API" halves of src/vkt/{ExecutionPolicy,Memory,
 // StructuredVolume,Voxel,Fill,Copy,Arithmetic,Transform}.cpp).  The opaque handle wraps a vkt::StructuredVolume.
 #include <vkt/Arithmetic.h>
+#include <vkt/Array3D.h>
 #include <vkt/Copy.h>
+#include <vkt/Decompose.h>
 #include <vkt/ExecutionPolicy.h>
 #include <vkt/Fill.h>
 #include <vkt/Flip.h>
@@ -13,6 +15,7 @@
 
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
+#include <vkt/Decompose.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
 #include <vkt/Flip.hpp>
@@ -22,6 +25,10 @@
 #include <vkt/Transform.hpp>
 #include <vkt/Voxel.hpp>
 
+#include <vector>
+
+#include "serial.hpp"
+
 struct vktStructuredVolume_impl
 {
     vktStructuredVolume_impl(int32_t x, int32_t y, int32_t z, vkt::DataFormat f, float dx, float dy, float dz, float lo, float hi)
@@ -29,6 +36,14 @@ struct vktStructuredVolume_impl
     explicit vktStructuredVolume_impl(vkt::StructuredVolume& rhs) : volume(rhs) {}
     vkt::StructuredVolume volume;
 };
+
+struct vktArray3D_vktStructuredVolume_impl
+{
+    std::vector<vktStructuredVolume> slots;   // x-fastest; NULL until a volume is created in the slot
+    vktVec3i_t dims;
+};
+
+static size_t slotCount(vktVec3i_t d) { return d.x * (size_t)d.y * d.z; }
 
 // vktVoxelView_t and vkt::VoxelView are layout-identical PODs passed by value: the op pointer is re-typed, as the
 // reference does (src/vkt/Transform.cpp:79-153)
@@ -131,6 +146,84 @@ vktError vktCopyRangeSV(vktStructuredVolume dst, vktStructuredVolume src, int32_
                         int32_t ly, int32_t lz, int32_t ox, int32_t oy, int32_t oz)
 {
     return (vktError)vkt::CopyRange(dst->volume, src->volume, fx, fy, fz, lx, ly, lz, ox, oy, oz);
+}
+
+//--- Array3D of volume handles (reference include/c/vkt/Array3D.h:18-231) -------------------------------------
+void vktArray3D_vktStructuredVolume_CreateEmpty(vktArray3D_vktStructuredVolume* arr)
+{
+    *arr = new vktArray3D_vktStructuredVolume_impl();
+    (*arr)->dims = vktVec3i_t{ 0, 0, 0 };
+}
+void vktArray3D_vktStructuredVolume_Create(vktArray3D_vktStructuredVolume* arr, vktVec3i_t dims)
+{
+    *arr = new vktArray3D_vktStructuredVolume_impl();
+    (*arr)->slots.assign(slotCount(dims), nullptr);
+    (*arr)->dims = dims;
+}
+void vktArray3D_vktStructuredVolume_CreateCopy(vktArray3D_vktStructuredVolume* arr, vktArray3D_vktStructuredVolume rhs)
+{
+    *arr = new vktArray3D_vktStructuredVolume_impl(*rhs);   // copies the handles, like the reference's byte copy
+}
+void vktArray3D_vktStructuredVolume_Destroy(vktArray3D_vktStructuredVolume arr) { delete arr; }
+void vktArray3D_vktStructuredVolume_Resize(vktArray3D_vktStructuredVolume arr, vktVec3i_t dims)
+{
+    arr->slots.resize(slotCount(dims), nullptr);
+    arr->dims = dims;
+}
+void vktArray3D_vktStructuredVolume_Fill(vktArray3D_vktStructuredVolume arr, vktStructuredVolume value)
+{
+    arr->slots.assign(arr->slots.size(), value);
+}
+vktStructuredVolume* vktArray3D_vktStructuredVolume_Data(vktArray3D_vktStructuredVolume arr) { return arr->slots.data(); }
+vktStructuredVolume const* vktArray3D_vktStructuredVolume_CData(vktArray3D_vktStructuredVolume arr) { return arr->slots.data(); }
+vktStructuredVolume* vktArray3D_vktStructuredVolume_Begin(vktArray3D_vktStructuredVolume arr) { return arr->slots.data(); }
+vktStructuredVolume const* vktArray3D_vktStructuredVolume_CBegin(vktArray3D_vktStructuredVolume arr) { return arr->slots.data(); }
+vktStructuredVolume* vktArray3D_vktStructuredVolume_End(vktArray3D_vktStructuredVolume arr) { return arr->slots.data() + arr->slots.size(); }
+vktStructuredVolume const* vktArray3D_vktStructuredVolume_CEnd(vktArray3D_vktStructuredVolume arr) { return arr->slots.data() + arr->slots.size(); }
+vktStructuredVolume* vktArray3D_vktStructuredVolume_Access(vktArray3D_vktStructuredVolume arr, vktVec3i_t i)
+{
+    return arr->slots.data() + (i.z * arr->dims.x * (size_t)arr->dims.y + i.y * (size_t)arr->dims.x + i.x);
+}
+vktStructuredVolume const* vktArray3D_vktStructuredVolume_CAccess(vktArray3D_vktStructuredVolume arr, vktVec3i_t i)
+{
+    return vktArray3D_vktStructuredVolume_Access(arr, i);
+}
+vktBool_t vktArray3D_vktStructuredVolume_Empty(vktArray3D_vktStructuredVolume arr) { return arr->slots.empty() ? 1 : 0; }
+vktVec3i_t vktArray3D_vktStructuredVolume_Dims(vktArray3D_vktStructuredVolume arr) { return arr->dims; }
+size_t vktArray3D_vktStructuredVolume_NumElements(vktArray3D_vktStructuredVolume arr) { return arr->slots.size(); }
+
+//--- BrickDecompose (reference src/vkt/Decompose.cpp:152-256) ---------------------------------------------------
+vktError vktBrickDecomposeSV(vktArray3D_vktStructuredVolume decomp, vktStructuredVolume source, int32_t bx, int32_t by,
+                             int32_t bz, int32_t nx, int32_t ny, int32_t nz, int32_t px, int32_t py, int32_t pz)
+{
+    std::vector<vkt::StructuredVolume*> bricks(decomp->slots.size());
+    for (size_t i = 0; i < bricks.size(); ++i) {
+        if (!decomp->slots[i]) return vktInvalidValue;
+        bricks[i] = &decomp->slots[i]->volume;
+    }
+    vkt::Vec3i nb{ decomp->dims.x, decomp->dims.y, decomp->dims.z };
+    return (vktError)vkt::host::brickDecompose(bricks.data(), nb, source->volume, vkt::Vec3i{ bx, by, bz },
+                                               vkt::Vec3i{ nx, ny, nz }, vkt::Vec3i{ px, py, pz });
+}
+
+vktError vktBrickDecomposeResizeSV(vktArray3D_vktStructuredVolume decomp, vktStructuredVolume source, int32_t bx,
+                                   int32_t by, int32_t bz, int32_t nx, int32_t ny, int32_t nz, int32_t px, int32_t py,
+                                   int32_t pz)
+{
+    if (bx <= 0 || by <= 0 || bz <= 0) return vktInvalidValue;
+    vkt::StructuredVolume& s = source->volume;
+    vkt::Vec3i sd = s.getDims(), bs{ bx, by, bz }, nb = vkt::host::brickCount(sd, bs);
+    vktArray3D_vktStructuredVolume_Resize(decomp, vktVec3i_t{ nb.x, nb.y, nb.z });
+    vkt::Vec3f dist = s.getDist();
+    vkt::Vec2f m = s.getVoxelMapping();
+    for (int z = 0; z < nb.z; ++z)
+        for (int y = 0; y < nb.y; ++y)
+            for (int x = 0; x < nb.x; ++x) {
+                vkt::Vec3i d = vkt::host::brickDims(sd, bs, vkt::Vec3i{ nx, ny, nz }, vkt::Vec3i{ px, py, pz }, vkt::Vec3i{ x, y, z });
+                vktStructuredVolumeCreate(vktArray3D_vktStructuredVolume_Access(decomp, vktVec3i_t{ x, y, z }), d.x, d.y, d.z,
+                                          (vktDataFormat)s.getDataFormat(), dist.x, dist.y, dist.z, m.x, m.y);
+            }
+    return vktNoError;
 }
 
 //--- Flip (reference src/vkt/Flip.cpp:127-167) -------------------------------------------------------------------

@@ -173,5 +173,23 @@ namespace host
                     else if (b > -1.0f && b < 0.0f) bins[0]++;
                 }
     }
+
+    //--- BrickDecomposeResize layout: reference src/vkt/Decompose.cpp:96-146 ------------------------------------
+    Vec3i brickCount(Vec3i d, Vec3i b)
+    {
+        return Vec3i{ (d.x + b.x - 1) / b.x, (d.y + b.y - 1) / b.y, (d.z + b.z - 1) / b.z };
+    }
+
+    Vec3i brickDims(Vec3i d, Vec3i b, Vec3i neg, Vec3i pos, Vec3i index)
+    {
+        Vec3i n = brickCount(d, b);
+        // brick size (without halos) at the far borders: what is left of the volume there
+        Vec3i border{ d.x % b.x == 0 ? b.x : b.x - n.x * b.x + d.x,
+                      d.y % b.y == 0 ? b.y : b.y - n.y * b.y + d.y,
+                      d.z % b.z == 0 ? b.z : b.z - n.z * b.z + d.z };
+        return Vec3i{ neg.x + (index.x < n.x - 1 ? b.x : border.x) + pos.x,
+                      neg.y + (index.y < n.y - 1 ? b.y : border.y) + pos.y,
+                      neg.z + (index.z < n.z - 1 ? b.z : border.z) + pos.z };
+    }
 } // host
 } // vkt

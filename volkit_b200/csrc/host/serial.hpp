@@ -36,5 +36,18 @@ namespace host
     void resample(View dst, View src, int filter);
     void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset, int axis);
     void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins);
+
+    // BrickDecomposeResize's brick grid (reference src/vkt/Decompose.cpp:96-146): number of bricks and the dims of
+    // brick `index` including its halos
+    Vec3i brickCount(Vec3i sourceDims, Vec3i brickSize);
+    Vec3i brickDims(Vec3i sourceDims, Vec3i brickSize, Vec3i haloNeg, Vec3i haloPos, Vec3i index);
+} // host
+
+    class StructuredVolume;
+namespace host
+{
+    // body shared by vkt::BrickDecompose and vktBrickDecomposeSV: bricks[i] in x-fastest order (algorithms.cpp)
+    Error brickDecompose(StructuredVolume* const* bricks, Vec3i numBricks, StructuredVolume& source, Vec3i brickSize,
+                         Vec3i haloNeg, Vec3i haloPos);
 } // host
 } // vkt

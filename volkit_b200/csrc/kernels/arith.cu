@@ -45,14 +45,15 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
             pl.p.d.base, pl.p.a.base, pl.p.b.base, pl.n, pl.p.md, pl.p.ma, pl.p.mb, pl.p.alias);
     } else {
         RowsLaunch l = rowsLaunch(pl.p.g.nx, (long long)pl.p.g.ny * pl.p.g.nz, V);
-        const ArithParams& q = pl.p;
+        ArithParams q = pl.p;
         const uintptr_t phase = reinterpret_cast<uintptr_t>(q.d.base) & 15u;
+        // every row of an operand in one 16-byte phase; a source phase other than dst's is absorbed by shifted loads
         const bool uniform = ((q.d.pitchY | q.d.pitchZ | q.a.pitchY | q.a.pitchZ | q.b.pitchY | q.b.pitchZ) & 15) == 0
-                          && phase == (reinterpret_cast<uintptr_t>(q.a.base) & 15u)
-                          && phase == (reinterpret_cast<uintptr_t>(q.b.base) & 15u)
                           && (long long)q.g.ny * q.g.nz < 0x7fffffffLL;
+        q.shifted = phase != (reinterpret_cast<uintptr_t>(q.a.base) & 15u)
+                 || phase != (reinterpret_cast<uintptr_t>(q.b.base) & 15u);
         if (uniform)
-            arithRowsUniformKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p, (int)(phase / bytesPerVoxel(F)));
+            arithRowsUniformKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
         else
             arithRowsKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p);
     }
@@ -102,6 +103,9 @@ cudaError_t launchArith(const LaunchCtx& c, int op, const VolDesc& dst, const Vo
     pl.p.b = operandAt(s2, first[0], first[1], first[2]);
     pl.p.md = dst.map; pl.p.ma = s1.map; pl.p.mb = s2.map;
     pl.p.alias = (overlaps(dst, s1) || overlaps(dst, s2)) ? 1 : 0;
+    pl.p.aEnd = s1.data + (size_t)s1.dims[0] * s1.dims[1] * s1.dims[2] * bytesPerVoxel(s1.format);
+    pl.p.bEnd = s2.data + (size_t)s2.dims[0] * s2.dims[1] * s2.dims[2] * bytesPerVoxel(s2.format);
+    pl.p.shifted = 0;
     pl.fd = dst.format; pl.fa = s1.format; pl.fb = s2.format;
     pl.homogeneous = pl.fd == pl.fa && pl.fd == pl.fb;
     pl.identity = dst.map.identity && s1.map.identity && s2.map.identity;

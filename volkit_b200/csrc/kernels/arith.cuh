@@ -32,6 +32,9 @@ struct ArithParams
     Range   g;
     Mapping md, ma, mb;
     int     alias;        // a source overlaps dst (in-place use): no non-coherent loads
+    const uint8_t* aEnd;  // one past the last byte of each source volume (bounds the funnel-shifted loads)
+    const uint8_t* bEnd;
+    int     shifted;      // uniform kernel: a source row sits at another 16-byte phase than the dst row
 };
 
 // Homogeneous formats: one 128-bit vector per operand per chunk.
@@ -207,10 +210,12 @@ arithRowsKernel(ArithParams p)
         uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
         const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
         const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
-        const bool vec = full && ((reinterpret_cast<uintptr_t>(ap) | reinterpret_cast<uintptr_t>(bp)) & 15u) == 0;
-        if (vec) {
-            uint4 va = p.alias ? ldPlain(ap) : ldStream(ap);
-            uint4 vb = p.alias ? ldPlain(bp) : ldStream(bp);
+        const bool aligned = ((reinterpret_cast<uintptr_t>(ap) | reinterpret_cast<uintptr_t>(bp)) & 15u) == 0;
+        if (full && (aligned || (unalignedReadable(ap, p.aEnd) && unalignedReadable(bp, p.bEnd)))) {
+            uint4 va, vb;
+            if (!aligned)     { va = ldUnaligned(ap, p.alias); vb = ldUnaligned(bp, p.alias); }
+            else if (p.alias) { va = ldPlain(ap); vb = ldPlain(bp); }
+            else              { va = ldStream(ap); vb = ldStream(bp); }
             uint32_t w[4] = { 0u, 0u, 0u, 0u };
 #pragma unroll
             for (int i = 0; i < V; ++i)
@@ -240,7 +245,8 @@ arithRowsUniformKernel(ArithParams p, int shift)
             const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
             const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
             ArithPair q;
-            if (p.alias) { q.a = ldPlain(ap); q.b = ldPlain(bp); }
+            if (p.shifted)    { q.a = ldUnalignedWithin(ap, p.aEnd, p.alias); q.b = ldUnalignedWithin(bp, p.bEnd, p.alias); }
+            else if (p.alias) { q.a = ldPlain(ap); q.b = ldPlain(bp); }
             else         { q.a = ldStream(ap); q.b = ldStream(bp); }
             return q;
         },

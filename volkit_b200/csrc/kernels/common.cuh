@@ -31,6 +31,42 @@ __device__ __forceinline__ void stStream(void* p, const uint4& v)
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// 16 bytes from an address of any alignment: the two enclosing aligned vectors, word-rotated and funnel-shifted
+// (a *Range call whose sources sit at another 16-byte phase than the destination would otherwise fall back to
+// per-voxel loads).  Both vectors go through L1 (the neighbouring thread re-reads `hi` as its `lo`).  The caller
+// guarantees that the second vector is readable: (p & ~15) + 32 <= end of the buffer.  `coherent`: the source may
+// alias memory this kernel writes.
+__device__ __forceinline__ uint4 ldUnaligned(const uint8_t* p, bool coherent = false)
+{
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint4* v = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
+    const unsigned sh = (unsigned)a & 15u;
+    const uint4 lo = coherent ? *v : __ldg(v);
+    if (sh == 0) return lo;
+    const uint4 hi = coherent ? v[1] : __ldg(v + 1);
+    uint32_t w0 = lo.x, w1 = lo.y, w2 = lo.z, w3 = lo.w, w4 = hi.x, w5 = hi.y;
+    if (sh & 8u) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = hi.z; w5 = hi.w; }
+    if (sh & 4u) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; }
+    const unsigned bits = (sh & 3u) * 8u;
+    return make_uint4(__funnelshift_r(w0, w1, bits), __funnelshift_r(w1, w2, bits),
+                      __funnelshift_r(w2, w3, bits), __funnelshift_r(w3, w4, bits));
+}
+// whether ldUnaligned(p) stays inside a buffer that ends at `end`
+__device__ __forceinline__ bool unalignedReadable(const uint8_t* p, const uint8_t* end)
+{
+    return (reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)15) + 32u <= reinterpret_cast<uintptr_t>(end)
+        || (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+
+// ldUnaligned with the (rare) byte-wise fallback for the one chunk whose second vector would leave the buffer
+__device__ __forceinline__ uint4 ldUnalignedWithin(const uint8_t* p, const uint8_t* end, bool coherent = false)
+{
+    if (unalignedReadable(p, end)) return ldUnaligned(p, coherent);
+    uint32_t w[4] = { 0u, 0u, 0u, 0u };
+    for (int i = 0; i < 16; ++i) w[i >> 2] |= (uint32_t)p[i] << ((i & 3) * 8);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 __device__ __forceinline__ void stStream32(void* p, uint32_t v)
 {
     asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");

@@ -36,6 +36,8 @@ Mapping makeMapping(float lo, float hi);
 cudaError_t launchFill(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], float value);
 cudaError_t launchCopy(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
                        const int32_t last[3], const int32_t off[3]);
+cudaError_t launchCopyBatch(const LaunchCtx&, int n, const VolDesc* dsts, const VolDesc& src, const int32_t* firsts,
+                            const int32_t* lasts, const int32_t* offs);
 cudaError_t launchArith(const LaunchCtx&, int op, const VolDesc& dst, const VolDesc& s1, const VolDesc& s2,
                         const int32_t first[3], const int32_t last[3], const int32_t off[3]);
 cudaError_t launchTransform1(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], int op);

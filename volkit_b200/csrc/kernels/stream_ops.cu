@@ -4,6 +4,7 @@
 // Copy     reference src/vkt/Copy_serial.hpp:13-82      dst[p-first+off] = src[clamp(p)]             2 bpv (or bpv_s+bpv_d)
 // Memset   reference src/vkt/Memory_cuda.cu:15-49       dst[i*pat .. ] = pattern                     dstBytes
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 #include "launch.hpp"
@@ -110,7 +111,9 @@ struct CopyParams
 {
     Operand d;            // dst at dstOffset
     const uint8_t* s;     // src volume base
+    const uint8_t* sEnd;  // one past its last byte
     int sx, sy, sz;       // src dims
+    int shifted;          // uniform kernel: src rows sit at another 16-byte phase than dst rows
     Range g;              // x0,y0,z0 = first (may be negative: clamped)
     Mapping md, ms;
     int fd, fs;
@@ -129,8 +132,11 @@ copyRowsKernel(CopyParams p)
         uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
         const int ax = p.g.x0 + xr;   // absolute src x of the chunk's first voxel
         const uint8_t* sp = srow + (long long)ax * BPV;
-        if (full && ax >= 0 && ax + V <= p.sx && (reinterpret_cast<uintptr_t>(sp) & 15u) == 0) {
+        const bool whole = full && ax >= 0 && ax + V <= p.sx;   // nothing to clamp in this chunk
+        if (whole && (reinterpret_cast<uintptr_t>(sp) & 15u) == 0) {
             stStream(dp, ldStream(sp));
+        } else if (whole && unalignedReadable(sp, p.sEnd)) {
+            stStream(dp, ldUnaligned(sp));
         } else {
             for (int i = 0; i < n; ++i)
                 storeRaw(dp + i * BPV, BPV, loadRaw(srow + (long long)clampi(ax + i, 0, p.sx - 1) * BPV, BPV));
@@ -138,7 +144,8 @@ copyRowsKernel(CopyParams p)
     });
 }
 
-// bytewise copy of a box whose rows share one 16-byte phase in dst and src and need no clamping
+// bytewise copy of a box that needs no clamping and whose rows share one 16-byte phase per operand (p.shifted: the
+// src phase differs from the dst phase -> funnel-shifted loads)
 template <int BPV>
 __global__ void __launch_bounds__(kThreads)
 copyRowsUniformKernel(CopyParams p, int shift)
@@ -147,13 +154,202 @@ copyRowsUniformKernel(CopyParams p, int shift)
     const uint8_t* s0 = p.s + (((long long)p.g.z0 * p.sy + p.g.y0) * (long long)p.sx + p.g.x0) * BPV;
     const long long spy = (long long)p.sx * BPV, spz = spy * p.sy;
     forEachRowChunkUniform<V, 4, uint4>(p.g, shift,
-        [&](int y, int z, int xr) { return ldStream(s0 + y * spy + z * spz + (long long)xr * BPV); },
+        [&](int y, int z, int xr) {
+            const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
+            return p.shifted ? ldUnalignedWithin(sp, p.sEnd) : ldStream(sp);
+        },
         [&](int y, int z, int xr, const uint4& q) { stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, q); },
         [&](int y, int z, int xr, int n) {
             const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
             uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
             for (int i = 0; i < n; ++i) storeRaw(dp + i * BPV, BPV, loadRaw(sp + i * BPV, BPV));
         });
+}
+
+// ---------------------------------------------------------------- Copy, many boxes of one source -----------
+// BrickDecompose (reference src/vkt/Decompose_serial.hpp:15-48) is a loop of CopyRange(dest[index], source, first,
+// last) calls; at 64^3 bricks a 2048^3 volume makes 32768 of them, far too many launches.  One launch instead:
+// blockIdx.y picks the box, blockIdx.x a group of its z planes; rows are walked two at a time (two 128-bit loads in
+// flight per thread), chunks cut at 16-byte boundaries of the dst row, the src side clamped and funnel-shifted.
+struct BoxRec
+{
+    uint8_t*  d;                // dst voxel that receives the box's first voxel
+    long long pitchY, pitchZ;   // dst pitches in bytes
+    int nx, ny, nz;             // extents of [first, last)
+    int x0, y0, z0;             // first (may be negative: clamped)
+    unsigned nvox;              // flat kernel: nx*ny*nz (< 2^31)
+    unsigned mulX, mulY;        // e / nx == (e * mulX) >> shX for e < 2^31 (likewise ny): no division per vector
+    int shX, shY;
+};
+
+// floor(e / d) for e < 2^31 as one widening multiply and a shift: m = ceil(2^(31+l) / d), l = ceil(log2 d).
+// The error e*r/(d*2^(31+l)) stays below 2^-l <= 1/d, so the floor never moves.
+inline void magicDivisor(unsigned d, unsigned& mul, int& sh)
+{
+    int l = 0;
+    while ((1ull << l) < d) ++l;
+    const unsigned long long p = 1ull << (31 + l);
+    mul = (unsigned)((p + d - 1) / d);
+    sh = 31 + l;
+}
+__device__ __forceinline__ unsigned magicDiv(unsigned e, unsigned mul, int sh)
+{
+    return (unsigned)(((unsigned long long)e * mul) >> sh);
+}
+
+// Boxes that fill their destination volume completely (every brick of a decomposition does) are ONE contiguous run
+// of dst bytes: cut it into aligned 128-bit vectors regardless of the rows (a 66-voxel UInt16 row is 132 bytes: cut
+// per row, two of its ten chunks would be partial).  A vector lies in one src row or straddles two; each piece is
+// one (funnel-shifted) 128-bit load and the two are merged bytewise, so every lane of a warp runs the same code
+// (ncu on the first version, which gathered the straddling vectors voxel by voxel: 12 of 32 lanes active on
+// average, 25 % of the HBM roofline).  Only vectors that touch the clamped x border of the volume, or the first /
+// last partial vector of a box, are gathered per voxel.  Four vectors in flight per thread.
+template <int BPV>
+__global__ void __launch_bounds__(kThreads)
+copyBoxesFlatKernel(const BoxRec* __restrict__ boxes, const uint8_t* __restrict__ s, const uint8_t* sEnd,
+                    int sx, int sy, int sz)
+{
+    constexpr int V = 16 / BPV;
+    constexpr int U = 4;
+    // blockIdx.x = box, blockIdx.y = which 1024 vectors of it: CTAs that run together work on the SAME rows of
+    // consecutive boxes, i.e. on x-adjacent bricks whose src pieces are neighbours in one src row -- with the box as
+    // the slow index each 128-byte piece of a src row was fetched at a different time (54 % of the roofline for
+    // aligned 64^3 bricks)
+    const BoxRec b = boxes[blockIdx.x];
+    const int shift = (int)((reinterpret_cast<uintptr_t>(b.d) & 15u) / BPV);
+    const unsigned nvec = (b.nvox + shift + V - 1) / V;
+    const unsigned k0 = blockIdx.y * (kThreads * U) + threadIdx.x;
+    if (blockIdx.y * (kThreads * U) >= nvec) return;
+    const long long rowBytes = (long long)sx * BPV;
+    auto srcRow = [&](int y, int z) {
+        return s + ((long long)clampi(b.z0 + z, 0, sz - 1) * sy + clampi(b.y0 + y, 0, sy - 1)) * rowBytes;
+    };
+    // 16 bytes at any phase, or false when the funnel-shifted load would leave the src buffer
+    auto load16 = [&](const uint8_t* sp, uint4& q) {
+        if (sp < s) return false;
+        if ((reinterpret_cast<uintptr_t>(sp) & 15u) == 0) { q = ldStream(sp); return true; }
+        if (!unalignedReadable(sp, sEnd)) return false;
+        q = ldUnaligned(sp);
+        return true;
+    };
+
+    struct Item { uint8_t* dp; int x, y, z, n, mode; uint4 q; };
+    Item it[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        Item& t = it[u];
+        const unsigned k = k0 + u * kThreads;
+        t.mode = 0;
+        if (k >= nvec) continue;
+        long long e = (long long)k * V - shift;
+        int n = V;
+        if (e < 0) { n += (int)e; e = 0; }
+        if (e + n > (long long)b.nvox) n = (int)(b.nvox - e);
+        const unsigned row = magicDiv((unsigned)e, b.mulX, b.shX);
+        t.x = (int)((unsigned)e - row * (unsigned)b.nx);
+        t.z = (int)magicDiv(row, b.mulY, b.shY);
+        t.y = (int)(row - (unsigned)t.z * (unsigned)b.ny);
+        t.n = n;
+        t.dp = b.d + e * BPV;
+        t.mode = 2;
+        if (n != V || b.nx < V) continue;
+        const int nA = min(V, b.nx - t.x);           // voxels of the vector that lie in its first row
+        const int ax = b.x0 + t.x;
+        if (ax < 0 || ax + nA > sx) continue;        // clamped border: gather
+        uint4 qa;
+        if (!load16(srcRow(t.y, t.z) + (long long)ax * BPV, qa)) continue;
+        if (nA < V) {
+            if (b.x0 < 0 || b.x0 + (V - nA) > sx) continue;
+            int y1 = t.y + 1, z1 = t.z;
+            if (y1 == b.ny) { y1 = 0; ++z1; }
+            // the second row's voxels land at byte nA*BPV of the vector: load from nA voxels before its start
+            uint4 qb;
+            if (!load16(srcRow(y1, z1) + ((long long)b.x0 - nA) * BPV, qb)) continue;
+            const int split = nA * BPV;              // bytes [0, split) from qa, the rest from qb
+            const uint32_t a[4] = { qa.x, qa.y, qa.z, qa.w }, c[4] = { qb.x, qb.y, qb.z, qb.w };
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int kb = min(max(split - 4 * i, 0), 4);
+                const uint32_t m = kb == 4 ? 0xffffffffu : ((1u << (8 * kb)) - 1u);
+                w[i] = (a[i] & m) | (c[i] & ~m);
+            }
+            qa = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        t.q = qa;
+        t.mode = 1;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const Item& t = it[u];
+        if (t.mode == 1) stStream(t.dp, t.q);
+        else if (t.mode == 2) {
+            uint32_t w[4] = { 0u, 0u, 0u, 0u };
+            int x = t.x, y = t.y, z = t.z;
+            const uint8_t* srow = srcRow(y, z);
+            for (int i = 0; i < t.n; ++i) {
+                const uint32_t raw = loadRaw(srow + (long long)clampi(b.x0 + x, 0, sx - 1) * BPV, BPV);
+                if (t.n == V) w[(i * BPV) >> 2] |= raw << (((i * BPV) & 3) * 8);
+                else storeRaw(t.dp + i * BPV, BPV, raw);
+                if (++x == b.nx) {
+                    x = 0;
+                    if (++y == b.ny) { y = 0; ++z; }
+                    srow = srcRow(y, z);
+                }
+            }
+            if (t.n == V) stStream(t.dp, make_uint4(w[0], w[1], w[2], w[3]));
+        }
+    }
+}
+
+template <int BPV>
+__global__ void __launch_bounds__(kThreads)
+copyBoxesKernel(const BoxRec* __restrict__ boxes, const uint8_t* __restrict__ s, const uint8_t* sEnd,
+                int sx, int sy, int sz, int zPer)
+{
+    constexpr int V = 16 / BPV;
+    const BoxRec b = boxes[blockIdx.y];
+    const int zBeg = blockIdx.x * zPer;
+    if (zBeg >= b.nz) return;
+    const int rows = (min(zBeg + zPer, b.nz) - zBeg) * b.ny;
+    const int chunks = (b.nx + V - 1) / V + 1;
+
+    struct Item { uint8_t* dp; const uint8_t* srow; int ax, n, mode; uint4 q; };
+    auto prepare = [&](int r, int chunk, Item& it) {
+        it.mode = 0;
+        if (r >= rows) return;
+        const int zz = r / b.ny, y = r - zz * b.ny, z = zBeg + zz;
+        uint8_t* drow = b.d + y * b.pitchY + z * b.pitchZ;
+        const int shift = (int)((reinterpret_cast<uintptr_t>(drow) & 15u) / BPV);
+        int xr = chunk * V - shift, n = V;
+        if (xr < 0) { n += xr; xr = 0; }
+        if (xr + n > b.nx) n = b.nx - xr;
+        if (n <= 0) return;
+        const int cy = clampi(b.y0 + y, 0, sy - 1), cz = clampi(b.z0 + z, 0, sz - 1);
+        it.srow = s + ((long long)cz * sy + cy) * (long long)sx * BPV;
+        it.dp = drow + (long long)xr * BPV;
+        it.ax = b.x0 + xr;
+        it.n = n;
+        const uint8_t* sp = it.srow + (long long)it.ax * BPV;
+        const bool whole = n == V && it.ax >= 0 && it.ax + V <= sx;
+        if (whole && (reinterpret_cast<uintptr_t>(sp) & 15u) == 0) { it.mode = 1; it.q = ldStream(sp); }
+        else if (whole && unalignedReadable(sp, sEnd))             { it.mode = 1; it.q = ldUnaligned(sp); }
+        else it.mode = 2;
+    };
+    auto finish = [&](const Item& it) {
+        if (it.mode == 1) stStream(it.dp, it.q);
+        else if (it.mode == 2)
+            for (int i = 0; i < it.n; ++i)
+                storeRaw(it.dp + i * BPV, BPV, loadRaw(it.srow + (long long)clampi(it.ax + i, 0, sx - 1) * BPV, BPV));
+    };
+    for (int chunk = threadIdx.x; chunk < chunks; chunk += blockDim.x)
+        for (int r = threadIdx.y; r < rows; r += 2 * blockDim.y) {
+            Item i0, i1;
+            prepare(r, chunk, i0);
+            prepare(r + blockDim.y, chunk, i1);
+            finish(i0);
+            finish(i1);
+        }
 }
 
 // ---------------------------------------------------------------- Copy (by value) ------------------------
@@ -328,6 +524,8 @@ cudaError_t launchCopy(const LaunchCtx& c, const VolDesc& dst, const VolDesc& sr
     p.s = src.data; p.sx = src.dims[0]; p.sy = src.dims[1]; p.sz = src.dims[2];
     p.md = dst.map; p.ms = src.map; p.fd = dst.format; p.fs = src.format;
     const int bd = bytesPerVoxel(dst.format), bs = bytesPerVoxel(src.format);
+    p.sEnd = src.data + (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bs;
+    p.shifted = 0;
     // reference Copy_serial.hpp:21-22: bytes iff format AND mapping (float ==) agree
     const bool bytewise = dst.format == src.format && dst.map.lo == src.map.lo && dst.map.hi == src.map.hi;
     const bool inside = first[0] >= 0 && first[1] >= 0 && first[2] >= 0
@@ -345,9 +543,9 @@ cudaError_t launchCopy(const LaunchCtx& c, const VolDesc& dst, const VolDesc& sr
             // all rows in one 16-byte phase, src == dst phase, nothing to clamp: several rows in flight per thread
             const long long spy = (long long)src.dims[0] * bs, spz = spy * src.dims[1];
             const bool uniform = inside && (p.d.pitchY % 16) == 0 && (p.d.pitchZ % 16) == 0 && (spy % 16) == 0 && (spz % 16) == 0
-                              && ((reinterpret_cast<uintptr_t>(p.d.base) ^ reinterpret_cast<uintptr_t>(s0)) & 15u) == 0
                               && (long long)g.ny * g.nz < 0x7fffffffLL;
             if (uniform) {
+                p.shifted = ((reinterpret_cast<uintptr_t>(p.d.base) ^ reinterpret_cast<uintptr_t>(s0)) & 15u) != 0;
                 const int shift = (int)((reinterpret_cast<uintptr_t>(p.d.base) & 15u) / bd);
                 if (bd == 1) copyRowsUniformKernel<1><<<l.grid, l.block, 0, c.stream>>>(p, shift);
                 else if (bd == 2) copyRowsUniformKernel<2><<<l.grid, l.block, 0, c.stream>>>(p, shift);
@@ -367,6 +565,99 @@ cudaError_t launchCopy(const LaunchCtx& c, const VolDesc& dst, const VolDesc& sr
     return launchConvertRows(c, dst, src, first, last, off);
 }
 
+// n boxes of one source in one launch (bytewise case); converting boxes go through launchCopy one by one.
+cudaError_t launchCopyBatch(const LaunchCtx& c, int n, const VolDesc* dsts, const VolDesc& src, const int32_t* firsts,
+                            const int32_t* lasts, const int32_t* offs)
+{
+    if (n <= 0) return cudaSuccess;
+    if (src.dims[0] <= 0 || src.dims[1] <= 0 || src.dims[2] <= 0) return cudaErrorInvalidValue;
+    const int bs = bytesPerVoxel(src.format);
+    std::vector<BoxRec> recs, flats;   // row-wise boxes / boxes that are one contiguous run of dst bytes
+    recs.reserve((size_t)n);
+    flats.reserve((size_t)n);
+    int maxNx = 0, maxNz = 0;
+    long long maxPlane = 0;
+    unsigned maxVox = 0;
+    for (int i = 0; i < n; ++i) {
+        const VolDesc& dst = dsts[i];
+        const int32_t* f = firsts + 3 * i; const int32_t* l = lasts + 3 * i; const int32_t* o = offs + 3 * i;
+        const bool bytewise = dst.format == src.format && dst.map.lo == src.map.lo && dst.map.hi == src.map.hi;
+        if (!bytewise) {
+            cudaError_t e = launchCopy(c, dst, src, f, l, o);
+            if (e != cudaSuccess) return e;
+            continue;
+        }
+        BoxRec r;
+        r.nx = l[0] - f[0]; r.ny = l[1] - f[1]; r.nz = l[2] - f[2];
+        if (r.nx <= 0 || r.ny <= 0 || r.nz <= 0) continue;
+        const Operand d = operandAt(dst, o[0], o[1], o[2]);
+        r.d = d.base; r.pitchY = d.pitchY; r.pitchZ = d.pitchZ;
+        r.x0 = f[0]; r.y0 = f[1]; r.z0 = f[2];
+        r.nvox = 0; r.mulX = r.mulY = 0; r.shX = r.shY = 0;
+        const long long vox = (long long)r.nx * r.ny * r.nz;
+        Range g; g.nx = r.nx; g.ny = r.ny; g.nz = r.nz; g.x0 = g.y0 = g.z0 = 0;
+        if (contiguous(dst, g) && vox < (long long)65535 * kThreads * 4 * (16 / bs)) {   // grid.y of the flat kernel
+            r.nvox = (unsigned)vox;
+            magicDivisor((unsigned)r.nx, r.mulX, r.shX);
+            magicDivisor((unsigned)r.ny, r.mulY, r.shY);
+            flats.push_back(r);
+            maxVox = r.nvox > maxVox ? r.nvox : maxVox;
+            continue;
+        }
+        recs.push_back(r);
+        maxNx = r.nx > maxNx ? r.nx : maxNx;
+        maxNz = r.nz > maxNz ? r.nz : maxNz;
+        const long long plane = (long long)r.nx * r.ny * bs;
+        maxPlane = plane > maxPlane ? plane : maxPlane;
+    }
+    if (recs.empty() && flats.empty()) return cudaSuccess;
+
+    const size_t nFlat = flats.size();
+    flats.insert(flats.end(), recs.begin(), recs.end());   // one table: flat boxes first
+    BoxRec* dev = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&dev, flats.size() * sizeof(BoxRec), c.stream);
+    if (e != cudaSuccess) return e;
+    // pageable source: the runtime stages the table before returning, the vectors may die with this frame
+    e = cudaMemcpyAsync(dev, flats.data(), flats.size() * sizeof(BoxRec), cudaMemcpyHostToDevice, c.stream);
+    if (e != cudaSuccess) { cudaFreeAsync(dev, c.stream); return e; }
+    const uint8_t* sEnd = src.data + (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bs;
+
+    if (nFlat) {
+        const unsigned perCta = kThreads * 4 * (16 / bs);                 // voxels per CTA
+        const unsigned gx = (maxVox + (16 / bs) + perCta - 1) / perCta;   // + one vector for a misaligned head
+        const size_t perLaunch = 0x7fffffff;
+        for (size_t b0 = 0; b0 < nFlat && e == cudaSuccess; b0 += perLaunch) {
+            dim3 grid((unsigned)(nFlat - b0 < perLaunch ? nFlat - b0 : perLaunch), gx, 1);
+            if (bs == 1) copyBoxesFlatKernel<1><<<grid, kThreads, 0, c.stream>>>(dev + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+            else if (bs == 2) copyBoxesFlatKernel<2><<<grid, kThreads, 0, c.stream>>>(dev + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+            else copyBoxesFlatKernel<4><<<grid, kThreads, 0, c.stream>>>(dev + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+            countLaunch();
+            e = cudaGetLastError();
+        }
+    }
+    if (recs.empty() || e != cudaSuccess) { cudaFreeAsync(dev, c.stream); return e; }
+    BoxRec* devRows = dev + nFlat;
+
+    // ~64 KiB of dst per CTA, but never fewer CTAs than two waves of the machine
+    int zPer = (int)((65536 + maxPlane - 1) / maxPlane);
+    if (zPer < 1) zPer = 1;
+    while (zPer > 1 && (long long)recs.size() * ((maxNz + zPer - 1) / zPer) < 2LL * c.smCount * 8) zPer = (zPer + 1) / 2;
+    const RowsLaunch l = rowsLaunch(maxNx, 1, 16 / bs);
+    const unsigned gx = (unsigned)((maxNz + zPer - 1) / zPer);
+    for (size_t b0 = 0; b0 < recs.size(); b0 += 65535) {
+        const unsigned gy = (unsigned)(recs.size() - b0 < 65535 ? recs.size() - b0 : 65535);
+        dim3 grid(gx, gy, 1);
+        if (bs == 1) copyBoxesKernel<1><<<grid, l.block, 0, c.stream>>>(devRows + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        else if (bs == 2) copyBoxesKernel<2><<<grid, l.block, 0, c.stream>>>(devRows + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        else copyBoxesKernel<4><<<grid, l.block, 0, c.stream>>>(devRows + b0, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        countLaunch();
+        e = cudaGetLastError();
+        if (e != cudaSuccess) break;
+    }
+    cudaFreeAsync(dev, c.stream);
+    return e;
+}
+
 // generic converting copy (runtime formats, clamped src), always by value
 cudaError_t launchConvertRows(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
                               const int32_t last[3], const int32_t off[3])
@@ -378,6 +669,8 @@ cudaError_t launchConvertRows(const LaunchCtx& c, const VolDesc& dst, const VolD
     if (g.nx <= 0 || g.ny <= 0 || g.nz <= 0) return cudaSuccess;
     p.d = operandAt(dst, off[0], off[1], off[2]);
     p.s = src.data; p.sx = src.dims[0]; p.sy = src.dims[1]; p.sz = src.dims[2];
+    p.sEnd = src.data + (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bytesPerVoxel(src.format);
+    p.shifted = 0;
     p.md = dst.map; p.ms = src.map; p.fd = dst.format; p.fs = src.format;
     long long rows = (long long)g.ny * g.nz;
     dim3 grid((unsigned)((g.nx + kThreads - 1) / kThreads), (unsigned)(rows > 65535 ? 65535 : rows), 1);
