@@ -63,6 +63,10 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
     for axis, name in ((0, "X"), (1, "Y (mirrors y and z, as the reference)")):
         record(f"Flip {name} {S}^3 UInt16", n, 4 * (n if S % 2 == 0 else n - S * S),
                lambda: capi.check(lib.vktb_flip_range(ctypes.byref(dd), ctypes.byref(da), z3, l3, z3, axis)))
+    # Scan, in place: x, y and z prefix passes
+    record(f"Scan {S}^3 UInt16 in place", n, 4 * n,
+           lambda: capi.check(lib.vktb_scan_range(ctypes.byref(dd), ctypes.byref(dd), z3, l3, z3)),
+           "alg_bytes = one read + one write per voxel (the ideal single pass); the kernel makes three passes")
     # BrickDecompose: 64^3 bricks, halo 1 on every side, all bricks in ONE launch
     bs, halo = 64, 1
     nb = (S + bs - 1) // bs

@@ -151,6 +151,14 @@ int vktb_resample_window_src_range3(int filter, int32_t dst_z0, int32_t dst_z1, 
  * source (in place, dst_offset 0).  Both volumes must have the same bytes per voxel. */
 int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                     const int32_t dst_offset[3], int axis);
+
+/* ScanRange_cuda(StructuredVolume& dst, StructuredVolume& src, Vec3i first, Vec3i last,
+ * Vec3i dstOffset) (src/vkt/Scan_cuda.hpp:11-17); semantics of ScanRange_serial (src/vkt/Scan_serial.hpp:18-152): dst
+ * receives CopyRange(dst, src, first, last, dst_offset) unless dst is src (same data pointer), then the 3-D
+ * inclusive prefix sum of the raw voxel integers, modulo 2^(8 bytesPerVoxel), over [first, last) + dst_offset,
+ * accumulating from `first` towards `last` on each axis (first > last = right to left; in place only). */
+int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                    const int32_t dst_offset[3]);
 /* ComputeHistogramRange_cuda(StructuredVolume&, Histogram&, Vec3i first, Vec3i last)
  * (src/vkt/Histogram_cuda.hpp:12-17); semantics of ComputeHistogramRange_serial (src/vkt/Histogram_serial.hpp:18-51):
  * bins (DEVICE pointer, num_bins 64-bit counters = Histogram::getBinCounts() under the GPU policy) are zeroed, then

@@ -84,6 +84,7 @@ class _Lib:
         f("resample", ctypes.c_int, [p, p, ctypes.c_int])
         f("flip_range", ctypes.c_int, [p, p, I3, I3, I3, ctypes.c_int])
         f("histogram_range", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p])
+        f("scan_range", ctypes.c_int, [p, p, I3, I3, I3])
         i32p = ctypes.POINTER(ctypes.c_int32)
         f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
         f("brick_decompose", ctypes.c_int, [p, I3, I3, I3, ctypes.c_void_p, ctypes.c_size_t])
@@ -137,6 +138,10 @@ class _Lib:
         assert self._histogram_range(ctypes.byref(vol.c()), I3(*first), I3(*last), bins.ctypes.data, num_bins,
                                      dropped.ctypes.data) == 0
         return bins, int(dropped[0])
+
+    def scan_range(self, dst: Vol, src: Vol, first, last, off=(0, 0, 0)):
+        """src may be dst itself (in place; then first > last on an axis scans right to left)"""
+        assert self._scan_range(ctypes.byref(dst.c()), ctypes.byref(src.c()), I3(*first), I3(*last), I3(*off)) == 0
 
     def brick_layout(self, sdims, brick, halo_neg=(0, 0, 0), halo_pos=(0, 0, 0)):
         """BrickDecomposeResize: (num_bricks (x, y, z), [brick dims (x, y, z), ...] in x-fastest brick order)"""

@@ -30,6 +30,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
 #include <vkt/Voxel.hpp>
@@ -284,6 +285,26 @@ int ref_histogram_range(RefVol const* vol, int32_t const* first, int32_t const* 
     std::size_t* c = h.getBinCounts();
     for (size_t i = 0; i < numBins; ++i) bins[i] = (uint64_t)c[i];
     if (dropped) *dropped = 0;
+    return 0;
+}
+
+// vkt::ScanRange (include/cpp/vkt/Scan.hpp -> src/vkt/Scan.cpp:53-71).  Same data pointer = the in-place call on ONE
+// volume object (the reference tests &dst != &src).
+int ref_scan_range(RefVol const* dst, RefVol const* src, int32_t const* first, int32_t const* last, int32_t const* off)
+{
+    for (int a = 0; a < 3; ++a) {
+        if (first[a] == last[a]) return -1;
+        if (dst->data != src->data && first[a] > last[a]) return -1;
+    }
+    if (dst->data == src->data) {
+        Staged v(dst);
+        vkt::ScanRange(v.vol, v.vol, v3(first), v3(last), v3(off));
+        v.writeBack();
+        return 0;
+    }
+    Staged d(dst), s(src);
+    vkt::ScanRange(d.vol, s.vol, v3(first), v3(last), v3(off));
+    d.writeBack();
     return 0;
 }
 

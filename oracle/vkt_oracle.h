@@ -61,6 +61,10 @@ int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3
 int vko_histogram_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                         size_t num_bins, uint64_t* dropped);
 
+/* 3-D prefix sum of the raw voxel integers mod 2^(8 bpv); dst->data == src->data means in place */
+int vko_scan_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
+                   const int32_t off[3]);
+
 /* BrickDecomposeResize's layout (num_bricks[3]; brick_dims = 3 ints per brick in x-fastest brick order, may be
  * NULL) -> total voxels of all bricks; vko_brick_decompose writes the bricks back to back into out */
 size_t vko_brick_layout(const int32_t src_dims[3], const int32_t brick[3], const int32_t halo_neg[3],

@@ -21,6 +21,18 @@ BRICK_CASES = [((16, 12, 10), (8, 4, 5), (0, 0, 0), (0, 0, 0)), ((17, 13, 9), (8
                ((9, 9, 9), (16, 16, 16), (1, 2, 3), (3, 2, 1)), ((12, 1, 5), (4, 1, 2), (0, 0, 0), (1, 0, 0))]
 
 
+# ScanRange: (dst dims, src dims, first, last, dstOffset, in place)
+SCAN_CASES = [((12, 9, 7), (12, 9, 7), (0, 0, 0), (12, 9, 7), (0, 0, 0), False),
+              ((12, 9, 7), (12, 9, 7), (0, 0, 0), (12, 9, 7), (0, 0, 0), True),
+              ((20, 14, 11), (12, 9, 7), (1, 2, 1), (11, 8, 6), (5, 3, 4), False),
+              ((17, 9, 8), (17, 9, 8), (3, 1, 2), (16, 8, 7), (0, 0, 0), True),
+              ((17, 9, 8), (17, 9, 8), (15, 1, 2), (2, 8, 7), (0, 0, 0), True),      # x right to left
+              ((17, 9, 8), (17, 9, 8), (3, 7, 6), (16, 0, 1), (0, 0, 0), True),      # y, z downwards
+              ((16, 8, 8), (16, 8, 8), (15, 7, 7), (-1, -1, -1), (0, 0, 0), True),   # every axis reversed, whole volume
+              ((40, 3, 2), (40, 3, 2), (0, 0, 0), (40, 1, 1), (0, 1, 1), False),     # a single row
+              ((5, 6, 40), (5, 6, 40), (2, 0, 0), (3, 6, 40), (0, 0, 0), True)]      # one voxel wide
+
+
 def mk(dims, fmt, seed, lo=0.0, hi=1.0):
     return po.Vol(po.synth(dims, fmt, seed), fmt, lo, hi)
 
@@ -89,6 +101,13 @@ def cases():
         for nb in (7, 256, 5000):
             out.append((f"hist/{fmt}/{lo}/{nb}", "hist",
                         dict(dims=(31, 14, 9), fmt=fmt, lo=lo, hi=hi, first=(1, 0, 2), last=(30, 13, 9), bins=nb)))
+    # --- BrickDecompose and Scan (rank 4)
+    for fmt in (U8, U16, F32):
+        for i, (sdims, brick, neg, pos) in enumerate(BRICK_CASES):
+            out.append((f"bricks/{fmt}/{i}", "bricks", dict(sdims=sdims, fmt=fmt, brick=brick, neg=neg, pos=pos)))
+        for i, (ddims, sdims, first, last, off, inplace) in enumerate(SCAN_CASES):
+            out.append((f"scan/{fmt}/{i}", "scan",
+                        dict(ddims=ddims, sdims=sdims, fmt=fmt, first=first, last=last, off=off, inplace=inplace)))
     # --- BASELINE config 1 (CLI pipeline on a 64^3 uint8 volume -> 32^3 uint16)
     out.append(("cli/config1", "cli1", dict()))
     return out
@@ -138,6 +157,17 @@ def run_case(lib, case) -> list[np.ndarray]:
         bins, dropped = lib.histogram_range(v, p["first"], p["last"], p["bins"])
         assert dropped == 0, "case must stay inside the reference's defined behaviour"
         return [bins]
+    if kind == "bricks":
+        s = mk(p["sdims"], p["fmt"], 3, -1000.0, 3000.0)
+        return list(lib.brick_decompose(s, p["brick"], p["neg"], p["pos"]))
+    if kind == "scan":
+        s = mk(p["sdims"], p["fmt"], 2)
+        if p["inplace"]:
+            lib.scan_range(s, s, p["first"], p["last"], p["off"])
+            return [s.a]
+        d = mk(p["ddims"], p["fmt"], 5)
+        lib.scan_range(d, s, p["first"], p["last"], p["off"])
+        return [d.a]
     if kind == "cli1":
         # declare-sv 64^3 uint8 | fill 0.1 | fill-range 1 [0,8)^3 | resample --dims 32^3 uint16
         # (reference src/cli/main.cpp:402-442, 521-574, 701-740; the CLI resamples with Nearest, :734)

@@ -16,6 +16,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
 
@@ -139,6 +140,13 @@ int main(int argc, char** argv)
     if (bricks.dims().x != 3 || bricks.dims().y != 3 || bricks.dims().z != 3) return 10;
     CHECK(BrickDecompose(bricks, a, Vec3i{ 20, 16, 16 }, Vec3i{ 1, 2, 0 }, Vec3i{ 2, 1, 1 }));
 
+    // Scan: out of place with a dst offset, then in place and right to left on x
+    StructuredVolume sc(64, 48, 44, DataFormat::UInt16), sci(b);
+    CHECK(Fill(sc, .5f));
+    CHECK(ScanRange(sc, a, Vec3i{ 2, 1, 3 }, Vec3i{ 46, 39, 35 }, Vec3i{ 5, 4, 3 }));
+    CHECK(ScanRange(sci, sci, Vec3i{ 45, 2, 1 }, Vec3i{ 3, 38, 30 }));
+    if (ScanRange(sc, a, Vec3i{ 5, 1, 3 }, Vec3i{ 2, 39, 35 }) != InvalidValue) return 11;
+
     // single-voxel accessors work under either policy
     sum.setValue(1, 2, 3, .75f);
     float back = sum.getValue(1, 2, 3);
@@ -147,6 +155,7 @@ int main(int argc, char** argv)
     SetThreadExecutionPolicy(cpu);
     save(sum, "out_sum.raw"); save(diff, "out_diff.raw"); save(prod, "out_prod.raw"); save(cpy, "out_cpy.raw");
     save(t1, "out_t1.raw"); save(t2, "out_t2.raw"); save(up, "out_up.raw"); save(down, "out_down.raw");
+    save(sc, "out_sc.raw"); save(sci, "out_sci.raw");
     save(fx, "out_fx.raw"); save(fy, "out_fy.raw"); save(fz, "out_fz.raw");
     {
         FILE* f = std::fopen((g_dir + "/out_hist.raw").c_str(), "wb");

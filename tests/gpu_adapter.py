@@ -39,6 +39,15 @@ class GpuLib:
         self._down(d, dst)
         s.free()
 
+    def scan_range(self, dst, src, first, last, off=(0, 0, 0)):
+        d = self._up(dst)
+        s = d if src is dst else self._up(src)
+        capi.check(self.lib.vktb_scan_range(ctypes.byref(d.desc()), ctypes.byref(s.desc()), I3(*first), I3(*last),
+                                            I3(*off)), "scan")
+        self._down(d, dst)
+        if s is not d:
+            s.free()
+
     def copy_range_batch(self, dsts, src, firsts, lasts, offs):
         """n CopyRange calls from one source in ONE vktb_copy_range_batch launch; dsts are updated in place"""
         n = len(dsts)

@@ -218,6 +218,46 @@ def test_range_ops_shifted_rows(gpu):
                 assert a.a.tobytes() == b.a.tobytes(), (fmt, sdims, "clamped")
 
 
+def test_scan_kernels(gpu):
+    """ScanRange (3-D prefix sum of the raw voxel integers): the catalogue's directions / offsets / in-place cases,
+    then shapes that take the warp-per-row x pass and the 16-byte column walk (pitches multiples of 16 bytes), ranges
+    at odd phases (partial head / tail chunks), and sizes whose sums wrap many times."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.UINT32, po.FLOAT32):
+        for ddims, sdims, first, last, off, in_place in cases.SCAN_CASES:
+            src = cases.mk(sdims, fmt, 2, -1000.0, 3000.0)
+            if in_place:
+                a, b = src.copy(), src.copy()
+                o.scan_range(a, a, first, last, off)
+                gpu.scan_range(b, b, first, last, off)
+            else:
+                a, b = cases.mk(ddims, fmt, 5, -1000.0, 3000.0), cases.mk(ddims, fmt, 5, -1000.0, 3000.0)
+                o.scan_range(a, src, first, last, off)
+                gpu.scan_range(b, src, first, last, off)
+            assert a.a.tobytes() == b.a.tobytes(), (fmt, ddims, first, last, off, in_place)
+        for dims, first, last in (((128, 40, 24), (0, 0, 0), (128, 40, 24)), ((128, 40, 24), (3, 1, 2), (125, 39, 23)),
+                                  ((1040, 6, 5), (0, 0, 0), (1040, 6, 5)), ((1040, 6, 5), (7, 1, 0), (1033, 6, 4)),
+                                  ((67, 13, 9), (0, 0, 0), (67, 13, 9)), ((67, 13, 9), (5, 2, 1), (66, 12, 9)),
+                                  ((64, 32, 16), (63, 31, 15), (-1, -1, -1)), ((64, 32, 16), (2, 31, 3), (60, 0, 14))):
+            src = cases.mk(dims, fmt, 4)
+            a, b = src.copy(), src.copy()
+            o.scan_range(a, a, first, last)
+            gpu.scan_range(b, b, first, last)
+            assert a.a.tobytes() == b.a.tobytes(), (fmt, dims, first, last)
+            if all(f < l for f, l in zip(first, last)):
+                a, b = cases.mk(dims, fmt, 6), cases.mk(dims, fmt, 6)   # dst != src: copy, then scan
+                o.scan_range(a, src, first, last)
+                gpu.scan_range(b, src, first, last)
+                assert a.a.tobytes() == b.a.tobytes(), (fmt, dims, first, last, "copy")
+    # converting copy in front of the scan (UInt16 source into a UInt8 / Float32 destination)
+    src = cases.mk((40, 12, 9), po.UINT16, 1)
+    for dfmt in (po.UINT8, po.FLOAT32):
+        a, b = cases.mk((48, 16, 12), dfmt, 3, -1.0, 2.0), cases.mk((48, 16, 12), dfmt, 3, -1.0, 2.0)
+        o.scan_range(a, src, (1, 0, 2), (40, 12, 9), (4, 3, 1))
+        gpu.scan_range(b, src, (1, 0, 2), (40, 12, 9), (4, 3, 1))
+        assert a.a.tobytes() == b.a.tobytes(), dfmt
+
+
 def test_brick_decompose_batch(gpu):
     """BrickDecompose as one vktb_copy_range_batch launch: cropped border bricks, halos clamped at the volume border,
     brick rows at every 16-byte phase; plus a batch that mixes bytewise and converting boxes and empty boxes."""

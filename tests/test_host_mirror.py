@@ -92,6 +92,13 @@ def run_cpp(programs, policy, tmp):
     assert raw(tmp / "out_fz.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     bins, dropped = o.histogram_range(a, (1, 2, 3), (47, 39, 35), 300)
     assert dropped == 0 and np.fromfile(tmp / "out_hist.raw", np.uint64).tobytes() == bins.tobytes()
+    ref = po.empty(cd, U16)
+    o.fill_range(ref, (0, 0, 0), cd, 0.5)
+    o.scan_range(ref, a, (2, 1, 3), (46, 39, 35), (5, 4, 3))
+    assert raw(tmp / "out_sc.raw", cd, np.uint16).tobytes() == ref.a.tobytes()
+    ref = b.copy()
+    o.scan_range(ref, ref, (45, 2, 1), (3, 38, 30))
+    assert raw(tmp / "out_sci.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     want = b"".join(x.tobytes() for x in o.brick_decompose(a, (20, 16, 16), (1, 2, 0), (2, 1, 1)))
     assert (tmp / "out_bricks.raw").read_bytes() == want
     if policy == "gpu-stream":

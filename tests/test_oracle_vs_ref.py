@@ -167,6 +167,38 @@ def test_histogram(fmt):
 
 
 @pytest.mark.parametrize("fmt", FMTS[:4])
+def test_scan(fmt):
+    """ScanRange: oracle (reference loops restated) == reference == numpy cumsum along x, y, z modulo 2^(8 bpv)."""
+    o, r = po.oracle(), po.reference()
+    for ddims, sdims, first, last, off, in_place in cases.SCAN_CASES:
+        src = mk(sdims, fmt, 2, -1000.0, 3000.0)
+        if in_place:
+            a, b = src.copy(), src.copy()
+            o.scan_range(a, a, first, last, off)
+            r.scan_range(b, b, first, last, off)
+        else:
+            a, b = mk(ddims, fmt, 5, -1000.0, 3000.0), mk(ddims, fmt, 5, -1000.0, 3000.0)
+            o.scan_range(a, src, first, last, off)
+            r.scan_range(b, src, first, last, off)
+        assert a.a.tobytes() == b.a.tobytes(), (ddims, first, last, off, in_place)
+        # independent statement: three cumulative sums of the raw integers, walked in the range's directions
+        base = src if in_place else mk(ddims, fmt, 5, -1000.0, 3000.0)
+        want = base.a.copy()
+        if not in_place:
+            o.copy_range(po.Vol(want, fmt, -1000.0, 3000.0), src, first, last, off)
+        sl = []
+        for ax in (2, 1, 0):                                   # numpy axes (z, y, x)
+            f, l = first[ax] + off[ax], last[ax] + off[ax]
+            sl.append(slice(f, l) if f < l else slice(f, l if l >= 0 else None, -1))
+        box = want[sl[0], sl[1], sl[2]].view({1: np.uint8, 2: np.uint16, 4: np.uint32}[want.dtype.itemsize])
+        acc = box.astype(np.uint64)
+        for ax in range(3):
+            acc = np.cumsum(acc, axis=ax, dtype=np.uint64)
+        box[...] = acc.astype(box.dtype)
+        assert want.tobytes() == a.a.tobytes(), (ddims, first, last, off, in_place)
+
+
+@pytest.mark.parametrize("fmt", FMTS[:4])
 def test_brick_decompose(fmt):
     """BrickDecomposeResize's brick grid and BrickDecompose's contents (halo voxels clamped at the volume border)."""
     o, r = po.oracle(), po.reference()

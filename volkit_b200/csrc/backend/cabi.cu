@@ -86,6 +86,23 @@ int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, cons
     return finish("vktb_copy_range_batch", launchCopyBatch(c, n, dv.data(), sv, firsts, lasts, offs));
 }
 
+int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                    const int32_t off[3])
+{
+    VolDesc dv, sv;
+    if (!first || !last || !off) return fail("vktb_scan_range: null range");
+    if (!toDesc("vktb_scan_range", dst, dv) || !toDesc("vktb_scan_range", src, sv)) return -1;
+    for (int a = 0; a < 3; ++a) {
+        if (first[a] == last[a]) return fail("vktb_scan_range: empty axis (the reference's loops never end on one)");
+        if (dv.data != sv.data && first[a] > last[a])
+            return fail("vktb_scan_range: a right-to-left range needs dst == src (the copy of such a range is undefined)");
+    }
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish("vktb_scan_range", launchScan(c, dv, sv, first, last, off));
+}
+
 int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2, const int32_t first[3],
                      const int32_t last[3], const int32_t off[3])
 {

@@ -15,6 +15,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
 
@@ -351,6 +352,42 @@ namespace
         return BrickDecomposeResize(dest, source, Vec3i{ brickSizeX, brickSizeY, brickSizeZ },
                                     Vec3i{ haloSizeNegX, haloSizeNegY, haloSizeNegZ },
                                     Vec3i{ haloSizePosX, haloSizePosY, haloSizePosZ });
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Scan (reference src/vkt/Scan.cpp:22-71)
+    //---------------------------------------------------------------------------------------------------------
+    Error ScanRange(StructuredVolume& dst, StructuredVolume& src, Vec3i first, Vec3i last, Vec3i dstOffset)
+    {
+        const bool inPlace = &dst == &src;
+        const int f[3] = { first.x, first.y, first.z }, l[3] = { last.x, last.y, last.z };
+        for (int a = 0; a < 3; ++a)
+            if (f[a] == l[a] || (!inPlace && f[a] > l[a])) return InvalidValue;   // the reference would not terminate
+        return dispatch("ScanRange",
+            [&] {
+                host::View d = viewOf(dst);
+                if (!inPlace) host::copyRange(d, viewOf(src), first, last, dstOffset);
+                host::scanRange(d, Vec3i{ first.x + dstOffset.x, first.y + dstOffset.y, first.z + dstOffset.z },
+                                Vec3i{ last.x + dstOffset.x, last.y + dstOffset.y, last.z + dstOffset.z });
+            },
+            [&] {
+                vktb_vol d = host::describe(dst), s = inPlace ? d : host::describe(src);
+                int32_t fa[3], la[3], oa[3];
+                toArray(first, fa); toArray(last, la); toArray(dstOffset, oa);
+                return vktb_scan_range(&d, &s, fa, la, oa);
+            });
+    }
+
+    Error ScanRange(StructuredVolume& dst, StructuredVolume& src, int32_t firstX, int32_t firstY, int32_t firstZ,
+                    int32_t lastX, int32_t lastY, int32_t lastZ, int32_t dstOffsetX, int32_t dstOffsetY, int32_t dstOffsetZ)
+    {
+        return ScanRange(dst, src, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ },
+                         Vec3i{ dstOffsetX, dstOffsetY, dstOffsetZ });
+    }
+
+    Error Scan(StructuredVolume& dst, StructuredVolume& src)
+    {
+        return ScanRange(dst, src, Vec3i{ 0, 0, 0 }, dst.getDims(), Vec3i{ 0, 0, 0 });   // dst dims: Scan.cpp:24-31
     }
 
     //---------------------------------------------------------------------------------------------------------

@@ -9,6 +9,7 @@
 #include <vkt/Flip.h>
 #include <vkt/Memory.h>
 #include <vkt/Resample.h>
+#include <vkt/Scan.h>
 #include <vkt/StructuredVolume.h>
 #include <vkt/Transform.h>
 #include <vkt/Voxel.h>
@@ -21,6 +22,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Memory.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
 #include <vkt/Voxel.hpp>
@@ -224,6 +226,17 @@ vktError vktBrickDecomposeResizeSV(vktArray3D_vktStructuredVolume decomp, vktStr
                                           (vktDataFormat)s.getDataFormat(), dist.x, dist.y, dist.z, m.x, m.y);
             }
     return vktNoError;
+}
+
+//--- Scan (reference src/vkt/Scan.cpp:79-122) -------------------------------------------------------------------
+vktError vktScanSV(vktStructuredVolume dst, vktStructuredVolume src)
+{
+    return (vktError)vkt::Scan(dst->volume, src->volume);
+}
+vktError vktScanRangeSV(vktStructuredVolume dst, vktStructuredVolume src, int32_t fx, int32_t fy, int32_t fz, int32_t lx,
+                        int32_t ly, int32_t lz, int32_t ox, int32_t oy, int32_t oz)
+{
+    return (vktError)vkt::ScanRange(dst->volume, src->volume, fx, fy, fz, lx, ly, lz, ox, oy, oz);
 }
 
 //--- Flip (reference src/vkt/Flip.cpp:127-167) -------------------------------------------------------------------

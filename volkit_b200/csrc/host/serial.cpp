@@ -174,6 +174,36 @@ namespace host
                 }
     }
 
+    //--- Scan: reference src/vkt/Scan_serial.hpp:18-152 ------------------------------------------------------------
+    // The reference's inclusion-exclusion over raw voxel integers (64-bit sums, low bpv bytes stored) equals three
+    // 1-D inclusive prefix sums modulo 2^(8 bpv): along x, then y, then z, each from `first` towards `last`.
+    void scanRange(View v, Vec3i first, Vec3i last)
+    {
+        const int f[3] = { first.x, first.y, first.z }, l[3] = { last.x, last.y, last.z };
+        int n[3], step[3];
+        for (int a = 0; a < 3; ++a) {
+            step[a] = f[a] < l[a] ? 1 : -1;
+            n[a] = step[a] > 0 ? l[a] - f[a] : f[a] - l[a];
+        }
+        const long long pitch[3] = { (long long)v.bpv * step[0], (long long)v.bpv * v.dims.x * step[1],
+                                     (long long)v.bpv * v.dims.x * v.dims.y * step[2] };
+        uint8_t* corner = v.data + v.offset(f[0], f[1], f[2]);
+        for (int axis = 0; axis < 3; ++axis) {
+            const int a1 = (axis + 1) % 3, a2 = (axis + 2) % 3;
+            for (int j = 0; j < n[a2]; ++j)
+                for (int i = 0; i < n[a1]; ++i) {
+                    uint8_t* e = corner + i * pitch[a1] + j * pitch[a2];
+                    uint64_t acc = 0;
+                    for (int s = 0; s < n[axis]; ++s, e += pitch[axis]) {
+                        uint64_t raw = 0;
+                        std::memcpy(&raw, e, (std::size_t)v.bpv);
+                        acc += raw;
+                        std::memcpy(e, &acc, (std::size_t)v.bpv);
+                    }
+                }
+        }
+    }
+
     //--- BrickDecomposeResize layout: reference src/vkt/Decompose.cpp:96-146 ------------------------------------
     Vec3i brickCount(Vec3i d, Vec3i b)
     {

@@ -35,6 +35,8 @@ namespace host
     void transformRange(View v1, View v2, Vec3i first, Vec3i last, TransformBinaryOp op);
     void resample(View dst, View src, int filter);
     void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset, int axis);
+    // in place on dst (already holding the copied range): first/last in dst space, first > last = downwards
+    void scanRange(View dst, Vec3i first, Vec3i last);
     void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins);
 
     // BrickDecomposeResize's brick grid (reference src/vkt/Decompose.cpp:96-146): number of bricks and the dims of

@@ -57,6 +57,8 @@ cudaError_t launchFlip(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
                        const int32_t off[3], int axis);
 cudaError_t launchHistogram(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3],
                             unsigned long long* bins, size_t numBins, unsigned long long* droppedDev);
+cudaError_t launchScan(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3], const int32_t last[3],
+                       const int32_t off[3]);
 cudaError_t launchDebugCodec(const LaunchCtx&, int format, Mapping m, const float* values, uint32_t* mapped,
                              float* unmapped, size_t n);
 
