@@ -94,6 +94,12 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
     record(f"Histogram 256 bins {S}^3 UInt16", n, 2 * n,
            lambda: capi.check(lib.vktb_histogram_range(ctypes.byref(da), z3, l3, bins, 256, None)))
     capi.check(lib.vktb_free(bins))
+    # Aggregates: one read pass, result on the host (the call is synchronous)
+    agg = capi.VktbAggregates()
+    record(f"Aggregates {S}^3 UInt16", n, 2 * n,
+           lambda: capi.check(lib.vktb_aggregates_range(ctypes.byref(da), z3, l3, ctypes.byref(agg))))
+    record(f"Aggregates {S}^3 UInt16 mapping (-1000,3000)", n, 2 * n,
+           lambda: capi.check(lib.vktb_aggregates_range(ctypes.byref(gm), z3, l3, ctypes.byref(agg))))
     b.free(); d.free()
 
     # ---- Resample S^3 -> (S/2)^3 and -> (3S/2)^3, UInt16 (BASELINE config 3)

@@ -168,6 +168,45 @@ int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                          size_t num_bins, uint64_t* dropped_host);
 
+/* ComputeAggregatesRange_cuda(StructuredVolume&, Aggregates&, Vec3i first, Vec3i last)
+ * (src/vkt/Aggregates_cuda.hpp:14-21, an empty body in the reference); semantics of ComputeAggregatesRange_serial
+ * (src/vkt/Aggregates_serial.hpp:20-83).  vktb_aggregates has the layout of vkt::Aggregates / vktAggregates_t
+ * (include/cpp/vkt/Aggregates.hpp:14-25).  Contract:
+ *   min, max, argmin, argmax   exact: strict compares, the first voxel in x-fastest order wins, NaN never enters,
+ *                              FLT_MAX / -FLT_MAX and argmin = argmax = (0,0,0) when no voxel qualifies;
+ *   sum, mean, var, stddev, prod   the reference accumulates these sequentially in binary32, which no parallel
+ *                              evaluation reproduces bit for bit.  Returned here: the real-number moments to about
+ *                              1e-7 relative (binary64 accumulation), pushed through the reference's final steps
+ *                              (mean = float(double(sum) / numElems) with numElems = the WHOLE volume's voxel
+ *                              count, var = sum (v - mean)^2 / numElems, stddev = sqrtf(var)).  The reference's
+ *                              own result lies within its a-priori bound n * 2^-24 * sum |terms| of that value;
+ *                              prod additionally within FLT_MIN where the running binary32 product goes subnormal.
+ * `out` is a HOST pointer; the call is synchronous.  An empty range gives the reference's initial values. */
+typedef struct vktb_aggregates
+{
+    float   min, max, mean, stddev, var, sum, prod;
+    int32_t argmin[3], argmax[3];
+} vktb_aggregates;
+int vktb_aggregates_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_aggregates* out);
+
+/* The same pass as combinable moments, for volumes sharded into z-slabs (one partial per rank, exchanged as bytes):
+ * sums of d = v - shift and d^2, prod = prod_mant * 2^prod_exp, extrema with their absolute voxel coordinates in
+ * `vol` (has_min / has_max = 0 when no voxel qualified).  vktb_aggregates_finish folds n partials IN ORDER (the
+ * earlier partial wins ties, so pass them in z order after moving argmin/argmax to whole-volume coordinates) and
+ * applies the final steps above with num_elems = the whole volume's voxel count.  Pure host arithmetic. */
+typedef struct vktb_agg_partial
+{
+    double   sum_d, sum_d2, prod_mant;
+    int64_t  prod_exp;
+    uint64_t count;
+    float    min, max, shift;
+    int32_t  has_min, has_max;
+    int32_t  argmin[3], argmax[3];
+    int32_t  pad;
+} vktb_agg_partial;
+int vktb_aggregates_partial(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_agg_partial* out);
+int vktb_aggregates_finish(const vktb_agg_partial* parts, int n, uint64_t num_elems, vktb_aggregates* out);
+
 /* ---- Host-resident volumes, streamed ---------------------------------------------------------------
  * Same semantics and results as the entry points above, but every vktb_vol.data is a HOST pointer (pinned:
  * vktb_host_alloc or cudaHostRegister; pageable memory works without overlap).  The range is cut into z-slabs and

@@ -42,6 +42,16 @@ class CVol(ctypes.Structure):
 I3 = ctypes.c_int32 * 3
 
 
+class Aggregates(ctypes.Structure):
+    """vkt::Aggregates (reference include/cpp/vkt/Aggregates.hpp:14-25)"""
+    _fields_ = [("min", ctypes.c_float), ("max", ctypes.c_float), ("mean", ctypes.c_float), ("stddev", ctypes.c_float),
+                ("var", ctypes.c_float), ("sum", ctypes.c_float), ("prod", ctypes.c_float),
+                ("argmin", ctypes.c_int32 * 3), ("argmax", ctypes.c_int32 * 3)]
+
+    def words(self) -> bytes:
+        return bytes(self)
+
+
 @dataclass
 class Vol:
     a: np.ndarray          # (Z, Y, X), C-contiguous, dtype DTYPES[fmt]
@@ -85,6 +95,7 @@ class _Lib:
         f("flip_range", ctypes.c_int, [p, p, I3, I3, I3, ctypes.c_int])
         f("histogram_range", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p])
         f("scan_range", ctypes.c_int, [p, p, I3, I3, I3])
+        f("aggregates_range", ctypes.c_int, [p, I3, I3, ctypes.POINTER(Aggregates)])
         i32p = ctypes.POINTER(ctypes.c_int32)
         f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
         f("brick_decompose", ctypes.c_int, [p, I3, I3, I3, ctypes.c_void_p, ctypes.c_size_t])
@@ -138,6 +149,11 @@ class _Lib:
         assert self._histogram_range(ctypes.byref(vol.c()), I3(*first), I3(*last), bins.ctypes.data, num_bins,
                                      dropped.ctypes.data) == 0
         return bins, int(dropped[0])
+
+    def aggregates_range(self, vol: Vol, first, last) -> "Aggregates":
+        a = Aggregates()
+        assert self._aggregates_range(ctypes.byref(vol.c()), I3(*first), I3(*last), ctypes.byref(a)) == 0
+        return a
 
     def scan_range(self, dst: Vol, src: Vol, first, last, off=(0, 0, 0)):
         """src may be dst itself (in place; then first > last on an axis scans right to left)"""

@@ -20,6 +20,7 @@
 #include <cstring>
 #include <cstdlib>
 
+#include <vkt/Aggregates.hpp>
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
 #include <vkt/Decompose.hpp>
@@ -285,6 +286,20 @@ int ref_histogram_range(RefVol const* vol, int32_t const* first, int32_t const* 
     std::size_t* c = h.getBinCounts();
     for (size_t i = 0; i < numBins; ++i) bins[i] = (uint64_t)c[i];
     if (dropped) *dropped = 0;
+    return 0;
+}
+
+// vkt::ComputeAggregatesRange (include/cpp/vkt/Aggregates.hpp:27-43 -> src/vkt/Aggregates.cpp:52-66).  out = the 52
+// bytes of vkt::Aggregates.
+int ref_aggregates_range(RefVol const* vol, int32_t const* first, int32_t const* last, void* out)
+{
+    for (int a = 0; a < 3; ++a)
+        if (first[a] > last[a]) return -1;
+    Staged v(vol);
+    vkt::Aggregates ag;
+    vkt::ComputeAggregatesRange(v.vol, ag, v3(first), v3(last));
+    static_assert(sizeof(ag) == 52, "vkt::Aggregates layout");
+    std::memcpy(out, &ag, sizeof(ag));
     return 0;
 }
 

@@ -61,6 +61,14 @@ int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3
 int vko_histogram_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                         size_t num_bins, uint64_t* dropped);
 
+/* vkt::Aggregates (reference include/cpp/vkt/Aggregates.hpp:14-25) */
+typedef struct vko_aggregates
+{
+    float   min, max, mean, stddev, var, sum, prod;
+    int32_t argmin[3], argmax[3];
+} vko_aggregates;
+int vko_aggregates_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], vko_aggregates* out);
+
 /* 3-D prefix sum of the raw voxel integers mod 2^(8 bpv); dst->data == src->data means in place */
 int vko_scan_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
                    const int32_t off[3]);

@@ -33,6 +33,77 @@ SCAN_CASES = [((12, 9, 7), (12, 9, 7), (0, 0, 0), (12, 9, 7), (0, 0, 0), False),
               ((5, 6, 40), (5, 6, 40), (2, 0, 0), (3, 6, 40), (0, 0, 0), True)]      # one voxel wide
 
 
+# ComputeAggregatesRange: (dims, first, last); whole volume, a range (numElems stays the whole volume's), a few voxels
+# (prod stays inside the binary32 range), one row, one voxel
+AGG_CASES = [((33, 9, 8), (0, 0, 0), (33, 9, 8)), ((33, 9, 8), (1, 2, 1), (30, 9, 7)), ((33, 9, 8), (5, 3, 2), (8, 5, 4)),
+             ((40, 3, 2), (0, 1, 1), (40, 2, 2)), ((7, 5, 3), (6, 4, 2), (7, 5, 3))]
+
+
+def agg_exact_words(a) -> np.ndarray:
+    """the order-independent fields of vkt::Aggregates: min, max (bit patterns), argmin, argmax"""
+    w = np.frombuffer(a.words(), np.uint32)
+    return np.concatenate([w[0:2], w[7:13]]).copy()
+
+
+def agg_accumulated_words(a) -> np.ndarray:
+    """mean, stddev, var, sum, prod: sequential binary32 accumulations in the reference"""
+    return np.frombuffer(a.words(), np.uint32)[2:7].copy()
+
+
+def unmapped(o, vol) -> np.ndarray:
+    """every voxel's getValue() as float32 (Z, Y, X): the oracle's equal-dims Resample into Float32 with the (0, 1)
+    mapping is map(unmap(v)) = unmap(v)"""
+    dims = vol.a.shape[::-1]
+    f = po.empty(dims, po.FLOAT32)
+    o.resample(f, vol, po.NEAREST)
+    return f.a
+
+
+def check_aggregates(o, got, ref, vol, first, last, what="", parallel=True):
+    """The contract of vktb_aggregates_range (include/vktb/backend.h): min/max/argmin/argmax identical to the
+    reference; sum, mean, var, stddev, prod within the reference's own a-priori rounding bound of the real-number
+    value, and the parallel result itself within 1e-6 of that value (float64 numpy)."""
+    assert agg_exact_words(got).tobytes() == agg_exact_words(ref).tobytes(), (what, "min/max/argmin/argmax")
+    v = unmapped(o, vol)[first[2]:last[2], first[1]:last[1], first[0]:last[0]].astype(np.float64).ravel()
+    n, eps = v.size, 2.0 ** -24
+    num_elems = float(vol.a.size)
+    if not np.isfinite(v).all():
+        return
+    sabs, ssum = np.abs(v).sum(), v.sum()
+    tiny = 1e-30
+    # sum: sequential binary32 summation error <= (n - 1) eps sum|v| (+ the final rounding of either side)
+    bsum = n * eps * sabs + 2 * eps * abs(ssum) + tiny
+    assert abs(float(got.sum) - float(ref.sum)) <= bsum + 1e-6 * sabs, (what, "sum", got.sum, ref.sum, bsum)
+    if parallel:
+        assert abs(float(got.sum) - ssum) <= 1e-6 * sabs + tiny, (what, "sum vs float64", got.sum, ssum)
+    bmean = bsum / num_elems + eps * abs(float(ref.mean))
+    assert abs(float(got.mean) - float(ref.mean)) <= bmean + 1e-6 * sabs / num_elems, (what, "mean", got.mean, ref.mean)
+    # var: terms (v - mean)^2 carry 3 roundings each, the running sum n more; the two means differ by <= dm
+    m = float(ref.mean)
+    dev = v - m
+    sq = (dev * dev).sum()
+    dm = abs(float(got.mean) - m)
+    bvar = ((n + 4) * eps * sq + 2 * abs(dev.sum()) * dm + n * dm * dm) / num_elems + 2 * eps * float(ref.var) + tiny
+    assert abs(float(got.var) - float(ref.var)) <= bvar + 1e-6 * sq / num_elems, (what, "var", got.var, ref.var, bvar)
+    if parallel:
+        assert abs(float(got.var) - ((v - float(got.mean)) ** 2).sum() / num_elems) <= 2e-6 * sq / num_elems + tiny, \
+            (what, "var vs float64")
+    assert np.float32(got.stddev) == np.sqrt(np.float32(got.var)), (what, "stddev = sqrtf(var)")
+    # prod: relative bound while the running product stays a normal binary32 number; 0 / inf classes otherwise
+    rp, gp = float(ref.prod), float(got.prod)
+    if np.isnan(rp):
+        return                                   # inf * 0 inside the reference's running product
+    if np.isinf(rp) or np.isinf(gp):
+        with np.errstate(all="ignore"):
+            mags = np.cumsum(np.log2(np.maximum(np.abs(v), 1e-300)))
+        if np.isinf(rp) and np.isinf(gp):
+            assert rp == gp, (what, "prod sign", gp, rp)
+        else:                                    # the running product left the binary32 range on the way
+            assert mags.max() > 126, (what, "prod", gp, rp)
+        return
+    assert abs(gp - rp) <= 2 * n * eps * abs(rp) + 1.2e-38, (what, "prod", gp, rp)
+
+
 def mk(dims, fmt, seed, lo=0.0, hi=1.0):
     return po.Vol(po.synth(dims, fmt, seed), fmt, lo, hi)
 
@@ -108,6 +179,11 @@ def cases():
         for i, (ddims, sdims, first, last, off, inplace) in enumerate(SCAN_CASES):
             out.append((f"scan/{fmt}/{i}", "scan",
                         dict(ddims=ddims, sdims=sdims, fmt=fmt, first=first, last=last, off=off, inplace=inplace)))
+    # --- Aggregates: [exact fields, accumulated fields] of the reference
+    for fmt in FMT4:
+        for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
+            for i, (dims, first, last) in enumerate(AGG_CASES):
+                out.append((f"agg/{fmt}/{lo}/{i}", "agg", dict(dims=dims, fmt=fmt, lo=lo, hi=hi, first=first, last=last)))
     # --- BASELINE config 1 (CLI pipeline on a 64^3 uint8 volume -> 32^3 uint16)
     out.append(("cli/config1", "cli1", dict()))
     return out
@@ -157,6 +233,10 @@ def run_case(lib, case) -> list[np.ndarray]:
         bins, dropped = lib.histogram_range(v, p["first"], p["last"], p["bins"])
         assert dropped == 0, "case must stay inside the reference's defined behaviour"
         return [bins]
+    if kind == "agg":
+        v = mk(p["dims"], p["fmt"], 4, p["lo"], p["hi"])
+        a = lib.aggregates_range(v, p["first"], p["last"])
+        return [agg_exact_words(a), agg_accumulated_words(a)]
     if kind == "bricks":
         s = mk(p["sdims"], p["fmt"], 3, -1000.0, 3000.0)
         return list(lib.brick_decompose(s, p["brick"], p["neg"], p["pos"]))

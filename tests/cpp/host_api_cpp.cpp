@@ -8,6 +8,7 @@
 #include <string>
 #include <thread>
 
+#include <vkt/Aggregates.hpp>
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
@@ -134,6 +135,11 @@ int main(int argc, char** argv)
     Histogram hist(300);
     CHECK(ComputeHistogramRange(a, hist, 1, 2, 3, 47, 39, 35));
 
+    // Aggregates over a range (numElems stays the whole volume's voxel count)
+    Aggregates agg;
+    CHECK(ComputeAggregatesRange(a, agg, 1, 2, 3, 47, 39, 35));
+    if (ComputeAggregatesRange(a, agg, Vec3i{ 5, 2, 3 }, Vec3i{ 1, 39, 35 }) != InvalidValue) return 12;
+
     // BrickDecompose: 20x16x16 bricks with halos (-1,-2,0)/(2,1,1): 3x3x3 bricks, the far ones cropped
     Array3D<StructuredVolume> bricks;
     CHECK(BrickDecomposeResize(bricks, a, Vec3i{ 20, 16, 16 }, Vec3i{ 1, 2, 0 }, Vec3i{ 2, 1, 1 }));
@@ -160,6 +166,11 @@ int main(int argc, char** argv)
     {
         FILE* f = std::fopen((g_dir + "/out_hist.raw").c_str(), "wb");
         std::fwrite(hist.getBinCounts(), sizeof(std::size_t), hist.getNumBins(), f);   // migrates the bins back
+        std::fclose(f);
+    }
+    {
+        FILE* f = std::fopen((g_dir + "/out_agg.raw").c_str(), "wb");
+        std::fwrite(&agg, sizeof(agg), 1, f);
         std::fclose(f);
     }
     {

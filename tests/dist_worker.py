@@ -12,6 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from oracle import pyoracle as po  # noqa: E402  (checker)
+import cases  # noqa: E402  (tests/cases.py: tolerance contract of the aggregates)
 from volkit_b200 import capi, sharded  # noqa: E402
 
 CASES = [
@@ -163,6 +164,44 @@ def main():
                 torch.cuda.synchronize()
             if got.cpu().numpy().astype(np.uint64).tobytes() != ref_bins.tobytes():
                 print(f"rank {rank}: MISMATCH in histogram {hfmt} {first} {last} {nb}", flush=True)
+                sys.exit(1)
+
+    # Aggregates: one partial per rank, all-gathered and folded in z order
+    for afmt, lo, hi in ((po.UINT16, 0.0, 1.0), (po.FLOAT32, -1.0, 2.0)):
+        whole = po.Vol(po.synth((33, 12, 21), afmt, 6), afmt, lo, hi)
+        if afmt == po.UINT16:
+            whole.a[:] = whole.a % 7                 # many ties: the first occurrence must win across slabs
+        av = sharded.ShardedVolume(torch, (33, 12, 21), afmt, rank, world, lo, hi, device=device)
+        fill_slab(av, whole)
+        for first, last in (((0, 0, 0), (33, 12, 21)), ((2, 1, 5), (30, 11, 17))):
+            ref_agg = o.aggregates_range(whole, first, last)
+
+            def cpu_partial(desc, f, l, part):
+                # test double of vktb_aggregates_partial: float64 moments of the slab's planes
+                sub = as_vol(desc, afmt, (lo, hi))
+                vals = cases.unmapped(o, sub)[f[2]:l[2], f[1]:l[1], f[0]:l[0]].astype(np.float64)
+                flat = vals.ravel()
+                part.shift = float(np.float32(flat[0]))
+                dd = flat - part.shift
+                part.sum_d, part.sum_d2, part.count = float(dd.sum()), float((dd * dd).sum()), flat.size
+                m, e = np.frexp(np.prod(flat[:8])) if flat.size <= 8 else (0.0, 0)
+                part.prod_mant, part.prod_exp = float(m), int(e)
+                nx, ny = l[0] - f[0], l[1] - f[1]
+                for name, pos in (("min", int(np.argmin(flat))), ("max", int(np.argmax(flat)))):
+                    setattr(part, name, float(flat[pos]))
+                    setattr(part, "has_" + name, 1)
+                    getattr(part, "arg" + name)[:] = [f[0] + pos % nx, f[1] + (pos // nx) % ny, f[2] + pos // (nx * ny)]
+
+            got = sharded.aggregates_sharded(av, first, last, dist, compute=None if gpu else cpu_partial)
+            got = po.Aggregates.from_buffer_copy(bytes(got))
+            try:
+                if gpu:
+                    cases.check_aggregates(o, got, ref_agg, whole, first, last, (afmt, first))
+                else:
+                    assert cases.agg_exact_words(got).tobytes() == cases.agg_exact_words(ref_agg).tobytes()
+                    assert abs(got.sum - ref_agg.sum) <= 1e-4 * abs(ref_agg.sum) and abs(got.var - ref_agg.var) <= 1e-4 * ref_agg.var
+            except AssertionError as e:
+                print(f"rank {rank}: MISMATCH in aggregates {afmt} {first} {last}: {e}", flush=True)
                 sys.exit(1)
 
     # elementwise ops need no exchange: slabs tile the volume exactly

@@ -110,6 +110,15 @@ class GpuLib:
             s.free()
         self._down(d, dst)
 
+    def aggregates_range(self, vol, first, last):
+        """vktb_aggregates_range -> po.Aggregates (same 13 words)"""
+        v = self._up(vol)
+        a = capi.VktbAggregates()
+        capi.check(self.lib.vktb_aggregates_range(ctypes.byref(v.desc()), I3(*first), I3(*last), ctypes.byref(a)),
+                   "aggregates")
+        v.free()
+        return po.Aggregates.from_buffer_copy(bytes(a))
+
     def histogram_range(self, vol, first, last, num_bins):
         import numpy as np
         v = self._up(vol)

@@ -47,6 +47,10 @@ def test_golden(gpu, kind):
         if case[1] != kind:
             continue
         outs = cases.run_case(gpu, case)
+        if kind == "agg":
+            # min/max/argmin/argmax are frozen; the accumulated fields follow a tolerance contract (test_aggregates)
+            assert hashlib.sha256(outs[0].tobytes()).hexdigest() == GOLD["sha256"][case[0]][0], case[0]
+            continue
         digest = [hashlib.sha256(a.tobytes()).hexdigest() for a in outs]
         if digest != GOLD["sha256"][case[0]]:
             # only Float32 NaN payloads may differ from the frozen reference bytes
@@ -587,6 +591,83 @@ def test_histogram_kernels(gpu):
     got, gd = gpu.histogram_range(v, (0, 0, 0), (64, 32, 16), 128)
     assert rd == gd and rd > 0 and got.tobytes() == ref.tobytes()
     assert int(got.sum()) + gd == 64 * 32 * 16
+
+
+def test_aggregates(gpu):
+    """ComputeAggregatesRange: min/max/argmin/argmax bit-exact (first occurrence, ties, NaN skipped, -0 / +0), the
+    accumulated statistics inside the reference's own rounding bound (cases.check_aggregates); flat and row kernels,
+    packed-integer and float min/max paths, vectors + scalar heads and tails."""
+    o = po.oracle()
+    rng = np.random.default_rng(11)
+    for fmt in cases.FMT4 + [po.INT16]:
+        for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
+            for dims, first, last in cases.AGG_CASES + [((70, 33, 20), (0, 0, 0), (70, 33, 20)),
+                                                        ((70, 33, 20), (3, 1, 2), (69, 30, 19)),
+                                                        ((128, 16, 9), (0, 0, 2), (128, 16, 7))]:
+                v = cases.mk(dims, fmt, 4, lo, hi)
+                cases.check_aggregates(o, gpu.aggregates_range(v, first, last), o.aggregates_range(v, first, last),
+                                       v, first, last, (fmt, lo, dims, first))
+    # ties: few distinct values, so the first occurrence decides argmin / argmax
+    for fmt, top in ((po.UINT8, 3), (po.UINT16, 5), (po.UINT32, 2), (po.FLOAT32, 4)):
+        for lo, hi in ((0.0, 1.0), (-2.0, 5.0)):
+            a = rng.integers(0, top, size=(9, 17, 67)).astype(po.DTYPES[fmt])
+            v = po.Vol(a, fmt, lo, hi)
+            for first, last in (((0, 0, 0), (67, 17, 9)), ((2, 1, 1), (66, 16, 8))):
+                cases.check_aggregates(o, gpu.aggregates_range(v, first, last), o.aggregates_range(v, first, last),
+                                       v, first, last, ("ties", fmt, lo, first))
+    # constant volume: min == max everywhere, argmin = argmax = first voxel of the range; var exactly 0 for a whole volume
+    v = po.Vol(np.full((6, 10, 48), 777, np.uint16), po.UINT16)
+    g = gpu.aggregates_range(v, (0, 0, 0), (48, 10, 6))
+    cases.check_aggregates(o, g, o.aggregates_range(v, (0, 0, 0), (48, 10, 6)), v, (0, 0, 0), (48, 10, 6), "constant")
+    # Float32 specials: NaN never enters min/max, -0 / +0 compare equal (first one's bits are kept), +-inf do enter
+    f = rng.random((5, 9, 40), dtype=np.float32) * 2 - 1
+    f[0, 0, 3] = np.nan; f[2, 4, 7] = np.nan
+    for mn, mx in (((-0.0, 0.0), None), ((0.0, -0.0), None), (None, (np.inf, np.inf)), ((-np.inf, -np.inf), (np.inf, np.inf))):
+        w = f.copy()
+        if mn:
+            w = np.where(w < 0, -w, w); w[1, 2, 5], w[3, 3, 9] = mn
+        if mx:
+            w[1, 6, 30], w[4, 1, 2] = mx
+        v = po.Vol(w, po.FLOAT32)
+        g, r = gpu.aggregates_range(v, (0, 0, 0), (40, 9, 5)), o.aggregates_range(v, (0, 0, 0), (40, 9, 5))
+        assert cases.agg_exact_words(g).tobytes() == cases.agg_exact_words(r).tobytes(), (mn, mx)
+    # no voxel qualifies: every voxel NaN -> the initial values
+    v = po.Vol(np.full((2, 3, 16), np.nan, np.float32), po.FLOAT32)
+    g, r = gpu.aggregates_range(v, (0, 0, 0), (16, 3, 2)), o.aggregates_range(v, (0, 0, 0), (16, 3, 2))
+    assert cases.agg_exact_words(g).tobytes() == cases.agg_exact_words(r).tobytes()
+    # empty range: the reference's initial values; first > last is rejected
+    v = cases.mk((16, 4, 4), po.UINT16, 1)
+    g, r = gpu.aggregates_range(v, (3, 1, 1), (3, 4, 4)), o.aggregates_range(v, (3, 1, 1), (3, 4, 4))
+    assert g.words() == r.words()
+    with pytest.raises(Exception):
+        gpu.aggregates_range(v, (5, 1, 1), (3, 4, 4))
+
+
+def test_aggregates_partials_combine(gpu):
+    """z-slab partials folded by vktb_aggregates_finish equal the one-call result (exact fields identical, moments to
+    rounding): the path aggregates_sharded() takes."""
+    from volkit_b200 import capi
+    from volkit_b200.device import DeviceVolume
+    lib = gpu.lib
+    for fmt in (po.UINT16, po.FLOAT32):
+        vol = cases.mk((50, 21, 24), fmt, 9, -3.0, 7.0)
+        dv = DeviceVolume.from_numpy(vol.a, fmt, -3.0, 7.0)
+        whole = capi.VktbAggregates()
+        z3, l3 = capi.I3(0, 0, 0), capi.I3(50, 21, 24)
+        capi.check(lib.vktb_aggregates_range(ctypes.byref(dv.desc()), z3, l3, ctypes.byref(whole)))
+        parts = (capi.VktbAggPartial * 3)()
+        for k, (z0, z1) in enumerate(((0, 7), (7, 16), (16, 24))):
+            capi.check(lib.vktb_aggregates_partial(ctypes.byref(dv.desc()), capi.I3(0, 0, z0), capi.I3(50, 21, z1),
+                                                   ctypes.byref(parts[k])))
+        folded = capi.VktbAggregates()
+        capi.check(lib.vktb_aggregates_finish(parts, 3, 50 * 21 * 24, ctypes.byref(folded)))
+        for name in ("min", "max"):
+            assert np.float32(getattr(folded, name)).tobytes() == np.float32(getattr(whole, name)).tobytes()
+        assert list(folded.argmin) == list(whole.argmin) and list(folded.argmax) == list(whole.argmax)
+        for name in ("sum", "mean", "var", "stddev"):
+            a, b = getattr(folded, name), getattr(whole, name)
+            assert abs(a - b) <= 4e-7 * max(abs(a), abs(b)), (name, a, b)
+        dv.free()
 
 
 def test_cabi_from_many_threads(gpu):

@@ -92,6 +92,12 @@ def run_cpp(programs, policy, tmp):
     assert raw(tmp / "out_fz.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     bins, dropped = o.histogram_range(a, (1, 2, 3), (47, 39, 35), 300)
     assert dropped == 0 and np.fromfile(tmp / "out_hist.raw", np.uint64).tobytes() == bins.tobytes()
+    got_agg = po.Aggregates.from_buffer_copy((tmp / "out_agg.raw").read_bytes())
+    ref_agg = o.aggregates_range(a, (1, 2, 3), (47, 39, 35))
+    if policy == "cpu":
+        assert got_agg.words() == ref_agg.words()            # the reference's sequential accumulation, word for word
+    else:
+        cases.check_aggregates(o, got_agg, ref_agg, a, (1, 2, 3), (47, 39, 35), policy)
     ref = po.empty(cd, U16)
     o.fill_range(ref, (0, 0, 0), cd, 0.5)
     o.scan_range(ref, a, (2, 1, 3), (46, 39, 35), (5, 4, 3))

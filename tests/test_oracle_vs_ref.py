@@ -166,6 +166,27 @@ def test_histogram(fmt):
             assert int(ha.sum()) == 23 * 9 * 6
 
 
+@pytest.mark.parametrize("fmt", FMTS)
+def test_aggregates(fmt):
+    """ComputeAggregatesRange: the restatement reproduces all 13 words of the reference's vkt::Aggregates; min / max /
+    argmin / argmax also equal an independent numpy statement (first occurrence in x-fastest order)."""
+    o, r = po.oracle(), po.reference()
+    for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
+        for dims, first, last in cases.AGG_CASES + [((21, 6, 5), (2, 2, 2), (2, 6, 5))]:      # + an empty range
+            v = mk(dims, fmt, 4, lo, hi)
+            a, b = o.aggregates_range(v, first, last), r.aggregates_range(v, first, last)
+            assert a.words() == b.words(), (dims, first, last, lo)
+            box = cases.unmapped(o, v)[first[2]:last[2], first[1]:last[1], first[0]:last[0]]
+            if box.size == 0:
+                assert a.min == np.finfo(np.float32).max and a.prod == 1.0 and a.sum == 0.0
+                continue
+            nx, ny = last[0] - first[0], last[1] - first[1]
+            for val, arg, pos in ((a.min, a.argmin, int(np.argmin(box))), (a.max, a.argmax, int(np.argmax(box)))):
+                assert np.float32(val) == box.ravel()[pos]
+                assert list(arg) == [first[0] + pos % nx, first[1] + (pos // nx) % ny, first[2] + pos // (nx * ny)]
+            cases.check_aggregates(o, a, b, v, first, last, parallel=False)   # the bound holds trivially for ref == ref
+
+
 @pytest.mark.parametrize("fmt", FMTS[:4])
 def test_scan(fmt):
     """ScanRange: oracle (reference loops restated) == reference == numpy cumsum along x, y, z modulo 2^(8 bpv)."""

@@ -27,6 +27,22 @@ class VktbVol(ctypes.Structure):
 
 I3 = ctypes.c_int32 * 3
 
+class VktbAggregates(ctypes.Structure):
+    """vktb_aggregates = vkt::Aggregates (reference include/cpp/vkt/Aggregates.hpp:14-25)"""
+    _fields_ = [("min", ctypes.c_float), ("max", ctypes.c_float), ("mean", ctypes.c_float), ("stddev", ctypes.c_float),
+                ("var", ctypes.c_float), ("sum", ctypes.c_float), ("prod", ctypes.c_float),
+                ("argmin", ctypes.c_int32 * 3), ("argmax", ctypes.c_int32 * 3)]
+
+
+class VktbAggPartial(ctypes.Structure):
+    """vktb_agg_partial: combinable moments of one z-slab"""
+    _fields_ = [("sum_d", ctypes.c_double), ("sum_d2", ctypes.c_double), ("prod_mant", ctypes.c_double),
+                ("prod_exp", ctypes.c_int64), ("count", ctypes.c_uint64), ("min", ctypes.c_float),
+                ("max", ctypes.c_float), ("shift", ctypes.c_float), ("has_min", ctypes.c_int32),
+                ("has_max", ctypes.c_int32), ("argmin", ctypes.c_int32 * 3), ("argmax", ctypes.c_int32 * 3),
+                ("pad", ctypes.c_int32)]
+
+
 # name -> (restype, argtypes); every symbol include/vktb/backend.h declares
 _P = ctypes.POINTER
 _VP = _P(VktbVol)
@@ -64,6 +80,9 @@ SIGNATURES = {
     "vktb_resample_window_src_range3": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, I3, I3,
                                                        _P(ctypes.c_int32), _P(ctypes.c_int32)]),
     "vktb_flip_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3, ctypes.c_int]),
+    "vktb_aggregates_range": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggregates)]),
+    "vktb_aggregates_partial": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggPartial)]),
+    "vktb_aggregates_finish": (ctypes.c_int, [_P(VktbAggPartial), ctypes.c_int, ctypes.c_uint64, _P(VktbAggregates)]),
     "vktb_histogram_range": (ctypes.c_int, [_VP, I3, I3, ctypes.c_void_p, ctypes.c_size_t, _P(ctypes.c_uint64)]),
     "vktb_hosted_arith_range": (ctypes.c_int, [ctypes.c_int, _VP, _VP, _VP, I3, I3, I3]),
     "vktb_hosted_transform_range1": (ctypes.c_int, [_VP, I3, I3, ctypes.c_int]),

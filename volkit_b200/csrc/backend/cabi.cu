@@ -1,6 +1,8 @@
 // C-ABI algorithm entry points (include/vktb/backend.h): argument validation, then one launcher call.
 #include "context.hpp"
 
+#include <cfloat>
+#include <cmath>
 #include <vector>
 #include <cstring>
 #include <mutex>
@@ -213,6 +215,100 @@ int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int3
     }
     cudaFreeAsync(dropped, s);
     return finish("vktb_histogram_range", e);
+}
+
+// ---- Aggregates ---------------------------------------------------------------------------------------------
+static void emptyPartial(vktb_agg_partial* o)
+{
+    std::memset(o, 0, sizeof(*o));
+    o->prod_mant = 1.0; o->min = FLT_MAX; o->max = -FLT_MAX;
+}
+
+int vktb_aggregates_partial(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_agg_partial* out)
+{
+    static_assert(sizeof(vktb_agg_partial) == 88, "vktb_agg_partial layout");
+    VolDesc v;
+    if (!first || !last || !out) return fail("vktb_aggregates_partial: null argument");
+    if (!toDesc("vktb_aggregates_partial", vol, v)) return -1;
+    emptyPartial(out);
+    for (int a = 0; a < 3; ++a) {
+        if (first[a] > last[a]) return fail("vktb_aggregates_partial: first > last (the reference's loops never end)");
+        if (first[a] < 0 || last[a] > v.dims[a]) return fail("vktb_aggregates_partial: range outside the volume");
+    }
+    if (first[0] == last[0] || first[1] == last[1] || first[2] == last[2]) return 0;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    cudaStream_t s = currentStream(d);
+    LaunchCtx c{ s, d->smCount };
+    AggPartial* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&scratch, aggregatesScratchBytes(c), s);
+    if (e != cudaSuccess) return fail("vktb_aggregates_partial", e);
+    AggPartial* totalDev = nullptr;
+    AggPartial t;
+    e = launchAggregates(c, v, first, last, scratch, &totalDev);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&t, totalDev, sizeof(t), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFreeAsync(scratch, s);
+    if (e != cudaSuccess) return fail("vktb_aggregates_partial", e);
+    const uint64_t nx = (uint64_t)(last[0] - first[0]), ny = (uint64_t)(last[1] - first[1]), nz = (uint64_t)(last[2] - first[2]);
+    out->sum_d = t.sumD; out->sum_d2 = t.sumD2; out->prod_mant = t.prodMant; out->prod_exp = t.prodExp;
+    out->count = nx * ny * nz;
+    out->min = t.min; out->max = t.max; out->shift = t.shift;
+    auto coords = [&](unsigned long long idx, int32_t* xyz) {
+        const uint64_t r = idx / nx;
+        xyz[0] = first[0] + (int32_t)(idx - r * nx);
+        xyz[1] = first[1] + (int32_t)(r % ny);
+        xyz[2] = first[2] + (int32_t)(r / ny);
+    };
+    if (t.minIdx != ~0ull) { out->has_min = 1; coords(t.minIdx, out->argmin); }
+    if (t.maxIdx != ~0ull) { out->has_max = 1; coords(t.maxIdx, out->argmax); }
+    return 0;
+}
+
+int vktb_aggregates_finish(const vktb_agg_partial* parts, int n, uint64_t numElems, vktb_aggregates* out)
+{
+    if (!out || n < 0 || (n > 0 && !parts)) return fail("vktb_aggregates_finish: bad arguments");
+    std::memset(out, 0, sizeof(*out));
+    out->min = FLT_MAX; out->max = -FLT_MAX;
+    double s1 = 0.0, s2 = 0.0, cnt = 0.0, mant = 1.0;
+    long long ex = 0;
+    const double c0 = n > 0 ? (double)parts[0].shift : 0.0;
+    for (int k = 0; k < n; ++k) {
+        const vktb_agg_partial& p = parts[k];
+        if (p.has_min && p.min < out->min) { out->min = p.min; std::memcpy(out->argmin, p.argmin, sizeof(p.argmin)); }
+        if (p.has_max && p.max > out->max) { out->max = p.max; std::memcpy(out->argmax, p.argmax, sizeof(p.argmax)); }
+        const double dc = (double)p.shift - c0, m = (double)p.count;     // re-base the moments on c0
+        s1 += p.sum_d + m * dc;
+        s2 += p.sum_d2 + 2.0 * dc * p.sum_d + m * dc * dc;
+        cnt += m;
+        int e2 = 0;
+        mant *= p.prod_mant;
+        if (std::isfinite(mant) && mant != 0.0) { mant = std::frexp(mant, &e2); ex += e2; }
+        ex += p.prod_exp;
+    }
+    const float sumF = (float)(s1 + cnt * c0);
+    out->sum = sumF;
+    // the reference divides its binary32 accumulator by (double)numElems and stores a float (Aggregates_serial.hpp:62-64)
+    out->mean = (float)((double)sumF / (double)numElems);
+    const double dm = (double)out->mean - c0;
+    double vs = s2 - 2.0 * dm * s1 + cnt * dm * dm;
+    if (vs < 0.0) vs = 0.0;
+    out->var = (float)((double)(float)vs / (double)numElems);           // :81
+    out->stddev = sqrtf(out->var);                                       // :82
+    if (ex > 4000) ex = 4000;
+    if (ex < -4000) ex = -4000;
+    out->prod = (float)std::ldexp(mant, (int)ex);
+    return 0;
+}
+
+int vktb_aggregates_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_aggregates* out)
+{
+    static_assert(sizeof(vktb_aggregates) == 52, "vktb_aggregates must match vkt::Aggregates");
+    if (!vol || !out) return fail("vktb_aggregates_range: null argument");
+    vktb_agg_partial p;
+    if (vktb_aggregates_partial(vol, first, last, &p) != 0) return -1;
+    const uint64_t numElems = (uint64_t)vol->dims[0] * (uint64_t)vol->dims[1] * (uint64_t)vol->dims[2];
+    return vktb_aggregates_finish(&p, 1, numElems, out);
 }
 
 // Host-side slab planner: the reference's own coordinate expression (Resample_serial.hpp:60-62) evaluated in

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <vector>
 
+#include <vkt/Aggregates.hpp>
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
 #include <vkt/Decompose.hpp>
@@ -428,6 +429,34 @@ namespace
     Error Flip(StructuredVolume& dest, StructuredVolume& source, Axis axis)
     {
         return FlipRange(dest, source, Vec3i{ 0, 0, 0 }, dest.getDims(), Vec3i{ 0, 0, 0 }, axis);   // dest dims: Flip.cpp:28-36
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Aggregates (reference src/vkt/Aggregates.cpp:23-66)
+    //---------------------------------------------------------------------------------------------------------
+    Error ComputeAggregatesRange(StructuredVolume& volume, Aggregates& aggregates, Vec3i first, Vec3i last)
+    {
+        static_assert(sizeof(Aggregates) == sizeof(vktb_aggregates), "vkt::Aggregates is the C-ABI struct");
+        if (first.x > last.x || first.y > last.y || first.z > last.z) return InvalidValue;   // the reference would not end
+        return dispatch("ComputeAggregatesRange",
+            [&] { host::aggregatesRange(viewOf(volume), first, last, aggregates); },
+            [&] {
+                vktb_vol v = host::describe(volume);
+                int32_t f[3], l[3];
+                toArray(first, f); toArray(last, l);
+                return vktb_aggregates_range(&v, f, l, reinterpret_cast<vktb_aggregates*>(&aggregates));
+            });
+    }
+
+    Error ComputeAggregatesRange(StructuredVolume& volume, Aggregates& aggregates, int32_t firstX, int32_t firstY,
+                                 int32_t firstZ, int32_t lastX, int32_t lastY, int32_t lastZ)
+    {
+        return ComputeAggregatesRange(volume, aggregates, Vec3i{ firstX, firstY, firstZ }, Vec3i{ lastX, lastY, lastZ });
+    }
+
+    Error ComputeAggregates(StructuredVolume& volume, Aggregates& aggregates)
+    {
+        return ComputeAggregatesRange(volume, aggregates, Vec3i{ 0, 0, 0 }, volume.getDims());
     }
 
     //---------------------------------------------------------------------------------------------------------

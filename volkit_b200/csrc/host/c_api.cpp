@@ -1,5 +1,6 @@
 // C99 API over the C++ host mirror (reference: the "C API" halves of src/vkt/{ExecutionPolicy,Memory,
 // StructuredVolume,Voxel,Fill,Copy,Arithmetic,Transform}.cpp).  The opaque handle wraps a vkt::StructuredVolume.
+#include <vkt/Aggregates.h>
 #include <vkt/Arithmetic.h>
 #include <vkt/Array3D.h>
 #include <vkt/Copy.h>
@@ -14,6 +15,7 @@
 #include <vkt/Transform.h>
 #include <vkt/Voxel.h>
 
+#include <vkt/Aggregates.hpp>
 #include <vkt/Arithmetic.hpp>
 #include <vkt/Copy.hpp>
 #include <vkt/Decompose.hpp>
@@ -27,6 +29,7 @@
 #include <vkt/Transform.hpp>
 #include <vkt/Voxel.hpp>
 
+#include <cstring>
 #include <vector>
 
 #include "serial.hpp"
@@ -226,6 +229,24 @@ vktError vktBrickDecomposeResizeSV(vktArray3D_vktStructuredVolume decomp, vktStr
                                           (vktDataFormat)s.getDataFormat(), dist.x, dist.y, dist.z, m.x, m.y);
             }
     return vktNoError;
+}
+
+//--- Aggregates (reference src/vkt/Aggregates.cpp:75-112) ---------------------------------------------------------
+vktError vktComputeAggregatesSV(vktStructuredVolume volume, vktAggregates_t* aggregates)
+{
+    static_assert(sizeof(vktAggregates_t) == sizeof(vkt::Aggregates), "same 13 words");
+    vkt::Aggregates a;
+    vktError e = (vktError)vkt::ComputeAggregates(volume->volume, a);
+    std::memcpy(aggregates, &a, sizeof(a));
+    return e;
+}
+vktError vktComputeAggregatesRangeSV(vktStructuredVolume volume, vktAggregates_t* aggregates, int32_t fx, int32_t fy,
+                                     int32_t fz, int32_t lx, int32_t ly, int32_t lz)
+{
+    vkt::Aggregates a;
+    vktError e = (vktError)vkt::ComputeAggregatesRange(volume->volume, a, fx, fy, fz, lx, ly, lz);
+    std::memcpy(aggregates, &a, sizeof(a));
+    return e;
 }
 
 //--- Scan (reference src/vkt/Scan.cpp:79-122) -------------------------------------------------------------------

@@ -1,5 +1,6 @@
 #include "serial.hpp"
 
+#include <cfloat>
 #include <cmath>
 #include <cstring>
 
@@ -157,6 +158,36 @@ namespace host
                     std::memcpy(dst.data + dst.offset(off.x + x, off.y + y, off.z + z), v2, dst.bpv);
                     std::memcpy(dst.data + dst.offset(off.x + xx, off.y + yy, off.z + zz), v1, dst.bpv);
                 }
+    }
+
+    // reference src/vkt/Aggregates_serial.hpp:20-83: binary32 running accumulators, x fastest; the divisions by the
+    // WHOLE volume's voxel count (:60) run in binary64 and are stored back as floats
+    void aggregatesRange(View vol, Vec3i first, Vec3i last, Aggregates& a)
+    {
+        std::memset(&a, 0, sizeof(a));
+        a.min = FLT_MAX;
+        a.max = -FLT_MAX;
+        a.prod = 1.f;
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    const float val = unmapVoxel(vol.data + vol.offset(x, y, z), vol.format, vol.lo, vol.hi);
+                    if (val < a.min) { a.min = val; a.argmin = { x, y, z }; }
+                    if (val > a.max) { a.max = val; a.argmax = { x, y, z }; }
+                    a.mean += val;
+                    a.sum += val;
+                    a.prod *= val;
+                }
+        const std::size_t numElems = vol.dims.x * std::size_t(vol.dims.y) * vol.dims.z;
+        a.mean = (float)(a.mean / (double)numElems);
+        for (int32_t z = first.z; z < last.z; ++z)
+            for (int32_t y = first.y; y < last.y; ++y)
+                for (int32_t x = first.x; x < last.x; ++x) {
+                    const float val = unmapVoxel(vol.data + vol.offset(x, y, z), vol.format, vol.lo, vol.hi);
+                    a.var += (val - a.mean) * (val - a.mean);
+                }
+        a.var = (float)(a.var / (double)numElems);
+        a.stddev = sqrtf(a.var);
     }
 
     // reference src/vkt/Histogram_serial.hpp:18-51; indices outside [0, numBins) are skipped (the reference's UB)

@@ -6,6 +6,7 @@
 
 #include <cstdint>
 
+#include <vkt/Aggregates.hpp>
 #include <vkt/Transform.hpp>
 #include <vkt/common.hpp>
 #include <vkt/linalg.hpp>
@@ -37,6 +38,8 @@ namespace host
     void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset, int axis);
     // in place on dst (already holding the copied range): first/last in dst space, first > last = downwards
     void scanRange(View dst, Vec3i first, Vec3i last);
+    // out: the 13 words of vkt::Aggregates
+    void aggregatesRange(View vol, Vec3i first, Vec3i last, Aggregates& out);
     void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins);
 
     // BrickDecomposeResize's brick grid (reference src/vkt/Decompose.cpp:96-146): number of bricks and the dims of

@@ -59,6 +59,21 @@ cudaError_t launchHistogram(const LaunchCtx&, const VolDesc& vol, const int32_t 
                             unsigned long long* bins, size_t numBins, unsigned long long* droppedDev);
 cudaError_t launchScan(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3], const int32_t last[3],
                        const int32_t off[3]);
+// Aggregates: combinable moments of a range (kernels/aggregates.cu).  minIdx / maxIdx are linear indices inside the
+// range (x fastest), ~0 when no voxel was below FLT_MAX (above -FLT_MAX).
+struct AggPartial
+{
+    double sumD, sumD2;          // sum (v - shift), sum (v - shift)^2
+    double prodMant;             // prod = prodMant * 2^prodExp
+    long long prodExp;
+    unsigned long long minIdx, maxIdx;
+    float min, max, shift;
+    int pad;
+};
+size_t aggregatesScratchBytes(const LaunchCtx&);
+// scratchDev: aggregatesScratchBytes() of device memory; *totalDev points at the range's total inside it
+cudaError_t launchAggregates(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3],
+                             AggPartial* scratchDev, AggPartial** totalDev);
 cudaError_t launchDebugCodec(const LaunchCtx&, int format, Mapping m, const float* values, uint32_t* mapped,
                              float* unmapped, size_t n);
 

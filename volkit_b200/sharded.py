@@ -291,3 +291,40 @@ def histogram_sharded(vol: ShardedVolume, first, last, num_bins: int, dist, comp
     if dist is not None and vol.world > 1:
         dist.all_reduce(bins, op=dist.ReduceOp.SUM)
     return bins
+
+
+# ---- Aggregates of a sharded volume: one 88-byte partial per rank, all-gathered, folded in rank (= z) order ------------
+
+def _cabi_aggregates_partial(vol_desc, first, last, part):
+    lib = capi.load()
+    capi.check(lib.vktb_aggregates_partial(ctypes.byref(vol_desc), capi.I3(*first), capi.I3(*last), ctypes.byref(part)),
+               "vktb_aggregates_partial")
+
+
+def aggregates_sharded(vol: ShardedVolume, first, last, dist, compute=None) -> "capi.VktbAggregates":
+    """ComputeAggregatesRange (reference src/vkt/Aggregates_serial.hpp:20-83) of a z-slab sharded volume: every rank
+    reduces the planes of [first, last) it owns to one vktb_agg_partial (moments, product, extrema with positions),
+    the partials travel through ONE all-gather (88 bytes per rank) and every rank folds them in rank order with
+    vktb_aggregates_finish (host arithmetic), so ties between slabs go to the lower z like the serial walk."""
+    torch = vol.torch
+    part = capi.VktbAggPartial()
+    part.prod_mant, part.min, part.max = 1.0, 3.4028234663852886e38, -3.4028234663852886e38
+    z0, z1 = max(first[2], vol.z0), min(last[2], vol.z1)
+    if z1 > z0 and last[0] > first[0] and last[1] > first[1]:
+        f = (first[0], first[1], z0 - vol.z0)
+        l = (last[0], last[1], z1 - vol.z0)
+        (compute or _cabi_aggregates_partial)(vol.desc(), f, l, part)
+        part.argmin[2] += vol.z0 if part.has_min else 0          # slab -> whole-volume coordinates
+        part.argmax[2] += vol.z0 if part.has_max else 0
+    world = vol.world if dist is not None else 1
+    raw = bytes(part)
+    if world > 1:
+        mine = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(vol.storage.device)
+        everyone = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(everyone, mine)
+        raw = b"".join(bytes(t.cpu().numpy().tobytes()) for t in everyone)
+    parts = (capi.VktbAggPartial * world).from_buffer_copy(raw)
+    out = capi.VktbAggregates()
+    num_elems = vol.dims[0] * vol.dims[1] * vol.dims[2]
+    capi.check(capi.load().vktb_aggregates_finish(parts, world, num_elems, ctypes.byref(out)), "vktb_aggregates_finish")
+    return out
