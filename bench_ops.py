@@ -94,6 +94,23 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, steps=5, warmup
     record(f"Histogram 256 bins {S}^3 UInt16", n, 2 * n,
            lambda: capi.check(lib.vktb_histogram_range(ctypes.byref(da), z3, l3, bins, 256, None)))
     capi.check(lib.vktb_free(bins))
+    # Scale / Rotate / ApplyFilter
+    F9, F3 = ctypes.c_float * 9, ctypes.c_float * 3
+    half = F3(S / 2, S / 2, S / 2)
+    record(f"Scale x1.5 about the centre {S}^3 UInt16", n, int(2 * n + 2 * n / 3.375),
+           lambda: capi.check(lib.vktb_affine_range(ctypes.byref(dd), ctypes.byref(da), z3, l3,
+                                                    F9(1 / 1.5, 0, 0, 0, 1 / 1.5, 0, 0, 0, 1 / 1.5), half)),
+           "every dst voxel is written; the (1/1.5)^3 of the source it maps to is read once")
+    import math
+    cs, sn = math.cos(0.5), math.sin(0.5)
+    record(f"Rotate 0.5 rad about z through the centre {S}^3 UInt16", n, 4 * n,
+           lambda: capi.check(lib.vktb_affine_range(ctypes.byref(dd), ctypes.byref(da), z3, l3,
+                                                    F9(cs, -sn, 0, sn, cs, 0, 0, 0, 1), half)),
+           "alg_bytes = one read + one write per voxel (upper bound: voxels that rotate out of the volume are skipped)")
+    box = (ctypes.c_float * 27)(*([1.0 / 27.0] * 27))
+    record(f"ApplyFilter 3x3x3 {S}^3 UInt16", n, 4 * n,
+           lambda: capi.check(lib.vktb_apply_filter(ctypes.byref(dd), ctypes.byref(da), box, capi.I3(3, 3, 3), 2)),
+           "27 FMUL + 27 FADD per voxel in the reference's order: CUDA-core bound, see DESIGN.md")
     # Aggregates: one read pass, result on the host (the call is synchronous)
     agg = capi.VktbAggregates()
     record(f"Aggregates {S}^3 UInt16", n, 2 * n,

@@ -168,6 +168,27 @@ int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                          size_t num_bins, uint64_t* dropped_host);
 
+/* ScaleRange_cuda / RotateRange_cuda (src/vkt/Scale_cuda.hpp, Rotate_cuda.hpp: empty bodies in
+ * the reference); semantics of ScaleRange_serial (src/vkt/Scale_serial.hpp:15-56) and RotateRange_serial
+ * (src/vkt/Rotate_serial.hpp:41-94), which differ only in the matrix: every voxel p of the WHOLE dst volume is mapped
+ * to q = M (p - center) + center in binary32; when first <= q < last on all axes the voxel receives
+ * sampleLinear((int)q.x, (int)q.y, (int)q.z) of src (integer parameters: the reference's 8-tap expression with
+ * frac 0, clamps as written), otherwise it keeps its value.  matrix = col0.xyz, col1.xyz, col2.xyz (vkt::Mat3f);
+ * Scale passes diag(1/s), Rotate the inverse rotation built from axis and angle on the host.  dst may be src. */
+int vktb_affine_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                      const float matrix[9], const float center[3]);
+
+/* ApplyFilterRange_cuda(StructuredVolume& dest, StructuredVolume& source, Vec3i first, Vec3i last, Filter, AddressMode)
+ * (src/vkt/Filter_cuda.hpp:12-21, an empty body in the reference); semantics of ApplyFilterRange_serial
+ * (src/vkt/Filter_serial.hpp:15-64) over [0, src dims) as vkt::ApplyFilter calls it (src/vkt/Filter.cpp:48-66): border
+ * voxels (a coordinate equal to 0 or dims - 1) receive map(0), all others the binary32 sum of weight * voxel over
+ * the filter window in z, y, x order (multiply and add rounded separately).  weights: filter_dims[0] *
+ * filter_dims[1] * filter_dims[2] HOST floats, x fastest (vkt::Filter's data); each filter dim must be 1, 2 or 3
+ * (the reference reads outside the volume with larger ones).  address_mode is accepted and ignored, as in the
+ * reference.  dst may be src (the reference filters a copy of the source). */
+int vktb_apply_filter(const vktb_vol* dst, const vktb_vol* src, const float* weights, const int32_t filter_dims[3],
+                      int address_mode);
+
 /* ComputeAggregatesRange_cuda(StructuredVolume&, Aggregates&, Vec3i first, Vec3i last)
  * (src/vkt/Aggregates_cuda.hpp:14-21, an empty body in the reference); semantics of ComputeAggregatesRange_serial
  * (src/vkt/Aggregates_serial.hpp:20-83).  vktb_aggregates has the layout of vkt::Aggregates / vktAggregates_t

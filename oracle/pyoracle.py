@@ -95,6 +95,10 @@ class _Lib:
         f("flip_range", ctypes.c_int, [p, p, I3, I3, I3, ctypes.c_int])
         f("histogram_range", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p])
         f("scan_range", ctypes.c_int, [p, p, I3, I3, I3])
+        F3 = ctypes.c_float * 3
+        f("scale", ctypes.c_int, [p, p, F3, F3])
+        f("rotate", ctypes.c_int, [p, p, F3, ctypes.c_float, F3])
+        f("apply_filter", ctypes.c_int, [p, p, ctypes.POINTER(ctypes.c_float), I3])
         f("aggregates_range", ctypes.c_int, [p, I3, I3, ctypes.POINTER(Aggregates)])
         i32p = ctypes.POINTER(ctypes.c_int32)
         f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
@@ -149,6 +153,20 @@ class _Lib:
         assert self._histogram_range(ctypes.byref(vol.c()), I3(*first), I3(*last), bins.ctypes.data, num_bins,
                                      dropped.ctypes.data) == 0
         return bins, int(dropped[0])
+
+    def scale(self, dst: Vol, src: Vol, factor, center):
+        F3 = ctypes.c_float * 3
+        assert self._scale(ctypes.byref(dst.c()), ctypes.byref(src.c()), F3(*factor), F3(*center)) == 0
+
+    def rotate(self, dst: Vol, src: Vol, axis, angle: float, center):
+        F3 = ctypes.c_float * 3
+        assert self._rotate(ctypes.byref(dst.c()), ctypes.byref(src.c()), F3(*axis), angle, F3(*center)) == 0
+
+    def apply_filter(self, dst: Vol, src: Vol, weights: np.ndarray):
+        """weights: float32 array shaped (fz, fy, fx); src may be dst itself"""
+        w = np.ascontiguousarray(weights, np.float32)
+        assert self._apply_filter(ctypes.byref(dst.c()), ctypes.byref(src.c()),
+                                  w.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), I3(*w.shape[::-1])) == 0
 
     def aggregates_range(self, vol: Vol, first, last) -> "Aggregates":
         a = Aggregates()

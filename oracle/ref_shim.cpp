@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <cstring>
 #include <cstdlib>
+#include <vector>
 
 #include <vkt/Aggregates.hpp>
 #include <vkt/Arithmetic.hpp>
@@ -28,9 +29,12 @@
 #include <vkt/StructuredVolume.h>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Filter.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Rotate.hpp>
+#include <vkt/Scale.hpp>
 #include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -286,6 +290,44 @@ int ref_histogram_range(RefVol const* vol, int32_t const* first, int32_t const* 
     std::size_t* c = h.getBinCounts();
     for (size_t i = 0; i < numBins; ++i) bins[i] = (uint64_t)c[i];
     if (dropped) *dropped = 0;
+    return 0;
+}
+
+// vkt::Scale (include/cpp/vkt/Scale.hpp:12-15 -> src/vkt/Scale.cpp:21-40), vkt::Rotate (include/cpp/vkt/Rotate.hpp:12-16
+// -> src/vkt/Rotate.cpp:21-42), vkt::ApplyFilter (include/cpp/vkt/Filter.hpp:42-45 -> src/vkt/Filter.cpp:48-66)
+int ref_scale(RefVol const* dst, RefVol const* src, float const* factor, float const* center)
+{
+    if (dst->data == src->data) return -1;
+    Staged d(dst), s(src);
+    vkt::Scale(d.vol, s.vol, { factor[0], factor[1], factor[2] }, { center[0], center[1], center[2] });
+    d.writeBack();
+    return 0;
+}
+
+int ref_rotate(RefVol const* dst, RefVol const* src, float const* axis, float angle, float const* center)
+{
+    if (dst->data == src->data) return -1;
+    Staged d(dst), s(src);
+    vkt::Rotate(d.vol, s.vol, { axis[0], axis[1], axis[2] }, angle, { center[0], center[1], center[2] });
+    d.writeBack();
+    return 0;
+}
+
+int ref_apply_filter(RefVol const* dst, RefVol const* src, float const* weights, int32_t const* fdims)
+{
+    for (int a = 0; a < 3; ++a)
+        if (fdims[a] < 1 || fdims[a] > 3) return -1;       // the reference would read outside the volume
+    std::vector<float> w(weights, weights + (size_t)fdims[0] * fdims[1] * fdims[2]);
+    vkt::Filter filter(w.data(), v3(fdims));
+    if (dst->data == src->data) {
+        Staged v(dst);
+        vkt::ApplyFilter(v.vol, v.vol, filter, vkt::AddressMode::Clamp);
+        v.writeBack();
+        return 0;
+    }
+    Staged d(dst), s(src);
+    vkt::ApplyFilter(d.vol, s.vol, filter, vkt::AddressMode::Clamp);
+    d.writeBack();
     return 0;
 }
 

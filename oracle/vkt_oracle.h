@@ -61,6 +61,16 @@ int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3
 int vko_histogram_range(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                         size_t num_bins, uint64_t* dropped);
 
+/* Scale / Rotate (range = [0, source dims)) and the shared body with an explicit matrix (col0, col1, col2) */
+void vko_scale_matrix(const float factor[3], float m[9]);
+void vko_rotate_matrix(const float axis[3], float angle, float m[9]);
+int vko_affine_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
+                     const float m[9], const float center[3]);
+int vko_scale(const vko_vol* dst, const vko_vol* src, const float factor[3], const float center[3]);
+int vko_rotate(const vko_vol* dst, const vko_vol* src, const float axis[3], float angle, const float center[3]);
+/* ApplyFilter over [0, source dims); weights x fastest, filter dims 1..3 */
+int vko_apply_filter(const vko_vol* dst, const vko_vol* src, const float* weights, const int32_t fdims[3]);
+
 /* vkt::Aggregates (reference include/cpp/vkt/Aggregates.hpp:14-25) */
 typedef struct vko_aggregates
 {

@@ -33,6 +33,25 @@ SCAN_CASES = [((12, 9, 7), (12, 9, 7), (0, 0, 0), (12, 9, 7), (0, 0, 0), False),
               ((5, 6, 40), (5, 6, 40), (2, 0, 0), (3, 6, 40), (0, 0, 0), True)]      # one voxel wide
 
 
+# Scale / Rotate: (source dims, dest dims, ("scale", factor, center) | ("rotate", axis, angle, center))
+AFFINE_CASES = [((21, 13, 11), (21, 13, 11), ("scale", (1.5, 0.75, 2.0), (10.0, 6.0, 5.0))),
+                ((21, 13, 11), (30, 9, 14), ("scale", (0.5, 1.0, 3.0), (0.0, 0.0, 0.0))),
+                ((16, 16, 16), (16, 16, 16), ("scale", (1.0, 1.0, 1.0), (3.5, 2.25, 8.0))),     # identity: a plain copy
+                ((21, 13, 11), (21, 13, 11), ("rotate", (1.0, 2.0, 0.5), 0.7, (10.0, 6.0, 5.0))),
+                ((21, 13, 11), (30, 9, 14), ("rotate", (0.0, 0.0, 1.0), 1.5707964, (10.0, 6.0, 5.0))),
+                ((24, 24, 8), (24, 24, 8), ("rotate", (0.0, 0.0, -3.0), 3.1415927, (11.5, 11.5, 4.0)))]
+# ApplyFilter: filter dims (x, y, z), each 1..3
+FILTER_DIMS = [(3, 3, 3), (1, 2, 3), (2, 2, 2), (3, 1, 1), (1, 1, 1)]
+
+
+def filter_weights(fdims, seed=0):
+    """(fz, fy, fx) float32 weights; seed 0 = the 3x3x3 box blur the reference's users pass, else random"""
+    n = fdims[0] * fdims[1] * fdims[2]
+    if seed == 0:
+        return np.full(fdims[::-1], np.float32(1.0) / np.float32(n), np.float32)
+    return np.random.default_rng(seed).standard_normal(fdims[::-1]).astype(np.float32)
+
+
 # ComputeAggregatesRange: (dims, first, last); whole volume, a range (numElems stays the whole volume's), a few voxels
 # (prod stays inside the binary32 range), one row, one voxel
 AGG_CASES = [((33, 9, 8), (0, 0, 0), (33, 9, 8)), ((33, 9, 8), (1, 2, 1), (30, 9, 7)), ((33, 9, 8), (5, 3, 2), (8, 5, 4)),
@@ -179,6 +198,14 @@ def cases():
         for i, (ddims, sdims, first, last, off, inplace) in enumerate(SCAN_CASES):
             out.append((f"scan/{fmt}/{i}", "scan",
                         dict(ddims=ddims, sdims=sdims, fmt=fmt, first=first, last=last, off=off, inplace=inplace)))
+    # --- Scale / Rotate / ApplyFilter
+    for sfmt, dfmt in ((U8, U8), (U16, U16), (U32, U32), (F32, F32), (U16, F32), (F32, U8)):
+        for i in range(len(AFFINE_CASES)):
+            out.append((f"affine/{sfmt}/{dfmt}/{i}", "affine", dict(sfmt=sfmt, dfmt=dfmt, i=i)))
+        for i, fd in enumerate(FILTER_DIMS):
+            for inplace in ((False, True) if sfmt == dfmt else (False,)):
+                out.append((f"filter/{sfmt}/{dfmt}/{i}/{int(inplace)}", "filter",
+                            dict(sfmt=sfmt, dfmt=dfmt, fdims=fd, seed=i, inplace=inplace)))
     # --- Aggregates: [exact fields, accumulated fields] of the reference
     for fmt in FMT4:
         for lo, hi in ((0.0, 1.0), (-1000.0, 3000.0)):
@@ -233,6 +260,24 @@ def run_case(lib, case) -> list[np.ndarray]:
         bins, dropped = lib.histogram_range(v, p["first"], p["last"], p["bins"])
         assert dropped == 0, "case must stay inside the reference's defined behaviour"
         return [bins]
+    if kind == "affine":
+        sdims, ddims, op = AFFINE_CASES[p["i"]]
+        src = mk(sdims, p["sfmt"], 2, -1000.0, 3000.0)
+        d = mk(ddims, p["dfmt"], 5, -1.0, 2.0)
+        if op[0] == "scale":
+            lib.scale(d, src, op[1], op[2])
+        else:
+            lib.rotate(d, src, op[1], op[2], op[3])
+        return [d.a]
+    if kind == "filter":
+        src = mk((26, 13, 11), p["sfmt"], 2, -1.0, 2.0)
+        w = filter_weights(p["fdims"], p["seed"])
+        if p["inplace"]:
+            lib.apply_filter(src, src, w)
+            return [src.a]
+        d = mk((29, 13, 12), p["dfmt"], 5, 0.0, 1.0)
+        lib.apply_filter(d, src, w)
+        return [d.a]
     if kind == "agg":
         v = mk(p["dims"], p["fmt"], 4, p["lo"], p["hi"])
         a = lib.aggregates_range(v, p["first"], p["last"])

@@ -13,10 +13,13 @@
 #include <vkt/Copy.hpp>
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Filter.hpp>
 #include <vkt/Decompose.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Rotate.hpp>
+#include <vkt/Scale.hpp>
 #include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -135,6 +138,22 @@ int main(int argc, char** argv)
     Histogram hist(300);
     CHECK(ComputeHistogramRange(a, hist, 1, 2, 3, 47, 39, 35));
 
+    // Scale, Rotate (into pre-filled volumes: voxels that map outside the source keep their value), ApplyFilter
+    StructuredVolume scl(X, Y, Z, DataFormat::UInt16), rot(64, 48, 44, DataFormat::UInt16), flt(X, Y, Z, DataFormat::UInt16), fin(a);
+    CHECK(Fill(scl, .125f));
+    CHECK(Fill(rot, .25f));
+    CHECK(Scale(scl, a, Vec3f{ 1.5f, .75f, 2.f }, Vec3f{ 20.f, 18.f, 16.f }));
+    CHECK(Rotate(rot, a, Vec3f{ 1.f, 2.f, .5f }, .7f, Vec3f{ 24.f, 20.f, 18.f }));
+    float box[27];
+    for (int i = 0; i < 27; ++i) box[i] = 1.f / 27.f;
+    Filter filter(box, Vec3i{ 3, 3, 3 });
+    CHECK(ApplyFilter(flt, a, filter, AddressMode::Clamp));
+    CHECK(ApplyFilter(fin, fin, filter, AddressMode::Clamp));        // in place: the reference filters a copy
+    float big[125] = {};
+    Filter tooBig(big, Vec3i{ 5, 5, 5 });
+    if (ApplyFilter(flt, a, tooBig, AddressMode::Clamp) != InvalidValue) return 13;
+    if (Scale(fin, fin, Vec3f{ 1.f, 1.f, 1.f }, Vec3f{ 0.f, 0.f, 0.f }) != InvalidValue) return 14;
+
     // Aggregates over a range (numElems stays the whole volume's voxel count)
     Aggregates agg;
     CHECK(ComputeAggregatesRange(a, agg, 1, 2, 3, 47, 39, 35));
@@ -162,6 +181,7 @@ int main(int argc, char** argv)
     save(sum, "out_sum.raw"); save(diff, "out_diff.raw"); save(prod, "out_prod.raw"); save(cpy, "out_cpy.raw");
     save(t1, "out_t1.raw"); save(t2, "out_t2.raw"); save(up, "out_up.raw"); save(down, "out_down.raw");
     save(sc, "out_sc.raw"); save(sci, "out_sci.raw");
+    save(scl, "out_scl.raw"); save(rot, "out_rot.raw"); save(flt, "out_flt.raw"); save(fin, "out_fin.raw");
     save(fx, "out_fx.raw"); save(fy, "out_fy.raw"); save(fz, "out_fz.raw");
     {
         FILE* f = std::fopen((g_dir + "/out_hist.raw").c_str(), "wb");

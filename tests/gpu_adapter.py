@@ -110,6 +110,39 @@ class GpuLib:
             s.free()
         self._down(d, dst)
 
+    def _affine(self, dst, src, m, center):
+        d, s = self._up(dst), self._up(src)
+        F9, F3 = ctypes.c_float * 9, ctypes.c_float * 3
+        capi.check(self.lib.vktb_affine_range(ctypes.byref(d.desc()), ctypes.byref(s.desc()), I3(0, 0, 0),
+                                              I3(*src.a.shape[::-1]), F9(*m), F3(*center)), "affine")
+        self._down(d, dst)
+        s.free()
+
+    def scale(self, dst, src, factor, center):
+        """the matrix comes from the host side of the boundary (vkt::Scale builds it); here: the oracle's twin"""
+        F3, F9 = ctypes.c_float * 3, ctypes.c_float * 9
+        m = F9()
+        po.oracle().lib.vko_scale_matrix(F3(*factor), m)
+        self._affine(dst, src, list(m), center)
+
+    def rotate(self, dst, src, axis, angle, center):
+        F3, F9 = ctypes.c_float * 3, ctypes.c_float * 9
+        m = F9()
+        po.oracle().lib.vko_rotate_matrix(F3(*axis), ctypes.c_float(angle), m)
+        self._affine(dst, src, list(m), center)
+
+    def apply_filter(self, dst, src, weights):
+        import numpy as np
+        w = np.ascontiguousarray(weights, np.float32)
+        d = self._up(dst)
+        s = d if src is dst else self._up(src)
+        capi.check(self.lib.vktb_apply_filter(ctypes.byref(d.desc()), ctypes.byref(s.desc()),
+                                              w.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), I3(*w.shape[::-1]), 2),
+                   "apply_filter")
+        self._down(d, dst)
+        if s is not d:
+            s.free()
+
     def aggregates_range(self, vol, first, last):
         """vktb_aggregates_range -> po.Aggregates (same 13 words)"""
         v = self._up(vol)

@@ -593,6 +593,49 @@ def test_histogram_kernels(gpu):
     assert int(got.sum()) + gd == 64 * 32 * 16
 
 
+def test_affine_and_filter_kernels(gpu):
+    """Scale / Rotate / ApplyFilter at sizes that engage the vector stores, the z-march chunks (ragged last chunk, z
+    chunk borders) and the one-tap / eight-tap / generic kernels; Float32 sources with NaN / Inf / -0 taps."""
+    o = po.oracle()
+    for sfmt, dfmt in ((po.UINT16, po.UINT16), (po.UINT8, po.UINT8), (po.FLOAT32, po.FLOAT32), (po.UINT16, po.FLOAT32),
+                       (po.UINT32, po.UINT16), (po.INT16, po.INT16)):
+        src = cases.mk((96, 40, 37), sfmt, 2, -3.0, 5.0)
+        if sfmt == po.FLOAT32:
+            src.a[3, 5, 7], src.a[10, 20, 95], src.a[36, 39, 95], src.a[0, 0, 0] = np.nan, np.inf, -np.inf, -0.0
+        for ddims, op in (((96, 40, 37), ("scale", (1.25, 0.8, 1.5), (40.0, 20.0, 18.0))),
+                          ((128, 33, 40), ("rotate", (0.3, -1.0, 2.0), 0.9, (48.0, 20.0, 18.0))),
+                          ((96, 40, 37), ("scale", (1.0, 1.0, 1.0), (0.0, 0.0, 0.0)))):
+            a, b = cases.mk(ddims, dfmt, 5, 0.0, 1.0), cases.mk(ddims, dfmt, 5, 0.0, 1.0)
+            for lib, d in ((gpu, a), (o, b)):
+                if op[0] == "scale":
+                    lib.scale(d, src, op[1], op[2])
+                else:
+                    lib.rotate(d, src, op[1], op[2], op[3])
+            assert same_bits(a.a, b.a), (sfmt, dfmt, ddims, op)
+        for fd, seed in (((3, 3, 3), 0), ((3, 3, 3), 3), ((2, 3, 1), 4)):
+            w = cases.filter_weights(fd, seed)
+            for ident in (True, False):
+                s2 = po.Vol(src.a, sfmt, 0.0, 1.0) if ident else src
+                a, b = cases.mk((96, 40, 37), dfmt, 5, 0.0 if ident else -1.0, 1.0), None
+                b = a.copy()
+                gpu.apply_filter(a, s2, w); o.apply_filter(b, s2, w)
+                assert same_bits(a.a, b.a), (sfmt, dfmt, fd, seed, ident)
+        if sfmt == dfmt:
+            a, b = src.copy(), src.copy()
+            w = cases.filter_weights((3, 3, 3), 9)
+            gpu.apply_filter(a, a, w); o.apply_filter(b, b, w)
+            assert same_bits(a.a, b.a), (sfmt, "in place")
+    # thin volumes: everything is border
+    for dims in ((40, 2, 9), (1, 1, 1), (2, 2, 2), (3, 3, 3), (40, 9, 1)):
+        src = cases.mk(dims, po.UINT16, 2)
+        a, b = cases.mk(dims, po.UINT16, 5), cases.mk(dims, po.UINT16, 5)
+        w = cases.filter_weights((3, 3, 3), 2)
+        gpu.apply_filter(a, src, w); o.apply_filter(b, src, w)
+        assert a.a.tobytes() == b.a.tobytes(), dims
+    with pytest.raises(Exception):
+        gpu.apply_filter(a, src, np.zeros((5, 3, 3), np.float32))
+
+
 def test_aggregates(gpu):
     """ComputeAggregatesRange: min/max/argmin/argmax bit-exact (first occurrence, ties, NaN skipped, -0 / +0), the
     accumulated statistics inside the reference's own rounding bound (cases.check_aggregates); flat and row kernels,

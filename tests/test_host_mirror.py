@@ -92,6 +92,19 @@ def run_cpp(programs, policy, tmp):
     assert raw(tmp / "out_fz.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     bins, dropped = o.histogram_range(a, (1, 2, 3), (47, 39, 35), 300)
     assert dropped == 0 and np.fromfile(tmp / "out_hist.raw", np.uint64).tobytes() == bins.tobytes()
+    ref = po.empty(dims, U16)
+    o.fill_range(ref, *full, 0.125)
+    o.scale(ref, a, (1.5, 0.75, 2.0), (20.0, 18.0, 16.0))
+    assert raw(tmp / "out_scl.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    ref = po.empty(cd, U16)
+    o.fill_range(ref, (0, 0, 0), cd, 0.25)
+    o.rotate(ref, a, (1.0, 2.0, 0.5), 0.7, (24.0, 20.0, 18.0))
+    assert raw(tmp / "out_rot.raw", cd, np.uint16).tobytes() == ref.a.tobytes()
+    box = np.full((3, 3, 3), np.float32(1.0) / np.float32(27.0), np.float32)
+    ref = po.empty(dims, U16)
+    o.apply_filter(ref, a, box)
+    assert raw(tmp / "out_flt.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    assert raw(tmp / "out_fin.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     got_agg = po.Aggregates.from_buffer_copy((tmp / "out_agg.raw").read_bytes())
     ref_agg = o.aggregates_range(a, (1, 2, 3), (47, 39, 35))
     if policy == "cpu":

@@ -80,6 +80,8 @@ SIGNATURES = {
     "vktb_resample_window_src_range3": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, I3, I3,
                                                        _P(ctypes.c_int32), _P(ctypes.c_int32)]),
     "vktb_flip_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3, ctypes.c_int]),
+    "vktb_affine_range": (ctypes.c_int, [_VP, _VP, I3, I3, _P(ctypes.c_float), _P(ctypes.c_float)]),
+    "vktb_apply_filter": (ctypes.c_int, [_VP, _VP, _P(ctypes.c_float), I3, ctypes.c_int]),
     "vktb_aggregates_range": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggregates)]),
     "vktb_aggregates_partial": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggPartial)]),
     "vktb_aggregates_finish": (ctypes.c_int, [_P(VktbAggPartial), ctypes.c_int, ctypes.c_uint64, _P(VktbAggregates)]),

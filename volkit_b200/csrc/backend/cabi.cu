@@ -217,6 +217,60 @@ int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int3
     return finish("vktb_histogram_range", e);
 }
 
+// ---- Scale / Rotate / ApplyFilter ------------------------------------------------------------------------------
+// The reference reads the source while it writes dest; with dest == source (or overlapping buffers) the serial walk
+// would see its own output.  Filter works on a copy by construction (Filter_serial.hpp:29); for the affine ops the
+// same copy is made here, which is what a caller who passes one volume twice can reasonably expect.
+static cudaError_t privateCopyIfOverlapping(const VolDesc& dst, VolDesc& src, cudaStream_t s, void** tmp)
+{
+    *tmp = nullptr;
+    if (!overlaps(dst, src)) return cudaSuccess;
+    const size_t bytes = (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bytesPerVoxel(src.format);
+    cudaError_t e = cudaMallocAsync(tmp, bytes ? bytes : 1, s);
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(*tmp, src.data, bytes, cudaMemcpyDeviceToDevice, s);
+    src.data = (uint8_t*)*tmp;
+    return e;
+}
+
+int vktb_affine_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
+                      const float matrix[9], const float center[3])
+{
+    VolDesc dv, sv;
+    if (!first || !last || !matrix || !center) return fail("vktb_affine_range: null argument");
+    if (!toDesc("vktb_affine_range", dst, dv) || !toDesc("vktb_affine_range", src, sv)) return -1;
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    cudaStream_t s = currentStream(d);
+    LaunchCtx c{ s, d->smCount };
+    void* tmp = nullptr;
+    cudaError_t e = privateCopyIfOverlapping(dv, sv, s, &tmp);
+    if (e == cudaSuccess) e = launchAffine(c, dv, sv, first, last, matrix, center);
+    if (tmp) cudaFreeAsync(tmp, s);
+    return finish("vktb_affine_range", e);
+}
+
+int vktb_apply_filter(const vktb_vol* dst, const vktb_vol* src, const float* weights, const int32_t fdims[3], int /*addressMode*/)
+{
+    VolDesc dv, sv;
+    if (!weights || !fdims) return fail("vktb_apply_filter: null argument");
+    if (!toDesc("vktb_apply_filter", dst, dv) || !toDesc("vktb_apply_filter", src, sv)) return -1;
+    for (int a = 0; a < 3; ++a)
+        if (fdims[a] < 1 || fdims[a] > 3)
+            return fail("vktb_apply_filter: filter dims must be 1..3 per axis (the reference reads outside the volume otherwise)");
+    for (int a = 0; a < 3; ++a)
+        if (dv.dims[a] < sv.dims[a]) return fail("vktb_apply_filter: dest is smaller than source");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    cudaStream_t s = currentStream(d);
+    LaunchCtx c{ s, d->smCount };
+    void* tmp = nullptr;
+    cudaError_t e = privateCopyIfOverlapping(dv, sv, s, &tmp);
+    if (e == cudaSuccess) e = launchFilter(c, dv, sv, weights, fdims);
+    if (tmp) cudaFreeAsync(tmp, s);
+    return finish("vktb_apply_filter", e);
+}
+
 // ---- Aggregates ---------------------------------------------------------------------------------------------
 static void emptyPartial(vktb_agg_partial* o)
 {

@@ -13,9 +13,12 @@
 #include <vkt/Copy.hpp>
 #include <vkt/Decompose.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Filter.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Rotate.hpp>
+#include <vkt/Scale.hpp>
 #include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -429,6 +432,68 @@ namespace
     Error Flip(StructuredVolume& dest, StructuredVolume& source, Axis axis)
     {
         return FlipRange(dest, source, Vec3i{ 0, 0, 0 }, dest.getDims(), Vec3i{ 0, 0, 0 }, axis);   // dest dims: Flip.cpp:28-36
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // Scale / Rotate (reference src/vkt/Scale.cpp:21-40, src/vkt/Rotate.cpp:21-42): range = [0, source dims)
+    //---------------------------------------------------------------------------------------------------------
+    namespace
+    {
+        Error affine(char const* name, StructuredVolume& dest, StructuredVolume& source, const float m[9], Vec3f center)
+        {
+            if (&dest == &source) return InvalidValue;      // the serial walk would read its own output
+            const Vec3i first{ 0, 0, 0 }, last = source.getDims();
+            return dispatch(name,
+                [&] { host::affineRange(viewOf(dest), viewOf(source), first, last, m, center); },
+                [&] {
+                    vktb_vol d = host::describe(dest), s = host::describe(source);
+                    int32_t f[3], l[3];
+                    toArray(first, f); toArray(last, l);
+                    const float c[3] = { center.x, center.y, center.z };
+                    return vktb_affine_range(&d, &s, f, l, m, c);
+                });
+        }
+    }
+
+    Error Scale(StructuredVolume& dest, StructuredVolume& source, Vec3f scalingFactor, Vec3f centerOfScaling)
+    {
+        float m[9];
+        host::scaleMatrix(scalingFactor, m);
+        return affine("ScaleRange", dest, source, m, centerOfScaling);
+    }
+
+    Error Rotate(StructuredVolume& dest, StructuredVolume& source, Vec3f axis, float angleInRadians, Vec3f centerOfRotation)
+    {
+        float m[9];
+        host::rotateMatrix(axis, angleInRadians, m);
+        return affine("RotateRange", dest, source, m, centerOfRotation);
+    }
+
+    //---------------------------------------------------------------------------------------------------------
+    // ApplyFilter (reference src/vkt/Filter.cpp:25-66)
+    //---------------------------------------------------------------------------------------------------------
+    Filter::Filter(float* data, Vec3i dims)
+        : data_(data, data + (dims.x > 0 && dims.y > 0 && dims.z > 0 ? dims.x * std::size_t(dims.y) * dims.z : 0)), dims_(dims) {}
+    float* Filter::getData() { return data_.data(); }
+    Vec3i Filter::getDims() const { return dims_; }
+
+    Error ApplyFilter(StructuredVolume& dest, StructuredVolume& source, Filter& filter, AddressMode am)
+    {
+        const Vec3i fd = filter.getDims();
+        if (fd.x < 1 || fd.x > 3 || fd.y < 1 || fd.y > 3 || fd.z < 1 || fd.z > 3) return InvalidValue;
+        const Vec3i dd = dest.getDims(), sd = source.getDims();
+        if (dd.x < sd.x || dd.y < sd.y || dd.z < sd.z) return InvalidValue;
+        return dispatch("ApplyFilterRange",
+            [&] {
+                host::View d = viewOf(dest);
+                host::applyFilter(d, &dest == &source ? d : viewOf(source), filter.getData(), fd);
+            },
+            [&] {
+                vktb_vol d = host::describe(dest), s = &dest == &source ? d : host::describe(source);
+                int32_t f[3];
+                toArray(fd, f);
+                return vktb_apply_filter(&d, &s, filter.getData(), f, (int)am);
+            });
     }
 
     //---------------------------------------------------------------------------------------------------------

@@ -10,6 +10,8 @@
 #include <vkt/Flip.h>
 #include <vkt/Memory.h>
 #include <vkt/Resample.h>
+#include <vkt/Rotate.h>
+#include <vkt/Scale.h>
 #include <vkt/Scan.h>
 #include <vkt/StructuredVolume.h>
 #include <vkt/Transform.h>
@@ -24,6 +26,8 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Memory.hpp>
 #include <vkt/Resample.hpp>
+#include <vkt/Rotate.hpp>
+#include <vkt/Scale.hpp>
 #include <vkt/Scan.hpp>
 #include <vkt/StructuredVolume.hpp>
 #include <vkt/Transform.hpp>
@@ -229,6 +233,19 @@ vktError vktBrickDecomposeResizeSV(vktArray3D_vktStructuredVolume decomp, vktStr
                                           (vktDataFormat)s.getDataFormat(), dist.x, dist.y, dist.z, m.x, m.y);
             }
     return vktNoError;
+}
+
+//--- Scale / Rotate (reference src/vkt/Scale.cpp:47-65, src/vkt/Rotate.cpp:49-69) ------------------------------------
+vktError vktScaleSV(vktStructuredVolume dest, vktStructuredVolume source, vktVec3f_t scalingFactor, vktVec3f_t centerOfScaling)
+{
+    return (vktError)vkt::Scale(dest->volume, source->volume, { scalingFactor.x, scalingFactor.y, scalingFactor.z },
+                                { centerOfScaling.x, centerOfScaling.y, centerOfScaling.z });
+}
+vktError vktRotateSV(vktStructuredVolume dest, vktStructuredVolume source, vktVec3f_t axis, float angleInRadians,
+                     vktVec3f_t centerOfRotation)
+{
+    return (vktError)vkt::Rotate(dest->volume, source->volume, { axis.x, axis.y, axis.z }, angleInRadians,
+                                 { centerOfRotation.x, centerOfRotation.y, centerOfRotation.z });
 }
 
 //--- Aggregates (reference src/vkt/Aggregates.cpp:75-112) ---------------------------------------------------------

@@ -3,6 +3,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #include "host_codec.hpp"
 
@@ -141,6 +142,86 @@ namespace host
             }
         }
     }
+    // StructuredVolumeView::sampleLinear(int32_t, int32_t, int32_t) (src/vkt/StructuredVolumeView.hpp:80-119), clamps as written
+    static float sampleLinearRef(const View& src, int sx, int sy, int sz)
+    {
+        const Vec3i S = src.dims;
+        const long long row = S.x, plane = (long long)S.x * S.y;
+        const int lx = clampi(sx, 0, S.x - 1), ly = clampi(sy, 0, S.y - 1), lz = sz;
+        const int hx = sx + 1, hy = clampi(sy + 1, 0, S.y - 1), hz = clampi(sz + 1, 0, S.z - 1);
+        const float fx = (float)sx - (float)lx, fy = (float)sy - (float)ly, fz = (float)sz - (float)lz;
+        const float v0 = tap(src, lz * plane + ly * row + lx), v1 = tap(src, lz * plane + ly * row + hx);
+        const float v2 = tap(src, lz * plane + hy * row + lx), v3 = tap(src, lz * plane + hy * row + hx);
+        const float v4 = tap(src, hz * plane + ly * row + lx), v5 = tap(src, hz * plane + ly * row + hx);
+        const float v6 = tap(src, hz * plane + hy * row + lx), v7 = tap(src, hz * plane + hy * row + hx);
+        return refLerp(refLerp(refLerp(v0, v1, fx), refLerp(v2, v3, fx), fy),
+                       refLerp(refLerp(v4, v5, fx), refLerp(v6, v7, fx), fy), fz);
+    }
+
+    // reference src/vkt/Scale_serial.hpp:27-31
+    void scaleMatrix(Vec3f f, float m[9])
+    {
+        for (int i = 0; i < 9; ++i) m[i] = 0.f;
+        m[0] = 1.f / f.x; m[4] = 1.f / f.y; m[8] = 1.f / f.z;
+    }
+
+    // reference src/vkt/Rotate_serial.hpp:55-72 (normalised axis, inverted angle, quaternion) and :17-39 (to a matrix)
+    void rotateMatrix(Vec3f axis, float angle, float m[9])
+    {
+        const float len = sqrtf(axis.x * axis.x + axis.y * axis.y + axis.z * axis.z);
+        const float ax = axis.x / len, ay = axis.y / len, az = axis.z / len;
+        angle = 6.28319f - angle;
+        const float re = cosf(angle * .5f);
+        const float ix = ax * sinf(angle * .5f), iy = ay * sinf(angle * .5f), iz = az * sinf(angle * .5f);
+        const float xx = ix * ix, xy = ix * iy, xz = ix * iz, xw = ix * re, yy = iy * iy, yz = iy * iz, yw = iy * re;
+        const float zz = iz * iz, zw = iz * re, ww = re * re;
+        m[0] = 2.f * (ww + xx) - 1.f; m[1] = 2.f * (xy + zw);       m[2] = 2.f * (xz - yw);
+        m[3] = 2.f * (xy - zw);       m[4] = 2.f * (ww + yy) - 1.f; m[5] = 2.f * (yz + xw);
+        m[6] = 2.f * (xz + yw);       m[7] = 2.f * (yz - xw);       m[8] = 2.f * (ww + zz) - 1.f;
+    }
+
+    // reference src/vkt/Scale_serial.hpp:36-55 / Rotate_serial.hpp:77-93: the whole dst volume is walked
+    void affineRange(View dst, View src, Vec3i first, Vec3i last, const float m[9], Vec3f c)
+    {
+        for (int32_t z = 0; z < dst.dims.z; ++z)
+            for (int32_t y = 0; y < dst.dims.y; ++y)
+                for (int32_t x = 0; x < dst.dims.x; ++x) {
+                    const float px = (float)x - c.x, py = (float)y - c.y, pz = (float)z - c.z;
+                    float qx = m[0] * px + m[3] * py + m[6] * pz;
+                    float qy = m[1] * px + m[4] * py + m[7] * pz;
+                    float qz = m[2] * px + m[5] * py + m[8] * pz;
+                    qx = qx + c.x; qy = qy + c.y; qz = qz + c.z;
+                    if (qx >= (float)first.x && qx < (float)last.x && qy >= (float)first.y && qy < (float)last.y
+                        && qz >= (float)first.z && qz < (float)last.z)
+                        mapVoxel(dst.data + dst.offset(x, y, z), sampleLinearRef(src, cvtt32(qx), cvtt32(qy), cvtt32(qz)),
+                                 dst.format, dst.lo, dst.hi);
+                }
+    }
+
+    // reference src/vkt/Filter_serial.hpp:15-64 over [0, src dims)
+    void applyFilter(View dst, View src, const float* w, Vec3i fd)
+    {
+        const std::size_t bytes = (std::size_t)src.dims.x * src.dims.y * src.dims.z * src.bpv;
+        std::vector<uint8_t> copy(src.data, src.data + bytes);
+        View temp = src;
+        temp.data = copy.data();
+        const Vec3i last = src.dims;
+        const int hx = fd.x / 2, hy = fd.y / 2, hz = fd.z / 2;
+        for (int32_t z = 0; z < last.z; ++z)
+            for (int32_t y = 0; y < last.y; ++y)
+                for (int32_t x = 0; x < last.x; ++x) {
+                    float value = 0.f;
+                    if (!(x == 0 || y == 0 || z == 0 || x == last.x - 1 || y == last.y - 1 || z == last.z - 1))
+                        for (int32_t zz = 0; zz < fd.z; ++zz)
+                            for (int32_t yy = 0; yy < fd.y; ++yy)
+                                for (int32_t xx = 0; xx < fd.x; ++xx)
+                                    value += w[(zz * fd.y + yy) * fd.x + xx]
+                                             * unmapVoxel(temp.data + temp.offset(x - hx + xx, y - hy + yy, z - hz + zz),
+                                                          temp.format, temp.lo, temp.hi);
+                    mapVoxel(dst.data + dst.offset(x, y, z), value, dst.format, dst.lo, dst.hi);
+                }
+    }
+
     // reference src/vkt/Flip_serial.hpp:11-63, as written (first ignored, z mirrored on Axis::Y, Axis::Z mirrors nothing)
     void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i off, int axis)
     {

@@ -38,6 +38,12 @@ namespace host
     void flipRange(View dst, View src, Vec3i first, Vec3i last, Vec3i dstOffset, int axis);
     // in place on dst (already holding the copied range): first/last in dst space, first > last = downwards
     void scanRange(View dst, Vec3i first, Vec3i last);
+    // Scale / Rotate: m = col0.xyz, col1.xyz, col2.xyz; dst.data != src.data
+    void scaleMatrix(Vec3f factor, float m[9]);
+    void rotateMatrix(Vec3f axis, float angleInRadians, float m[9]);
+    void affineRange(View dst, View src, Vec3i first, Vec3i last, const float m[9], Vec3f center);
+    // weights x fastest, fdims in 1..3; dst may alias src (a copy is filtered)
+    void applyFilter(View dst, View src, const float* weights, Vec3i fdims);
     // out: the 13 words of vkt::Aggregates
     void aggregatesRange(View vol, Vec3i first, Vec3i last, Aggregates& out);
     void histogramRange(View vol, Vec3i first, Vec3i last, std::size_t* bins, std::size_t numBins);

@@ -1,0 +1,357 @@
+// Scale / Rotate (inverse-mapped affine gather) and ApplyFilter (small dense convolution).
+//
+// Scale / Rotate -- reference src/vkt/Scale_serial.hpp:15-56, Rotate_serial.hpp:41-94.  Both walk the WHOLE dst
+// volume, map every dst voxel through p' = M (p - c) + c (binary32, the sum of the three products evaluated left
+// to right: linalg.hpp:584-591) and, when p' lies inside [first, last) (float compares against the converted
+// integers), store sampleLinear(p'.x, p'.y, p'.z) -- whose parameters are int32_t, so the coordinates are truncated
+// and the "linear" filter degenerates to the reference-faithful 8-tap expression with frac = 0 (the same
+// body Resample uses).  Voxels that map outside the range keep their dst value.  The matrix is built on the host
+// (1 / scalingFactor on the diagonal; quaternion -> matrix with the host libm's sinf / cosf, exactly the
+// reference's expressions) and arrives here as nine floats.
+//
+// ApplyFilter -- reference src/vkt/Filter_serial.hpp:15-64: over [0, src dims): voxels with a coordinate equal to 0
+// or last - 1 receive map(0); every other voxel receives sum_{zz,yy,xx} f(xx,yy,zz) * src(x - fx/2 + xx, ...),
+// accumulated in binary32 from 0 in exactly that order (multiply, round, add, round -- no FMA); the address mode is
+// ignored.  The reference reads a copy of the source, so dst may alias src (the launcher copies then).  Filter dims
+// are limited to 1..3 per axis: larger ones make the reference read outside the volume.
+//   3x3x3, same format on both sides: z-march -- a thread owns one (x, y) column of a z chunk, keeps the unmapped
+//   3x3 neighbourhoods of two planes in registers and reads nine voxels per output through the read-only L1 path
+//   (neighbouring threads share them); 27 FMUL + 27 FADD per voxel in the reference's order make this kernel
+//   CUDA-core bound, not HBM bound.
+//   anything else: one thread per voxel, runtime codec (parity path).
+// Algorithmic bytes: bpv_src + bpv_dst per voxel for both.
+#include "launch.hpp"
+
+#include <cmath>
+
+namespace vktb {
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------
+// affine gather
+// ---------------------------------------------------------------------------------------------------------------
+struct AffineParams
+{
+    uint8_t*       d;
+    const uint8_t* s;
+    int Dx, Dy, Dz;
+    int Sx, Sy, Sz;
+    float m[9];              // col0.xyz, col1.xyz, col2.xyz
+    float c[3];
+    float first[3], last[3]; // the range, converted int -> float like the reference's compares do
+    Mapping md, ms;
+};
+
+template <int FS>
+__device__ __forceinline__ float affTap(const AffineParams& p, long long idx, long long count)
+{
+    constexpr int BS = bytesPerVoxel(FS);
+    // a tap outside the buffer (the unclamped hi.x of the volume's last voxel, an unclamped lo.z) reads as a zero voxel
+    const uint32_t raw = (idx >= 0 && idx < count) ? loadRaw(p.s + idx * BS, BS) : 0u;
+    return unmapVoxel<FS, false>(raw, p.ms);
+}
+
+// StructuredVolumeView::sampleLinear(int32_t, int32_t, int32_t), src/vkt/StructuredVolumeView.hpp:80-119, clamps as written
+template <int FS>
+__device__ __forceinline__ float sampleLinearRef(const AffineParams& p, int x, int y, int z)
+{
+    const float xf1 = __int2float_rn(x), yf1 = __int2float_rn(y), zf1 = __int2float_rn(z);
+    int lx = (int)x86Cvtt32(xf1), ly = (int)x86Cvtt32(yf1);
+    const int lz = (int)x86Cvtt32(zf1);
+    const int hx = (int)x86Cvtt32(__fadd_rn(xf1, 1.f));
+    int hy = (int)x86Cvtt32(__fadd_rn(yf1, 1.f)), hz = (int)x86Cvtt32(__fadd_rn(zf1, 1.f));
+    lx = min(max(lx, 0), p.Sx - 1); ly = min(max(ly, 0), p.Sy - 1);
+    hy = min(max(hy, 0), p.Sy - 1); hz = min(max(hz, 0), p.Sz - 1);
+    const float fx = __fsub_rn(xf1, __int2float_rn(lx)), fy = __fsub_rn(yf1, __int2float_rn(ly));
+    const float fz = __fsub_rn(zf1, __int2float_rn(lz));
+    const long long plane = (long long)p.Sx * p.Sy, count = plane * p.Sz;
+    const long long r00 = lz * plane + (long long)ly * p.Sx, r10 = lz * plane + (long long)hy * p.Sx;
+    const long long r01 = hz * plane + (long long)ly * p.Sx, r11 = hz * plane + (long long)hy * p.Sx;
+    const float v0 = affTap<FS>(p, r00 + lx, count), v1 = affTap<FS>(p, r00 + hx, count);
+    const float v2 = affTap<FS>(p, r10 + lx, count), v3 = affTap<FS>(p, r10 + hx, count);
+    const float v4 = affTap<FS>(p, r01 + lx, count), v5 = affTap<FS>(p, r01 + hx, count);
+    const float v6 = affTap<FS>(p, r11 + lx, count), v7 = affTap<FS>(p, r11 + hx, count);
+    return refLerp(refLerp(refLerp(v0, v1, fx), refLerp(v2, v3, fx), fy),
+                   refLerp(refLerp(v4, v5, fx), refLerp(v6, v7, fx), fy), fz);
+}
+
+// one thread = V consecutive dst voxels of one row; ONETAP: the range lies inside the source and every tap of an
+// integer source unmaps to a finite float, so the 8-tap chain with frac 0 returns the lo tap bit for bit
+template <int FS, int FD, bool ONETAP>
+__global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
+{
+    constexpr int BS = bytesPerVoxel(FS), BD = bytesPerVoxel(FD);
+    constexpr int V = 16 / BD;
+    const int chunks = (p.Dx + V - 1) / V;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= chunks) return;
+    const int x0 = c * V, n = min(V, p.Dx - x0);
+    const long long rows = (long long)p.Dy * p.Dz;
+    const long long plane = (long long)p.Sx * p.Sy;
+    for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows; r += (long long)gridDim.y * blockDim.y) {
+        const int z = (int)(r / p.Dy), y = (int)(r - (long long)z * p.Dy);
+        const float py = __fsub_rn(__int2float_rn(y), p.c[1]), pz = __fsub_rn(__int2float_rn(z), p.c[2]);
+        uint8_t* dp = p.d + (r * p.Dx + x0) * BD;
+        uint32_t out[V];
+        unsigned inside = 0;
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            if (i >= n) continue;
+            const float px = __fsub_rn(__int2float_rn(x0 + i), p.c[0]);
+            // (a*x + b*y) + c*z, then + center
+            const float qx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[0], px), __fmul_rn(p.m[3], py)), __fmul_rn(p.m[6], pz)), p.c[0]);
+            const float qy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[1], px), __fmul_rn(p.m[4], py)), __fmul_rn(p.m[7], pz)), p.c[1]);
+            const float qz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[2], px), __fmul_rn(p.m[5], py)), __fmul_rn(p.m[8], pz)), p.c[2]);
+            if (qx >= p.first[0] && qx < p.last[0] && qy >= p.first[1] && qy < p.last[1] && qz >= p.first[2] && qz < p.last[2]) {
+                const int sx = (int)x86Cvtt32(qx), sy = (int)x86Cvtt32(qy), sz = (int)x86Cvtt32(qz);
+                float v;
+                if (ONETAP) v = unmapVoxel<FS, false>(loadRaw(p.s + (sz * plane + (long long)sy * p.Sx + sx) * BS, BS), p.ms);
+                else v = sampleLinearRef<FS>(p, sx, sy, sz);
+                out[i] = mapVoxel<FD, false>(v, p.md);
+                inside |= 1u << i;
+            }
+        }
+        if (inside == (1u << V) - 1u && (reinterpret_cast<uintptr_t>(dp) & 15u) == 0) {
+            uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+            for (int i = 0; i < V; ++i) vecSet<BD>(w, i, out[i]);
+            stStream(dp, make_uint4(w[0], w[1], w[2], w[3]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+                if (inside & (1u << i)) storeRaw(dp + i * BD, BD, out[i]);
+        }
+    }
+}
+
+bool oneTapExact(const VolDesc& src)
+{
+    if (src.format == F_F32) return false;
+    const float e[2] = { src.map.lo, src.map.hi };
+    for (int i = 0; i < 2; ++i) {
+        if (!std::isfinite(e[i]) || std::fabs(e[i]) >= 1e38f) return false;
+        if (std::signbit(e[i]) && std::fabs(e[i]) < 1e-30f) return false;
+    }
+    return true;
+}
+
+template <int FS, int FD>
+cudaError_t launchAffineFF(const LaunchCtx& c, const AffineParams& p, bool oneTap)
+{
+    constexpr int V = 16 / bytesPerVoxel(FD);
+    const RowsLaunch l = rowsLaunch(p.Dx, (long long)p.Dy * p.Dz, V);
+    if (oneTap) affineKernel<FS, FD, true><<<l.grid, l.block, 0, c.stream>>>(p);
+    else affineKernel<FS, FD, false><<<l.grid, l.block, 0, c.stream>>>(p);
+    countLaunch();
+    return cudaGetLastError();
+}
+
+template <int FS>
+cudaError_t launchAffineF(const LaunchCtx& c, const AffineParams& p, int fd, bool oneTap)
+{
+    switch (fd) {
+    case F_U8:    return launchAffineFF<FS, F_U8>(c, p, oneTap);
+    case F_U16:   return launchAffineFF<FS, F_U16>(c, p, oneTap);
+    case F_INT16: return launchAffineFF<FS, F_INT16>(c, p, oneTap);
+    case F_U32:   return launchAffineFF<FS, F_U32>(c, p, oneTap);
+    case F_F32:   return launchAffineFF<FS, F_F32>(c, p, oneTap);
+    }
+    return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// ApplyFilter
+// ---------------------------------------------------------------------------------------------------------------
+struct FilterParams
+{
+    uint8_t*       d;
+    const uint8_t* s;
+    int nx, ny, nz;          // the range [0, src dims)
+    int Dx, Dy;              // dst row length / rows per plane (setValue indexes with the dst dims)
+    int fx, fy, fz;          // filter dims, 1..3
+    int zChunk;
+    float w[27];             // f(xx, yy, zz) at [zz * fx * fy + yy * fx + xx]
+    Mapping md, ms;
+    int fs, fd;              // formats (generic kernel)
+};
+
+// nine unmapped voxels around (x, y) in plane z
+template <int F, bool IDENT>
+__device__ __forceinline__ void loadPlane9(float (&v)[9], const FilterParams& p, int x, int y, int z)
+{
+    constexpr int B = bytesPerVoxel(F);
+    const uint8_t* row = p.s + (((long long)z * p.ny + (y - 1)) * p.nx + (x - 1)) * B;
+#pragma unroll
+    for (int yy = 0; yy < 3; ++yy) {
+#pragma unroll
+        for (int xx = 0; xx < 3; ++xx) {
+            uint32_t raw;
+            if (B == 1) raw = __ldg(row + xx);
+            else if (B == 2) raw = __ldg(reinterpret_cast<const uint16_t*>(row) + xx);
+            else raw = __ldg(reinterpret_cast<const uint32_t*>(row) + xx);
+            v[yy * 3 + xx] = unmapVoxel<F, IDENT>(raw, p.ms);
+        }
+        row += (long long)p.nx * B;
+    }
+}
+
+__device__ __forceinline__ float accPlane9(float acc, const float (&v)[9], const float* w)
+{
+#pragma unroll
+    for (int i = 0; i < 9; ++i) acc = __fadd_rn(acc, __fmul_rn(w[i], v[i]));
+    return acc;
+}
+
+// 3x3x3, src format == dst format.  block (32, 8): a 32 x 8 tile of columns; blockIdx.z: z chunk
+template <int F, bool IDS, bool IDD>
+__global__ void __launch_bounds__(kThreads) filter3MarchKernel(FilterParams p)
+{
+    constexpr int B = bytesPerVoxel(F);
+    const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    if (x >= p.nx || y >= p.ny) return;
+    const int z0 = blockIdx.z * p.zChunk, z1 = min(z0 + p.zChunk, p.nz);
+    const uint32_t zero = mapVoxel<F, IDD>(0.f, p.md);
+    uint8_t* dcol = p.d + ((long long)y * p.Dx + x) * B;
+    const long long dPlane = (long long)p.Dx * p.Dy * B;
+    auto put = [&](int z, uint32_t raw) {
+        uint8_t* q = dcol + z * dPlane;
+        if (B == 1) *q = (uint8_t)raw;
+        else if (B == 2) *reinterpret_cast<uint16_t*>(q) = (uint16_t)raw;
+        else *reinterpret_cast<uint32_t*>(q) = raw;
+    };
+    if (x == 0 || y == 0 || x == p.nx - 1 || y == p.ny - 1) {
+        for (int z = z0; z < z1; ++z) put(z, zero);
+        return;
+    }
+    int zs = z0, ze = z1;
+    if (zs == 0) { put(0, zero); zs = 1; }
+    if (ze == p.nz) { if (p.nz - 1 >= zs) put(p.nz - 1, zero); ze = p.nz - 1; }
+    if (zs >= ze) return;
+    float a[9], b[9], cc[9];
+    loadPlane9<F, IDS>(a, p, x, y, zs - 1);
+    loadPlane9<F, IDS>(b, p, x, y, zs);
+    int z = zs;
+    // three planes per round so that the register planes rotate by renaming
+    for (; z + 2 < ze; z += 3) {
+        loadPlane9<F, IDS>(cc, p, x, y, z + 1);
+        put(z, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, a, p.w), b, p.w + 9), cc, p.w + 18), p.md));
+        loadPlane9<F, IDS>(a, p, x, y, z + 2);
+        put(z + 1, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, b, p.w), cc, p.w + 9), a, p.w + 18), p.md));
+        loadPlane9<F, IDS>(b, p, x, y, z + 3);
+        put(z + 2, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, cc, p.w), a, p.w + 9), b, p.w + 18), p.md));
+    }
+    for (; z < ze; ++z) {
+        loadPlane9<F, IDS>(cc, p, x, y, z + 1);
+        put(z, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, a, p.w), b, p.w + 9), cc, p.w + 18), p.md));
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { a[i] = b[i]; b[i] = cc[i]; }
+    }
+}
+
+// any filter dims in 1..3, any formats: one thread per voxel
+__global__ void __launch_bounds__(kThreads) filterGenericKernel(FilterParams p)
+{
+    const int bs = bytesPerVoxel(p.fs), bd = bytesPerVoxel(p.fd);
+    const long long n = (long long)p.nx * p.ny * p.nz;
+    const int hx = p.fx / 2, hy = p.fy / 2, hz = p.fz / 2;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(i % p.nx);
+        const long long r = i / p.nx;
+        const int y = (int)(r % p.ny), z = (int)(r / p.ny);
+        float value = 0.f;
+        if (!(x == 0 || y == 0 || z == 0 || x == p.nx - 1 || y == p.ny - 1 || z == p.nz - 1)) {
+            for (int zz = 0; zz < p.fz; ++zz)
+                for (int yy = 0; yy < p.fy; ++yy)
+                    for (int xx = 0; xx < p.fx; ++xx) {
+                        const long long si = ((long long)(z - hz + zz) * p.ny + (y - hy + yy)) * p.nx + (x - hx + xx);
+                        const float v = unmapVoxelRt(p.fs, loadRaw(p.s + si * bs, bs), p.ms);
+                        value = __fadd_rn(value, __fmul_rn(p.w[(zz * p.fy + yy) * p.fx + xx], v));
+                    }
+        }
+        storeRaw(p.d + (((long long)z * p.Dy + y) * p.Dx + x) * bd, bd, mapVoxelRt(p.fd, value, p.md));
+    }
+}
+
+template <int F>
+cudaError_t launchFilter3(const LaunchCtx& c, const FilterParams& p, dim3 grid)
+{
+    const dim3 block(32, 8, 1);
+    const bool ids = p.ms.identity && F != F_INT16, idd = p.md.identity && F != F_INT16;
+    if (ids && idd) filter3MarchKernel<F, true, true><<<grid, block, 0, c.stream>>>(p);
+    else filter3MarchKernel<F, false, false><<<grid, block, 0, c.stream>>>(p);
+    countLaunch();
+    return cudaGetLastError();
+}
+
+} // namespace
+
+cudaError_t launchAffine(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
+                         const int32_t last[3], const float m[9], const float center[3])
+{
+    if (dst.dims[0] <= 0 || dst.dims[1] <= 0 || dst.dims[2] <= 0) return cudaSuccess;
+    if (src.dims[0] <= 0 || src.dims[1] <= 0 || src.dims[2] <= 0) return cudaErrorInvalidValue;
+    AffineParams p;
+    p.d = dst.data; p.s = src.data;
+    p.Dx = dst.dims[0]; p.Dy = dst.dims[1]; p.Dz = dst.dims[2];
+    p.Sx = src.dims[0]; p.Sy = src.dims[1]; p.Sz = src.dims[2];
+    for (int i = 0; i < 9; ++i) p.m[i] = m[i];
+    bool insideSrc = true;
+    for (int a = 0; a < 3; ++a) {
+        p.c[a] = center[a];
+        p.first[a] = (float)first[a]; p.last[a] = (float)last[a];
+        if (first[a] < 0 || last[a] > src.dims[a]) insideSrc = false;
+    }
+    p.md = dst.map; p.ms = src.map;
+    const bool oneTap = insideSrc && oneTapExact(src);
+    switch (src.format) {
+    case F_U8:    return launchAffineF<F_U8>(c, p, dst.format, oneTap);
+    case F_U16:   return launchAffineF<F_U16>(c, p, dst.format, oneTap);
+    case F_INT16: return launchAffineF<F_INT16>(c, p, dst.format, oneTap);
+    case F_U32:   return launchAffineF<F_U32>(c, p, dst.format, oneTap);
+    case F_F32:   return launchAffineF<F_F32>(c, p, dst.format, oneTap);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launchFilter(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, const float* weights,
+                         const int32_t fdims[3])
+{
+    FilterParams p;
+    p.nx = src.dims[0]; p.ny = src.dims[1]; p.nz = src.dims[2];
+    if (p.nx <= 0 || p.ny <= 0 || p.nz <= 0) return cudaSuccess;
+    for (int a = 0; a < 3; ++a)
+        if (fdims[a] < 1 || fdims[a] > 3) return cudaErrorInvalidValue;
+    p.d = dst.data; p.s = src.data;
+    p.Dx = dst.dims[0]; p.Dy = dst.dims[1];
+    p.fx = fdims[0]; p.fy = fdims[1]; p.fz = fdims[2];
+    for (int i = 0; i < 27; ++i) p.w[i] = i < p.fx * p.fy * p.fz ? weights[i] : 0.f;
+    p.md = dst.map; p.ms = src.map;
+    p.fs = src.format; p.fd = dst.format;
+    if (p.fx == 3 && p.fy == 3 && p.fz == 3 && src.format == dst.format) {
+        // z chunks: enough CTAs for every SM a few times over, at least 16 planes each (two extra plane loads per chunk)
+        const long long tiles = (long long)((p.nx + 31) / 32) * ((p.ny + 7) / 8);
+        int chunks = (int)(((long long)c.smCount * 16 + tiles - 1) / tiles);
+        if (chunks < 1) chunks = 1;
+        int zChunk = (p.nz + chunks - 1) / chunks;
+        if (zChunk < 16) zChunk = 16;
+        if (zChunk > p.nz) zChunk = p.nz;
+        p.zChunk = zChunk;
+        const dim3 grid((p.nx + 31) / 32, (p.ny + 7) / 8, (p.nz + zChunk - 1) / zChunk);
+        if (grid.y <= 65535 && grid.z <= 65535) {
+            switch (src.format) {
+            case F_U8:    return launchFilter3<F_U8>(c, p, grid);
+            case F_U16:   return launchFilter3<F_U16>(c, p, grid);
+            case F_INT16: return launchFilter3<F_INT16>(c, p, grid);
+            case F_U32:   return launchFilter3<F_U32>(c, p, grid);
+            case F_F32:   return launchFilter3<F_F32>(c, p, grid);
+            }
+        }
+    }
+    p.zChunk = 0;
+    const size_t n = (size_t)p.nx * p.ny * p.nz;
+    filterGenericKernel<<<flatGrid(n, kThreads, c.smCount, 16), kThreads, 0, c.stream>>>(p);
+    countLaunch();
+    return cudaGetLastError();
+}
+
+} // namespace vktb

@@ -74,6 +74,13 @@ size_t aggregatesScratchBytes(const LaunchCtx&);
 // scratchDev: aggregatesScratchBytes() of device memory; *totalDev points at the range's total inside it
 cudaError_t launchAggregates(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3],
                              AggPartial* scratchDev, AggPartial** totalDev);
+// Scale / Rotate: dst voxel p -> M (p - center) + center, sampled with the reference's sampleLinear when it falls
+// inside [first, last); m = col0.xyz, col1.xyz, col2.xyz.  dst must not overlap src (the C-ABI copies src then).
+cudaError_t launchAffine(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
+                         const int32_t last[3], const float m[9], const float center[3]);
+// ApplyFilter over [0, src dims); weights: fdims[0] * fdims[1] * fdims[2] HOST floats, x fastest; fdims in 1..3
+cudaError_t launchFilter(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const float* weights,
+                         const int32_t fdims[3]);
 cudaError_t launchDebugCodec(const LaunchCtx&, int format, Mapping m, const float* values, uint32_t* mapped,
                              float* unmapped, size_t n);
 
