@@ -96,6 +96,22 @@ namespace vkt
             data_ = moved;
         }
 
+        // volkit-b200 extension: migrate() for a buffer whose whole content is about to be overwritten (InputStream::read
+        // under the GPU policy): allocate on the new device, free the old allocation, copy nothing
+        void migrateDiscard()
+        {
+            ExecutionPolicy ep = GetThreadExecutionPolicy();
+            if (ep.device == lastAllocationPolicy_.device)
+                return;
+            T* fresh = nullptr;
+            Allocate((void**)&fresh, size_ * sizeof(T));
+            SetThreadExecutionPolicy(lastAllocationPolicy_);
+            Free(data_);
+            SetThreadExecutionPolicy(ep);
+            lastAllocationPolicy_ = ep;
+            data_ = fresh;
+        }
+
         // volkit-b200 extension: where the bytes live right now, and the pointer WITHOUT migrating
         bool residesOnHost() const { return lastAllocationPolicy_.device == ExecutionPolicy::Device::CPU; }
         T* dataInPlace() { return data_; }

@@ -44,4 +44,16 @@ namespace vkt
 
     class StructuredVolume;
 
+    // Data source base class for file I/O (reference include/cpp/vkt/common.hpp:81-91)
+    class DataSource
+    {
+    public:
+        virtual ~DataSource() {}
+        virtual std::size_t read(char* buf, std::size_t len) = 0;
+        virtual std::size_t write(char const* buf, std::size_t len) = 0;
+        virtual bool seek(std::size_t pos) = 0;
+        virtual bool flush() = 0;
+        virtual bool good() const = 0;
+    };
+
 } // vkt

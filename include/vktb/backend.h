@@ -82,6 +82,19 @@ int         vktb_sync(void);                       /* waits for compute + copy s
  * src/vkt/Memory_cuda.hpp:16-32, src/vkt/Memory.cpp:40-74, src/vkt/Memory_cuda.cu:15-49 */
 int vktb_alloc(void** ptr, size_t bytes);          /* pooled, stream-ordered device allocation */
 int vktb_free(void* ptr);
+/* what InputStream::read / OutputStream::write (src/vkt/InputStream.cpp:27-39,
+ * OutputStream.cpp:25-36) bottom out in under the GPU policy, where the reference hands the DEVICE pointer of
+ * volume.getData() to DataSource::read (fread into device memory).  The producer / consumer is called once per
+ * 16 MiB chunk with a slot of the pinned staging ring, so a chunk is read from the file while the previous chunks'
+ * DMAs run (stream_in), or written while the next chunks arrive (stream_out); no host copy of the volume exists.
+ * *sum (may be NULL) receives the sum of the callback's return values: the caller compares it with `bytes` the way
+ * the reference compares DataSource::read's return value.  Synchronous with respect to the callbacks; stream_in's
+ * data is ordered before later work on the current stream. */
+typedef size_t (*vktb_read_fn)(void* ctx, void* buf, size_t len);
+typedef size_t (*vktb_write_fn)(void* ctx, const void* buf, size_t len);
+int vktb_stream_in(void* dev_dst, size_t bytes, vktb_read_fn read, void* ctx, size_t* sum);
+int vktb_stream_out(const void* dev_src, size_t bytes, vktb_write_fn write, void* ctx, size_t* sum);
+
 /* Blocking contract of ManagedBuffer::migrate (include/cpp/vkt/ManagedBuffer.hpp:168-198): on return
  * the SOURCE may be freed or overwritten.  H2D from pageable memory is pipelined through pinned staging
  * (returns once the last chunk left the source; the DMA tail is ordered before later kernels);

@@ -99,6 +99,15 @@ class _Lib:
         f("scale", ctypes.c_int, [p, p, F3, F3])
         f("rotate", ctypes.c_int, [p, p, F3, ctypes.c_float, F3])
         f("apply_filter", ctypes.c_int, [p, p, ctypes.POINTER(ctypes.c_float), I3])
+        if kind == "reference":
+            f("write_range", ctypes.c_int, [p, I3, I3, ctypes.c_char_p])
+            f("read_range", ctypes.c_int, [p, I3, I3, ctypes.c_char_p])
+            f("write", ctypes.c_int, [p, ctypes.c_char_p])
+            f("read", ctypes.c_int, [p, ctypes.c_char_p])
+        else:
+            f("rows_gather", ctypes.c_size_t, [p, I3, I3, ctypes.c_void_p])
+            f("rows_scatter", ctypes.c_size_t, [p, I3, I3, ctypes.c_void_p])
+        f("rawfile_parse", None, [ctypes.c_char_p, I3, ctypes.POINTER(ctypes.c_int32)])
         f("aggregates_range", ctypes.c_int, [p, I3, I3, ctypes.POINTER(Aggregates)])
         i32p = ctypes.POINTER(ctypes.c_int32)
         f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
@@ -167,6 +176,38 @@ class _Lib:
         w = np.ascontiguousarray(weights, np.float32)
         assert self._apply_filter(ctypes.byref(dst.c()), ctypes.byref(src.c()),
                                   w.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), I3(*w.shape[::-1])) == 0
+
+    # ---- stream I/O.  The restatement works on byte buffers, the reference on real files.
+    def rows_gather(self, vol: Vol, first, last) -> bytes:
+        """the bytes OutputStream::writeRange emits"""
+        n = max(0, last[0] - first[0]) * max(0, last[1] - first[1]) * max(0, last[2] - first[2]) * vol.a.dtype.itemsize
+        buf = np.zeros(max(n, 1), np.uint8)
+        got = self._rows_gather(ctypes.byref(vol.c()), I3(*first), I3(*last), buf.ctypes.data)
+        return buf[:got].tobytes()
+
+    def rows_scatter(self, vol: Vol, first, last, data: bytes):
+        """what InputStream::readRange does with the stream `data`"""
+        buf = np.frombuffer(data, np.uint8).copy()
+        self._rows_scatter(ctypes.byref(vol.c()), I3(*first), I3(*last), buf.ctypes.data)
+
+    def write_range(self, vol: Vol, first, last, path: str) -> int:
+        return self._write_range(ctypes.byref(vol.c()), I3(*first), I3(*last), path.encode())
+
+    def read_range(self, vol: Vol, first, last, path: str) -> int:
+        return self._read_range(ctypes.byref(vol.c()), I3(*first), I3(*last), path.encode())
+
+    def write(self, vol: Vol, path: str) -> int:
+        return self._write(ctypes.byref(vol.c()), path.encode())
+
+    def read(self, vol: Vol, path: str) -> int:
+        return self._read(ctypes.byref(vol.c()), path.encode())
+
+    def rawfile_parse(self, name: str):
+        """(dims, DataFormat) RawFile's constructor parses out of a file name (the reference needs the file to exist:
+        its destructor fclose()s a null FILE* otherwise)"""
+        dims, fmt = I3(), ctypes.c_int32()
+        self._rawfile_parse(name.encode(), dims, ctypes.byref(fmt))
+        return tuple(dims), fmt.value
 
     def aggregates_range(self, vol: Vol, first, last) -> "Aggregates":
         a = Aggregates()

@@ -32,6 +32,9 @@
 #include <vkt/Filter.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
+#include <vkt/InputStream.hpp>
+#include <vkt/OutputStream.hpp>
+#include <vkt/RawFile.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/Rotate.hpp>
 #include <vkt/Scale.hpp>
@@ -329,6 +332,57 @@ int ref_apply_filter(RefVol const* dst, RefVol const* src, float const* weights,
     vkt::ApplyFilter(d.vol, s.vol, filter, vkt::AddressMode::Clamp);
     d.writeBack();
     return 0;
+}
+
+// vkt::OutputStream::writeRange / vkt::InputStream::readRange over a vkt::RawFile (include/cpp/vkt/OutputStream.hpp,
+// InputStream.hpp, RawFile.hpp -> src/vkt/OutputStream.cpp:38-71, InputStream.cpp:41-72, RawFile.cpp:42-135).  The
+// whole-volume read()/write() are the same calls with one line = the volume.  Returns the vkt::Error of the call.
+int ref_write_range(RefVol const* vol, int32_t const* first, int32_t const* last, char const* path)
+{
+    Staged v(vol);
+    vkt::RawFile file(path, "wb");
+    vkt::OutputStream os(file);
+    int e = (int)os.writeRange(v.vol, v3(first), v3(last));
+    os.flush();
+    return e;
+}
+
+int ref_read_range(RefVol const* vol, int32_t const* first, int32_t const* last, char const* path)
+{
+    Staged v(vol);
+    vkt::RawFile file(path, "rb");
+    vkt::InputStream is(file);
+    int e = (int)is.readRange(v.vol, v3(first), v3(last));
+    v.writeBack();
+    return e;
+}
+
+int ref_write(RefVol const* vol, char const* path)
+{
+    Staged v(vol);
+    vkt::RawFile file(path, "wb");
+    vkt::OutputStream os(file);
+    int e = (int)os.write(v.vol);
+    os.flush();
+    return e;
+}
+
+int ref_read(RefVol const* vol, char const* path)
+{
+    Staged v(vol);
+    vkt::RawFile file(path, "rb");
+    vkt::InputStream is(file);
+    int e = (int)is.read(v.vol);
+    v.writeBack();
+    return e;
+}
+
+void ref_rawfile_parse(char const* name, int32_t* dims, int32_t* format)
+{
+    vkt::RawFile file(name, "rb");      // opens nothing when the file does not exist; the parser runs regardless
+    vkt::Vec3i d = file.getDims();
+    dims[0] = d.x; dims[1] = d.y; dims[2] = d.z;
+    *format = (int32_t)file.getDataFormat();
 }
 
 // vkt::ComputeAggregatesRange (include/cpp/vkt/Aggregates.hpp:27-43 -> src/vkt/Aggregates.cpp:52-66).  out = the 52

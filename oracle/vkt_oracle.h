@@ -71,6 +71,11 @@ int vko_rotate(const vko_vol* dst, const vko_vol* src, const float axis[3], floa
 /* ApplyFilter over [0, source dims); weights x fastest, filter dims 1..3 */
 int vko_apply_filter(const vko_vol* dst, const vko_vol* src, const float* weights, const int32_t fdims[3]);
 
+/* OutputStream::writeRange / InputStream::readRange as byte streams, RawFile's file-name parser */
+size_t vko_rows_gather(const vko_vol* vol, const int32_t first[3], const int32_t last[3], uint8_t* bytes);
+size_t vko_rows_scatter(const vko_vol* vol, const int32_t first[3], const int32_t last[3], const uint8_t* bytes);
+void vko_rawfile_parse(const char* name, int32_t dims[3], int32_t* format);
+
 /* vkt::Aggregates (reference include/cpp/vkt/Aggregates.hpp:14-25) */
 typedef struct vko_aggregates
 {

@@ -17,6 +17,9 @@
 #include <vkt/Decompose.hpp>
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
+#include <vkt/InputStream.hpp>
+#include <vkt/OutputStream.hpp>
+#include <vkt/RawFile.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/Rotate.hpp>
 #include <vkt/Scale.hpp>
@@ -154,6 +157,38 @@ int main(int argc, char** argv)
     if (ApplyFilter(flt, a, tooBig, AddressMode::Clamp) != InvalidValue) return 13;
     if (Scale(fin, fin, Vec3f{ 1.f, 1.f, 1.f }, Vec3f{ 0.f, 0.f, 0.f }) != InvalidValue) return 14;
 
+    // Stream I/O under the running policy: whole volume out and back in, then rows of a range (lines start at x = 0
+    // of each row, as the reference addresses them).  RawFile counts items, so the codes are Write/ReadError.
+    StructuredVolume ioBack(X, Y, Z, DataFormat::UInt16), ioRange(X, Y, Z, DataFormat::UInt16);
+    CHECK(Fill(ioBack, .5f));
+    CHECK(Fill(ioRange, .75f));
+    {
+        std::string whole = g_dir + "/io_48x40x36_uint16.raw", part = g_dir + "/io_part.raw";
+        {
+            RawFile f(whole.c_str(), "wb");
+            if (f.getDims().x != 48 || f.getDims().y != 40 || f.getDims().z != 36 || f.getDataFormat() != DataFormat::UInt16) return 15;
+            OutputStream os(f);
+            if (os.write(a) != WriteError) return 16;          // the bytes are written; RawFile::write returned 1 item
+            CHECK(os.flush());
+        }
+        {
+            RawFile f(whole.c_str(), "rb");
+            InputStream is(f);
+            if (is.read(ioBack) != ReadError) return 17;       // likewise
+        }
+        {
+            RawFile f(part.c_str(), "wb");
+            OutputStream os(f);
+            os.writeRange(b, Vec3i{ 3, 1, 2 }, Vec3i{ 41, 38, 30 });
+            CHECK(os.flush());
+        }
+        {
+            RawFile f(part.c_str(), "rb");
+            InputStream is(f);
+            is.readRange(ioRange, Vec3i{ 3, 1, 2 }, Vec3i{ 41, 38, 30 });
+        }
+    }
+
     // Aggregates over a range (numElems stays the whole volume's voxel count)
     Aggregates agg;
     CHECK(ComputeAggregatesRange(a, agg, 1, 2, 3, 47, 39, 35));
@@ -181,6 +216,7 @@ int main(int argc, char** argv)
     save(sum, "out_sum.raw"); save(diff, "out_diff.raw"); save(prod, "out_prod.raw"); save(cpy, "out_cpy.raw");
     save(t1, "out_t1.raw"); save(t2, "out_t2.raw"); save(up, "out_up.raw"); save(down, "out_down.raw");
     save(sc, "out_sc.raw"); save(sci, "out_sci.raw");
+    save(ioBack, "out_ioback.raw"); save(ioRange, "out_iorange.raw");
     save(scl, "out_scl.raw"); save(rot, "out_rot.raw"); save(flt, "out_flt.raw"); save(fin, "out_fin.raw");
     save(fx, "out_fx.raw"); save(fy, "out_fy.raw"); save(fz, "out_fz.raw");
     {

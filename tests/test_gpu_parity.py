@@ -636,6 +636,43 @@ def test_affine_and_filter_kernels(gpu):
         gpu.apply_filter(a, src, np.zeros((5, 3, 3), np.float32))
 
 
+def test_stream_in_out_many_chunks(gpu):
+    """vktb_stream_in / vktb_stream_out (what InputStream::read / OutputStream::write use under the GPU policy): 70 MiB
+    + 5 bytes travel through the 16 MiB staging slots in both directions; the callbacks' return values are summed."""
+    from volkit_b200 import capi
+    lib = gpu.lib
+    n = 70 * (1 << 20) + 5
+    src = np.random.default_rng(1).integers(0, 256, n, dtype=np.uint8)
+    dev = ctypes.c_void_p()
+    capi.check(lib.vktb_alloc(ctypes.byref(dev), n))
+    pos, calls = [0], [0]
+
+    def produce(ctx, buf, length):
+        ctypes.memmove(buf, src.ctypes.data + pos[0], length)
+        pos[0] += length
+        calls[0] += 1
+        return length
+
+    total = ctypes.c_size_t(0)
+    capi.check(lib.vktb_stream_in(dev, n, capi.READ_FN(produce), None, ctypes.byref(total)))
+    assert total.value == n and pos[0] == n and calls[0] == 5
+    out = np.zeros(n, np.uint8)
+    wpos = [0]
+
+    def consume(ctx, buf, length):
+        ctypes.memmove(out.ctypes.data + wpos[0], buf, length)
+        wpos[0] += length
+        return 1                                    # an item-counting sink, like RawFile::write
+
+    capi.check(lib.vktb_stream_out(dev, n, capi.WRITE_FN(consume), None, ctypes.byref(total)))
+    assert total.value == 5 and wpos[0] == n and out.tobytes() == src.tobytes()
+    # and the device really holds the bytes: an ordinary D2H agrees
+    back = np.zeros(n, np.uint8)
+    capi.check(lib.vktb_memcpy(back.ctypes.data, dev, n, capi.D2H))
+    assert back.tobytes() == src.tobytes()
+    capi.check(lib.vktb_free(dev))
+
+
 def test_aggregates(gpu):
     """ComputeAggregatesRange: min/max/argmin/argmax bit-exact (first occurrence, ties, NaN skipped, -0 / +0), the
     accumulated statistics inside the reference's own rounding bound (cases.check_aggregates); flat and row kernels,

@@ -105,6 +105,15 @@ def run_cpp(programs, policy, tmp):
     o.apply_filter(ref, a, box)
     assert raw(tmp / "out_flt.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     assert raw(tmp / "out_fin.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
+    # stream I/O: the file holds a's bytes, they come back unchanged; range rows as the reference addresses them
+    assert (tmp / "io_48x40x36_uint16.raw").read_bytes() == a.a.tobytes()
+    assert raw(tmp / "out_ioback.raw", dims, np.uint16).tobytes() == a.a.tobytes()
+    part = o.rows_gather(b, (3, 1, 2), (41, 38, 30))
+    assert (tmp / "io_part.raw").read_bytes() == part
+    ref = po.empty(dims, U16)
+    o.fill_range(ref, *full, 0.75)
+    o.rows_scatter(ref, (3, 1, 2), (41, 38, 30), part)
+    assert raw(tmp / "out_iorange.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     got_agg = po.Aggregates.from_buffer_copy((tmp / "out_agg.raw").read_bytes())
     ref_agg = o.aggregates_range(a, (1, 2, 3), (47, 39, 35))
     if policy == "cpu":

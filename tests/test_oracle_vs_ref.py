@@ -203,6 +203,38 @@ def test_scale_rotate_filter(fmt):
     del rng
 
 
+def test_stream_io(tmp_path):
+    """OutputStream::writeRange / InputStream::readRange / RawFile: the byte-buffer restatement against the reference
+    run on real files, and against a numpy statement (lines of last.x - first.x voxels from the START of each row)."""
+    o, r = po.oracle(), po.reference()
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        vol = mk((21, 9, 8), fmt, 2)
+        for first, last in (((0, 0, 0), (21, 9, 8)), ((3, 1, 2), (17, 8, 7)), ((5, 0, 0), (6, 9, 1)), ((2, 2, 2), (2, 5, 5))):
+            path = str(tmp_path / f"range_{fmt}_{first[0]}_{last[0]}.raw")
+            err = r.write_range(vol, first, last, path)
+            want = o.rows_gather(vol, first, last)
+            assert open(path, "rb").read() == want, (fmt, first, last)
+            nx = last[0] - first[0]
+            assert want == b"".join(vol.a[z, y, :nx].tobytes() for z in range(first[2], last[2]) for y in range(first[1], last[1]))
+            # RawFile::write returns fwrite's item count, so the reference reports WriteError (3) unless one item == the total
+            items = (last[1] - first[1]) * (last[2] - first[2]) if nx > 0 else 0     # fwrite of 0 bytes returns 0
+            assert err == (0 if items == len(want) else 3)
+            a, b = mk((21, 9, 8), fmt, 5), mk((21, 9, 8), fmt, 5)
+            r.read_range(a, first, last, path)
+            o.rows_scatter(b, first, last, want)
+            assert a.a.tobytes() == b.a.tobytes(), (fmt, first, last)
+        path = str(tmp_path / f"whole_{fmt}.raw")
+        assert r.write(vol, path) == 3 and open(path, "rb").read() == vol.a.tobytes()    # bytes arrive, the code says WriteError
+        back = mk((21, 9, 8), fmt, 5)
+        assert r.read(back, path) == 2 and back.a.tobytes() == vol.a.tobytes()           # ... and ReadError
+    for name in ("vol_48x40x36_uint16.raw", "a_b_512x256x128_int8_x.raw", "foo.raw", "x_10x20x30.raw", "s_uint32_7x8x9_uint64.raw",
+                 "trailing_4x4x4_uint16_"):
+        full = tmp_path / name
+        full.write_bytes(b"")
+        assert o.rawfile_parse(str(full)) == r.rawfile_parse(str(full)), name
+    assert o.rawfile_parse("vol_48x40x36_uint16.raw") == ((48, 40, 36), po.UINT16)
+
+
 @pytest.mark.parametrize("fmt", FMTS)
 def test_aggregates(fmt):
     """ComputeAggregatesRange: the restatement reproduces all 13 words of the reference's vkt::Aggregates; min / max /

@@ -43,6 +43,9 @@ class VktbAggPartial(ctypes.Structure):
                 ("pad", ctypes.c_int32)]
 
 
+READ_FN = ctypes.CFUNCTYPE(ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+WRITE_FN = ctypes.CFUNCTYPE(ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+
 # name -> (restype, argtypes); every symbol include/vktb/backend.h declares
 _P = ctypes.POINTER
 _VP = _P(VktbVol)
@@ -80,6 +83,8 @@ SIGNATURES = {
     "vktb_resample_window_src_range3": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, I3, I3,
                                                        _P(ctypes.c_int32), _P(ctypes.c_int32)]),
     "vktb_flip_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3, ctypes.c_int]),
+    "vktb_stream_in": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, READ_FN, ctypes.c_void_p, _P(ctypes.c_size_t)]),
+    "vktb_stream_out": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, WRITE_FN, ctypes.c_void_p, _P(ctypes.c_size_t)]),
     "vktb_affine_range": (ctypes.c_int, [_VP, _VP, I3, I3, _P(ctypes.c_float), _P(ctypes.c_float)]),
     "vktb_apply_filter": (ctypes.c_int, [_VP, _VP, _P(ctypes.c_float), I3, ctypes.c_int]),
     "vktb_aggregates_range": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggregates)]),

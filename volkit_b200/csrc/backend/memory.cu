@@ -301,6 +301,68 @@ int stagedD2H(DeviceCtx* d, uint8_t* dst, const uint8_t* src, size_t bytes)
     return 0;
 }
 
+// producer -> device: `read` fills one staging slot while the DMA of the previous slots runs.  *sum receives the
+// sum of the producer's return values (the caller compares it with `bytes`, whatever the producer's convention).
+int streamIn(DeviceCtx* d, uint8_t* dst, size_t bytes, vktb_read_fn read, void* ctx, size_t* sum)
+{
+    std::lock_guard<std::mutex> lock(d->stageMutex);
+    if (ensureStage(d)) return -1;
+    cudaStream_t cs = d->copy;
+    cudaEvent_t ready;
+    cudaEventCreateWithFlags(&ready, cudaEventDisableTiming);
+    cudaEventRecord(ready, currentStream(d));
+    cudaStreamWaitEvent(cs, ready, 0);
+    cudaEventDestroy(ready);
+    size_t total = 0;
+    int slot = 0;
+    for (size_t off = 0; off < bytes; off += kStageBytes, slot = (slot + 1) % kStageSlots) {
+        const size_t n = std::min(kStageBytes, bytes - off);
+        if (d->stageInFlight[slot]) { cudaEventSynchronize(d->stageDone[slot]); d->stageInFlight[slot] = false; }
+        total += read(ctx, d->stage[slot], n);
+        cudaError_t e = cudaMemcpyAsync(dst + off, d->stage[slot], n, cudaMemcpyHostToDevice, cs);
+        if (e != cudaSuccess) return fail("cudaMemcpyAsync(H2D streamed)", e);
+        cudaEventRecord(d->stageDone[slot], cs);
+        d->stageInFlight[slot] = true;
+    }
+    cudaEvent_t tail;
+    cudaEventCreateWithFlags(&tail, cudaEventDisableTiming);
+    cudaEventRecord(tail, cs);
+    cudaStreamWaitEvent(currentStream(d), tail, 0);
+    cudaEventDestroy(tail);
+    if (sum) *sum = total;
+    return 0;
+}
+
+// device -> consumer: up to kStageSlots D2H copies in flight while `write` drains the oldest slot
+int streamOut(DeviceCtx* d, const uint8_t* src, size_t bytes, vktb_write_fn write, void* ctx, size_t* sum)
+{
+    std::lock_guard<std::mutex> lock(d->stageMutex);
+    if (ensureStage(d)) return -1;
+    cudaStream_t s = currentStream(d);
+    for (int i = 0; i < kStageSlots; ++i)
+        if (d->stageInFlight[i]) { cudaEventSynchronize(d->stageDone[i]); d->stageInFlight[i] = false; }
+    const size_t nChunks = (bytes + kStageBytes - 1) / kStageBytes;
+    size_t issued = 0, drained = 0, total = 0;
+    while (drained < nChunks) {
+        while (issued < nChunks && issued < drained + kStageSlots) {
+            const size_t off = issued * kStageBytes, n = std::min(kStageBytes, bytes - off);
+            const int slot = (int)(issued % kStageSlots);
+            cudaError_t e = cudaMemcpyAsync(d->stage[slot], src + off, n, cudaMemcpyDeviceToHost, s);
+            if (e != cudaSuccess) return fail("cudaMemcpyAsync(D2H streamed)", e);
+            cudaEventRecord(d->stageDone[slot], s);
+            ++issued;
+        }
+        const size_t off = drained * kStageBytes, n = std::min(kStageBytes, bytes - off);
+        const int slot = (int)(drained % kStageSlots);
+        cudaError_t e = cudaEventSynchronize(d->stageDone[slot]);
+        if (e != cudaSuccess) return fail("D2H streamed wait", e);
+        total += write(ctx, d->stage[slot], n);
+        ++drained;
+    }
+    if (sum) *sum = total;
+    return 0;
+}
+
 bool isPinnedHost(const void* p)
 {
     cudaPointerAttributes a;
@@ -387,6 +449,26 @@ int vktb_memcpy(void* dst, const void* src, size_t bytes, int kind)
         return e == cudaSuccess ? 0 : fail("cudaMemcpyAsync(D2D)", e);
     }
     return fail("vktb_memcpy: bad copy kind");
+}
+
+int vktb_stream_in(void* devDst, size_t bytes, vktb_read_fn read, void* ctx, size_t* sum)
+{
+    if (sum) *sum = 0;
+    if (bytes == 0) return 0;
+    if (!devDst || !read) return fail("vktb_stream_in: null argument");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    return streamIn(d, (uint8_t*)devDst, bytes, read, ctx, sum);
+}
+
+int vktb_stream_out(const void* devSrc, size_t bytes, vktb_write_fn write, void* ctx, size_t* sum)
+{
+    if (sum) *sum = 0;
+    if (bytes == 0) return 0;
+    if (!devSrc || !write) return fail("vktb_stream_out: null argument");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    return streamOut(d, (const uint8_t*)devSrc, bytes, write, ctx, sum);
 }
 
 int vktb_memset_range(void* dst, const void* pattern, size_t dstBytes, size_t patBytes)

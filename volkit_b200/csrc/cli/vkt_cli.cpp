@@ -5,7 +5,10 @@
 // (declare-sv), :521-574 (fill / fill-range), :701-740 (resample, always FilterMode::Nearest), :445-519 (dump).
 //
 // volkit-b200 addition: the execution policy of every stage is chosen with `--device cpu|gpu` or the environment
-// variable VKT_B200_DEVICE (default cpu, as in the reference where the CLI never sets a policy).
+// variable VKT_B200_DEVICE (default cpu, as in the reference where the CLI never sets a policy).  Under the GPU
+// policy the voxels of the pipe go through vkt::InputStream / vkt::OutputStream: stdin is read
+// in 16 MiB pieces straight into the backend's pinned staging ring while the previous pieces are on their way to
+// the device, and the result leaves the same way -- the stage never holds a host copy of the volume.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +18,8 @@
 
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/InputStream.hpp>
+#include <vkt/OutputStream.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
 
@@ -87,7 +92,21 @@ bool parse(int argc, char** argv, Options& o)
 
 bool readAll(void* dst, size_t n) { return std::fread(dst, 1, n, stdin) == n; }
 
-// reads header + voxels from stdin into a volume allocated under the CPU policy
+// stdin / stdout as a DataSource that counts bytes
+class PipeSource : public DataSource
+{
+public:
+    explicit PipeSource(FILE* f) : file_(f) {}
+    std::size_t read(char* buf, std::size_t len) override { return std::fread(buf, 1, len, file_); }
+    std::size_t write(char const* buf, std::size_t len) override { return std::fwrite(buf, 1, len, file_); }
+    bool seek(std::size_t) override { return false; }
+    bool flush() override { return std::fflush(file_) == 0; }
+    bool good() const override { return file_ != nullptr; }
+private:
+    FILE* file_;
+};
+
+// reads header + voxels from stdin into a volume allocated under the calling thread's policy
 bool readVolume(StructuredVolume& volume)
 {
     Header h;
@@ -96,11 +115,12 @@ bool readVolume(StructuredVolume& volume)
     if (h.assetType != 0u) return fail("Cannot read structured volume, wrong type");
     volume = StructuredVolume(h.dims[0], h.dims[1], h.dims[2], (DataFormat)h.dataFormat, h.dist[0], h.dist[1], h.dist[2],
                               h.mapping[0], h.mapping[1]);
-    if (!readAll(volume.getData(), volume.getSizeInBytes())) return fail("Cannot read structured volume: short data");
+    PipeSource in(stdin);
+    if (InputStream(in).read(volume) != NoError) return fail("Cannot read structured volume: short data");
     return true;
 }
 
-// getData() under the CPU policy migrates the result back to the host before it is written
+// CPU policy: getData() migrates the result back to the host before it is written; GPU policy: streamed out
 void writeVolume(StructuredVolume& volume)
 {
     Header h;
@@ -111,8 +131,10 @@ void writeVolume(StructuredVolume& volume)
     h.dist[0] = s.x; h.dist[1] = s.y; h.dist[2] = s.z;
     h.mapping[0] = m.x; h.mapping[1] = m.y;
     std::fwrite(&h, 1, sizeof h, stdout);
-    std::fwrite(volume.getData(), 1, volume.getSizeInBytes(), stdout);
-    std::fflush(stdout);
+    PipeSource out(stdout);
+    OutputStream os(out);
+    os.write(volume);
+    os.flush();
 }
 
 bool checkParams(StructuredVolume& v)
@@ -152,6 +174,7 @@ int main(int argc, char** argv)
         std::memset(volume.getData(), 0, volume.getSizeInBytes());
         writeVolume(volume);
     } else if (o.command == "fill" || o.command == "fill-range") {
+        SetThreadExecutionPolicy(runPolicy);          // the pipe is streamed to / from the device that computes
         StructuredVolume volume;
         if (!readVolume(volume) || !checkParams(volume)) return EXIT_FAILURE;
         const long long range = (long long)(o.last.x - o.first.x) * (o.last.y - o.first.y) * (o.last.z - o.first.z);
@@ -161,12 +184,12 @@ int main(int argc, char** argv)
             Vec3i d = volume.getDims();
             if (o.last.x > d.x || o.last.y > d.y || o.last.z > d.z) { fail("Range overflow"); return EXIT_FAILURE; }
         }
-        SetThreadExecutionPolicy(runPolicy);
         Error e = range > 0 ? FillRange(volume, o.first, o.last, o.value) : Fill(volume, o.value);
-        SetThreadExecutionPolicy(cpuPolicy);
         if (e != NoError) return EXIT_FAILURE;
         writeVolume(volume);
+        SetThreadExecutionPolicy(cpuPolicy);
     } else if (o.command == "resample") {
+        SetThreadExecutionPolicy(runPolicy);
         StructuredVolume src;
         if (!readVolume(src)) return EXIT_FAILURE;
         Vec3i dims = (long long)o.dims.x * o.dims.y * o.dims.z <= 0 ? src.getDims() : o.dims;
@@ -174,11 +197,10 @@ int main(int argc, char** argv)
         Vec3f dist = o.dist.x * o.dist.y * o.dist.z <= 0.f ? src.getDist() : o.dist;
         Vec2f mapping = o.mapping.y - o.mapping.x <= 0.f ? src.getVoxelMapping() : o.mapping;
         StructuredVolume dst(dims.x, dims.y, dims.z, f, dist.x, dist.y, dist.z, mapping.x, mapping.y);
-        SetThreadExecutionPolicy(runPolicy);
         Error e = Resample(dst, src, FilterMode::Nearest);
-        SetThreadExecutionPolicy(cpuPolicy);
         if (e != NoError) return EXIT_FAILURE;
         writeVolume(dst);
+        SetThreadExecutionPolicy(cpuPolicy);
     } else {   // dump / dump-range
         StructuredVolume volume;
         if (!readVolume(volume)) return EXIT_FAILURE;

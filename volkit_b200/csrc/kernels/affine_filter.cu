@@ -40,6 +40,8 @@ struct AffineParams
     float c[3];
     float first[3], last[3]; // the range, converted int -> float like the reference's compares do
     Mapping md, ms;
+    int diag;                // off-diagonal matrix entries are all +-0
+    int fastTrunc;           // the range lies inside [0, 2^23)
 };
 
 template <int FS>
@@ -75,9 +77,23 @@ __device__ __forceinline__ float sampleLinearRef(const AffineParams& p, int x, i
                    refLerp(refLerp(v4, v5, fx), refLerp(v6, v7, fx), fy), fz);
 }
 
-// one thread = V consecutive dst voxels of one row; ONETAP: the range lies inside the source and every tap of an
-// integer source unmaps to a finite float, so the 8-tap chain with frac 0 returns the lo tap bit for bit
-template <int FS, int FD, bool ONETAP>
+// float -> int of a coordinate that passed the range test.  fast: the range lies in [0, 2^23), where adding 2^23 with
+// round-toward-zero leaves floor(q) in the mantissa (an FP32-pipe add instead of the conversion pipe's F2I).
+__device__ __forceinline__ int truncCoord(float q, bool fast)
+{
+    return fast ? (int)(__float_as_uint(__fadd_rz(q, 8388608.f)) & 0x7fffffu) : (int)x86Cvtt32(q);
+}
+
+// one thread = V consecutive dst voxels of one row.
+//   MODE 0  the reference's 8-tap expression (Float32 sources, ranges that leave the source, exotic mappings)
+//   MODE 1  one tap, unmap -> map: the range lies inside the source and every tap of an integer source unmaps to a
+//           finite float, so the 8-tap chain with frac 0 returns the lo tap bit for bit
+//   MODE 2  one tap, raw voxel moved: MODE 1 with map(unmap(raw)) == raw for every raw (same format, UInt8 / UInt16
+//           with the identity mapping on both sides)
+// p.diag: the matrix is diagonal (Scale).  The off-diagonal products are +-0 and only flip the sign of a zero, which
+// neither the range test nor the truncation can see, so q.y and q.z are computed once per row (rows that map
+// outside the range are skipped) and q.x costs one multiply and one add per voxel.
+template <int FS, int FD, int MODE>
 __global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
 {
     constexpr int BS = bytesPerVoxel(FS), BD = bytesPerVoxel(FD);
@@ -88,35 +104,55 @@ __global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
     const int x0 = c * V, n = min(V, p.Dx - x0);
     const long long rows = (long long)p.Dy * p.Dz;
     const long long plane = (long long)p.Sx * p.Sy;
+    const bool fast = p.fastTrunc != 0, diag = p.diag != 0;
+    const float fx0 = __int2float_rn(x0);      // x0 + i < 2^24: float(x0) + float(i) is exact
     for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows; r += (long long)gridDim.y * blockDim.y) {
         const int z = (int)(r / p.Dy), y = (int)(r - (long long)z * p.Dy);
         const float py = __fsub_rn(__int2float_rn(y), p.c[1]), pz = __fsub_rn(__int2float_rn(z), p.c[2]);
+        float rqy = 0.f, rqz = 0.f;
+        long long rowBase = 0;
+        if (diag) {
+            rqy = __fadd_rn(__fmul_rn(p.m[4], py), p.c[1]);
+            rqz = __fadd_rn(__fmul_rn(p.m[8], pz), p.c[2]);
+            if (!(rqy >= p.first[1] && rqy < p.last[1] && rqz >= p.first[2] && rqz < p.last[2])) continue;
+            if (MODE != 0) rowBase = truncCoord(rqz, fast) * plane + (long long)truncCoord(rqy, fast) * p.Sx;
+        }
         uint8_t* dp = p.d + (r * p.Dx + x0) * BD;
         uint32_t out[V];
         unsigned inside = 0;
 #pragma unroll
         for (int i = 0; i < V; ++i) {
             if (i >= n) continue;
-            const float px = __fsub_rn(__int2float_rn(x0 + i), p.c[0]);
-            // (a*x + b*y) + c*z, then + center
-            const float qx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[0], px), __fmul_rn(p.m[3], py)), __fmul_rn(p.m[6], pz)), p.c[0]);
-            const float qy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[1], px), __fmul_rn(p.m[4], py)), __fmul_rn(p.m[7], pz)), p.c[1]);
-            const float qz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[2], px), __fmul_rn(p.m[5], py)), __fmul_rn(p.m[8], pz)), p.c[2]);
-            if (qx >= p.first[0] && qx < p.last[0] && qy >= p.first[1] && qy < p.last[1] && qz >= p.first[2] && qz < p.last[2]) {
-                const int sx = (int)x86Cvtt32(qx), sy = (int)x86Cvtt32(qy), sz = (int)x86Cvtt32(qz);
-                float v;
-                if (ONETAP) v = unmapVoxel<FS, false>(loadRaw(p.s + (sz * plane + (long long)sy * p.Sx + sx) * BS, BS), p.ms);
-                else v = sampleLinearRef<FS>(p, sx, sy, sz);
-                out[i] = mapVoxel<FD, false>(v, p.md);
-                inside |= 1u << i;
+            const float px = __fsub_rn(__fadd_rn(fx0, (float)i), p.c[0]);
+            float qx, qy, qz;
+            if (diag) {
+                qx = __fadd_rn(__fmul_rn(p.m[0], px), p.c[0]); qy = rqy; qz = rqz;
+                if (!(qx >= p.first[0] && qx < p.last[0])) continue;
+            } else {
+                // (a*x + b*y) + c*z, then + center
+                qx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[0], px), __fmul_rn(p.m[3], py)), __fmul_rn(p.m[6], pz)), p.c[0]);
+                qy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[1], px), __fmul_rn(p.m[4], py)), __fmul_rn(p.m[7], pz)), p.c[1]);
+                qz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[2], px), __fmul_rn(p.m[5], py)), __fmul_rn(p.m[8], pz)), p.c[2]);
+                if (!(qx >= p.first[0] && qx < p.last[0] && qy >= p.first[1] && qy < p.last[1] && qz >= p.first[2] && qz < p.last[2]))
+                    continue;
             }
+            const int sx = truncCoord(qx, fast);
+            if (MODE == 0) {
+                out[i] = mapVoxel<FD, false>(sampleLinearRef<FS>(p, sx, truncCoord(qy, fast), truncCoord(qz, fast)), p.md);
+            } else {
+                const long long idx = diag ? rowBase + sx
+                                           : truncCoord(qz, fast) * plane + (long long)truncCoord(qy, fast) * p.Sx + sx;
+                const uint32_t raw = loadRaw(p.s + idx * BS, BS);
+                out[i] = MODE == 2 ? raw : mapVoxel<FD, false>(unmapVoxel<FS, false>(raw, p.ms), p.md);
+            }
+            inside |= 1u << i;
         }
         if (inside == (1u << V) - 1u && (reinterpret_cast<uintptr_t>(dp) & 15u) == 0) {
             uint32_t w[4] = { 0u, 0u, 0u, 0u };
 #pragma unroll
             for (int i = 0; i < V; ++i) vecSet<BD>(w, i, out[i]);
             stStream(dp, make_uint4(w[0], w[1], w[2], w[3]));
-        } else {
+        } else if (inside) {
 #pragma unroll
             for (int i = 0; i < V; ++i)
                 if (inside & (1u << i)) storeRaw(dp + i * BD, BD, out[i]);
@@ -140,8 +176,10 @@ cudaError_t launchAffineFF(const LaunchCtx& c, const AffineParams& p, bool oneTa
 {
     constexpr int V = 16 / bytesPerVoxel(FD);
     const RowsLaunch l = rowsLaunch(p.Dx, (long long)p.Dy * p.Dz, V);
-    if (oneTap) affineKernel<FS, FD, true><<<l.grid, l.block, 0, c.stream>>>(p);
-    else affineKernel<FS, FD, false><<<l.grid, l.block, 0, c.stream>>>(p);
+    const bool rawMove = oneTap && FS == FD && (FS == F_U8 || FS == F_U16) && p.ms.identity && p.md.identity;
+    if (rawMove) affineKernel<FS, FD, 2><<<l.grid, l.block, 0, c.stream>>>(p);
+    else if (oneTap) affineKernel<FS, FD, 1><<<l.grid, l.block, 0, c.stream>>>(p);
+    else affineKernel<FS, FD, 0><<<l.grid, l.block, 0, c.stream>>>(p);
     countLaunch();
     return cudaGetLastError();
 }
@@ -177,7 +215,7 @@ struct FilterParams
 
 // nine unmapped voxels around (x, y) in plane z
 template <int F, bool IDENT>
-__device__ __forceinline__ void loadPlane9(float (&v)[9], const FilterParams& p, int x, int y, int z)
+__device__ __forceinline__ void loadPlane9(float (&v)[9], const FilterParams& p, const float* lut, int x, int y, int z)
 {
     constexpr int B = bytesPerVoxel(F);
     const uint8_t* row = p.s + (((long long)z * p.ny + (y - 1)) * p.nx + (x - 1)) * B;
@@ -189,7 +227,7 @@ __device__ __forceinline__ void loadPlane9(float (&v)[9], const FilterParams& p,
             if (B == 1) raw = __ldg(row + xx);
             else if (B == 2) raw = __ldg(reinterpret_cast<const uint16_t*>(row) + xx);
             else raw = __ldg(reinterpret_cast<const uint32_t*>(row) + xx);
-            v[yy * 3 + xx] = unmapVoxel<F, IDENT>(raw, p.ms);
+            v[yy * 3 + xx] = F == F_U8 ? lut[raw] : unmapVoxel<F, IDENT>(raw, p.ms);   // UInt8: the unmap divides
         }
         row += (long long)p.nx * B;
     }
@@ -207,6 +245,12 @@ template <int F, bool IDS, bool IDD>
 __global__ void __launch_bounds__(kThreads) filter3MarchKernel(FilterParams p)
 {
     constexpr int B = bytesPerVoxel(F);
+    __shared__ float lut[F == F_U8 ? 256 : 1];
+    if (F == F_U8) {
+        const int t = threadIdx.y * 32 + threadIdx.x;
+        lut[t] = unmapVoxel<F_U8, IDS>((uint32_t)t, p.ms);
+        __syncthreads();
+    }
     const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
     if (x >= p.nx || y >= p.ny) return;
     const int z0 = blockIdx.z * p.zChunk, z1 = min(z0 + p.zChunk, p.nz);
@@ -228,20 +272,20 @@ __global__ void __launch_bounds__(kThreads) filter3MarchKernel(FilterParams p)
     if (ze == p.nz) { if (p.nz - 1 >= zs) put(p.nz - 1, zero); ze = p.nz - 1; }
     if (zs >= ze) return;
     float a[9], b[9], cc[9];
-    loadPlane9<F, IDS>(a, p, x, y, zs - 1);
-    loadPlane9<F, IDS>(b, p, x, y, zs);
+    loadPlane9<F, IDS>(a, p, lut, x, y, zs - 1);
+    loadPlane9<F, IDS>(b, p, lut, x, y, zs);
     int z = zs;
     // three planes per round so that the register planes rotate by renaming
     for (; z + 2 < ze; z += 3) {
-        loadPlane9<F, IDS>(cc, p, x, y, z + 1);
+        loadPlane9<F, IDS>(cc, p, lut, x, y, z + 1);
         put(z, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, a, p.w), b, p.w + 9), cc, p.w + 18), p.md));
-        loadPlane9<F, IDS>(a, p, x, y, z + 2);
+        loadPlane9<F, IDS>(a, p, lut, x, y, z + 2);
         put(z + 1, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, b, p.w), cc, p.w + 9), a, p.w + 18), p.md));
-        loadPlane9<F, IDS>(b, p, x, y, z + 3);
+        loadPlane9<F, IDS>(b, p, lut, x, y, z + 3);
         put(z + 2, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, cc, p.w), a, p.w + 9), b, p.w + 18), p.md));
     }
     for (; z < ze; ++z) {
-        loadPlane9<F, IDS>(cc, p, x, y, z + 1);
+        loadPlane9<F, IDS>(cc, p, lut, x, y, z + 1);
         put(z, mapVoxel<F, IDD>(accPlane9(accPlane9(accPlane9(0.f, a, p.w), b, p.w + 9), cc, p.w + 18), p.md));
 #pragma unroll
         for (int i = 0; i < 9; ++i) { a[i] = b[i]; b[i] = cc[i]; }
@@ -302,6 +346,17 @@ cudaError_t launchAffine(const LaunchCtx& c, const VolDesc& dst, const VolDesc& 
         if (first[a] < 0 || last[a] > src.dims[a]) insideSrc = false;
     }
     p.md = dst.map; p.ms = src.map;
+    p.diag = 1;
+    for (int i = 0; i < 9; ++i)
+        if (i % 4 != 0 && m[i] != 0.f) p.diag = 0;
+    for (int i = 0; i < 9; i += 4)
+        if (!std::isfinite(m[i])) p.diag = 0;         // 0 * inf would be NaN, not +-0
+    for (int a = 0; a < 3; ++a)
+        if (!std::isfinite(center[a])) p.diag = 0;
+    p.fastTrunc = 1;
+    for (int a = 0; a < 3; ++a)
+        if (first[a] < 0 || last[a] > (1 << 23)) p.fastTrunc = 0;
+    if (dst.dims[0] >= (1 << 24)) return cudaErrorInvalidValue;
     const bool oneTap = insideSrc && oneTapExact(src);
     switch (src.format) {
     case F_U8:    return launchAffineF<F_U8>(c, p, dst.format, oneTap);

@@ -7,8 +7,9 @@
 // reproducible by any parallel evaluation (binary32 addition does not associate, and the running sum of a large
 // volume stops growing once it passes 2^24 times the voxel values); for them this kernel returns moments that are
 // accurate to ~1e-7 of the real-number value -- per-vector binary32 partial sums of SHIFTED values d = v - c (c =
-// the range's first voxel, which keeps near-constant volumes free of cancellation), accumulated in binary64 -- and
-// the contract (include/vktb/backend.h) is the reference's own a-priori rounding bound around that value.
+// the range's first voxel, which keeps near-constant volumes free of cancellation), accumulated in binary64; UInt8 and
+// UInt16 volumes with the identity mapping, whose unmap is linear in the raw integer, use exact integer moments
+// instead (sum raw by dp4a / dp2a, sum raw^2 by dp4a / 64-bit multiply-adds) -- and the contract (include/vktb/backend.h) is the reference's own a-priori rounding bound around that value.
 //
 // One pass instead of the reference's two: sum (v - mean)^2 = sum d^2 - 2 (mean - c) sum d + n (mean - c)^2 is
 // evaluated in binary64 by the finisher (launchAggregates), `mean` being the binary32 mean the reference would
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
         return unmapVoxel<F, IDENT>(raw, p.m);
     };
     // the shift: the range's first voxel (every thread reads the same 1-4 bytes)
-    float c = value(loadRaw(p.s, BPV));
+    float c = PACKED ? 0.f : value(loadRaw(p.s, BPV));
     if (!(fabsf(c) <= FLT_MAX)) c = 0.f;
 
     AggThread t;
@@ -146,35 +147,59 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
         if ((FINITE && t.P == 0.0) || (CONTRACTING && t.E < -400)) dead = true;
     };
 
+    // PACKED: exact integer moments S1 = sum raw, S2 = sum raw^2 (the unmap is raw * 2^-16 for UInt16, raw / 255.999f
+    // for UInt8, so sum v = S1 * scale and sum v^2 = S2 * scale^2; the shift c is 0 on this path)
+    unsigned long long S1 = 0, S2 = 0;
+
     auto accVec = [&](const uint4& q, unsigned long long idx) {
-        float v[V];
-#pragma unroll
-        for (int i = 0; i < V; ++i) v[i] = value(vecGet<BPV>(q, i));
         if (PACKED) {
-            uint32_t lo, hi;
+            uint32_t lo, hi, s1 = 0;
             if (F == F_U16) {
                 lo = __vminu2(__vminu2(q.x, q.y), __vminu2(q.z, q.w));
                 hi = __vmaxu2(__vmaxu2(q.x, q.y), __vmaxu2(q.z, q.w));
                 lo = min(lo & 0xffffu, lo >> 16);
                 hi = max(hi & 0xffffu, hi >> 16);
+                const uint32_t w[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    s1 = __dp2a_lo(w[k], 0x0101u, s1);
+                    const uint32_t a = w[k] & 0xffffu, b = w[k] >> 16;
+                    S2 += (unsigned long long)a * a;
+                    S2 += (unsigned long long)b * b;
+                }
             } else {
                 lo = __vminu4(__vminu4(q.x, q.y), __vminu4(q.z, q.w));
                 hi = __vmaxu4(__vmaxu4(q.x, q.y), __vmaxu4(q.z, q.w));
                 lo = __vminu4(lo, lo >> 16); lo = min(lo & 0xffu, (lo >> 8) & 0xffu);
                 hi = __vmaxu4(hi, hi >> 16); hi = max(hi & 0xffu, (hi >> 8) & 0xffu);
+                uint32_t s2 = 0;
+                const uint32_t w[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { s1 = __dp4a(w[k], 0x01010101u, s1); s2 = __dp4a(w[k], w[k], s2); }
+                S2 += s2;
             }
+            S1 += s1;
             if (lo < rmn) { rmn = lo; t.mnIdx = idx | kVecTag; }
             if (hi + 1u > rmx) { rmx = hi + 1u; t.mxIdx = idx | kVecTag; }
-        } else {
-            const float mn0 = t.mn, mx0 = t.mx;
+            if (!dead) {
 #pragma unroll
-            for (int i = 0; i < V; ++i) {
-                t.mn = v[i] < t.mn ? v[i] : t.mn;
-                t.mx = v[i] > t.mx ? v[i] : t.mx;
+                for (int i = 0; i < V; i += 4)
+                    mulProd4(value(vecGet<BPV>(q, i)), value(vecGet<BPV>(q, i + 1)), value(vecGet<BPV>(q, i + 2)),
+                             value(vecGet<BPV>(q, i + 3)));
             }
-            if (t.mn < mn0) t.mnIdx = idx | kVecTag;
-            if (t.mx > mx0) t.mxIdx = idx | kVecTag;
+            return;
         }
+        float v[V];
+#pragma unroll
+        for (int i = 0; i < V; ++i) v[i] = value(vecGet<BPV>(q, i));
+        const float mn0 = t.mn, mx0 = t.mx;
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            t.mn = v[i] < t.mn ? v[i] : t.mn;
+            t.mx = v[i] > t.mx ? v[i] : t.mx;
+        }
+        if (t.mn < mn0) t.mnIdx = idx | kVecTag;
+        if (t.mx > mx0) t.mxIdx = idx | kVecTag;
         float s[V], sq[V];
 #pragma unroll
         for (int i = 0; i < V; ++i) { s[i] = __fsub_rn(v[i], c); sq[i] = __fmul_rn(s[i], s[i]); }
@@ -190,14 +215,17 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
         }
     };
     auto accOne = [&](uint32_t raw, unsigned long long idx) {
-        const float v = value(raw);
         if (PACKED) {
             if (raw < rmn) { rmn = raw; t.mnIdx = idx; }
             if (raw + 1u > rmx) { rmx = raw + 1u; t.mxIdx = idx; }
-        } else {
-            if (v < t.mn) { t.mn = v; t.mnIdx = idx; }
-            if (v > t.mx) { t.mx = v; t.mxIdx = idx; }
+            S1 += raw;
+            S2 += (unsigned long long)raw * raw;
+            if (!dead) mulProd4(value(raw), 1.f, 1.f, 1.f);
+            return;
         }
+        const float v = value(raw);
+        if (v < t.mn) { t.mn = v; t.mnIdx = idx; }
+        if (v > t.mx) { t.mx = v; t.mxIdx = idx; }
         const float d = __fsub_rn(v, c);
         t.sumD += (double)d;
         t.sumD2 += (double)__fmul_rn(d, d);
@@ -261,6 +289,9 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
     if (PACKED) {
         if (t.mnIdx != kNone) t.mn = value(rmn);
         if (t.mxIdx != kNone) t.mx = value(rmx - 1u);
+        const double scale = F == F_U16 ? 1.52587890625e-05 : 1.0 / (double)255.999f;
+        t.sumD = (double)S1 * scale;
+        t.sumD2 = (double)S2 * (scale * scale);
     }
     auto resolve = [&](unsigned long long tag, float target, uint32_t rawTarget) -> unsigned long long {
         if (tag == kNone || !(tag & kVecTag)) return tag;
