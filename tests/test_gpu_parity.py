@@ -253,6 +253,20 @@ def test_scan_kernels(gpu):
                 o.scan_range(a, src, first, last)
                 gpu.scan_range(b, src, first, last)
                 assert a.a.tobytes() == b.a.tobytes(), (fmt, dims, first, last, "copy")
+    # the fused x+y pass (one CTA per plane; needs at least two planes per SM): one, two and four vectors per thread,
+    # rows shorter than the CTA, a range inside the volume that keeps the 16-byte phase, z and y walked downwards
+    for fmt, dims, first, last in ((po.UINT16, (64, 9, 320), (0, 0, 0), (64, 9, 320)),
+                                   (po.UINT16, (2048, 5, 300), (0, 0, 0), (2048, 5, 300)),
+                                   (po.UINT8, (4112, 3, 300), (0, 0, 0), (4112, 3, 300)),
+                                   (po.UINT8, (8208, 3, 300), (0, 0, 0), (8208, 3, 300)),
+                                   (po.FLOAT32, (1032, 4, 310), (0, 0, 0), (1032, 4, 310)),
+                                   (po.UINT16, (64, 12, 330), (8, 2, 5), (56, 11, 325)),
+                                   (po.UINT32, (32, 12, 330), (4, 10, 320), (28, 1, 3))):
+        src = cases.mk(dims, fmt, 4)
+        a, b = src.copy(), src.copy()
+        o.scan_range(a, a, first, last)
+        gpu.scan_range(b, b, first, last)
+        assert a.a.tobytes() == b.a.tobytes(), ("fused xy", fmt, dims, first, last)
     # converting copy in front of the scan (UInt16 source into a UInt8 / Float32 destination)
     src = cases.mk((40, 12, 9), po.UINT16, 1)
     for dfmt in (po.UINT8, po.FLOAT32):

@@ -151,41 +151,56 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
     // for UInt8, so sum v = S1 * scale and sum v^2 = S2 * scale^2; the shift c is 0 on this path)
     unsigned long long S1 = 0, S2 = 0;
 
-    auto accVec = [&](const uint4& q, unsigned long long idx) {
+    // the linear index of a vector is base + i * V; it is only needed on the rare paths that move an extremum
+    uint32_t mn2 = 0xffffffffu, mx2 = 0u;      // PACKED: running lane-wise extrema
+    uint32_t s1acc = 0;                        // PACKED: 32-bit part of S1, flushed every vector batch
+    auto accVec = [&](const uint4& q, unsigned long long base, unsigned long long i) {
         if (PACKED) {
             uint32_t lo, hi, s1 = 0;
             if (F == F_U16) {
                 lo = __vminu2(__vminu2(q.x, q.y), __vminu2(q.z, q.w));
                 hi = __vmaxu2(__vmaxu2(q.x, q.y), __vmaxu2(q.z, q.w));
-                lo = min(lo & 0xffffu, lo >> 16);
-                hi = max(hi & 0xffffu, hi >> 16);
                 const uint32_t w[4] = { q.x, q.y, q.z, q.w };
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     s1 = __dp2a_lo(w[k], 0x0101u, s1);
-                    const uint32_t a = w[k] & 0xffffu, b = w[k] >> 16;
+                    const uint32_t b = __umulhi(w[k], 65536u), a = w[k] - (b << 16);
                     S2 += (unsigned long long)a * a;
                     S2 += (unsigned long long)b * b;
                 }
             } else {
                 lo = __vminu4(__vminu4(q.x, q.y), __vminu4(q.z, q.w));
                 hi = __vmaxu4(__vmaxu4(q.x, q.y), __vmaxu4(q.z, q.w));
-                lo = __vminu4(lo, lo >> 16); lo = min(lo & 0xffu, (lo >> 8) & 0xffu);
-                hi = __vmaxu4(hi, hi >> 16); hi = max(hi & 0xffu, (hi >> 8) & 0xffu);
                 uint32_t s2 = 0;
                 const uint32_t w[4] = { q.x, q.y, q.z, q.w };
 #pragma unroll
                 for (int k = 0; k < 4; ++k) { s1 = __dp4a(w[k], 0x01010101u, s1); s2 = __dp4a(w[k], w[k], s2); }
                 S2 += s2;
             }
-            S1 += s1;
-            if (lo < rmn) { rmn = lo; t.mnIdx = idx | kVecTag; }
-            if (hi + 1u > rmx) { rmx = hi + 1u; t.mxIdx = idx | kVecTag; }
+            s1acc += s1;                       // <= 4 vectors (2 MiB of voxel sum) between flushes
+            // lane-wise running extrema: one packed min / max and one compare per vector; the horizontal reduction
+            // and the position bookkeeping run only when a lane moved
+            const uint32_t nlo = F == F_U16 ? __vminu2(mn2, lo) : __vminu4(mn2, lo);
+            const uint32_t nhi = F == F_U16 ? __vmaxu2(mx2, hi) : __vmaxu4(mx2, hi);
+            if (nlo != mn2) {
+                mn2 = nlo;
+                uint32_t h;
+                if (F == F_U16) h = min(nlo & 0xffffu, nlo >> 16);
+                else { h = __vminu4(nlo, nlo >> 16); h = min(h & 0xffu, (h >> 8) & 0xffu); }
+                if (h < rmn) { rmn = h; t.mnIdx = (base + i * V) | kVecTag; }
+            }
+            if (nhi != mx2) {
+                mx2 = nhi;
+                uint32_t h;
+                if (F == F_U16) h = max(nhi & 0xffffu, nhi >> 16);
+                else { h = __vmaxu4(nhi, nhi >> 16); h = max(h & 0xffu, (h >> 8) & 0xffu); }
+                if (h + 1u > rmx) { rmx = h + 1u; t.mxIdx = (base + i * V) | kVecTag; }
+            }
             if (!dead) {
 #pragma unroll
-                for (int i = 0; i < V; i += 4)
-                    mulProd4(value(vecGet<BPV>(q, i)), value(vecGet<BPV>(q, i + 1)), value(vecGet<BPV>(q, i + 2)),
-                             value(vecGet<BPV>(q, i + 3)));
+                for (int k = 0; k < V; k += 4)
+                    mulProd4(value(vecGet<BPV>(q, k)), value(vecGet<BPV>(q, k + 1)), value(vecGet<BPV>(q, k + 2)),
+                             value(vecGet<BPV>(q, k + 3)));
             }
             return;
         }
@@ -198,8 +213,8 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
             t.mn = v[i] < t.mn ? v[i] : t.mn;
             t.mx = v[i] > t.mx ? v[i] : t.mx;
         }
-        if (t.mn < mn0) t.mnIdx = idx | kVecTag;
-        if (t.mx > mx0) t.mxIdx = idx | kVecTag;
+        if (t.mn < mn0) t.mnIdx = (base + i * V) | kVecTag;
+        if (t.mx > mx0) t.mxIdx = (base + i * V) | kVecTag;
         float s[V], sq[V];
 #pragma unroll
         for (int i = 0; i < V; ++i) { s[i] = __fsub_rn(v[i], c); sq[i] = __fmul_rn(s[i], s[i]); }
@@ -255,10 +270,11 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
         for (; i + 3 * stride < nvec; i += 4 * stride) {
             const uint4 q0 = ldStream(body + i * 16), q1 = ldStream(body + (i + stride) * 16);
             const uint4 q2 = ldStream(body + (i + 2 * stride) * 16), q3 = ldStream(body + (i + 3 * stride) * 16);
-            accVec(q0, head + i * V); accVec(q1, head + (i + stride) * V);
-            accVec(q2, head + (i + 2 * stride) * V); accVec(q3, head + (i + 3 * stride) * V);
+            accVec(q0, head, i); accVec(q1, head, i + stride);
+            accVec(q2, head, i + 2 * stride); accVec(q3, head, i + 3 * stride);
+            if (PACKED) { S1 += s1acc; s1acc = 0; }
         }
-        for (; i < nvec; i += stride) accVec(ldStream(body + i * 16), head + i * V);
+        for (; i < nvec; i += stride) { accVec(ldStream(body + i * 16), head, i); if (PACKED) { S1 += s1acc; s1acc = 0; } }
         for (size_t k = tail0 + tid; k < n; k += stride) accOne(loadRaw(p.s + k * BPV, BPV), k);
     } else {
         const long long rows = (long long)p.ny * p.nz;
@@ -276,10 +292,14 @@ __global__ void __launch_bounds__(kThreads) aggregatesKernel(AggParams p)
             int v = threadIdx.x;
             for (; v + (int)blockDim.x < nvec; v += 2 * blockDim.x) {
                 const uint4 q0 = ldStream(body + v * 16LL), q1 = ldStream(body + (v + (int)blockDim.x) * 16LL);
-                accVec(q0, rowIdx + head + (unsigned long long)v * V);
-                accVec(q1, rowIdx + head + (unsigned long long)(v + (int)blockDim.x) * V);
+                accVec(q0, rowIdx + head, (unsigned long long)v);
+                accVec(q1, rowIdx + head, (unsigned long long)(v + (int)blockDim.x));
+                if (PACKED) { S1 += s1acc; s1acc = 0; }
             }
-            for (; v < nvec; v += blockDim.x) accVec(ldStream(body + v * 16LL), rowIdx + head + (unsigned long long)v * V);
+            for (; v < nvec; v += blockDim.x) {
+                accVec(ldStream(body + v * 16LL), rowIdx + head, (unsigned long long)v);
+                if (PACKED) { S1 += s1acc; s1acc = 0; }
+            }
             for (int x = tail0 + threadIdx.x; x < p.nx; x += blockDim.x)
                 accOne(loadRaw(row + (long long)x * BPV, BPV), rowIdx + (unsigned long long)x);
         }

@@ -12,8 +12,10 @@
 //         carry along the row; the next vector is loaded before the current one is scanned
 //     y/z one thread per 16-byte column of a plane (y pass) or of an xy position (z pass): a running packed sum walks
 //         the lines, coalesced across x, several loads in flight
+//     x+y fused (aligned rows of up to 16 KiB, at least 2 planes per SM): one CTA per plane walks the rows with the
+//         column sums in registers -- two passes over the volume instead of three
 // Packed adds (__vadd4 / __vadd2) keep 16 / 8 voxels per 128-bit register for UInt8 / UInt16.
-// Algorithmic traffic: 2 bpv per voxel for the ideal single pass; the three passes move 6 bpv.
+// Algorithmic traffic: 2 bpv per voxel for the ideal single pass; the passes move 4 bpv (fused x+y) or 6 bpv.
 #include "common.cuh"
 #include "launch.hpp"
 #include "voxel_codec.cuh"
@@ -136,6 +138,77 @@ scanRowsKernel(ScanParams p)
     }
 }
 
+// ---- fused x + y pass: one CTA per plane ------------------------------------------------------------------------
+// out[y] = rowscan(in[y]) + out[y - 1]: the CTA walks the rows of its plane top to bottom; a thread owns VPT
+// consecutive 16-byte vectors of every row and keeps the previous output row's vectors (= the column sums) in
+// registers.  Per row: packed prefix inside the thread's vectors, shuffle scan of the thread totals, the warp totals
+// through shared memory (double buffered: ONE barrier per row), next row's vectors already in flight.  One read and
+// one write of the volume instead of two of each.  Launcher: x left to right, every row starts on a 16-byte boundary
+// and is a whole number of vectors, nvec <= kThreads * VPT.
+template <int BPV, int VPT>
+__global__ void __launch_bounds__(kThreads)
+scanPlaneXYKernel(ScanParams p, int nvec)
+{
+    __shared__ uint32_t warpTot[2][kThreads / 32];
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const int v0 = (int)threadIdx.x * VPT;
+    for (int z = blockIdx.x; z < p.nz; z += gridDim.x) {
+        uint8_t* base = p.d + z * p.pitchZ + (long long)v0 * 16;
+        uint4 col[VPT], cur[VPT];
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+            col[k] = make_uint4(0u, 0u, 0u, 0u);
+            cur[k] = v0 + k < nvec ? ldPlain(base + k * 16) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        for (int y = 0; y < p.ny; ++y) {
+            uint8_t* row = base + y * p.pitchY;
+            uint4 nxt[VPT];
+#pragma unroll
+            for (int k = 0; k < VPT; ++k)
+                nxt[k] = (y + 1 < p.ny && v0 + k < nvec) ? ldPlain(row + p.pitchY + k * 16) : make_uint4(0u, 0u, 0u, 0u);
+            // inside the thread: prefix over its VPT vectors
+            uint4 w[VPT];
+            uint32_t t = 0u;                        // running total, replicated into every element
+#pragma unroll
+            for (int k = 0; k < VPT; ++k) {
+                w[k].x = addPacked<BPV>(wordScan<BPV>(cur[k].x), t);
+                w[k].y = addPacked<BPV>(wordScan<BPV>(cur[k].y), lastBroadcast<BPV>(w[k].x));
+                w[k].z = addPacked<BPV>(wordScan<BPV>(cur[k].z), lastBroadcast<BPV>(w[k].y));
+                w[k].w = addPacked<BPV>(wordScan<BPV>(cur[k].w), lastBroadcast<BPV>(w[k].z));
+                t = lastBroadcast<BPV>(w[k].w);
+            }
+            // across the lanes, then across the warps
+#pragma unroll
+            for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, t, dlt);
+                if ((int)lane >= dlt) t = addPacked<BPV>(t, up);
+            }
+            uint32_t before = __shfl_up_sync(0xffffffffu, t, 1);
+            if (lane == 0) before = 0u;
+            if (lane == 31) warpTot[y & 1][warp] = t;
+            __syncthreads();
+            for (unsigned i = 0; i < warp; ++i) before = addPacked<BPV>(before, warpTot[y & 1][i]);
+#pragma unroll
+            for (int k = 0; k < VPT; ++k) {
+                const uint4 b4 = make_uint4(before, before, before, before);
+                col[k] = addPacked4<BPV>(addPacked4<BPV>(w[k], b4), col[k]);
+                if (v0 + k < nvec) stStream(row + k * 16, col[k]);
+                cur[k] = nxt[k];
+            }
+        }
+        __syncthreads();       // the next plane reuses warpTot[0]
+    }
+}
+
+template <int BPV, int VPT>
+cudaError_t launchPlaneXY(const LaunchCtx& c, const ScanParams& p, int nvec)
+{
+    const long long cap = (long long)c.smCount * 8;
+    scanPlaneXYKernel<BPV, VPT><<<(unsigned)(p.nz < cap ? p.nz : cap), kThreads, 0, c.stream>>>(p, nvec);
+    countLaunch();
+    return cudaGetLastError();
+}
+
 // ---- y / z pass: a running packed sum walks `steps` lines that lie `stepPitch` bytes apart -----------------------
 // Thread = one aligned 16-byte column chunk of line family (o1, o2); every line of the range has the same 16-byte
 // phase (launcher), so the chunk is the same byte window [c0, c1) of every line.
@@ -238,8 +311,18 @@ cudaError_t scanBpv(const LaunchCtx& c, const ScanParams& p, bool alignedBuffer)
     const long long rowBytes = (long long)p.nx * BPV;
     const long long ay = p.pitchY < 0 ? -p.pitchY : p.pitchY, az = p.pitchZ < 0 ? -p.pitchZ : p.pitchZ;
     cudaError_t e;
+    // ---- x and y in one pass when a CTA can own a plane's rows (and there are enough planes to fill the machine)
+    bool fusedXY = false;
+    if (p.nx > 1 && p.ny > 1 && p.stepX > 0 && (reinterpret_cast<uintptr_t>(p.d) & 15u) == 0 && rowBytes % 16 == 0
+        && ay % 16 == 0 && az % 16 == 0 && rowBytes / 16 <= kThreads * 4 && p.nz >= c.smCount * 2) {
+        const int nvec = (int)(rowBytes / 16);
+        e = nvec <= kThreads ? launchPlaneXY<BPV, 1>(c, p, nvec)
+          : nvec <= kThreads * 2 ? launchPlaneXY<BPV, 2>(c, p, nvec) : launchPlaneXY<BPV, 4>(c, p, nvec);
+        if (e != cudaSuccess) return e;
+        fusedXY = true;
+    }
     // ---- x
-    if (p.nx > 1) {
+    if (p.nx > 1 && !fusedXY) {
         if (p.stepX > 0 && alignedBuffer && (long long)p.ny * p.nz < 0x7fffffffLL) {
             const long long rows = (long long)p.ny * p.nz;
             long long ctas = (rows + kThreads / 32 - 1) / (kThreads / 32);
@@ -257,7 +340,7 @@ cudaError_t scanBpv(const LaunchCtx& c, const ScanParams& p, bool alignedBuffer)
     const bool walk = p.stepX > 0 && (ay % 16) == 0 && (az % 16) == 0 && rowBytes < 0x7fffffffLL;
     const int phase = (int)(reinterpret_cast<uintptr_t>(p.d) & 15u);
     const unsigned gx = (unsigned)((rowBytes + phase + 16 * kThreads - 1) / (16 * kThreads));
-    for (int axis = 1; axis <= 2; ++axis) {
+    for (int axis = fusedXY ? 2 : 1; axis <= 2; ++axis) {
         const int steps = axis == 1 ? p.ny : p.nz, outer = axis == 1 ? p.nz : p.ny;
         const long long stepPitch = axis == 1 ? p.pitchY : p.pitchZ, outerPitch = axis == 1 ? p.pitchZ : p.pitchY;
         if (steps <= 1) continue;
