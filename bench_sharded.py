@@ -58,6 +58,11 @@ def run_sharded_ops(torch, dist, lib, capi, ShardedVolume, sharded, rank, world,
     t = torch.tensor([got[0]], dtype=torch.int64, device="cuda")
     dist.all_reduce(t) if dist is not None else None
     out[f"SumRange dstOffset (0,0,{ZOFF}) {tag}"]["halo_bytes_all_ranks"] = int(t.item())
+    # the two ops with a real exchange step: per-rank partial results, one small collective
+    record(f"Histogram 256 bins {tag} (per-rank bins + SUM all-reduce)", n, n,
+           lambda: sharded.histogram_sharded(a, (0, 0, 0), (E, E, E), 256, dist))
+    record(f"Aggregates {tag} (per-rank partial + 88-byte all-gather)", n, n,
+           lambda: sharded.aggregates_sharded(a, (0, 0, 0), (E, E, E), dist))
     del a, b, d
     torch.cuda.empty_cache()
 

@@ -23,6 +23,7 @@
 #include "launch.hpp"
 
 #include <cmath>
+#include <cstdlib>
 
 namespace vktb {
 namespace {
@@ -175,7 +176,17 @@ template <int FS, int FD>
 cudaError_t launchAffineFF(const LaunchCtx& c, const AffineParams& p, bool oneTap)
 {
     constexpr int V = 16 / bytesPerVoxel(FD);
-    const RowsLaunch l = rowsLaunch(p.Dx, (long long)p.Dy * p.Dz, V);
+    RowsLaunch l = rowsLaunch(p.Dx, (long long)p.Dy * p.Dz, V);
+    if (!p.diag) {
+        // a general matrix maps a dst row to a slanted src line: a warp that covers 4 chunks x 8 rows gathers from a
+        // compact src patch instead of a 256-voxel line (fewer sectors per request, better L1 / L2 hit rates)
+        const int chunks = (p.Dx + V - 1) / V;
+        const long long rows = (long long)p.Dy * p.Dz;
+        long long gy = (rows + 63) / 64;
+        if (gy > 65535) gy = 65535;
+        l.block = dim3(4, 64, 1);
+        l.grid = dim3((unsigned)((chunks + 3) / 4), (unsigned)gy, 1);
+    }
     const bool rawMove = oneTap && FS == FD && (FS == F_U8 || FS == F_U16) && p.ms.identity && p.md.identity;
     if (rawMove) affineKernel<FS, FD, 2><<<l.grid, l.block, 0, c.stream>>>(p);
     else if (oneTap) affineKernel<FS, FD, 1><<<l.grid, l.block, 0, c.stream>>>(p);
@@ -208,6 +219,7 @@ struct FilterParams
     int Dx, Dy;              // dst row length / rows per plane (setValue indexes with the dst dims)
     int fx, fy, fz;          // filter dims, 1..3
     int zChunk;
+    int pairs;               // 3x3x3 march: a thread owns two output rows (filter3PairKernel)
     float w[27];             // f(xx, yy, zz) at [zz * fx * fy + yy * fx + xx]
     Mapping md, ms;
     int fs, fd;              // formats (generic kernel)
@@ -292,6 +304,119 @@ __global__ void __launch_bounds__(kThreads) filter3MarchKernel(FilterParams p)
     }
 }
 
+// ---- 3x3x3 as row PAIRS ------------------------------------------------------------------------------------------
+// A thread owns the outputs (x, ya) and (x, ya + 1) of a z chunk: four source rows of three voxels per plane serve both
+// (6 loads and unmaps per output instead of 9), and the two accumulators travel as one f32x2 register pair: per tap two
+// scalar multiplies (rounded, as the reference's `f * v`) and ONE packed add (FADD2: two independent roundings).  The
+// multiplies stay scalar on purpose: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under --fmad=false.
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi)
+{
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b)
+{
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+// twelve unmapped voxels: rows ya - 1 .. ya + 2 (the last one clamped to the volume), columns x - 1 .. x + 1
+template <int F, bool IDENT>
+__device__ __forceinline__ void loadPlane12(float (&v)[12], const FilterParams& p, const float* lut, int x, int ya, int z)
+{
+    constexpr int B = bytesPerVoxel(F);
+    const long long rowBytes = (long long)p.nx * B;
+    const uint8_t* row = p.s + (((long long)z * p.ny + (ya - 1)) * p.nx + (x - 1)) * B;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint8_t* q = (r == 3 && ya + 2 > p.ny - 1) ? row + 2 * rowBytes : row + r * rowBytes;
+#pragma unroll
+        for (int xx = 0; xx < 3; ++xx) {
+            uint32_t raw;
+            if (B == 1) raw = __ldg(q + xx);
+            else if (B == 2) raw = __ldg(reinterpret_cast<const uint16_t*>(q) + xx);
+            else raw = __ldg(reinterpret_cast<const uint32_t*>(q) + xx);
+            v[r * 3 + xx] = F == F_U8 ? lut[raw] : unmapVoxel<F, IDENT>(raw, p.ms);
+        }
+    }
+}
+
+// nine taps of one plane for both outputs: acc.lo += w * v[yy][xx], acc.hi += w * v[yy + 1][xx]
+__device__ __forceinline__ unsigned long long accPlanePair(unsigned long long acc, const float (&v)[12], const float* w)
+{
+#pragma unroll
+    for (int yy = 0; yy < 3; ++yy)
+#pragma unroll
+        for (int xx = 0; xx < 3; ++xx)
+            acc = add2(acc, pack2(__fmul_rn(w[yy * 3 + xx], v[yy * 3 + xx]), __fmul_rn(w[yy * 3 + xx], v[(yy + 1) * 3 + xx])));
+    return acc;
+}
+
+template <int F, bool IDS, bool IDD>
+__global__ void __launch_bounds__(128) filter3PairKernel(FilterParams p)
+{
+    constexpr int B = bytesPerVoxel(F);
+    __shared__ float lut[F == F_U8 ? 256 : 1];
+    if (F == F_U8) {
+        for (int t = threadIdx.y * 32 + threadIdx.x; t < 256; t += 128) lut[t] = unmapVoxel<F_U8, IDS>((uint32_t)t, p.ms);
+        __syncthreads();
+    }
+    const int x = blockIdx.x * 32 + threadIdx.x, j = blockIdx.y * 4 + threadIdx.y;      // block (32, 4): 72 registers x 128
+    const int ya = 1 + 2 * j, yb = ya + 1;
+    if (x >= p.nx) return;
+    const int z0 = blockIdx.z * p.zChunk, z1 = min(z0 + p.zChunk, p.nz);
+    const uint32_t zero = mapVoxel<F, IDD>(0.f, p.md);
+    const long long dPlane = (long long)p.Dx * p.Dy * B;
+    auto put = [&](int y, int z, uint32_t raw) {
+        uint8_t* q = p.d + ((long long)y * p.Dx + x) * B + z * dPlane;
+        if (B == 1) *q = (uint8_t)raw;
+        else if (B == 2) *reinterpret_cast<uint16_t*>(q) = (uint16_t)raw;
+        else *reinterpret_cast<uint32_t*>(q) = raw;
+    };
+    if (j == 0)
+        for (int z = z0; z < z1; ++z) put(0, z, zero);                 // the y = 0 border row
+    if (ya > p.ny - 1) return;
+    const bool aBorder = ya == p.ny - 1, bInside = yb <= p.ny - 2, bBorder = yb == p.ny - 1;
+    if (aBorder || x == 0 || x == p.nx - 1) {
+        for (int z = z0; z < z1; ++z) {
+            put(ya, z, zero);
+            if (bInside || bBorder) put(yb, z, zero);
+        }
+        return;
+    }
+    int zs = z0, ze = z1;
+    auto zeroPlane = [&](int z) { put(ya, z, zero); if (bInside || bBorder) put(yb, z, zero); };
+    if (zs == 0) { zeroPlane(0); zs = 1; }
+    if (ze == p.nz) { if (p.nz - 1 >= zs) zeroPlane(p.nz - 1); ze = p.nz - 1; }
+    if (bBorder)
+        for (int z = zs; z < ze; ++z) put(yb, z, zero);
+    if (zs >= ze) return;
+    auto emit = [&](int z, unsigned long long acc) {
+        put(ya, z, mapVoxel<F, IDD>(__uint_as_float((uint32_t)acc), p.md));
+        if (bInside) put(yb, z, mapVoxel<F, IDD>(__uint_as_float((uint32_t)(acc >> 32)), p.md));
+    };
+    float a[12], b[12], cc[12];
+    loadPlane12<F, IDS>(a, p, lut, x, ya, zs - 1);
+    loadPlane12<F, IDS>(b, p, lut, x, ya, zs);
+    int z = zs;
+    for (; z + 2 < ze; z += 3) {
+        loadPlane12<F, IDS>(cc, p, lut, x, ya, z + 1);
+        emit(z, accPlanePair(accPlanePair(accPlanePair(0ull, a, p.w), b, p.w + 9), cc, p.w + 18));
+        loadPlane12<F, IDS>(a, p, lut, x, ya, z + 2);
+        emit(z + 1, accPlanePair(accPlanePair(accPlanePair(0ull, b, p.w), cc, p.w + 9), a, p.w + 18));
+        loadPlane12<F, IDS>(b, p, lut, x, ya, z + 3);
+        emit(z + 2, accPlanePair(accPlanePair(accPlanePair(0ull, cc, p.w), a, p.w + 9), b, p.w + 18));
+    }
+    for (; z < ze; ++z) {
+        loadPlane12<F, IDS>(cc, p, lut, x, ya, z + 1);
+        emit(z, accPlanePair(accPlanePair(accPlanePair(0ull, a, p.w), b, p.w + 9), cc, p.w + 18));
+#pragma unroll
+        for (int i = 0; i < 12; ++i) { a[i] = b[i]; b[i] = cc[i]; }
+    }
+}
+
 // any filter dims in 1..3, any formats: one thread per voxel
 __global__ void __launch_bounds__(kThreads) filterGenericKernel(FilterParams p)
 {
@@ -319,9 +444,12 @@ __global__ void __launch_bounds__(kThreads) filterGenericKernel(FilterParams p)
 template <int F>
 cudaError_t launchFilter3(const LaunchCtx& c, const FilterParams& p, dim3 grid)
 {
-    const dim3 block(32, 8, 1);
+    const dim3 block(32, 8, 1), pairBlock(32, 4, 1);
     const bool ids = p.ms.identity && F != F_INT16, idd = p.md.identity && F != F_INT16;
-    if (ids && idd) filter3MarchKernel<F, true, true><<<grid, block, 0, c.stream>>>(p);
+    if (p.pairs) {
+        if (ids && idd) filter3PairKernel<F, true, true><<<grid, pairBlock, 0, c.stream>>>(p);
+        else filter3PairKernel<F, false, false><<<grid, pairBlock, 0, c.stream>>>(p);
+    } else if (ids && idd) filter3MarchKernel<F, true, true><<<grid, block, 0, c.stream>>>(p);
     else filter3MarchKernel<F, false, false><<<grid, block, 0, c.stream>>>(p);
     countLaunch();
     return cudaGetLastError();
@@ -384,14 +512,18 @@ cudaError_t launchFilter(const LaunchCtx& c, const VolDesc& dst, const VolDesc& 
     p.fs = src.format; p.fd = dst.format;
     if (p.fx == 3 && p.fy == 3 && p.fz == 3 && src.format == dst.format) {
         // z chunks: enough CTAs for every SM a few times over, at least 16 planes each (two extra plane loads per chunk)
-        const long long tiles = (long long)((p.nx + 31) / 32) * ((p.ny + 7) / 8);
+        // row pairs unless VKTB_FILTER_PAIRS=0 (kept for A/B measurements)
+        const char* pe = std::getenv("VKTB_FILTER_PAIRS");
+        p.pairs = !(pe && pe[0] == '0');
+        const int yTiles = p.pairs ? (p.ny / 2 + 1 + 3) / 4 : (p.ny + 7) / 8;   // pairs: blocks of 4 row pairs
+        const long long tiles = (long long)((p.nx + 31) / 32) * yTiles;
         int chunks = (int)(((long long)c.smCount * 16 + tiles - 1) / tiles);
         if (chunks < 1) chunks = 1;
         int zChunk = (p.nz + chunks - 1) / chunks;
         if (zChunk < 16) zChunk = 16;
         if (zChunk > p.nz) zChunk = p.nz;
         p.zChunk = zChunk;
-        const dim3 grid((p.nx + 31) / 32, (p.ny + 7) / 8, (p.nz + zChunk - 1) / zChunk);
+        const dim3 grid((p.nx + 31) / 32, yTiles, (p.nz + zChunk - 1) / zChunk);
         if (grid.y <= 65535 && grid.z <= 65535) {
             switch (src.format) {
             case F_U8:    return launchFilter3<F_U8>(c, p, grid);
@@ -402,7 +534,7 @@ cudaError_t launchFilter(const LaunchCtx& c, const VolDesc& dst, const VolDesc& 
             }
         }
     }
-    p.zChunk = 0;
+    p.zChunk = 0; p.pairs = 0;
     const size_t n = (size_t)p.nx * p.ny * p.nz;
     filterGenericKernel<<<flatGrid(n, kThreads, c.smCount, 16), kThreads, 0, c.stream>>>(p);
     countLaunch();
