@@ -486,6 +486,13 @@ cudaError_t launchAffine(const LaunchCtx& c, const VolDesc& dst, const VolDesc& 
         if (first[a] < 0 || last[a] > (1 << 23)) p.fastTrunc = 0;
     if (dst.dims[0] >= (1 << 24)) return cudaErrorInvalidValue;
     const bool oneTap = insideSrc && oneTapExact(src);
+    if (oneTap && p.diag && !(getenv("VKTB_SCALE_ROWS") && getenv("VKTB_SCALE_ROWS")[0] == '0')) {
+        // a Scale whose every dst voxel maps inside the source is a separable monotone gather: Resample's bulk-copy
+        // row pipeline (resample_rows.cu) with the affine coordinate maps
+        const float dm[3] = { m[0], m[4], m[8] };
+        const cudaError_t e = launchScaleRowRuns(c, dst, src, dm, center, first, last);
+        if (e != cudaErrorNotSupported) return e;
+    }
     switch (src.format) {
     case F_U8:    return launchAffineF<F_U8>(c, p, dst.format, oneTap);
     case F_U16:   return launchAffineF<F_U16>(c, p, dst.format, oneTap);

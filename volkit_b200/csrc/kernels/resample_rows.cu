@@ -17,6 +17,7 @@
 // lost to the 128-bit stores used here.
 //
 // Algorithmic traffic: bytes of the src rows that are hit + Dx*Dy*Dz*bpv_dst.
+#include <cmath>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -48,28 +49,39 @@ __device__ __forceinline__ int srcCoord(int d, int D, int S)
     return (int)x86Cvtt32(__fmul_rn(__fdiv_rn(__int2float_rn(d), __int2float_rn(D)), __int2float_rn(S)));
 }
 
+// Per-axis coordinate map of the plan: mode 0 = Resample's d / float(D) * S, mode 1 = Scale's m * (d - c) + c (the
+// diagonal case of the affine gather, affine_filter.cu; inside the range by the launcher's check, so the FP32-pipe
+// truncation is not needed here -- the plan runs once per launch)
+struct AxisMap { int mode, D, S; float m, c; };
+__device__ __forceinline__ int coordOf(const AxisMap& a, int d)
+{
+    if (a.mode == 0) return srcCoord(d, a.D, a.S);
+    return (int)x86Cvtt32(__fadd_rn(__fmul_rn(a.m, __fsub_rn(__int2float_rn(d), a.c)), a.c));
+}
+
 // Plan: block 0 -> x map; block 1 -> y runs; block 2 -> z runs.  1024 threads per block.
 // runs: start[k] = first dst index of run k (start[nRuns] = count), src[k] = its src coordinate.
 __global__ void __launch_bounds__(1024)
-resamplePlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz0, int Dz, int Sz)
+resamplePlanKernel(int* tab, int Dx, int Dy, int dzCount, int dz0, AxisMap mx, AxisMap my, AxisMap mz)
 {
     __shared__ int scan[1024];
     const int t = threadIdx.x;
     int* xmap = tab + kHdr;
     if (blockIdx.x == 0) {
-        for (int i = t; i < Dx; i += 1024) xmap[i] = srcCoord(i, Dx, Sx);
+        for (int i = t; i < Dx; i += 1024) xmap[i] = coordOf(mx, i);
         return;
     }
     const bool isY = blockIdx.x == 1;
-    const int n = isY ? Dy : dzCount, d0 = isY ? 0 : dz0, D = isY ? Dy : Dz, S = isY ? Sy : Sz;
+    const int n = isY ? Dy : dzCount, d0 = isY ? 0 : dz0;
+    const AxisMap am = isY ? my : mz;
     int* start = tab + kHdr + Dx + (isY ? 0 : 2 * Dy + 1);
     int* src = start + n + 1;
     const int seg = (n + 1023) / 1024;
     const int i0 = min(n, t * seg), i1 = min(n, i0 + seg);
     int cnt = 0;
-    int prev = i0 > 0 ? srcCoord(d0 + i0 - 1, D, S) : 0;
+    int prev = i0 > 0 ? coordOf(am, d0 + i0 - 1) : 0;
     for (int i = i0; i < i1; ++i) {
-        const int c = srcCoord(d0 + i, D, S);
+        const int c = coordOf(am, d0 + i);
         cnt += (i == 0 || c != prev) ? 1 : 0;
         prev = c;
     }
@@ -82,9 +94,9 @@ resamplePlanKernel(int* tab, int Dx, int Sx, int Dy, int Sy, int dzCount, int dz
         __syncthreads();
     }
     int k = scan[t] - cnt;   // exclusive prefix
-    prev = i0 > 0 ? srcCoord(d0 + i0 - 1, D, S) : 0;
+    prev = i0 > 0 ? coordOf(am, d0 + i0 - 1) : 0;
     for (int i = i0; i < i1; ++i) {
-        const int c = srcCoord(d0 + i, D, S);
+        const int c = coordOf(am, d0 + i);
         if (i == 0 || c != prev) { start[k] = i; src[k] = c; ++k; }
         prev = c;
     }
@@ -271,10 +283,12 @@ cudaError_t launchRowRunDst(const LaunchCtx& c, const RowRunParams& p, int fd, s
 
 } // namespace
 
-// One-tap resample through the TMA row pipeline.  Returns cudaErrorNotSupported when the operands do not
-// qualify (unaligned rows, Int16, giant dims); the caller then uses the direct-gather kernel.
-cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src,
-                                  int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3])
+// The pipeline's launcher, shared by Resample (one-tap modes) and Scale.
+// maps: the per-axis coordinate maps; spanNum / spanDen: src voxels per dst voxel along x (an upper bound of the
+// slope: a dst tile of w voxels taps at most w * spanNum / spanDen + 2 src voxels)
+static cudaError_t launchRowRunsMapped(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, int dstZ0,
+                                       const int32_t D[3], int srcZ0, const int32_t S[3], const AxisMap maps[3],
+                                       long long spanNum, long long spanDen, bool up)
 {
     const int bs = bytesPerVoxel(src.format), bd = bytesPerVoxel(dst.format);
     const int dzCount = dst.dims[2];
@@ -283,7 +297,6 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     // bulk copies need 16-byte aligned rows on both sides
     if ((reinterpret_cast<uintptr_t>(src.data) & 15u) || (reinterpret_cast<uintptr_t>(dst.data) & 15u)) return cudaErrorNotSupported;
     if (((long long)S[0] * bs) % 16 || ((long long)D[0] * bd) % 16) return cudaErrorNotSupported;
-    // (D-1)/float(D)*S < S must hold in binary32 so that every tap lies inside the src row: true below 2^24
     for (int a = 0; a < 3; ++a) if (D[a] > (1 << 24) || S[a] > (1 << 24)) return cudaErrorNotSupported;
 
     RowRunParams p;
@@ -298,7 +311,7 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     p.tileW = tileW;
     p.nXT = (D[0] + tileW - 1) / tileW;
     // src bytes a tile can span: floor(tileW*Sx/Dx)+2 voxels, plus the two 16-byte roundings
-    const long long spanVox = (long long)tileW * S[0] / D[0] + 2;
+    const long long spanVox = (long long)tileW * spanNum / spanDen + 2;
     long long srcRow = spanVox * bs + 32;
     if (srcRow > (long long)S[0] * bs) srcRow = (long long)S[0] * bs;
     srcRow = (srcRow + 15) / 16 * 16;
@@ -310,7 +323,6 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     if (R > 8) R = 8;
     // measured (profiles/r01_notes.md: sweeps over rows x stages x grid, repeated on one box): up-sampling runs best with
     // 2 rows per item and 2 stages (small CTAs, 8 resident per SM); down-sampling with one 16 KiB item and 3 stages
-    const bool up = D[0] > S[0];
     if (up && R > 2) R = 2;
     p.R = envInt("VKTB_RS_ROWS", R, 1, 8);
     p.stages = envInt("VKTB_RS_STAGES", up ? 2 : 3, 2, kMaxStages);
@@ -322,7 +334,7 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     cudaError_t e = cudaMallocAsync((void**)&tab, nTab * sizeof(int), c.stream);
     if (e != cudaSuccess) return e;
     p.tab = tab;
-    resamplePlanKernel<<<3, 1024, 0, c.stream>>>(tab, D[0], S[0], D[1], S[1], dzCount, dstZ0, D[2], S[2]);
+    resamplePlanKernel<<<3, 1024, 0, c.stream>>>(tab, D[0], D[1], dzCount, dstZ0, maps[0], maps[1], maps[2]);
     countLaunch();
 
     // persistent grid: as many CTAs per SM as shared memory allows (<= 8), a multiple of the x-tile count
@@ -359,6 +371,43 @@ cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const 
     }
     cudaFreeAsync(tab, c.stream);
     return e;
+}
+
+// One-tap resample through the TMA row pipeline.  Returns cudaErrorNotSupported when the operands do not
+// qualify (unaligned rows, Int16, giant dims); the caller then uses the direct-gather kernel.
+cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src,
+                                  int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3])
+{
+    // (D-1)/float(D)*S < S holds in binary32 below 2^24 (checked by the core), so every tap lies inside the src row
+    AxisMap maps[3];
+    for (int a = 0; a < 3; ++a) maps[a] = AxisMap{ 0, D[a], S[a], 0.f, 0.f };
+    return launchRowRunsMapped(c, dst, src, dstZ0, D, srcZ0, S, maps, S[0], D[0], D[0] > S[0]);
+}
+
+// Scale (diagonal affine gather, one-tap modes) whose EVERY dst voxel maps inside the source: a separable monotone
+// gather like Resample Nearest, so it runs on the same pipeline.  m[a] > 0 and center[a] are the diagonal and the
+// centre; the caller has verified the one-tap conditions.  cudaErrorNotSupported -> the affine kernel.
+cudaError_t launchScaleRowRuns(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, const float m[3],
+                               const float center[3], const int32_t first[3], const int32_t last[3])
+{
+    AxisMap maps[3];
+    for (int a = 0; a < 3; ++a) {
+        if (!(m[a] > 0.f) || !std::isfinite(m[a]) || !std::isfinite(center[a]) || dst.dims[a] <= 0) return cudaErrorNotSupported;
+        // q(d) = m * (d - c) + c is non-decreasing in d (every step is monotone under rounding): all dst voxels map
+        // inside [first, last) iff the two ends do.  volatile: one rounding per operation, as on the device.
+        auto q = [&](int d) {
+            volatile float p = (float)d - center[a];
+            volatile float t = m[a] * p;
+            volatile float r = t + center[a];
+            return (float)r;
+        };
+        if (!(q(0) >= (float)first[a]) || !(q(dst.dims[a] - 1) < (float)last[a])) return cudaErrorNotSupported;
+        if (first[a] < 0 || last[a] > src.dims[a]) return cudaErrorNotSupported;
+        maps[a] = AxisMap{ 1, dst.dims[a], src.dims[a], m[a], center[a] };
+    }
+    // slope bound along x as a fraction: ceil(m * 2^16) / 2^16
+    const long long num = (long long)std::ceil((double)m[0] * 65536.0) + 1;
+    return launchRowRunsMapped(c, dst, src, 0, dst.dims, 0, src.dims, maps, num, 65536, m[0] < 1.f);
 }
 
 } // namespace vktb
