@@ -618,7 +618,12 @@ def test_affine_and_filter_kernels(gpu):
             src.a[3, 5, 7], src.a[10, 20, 95], src.a[36, 39, 95], src.a[0, 0, 0] = np.nan, np.inf, -np.inf, -0.0
         for ddims, op in (((96, 40, 37), ("scale", (1.25, 0.8, 1.5), (40.0, 20.0, 18.0))),
                           ((128, 33, 40), ("rotate", (0.3, -1.0, 2.0), 0.9, (48.0, 20.0, 18.0))),
-                          ((96, 40, 37), ("scale", (1.0, 1.0, 1.0), (0.0, 0.0, 0.0)))):
+                          ((96, 40, 37), ("scale", (1.0, 1.0, 1.0), (0.0, 0.0, 0.0))),
+                          # every dst voxel maps inside the source: the bulk-copy row pipeline (integer sources)
+                          ((96, 40, 37), ("scale", (1.5, 2.0, 1.25), (48.0, 20.0, 18.0))),
+                          ((192, 80, 50), ("scale", (2.0, 2.0, 1.4), (0.0, 0.0, 0.0))),
+                          ((64, 24, 30), ("scale", (0.75, 0.625, 0.9), (0.0, 0.0, 0.0))),
+                          ((2048, 9, 5), ("scale", (21.5, 1.0, 1.0), (7.25, 3.0, 2.0)))):
             a, b = cases.mk(ddims, dfmt, 5, 0.0, 1.0), cases.mk(ddims, dfmt, 5, 0.0, 1.0)
             for lib, d in ((gpu, a), (o, b)):
                 if op[0] == "scale":
