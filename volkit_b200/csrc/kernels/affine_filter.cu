@@ -43,6 +43,7 @@ struct AffineParams
     Mapping md, ms;
     int diag;                // off-diagonal matrix entries are all +-0
     int fastTrunc;           // the range lies inside [0, 2^23)
+    int zsep;                // m[2], m[5], m[6], m[7] are all +-0: z does not mix with x, y (a rotation about z)
 };
 
 template <int FS>
@@ -118,6 +119,16 @@ __global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
             if (!(rqy >= p.first[1] && rqy < p.last[1] && rqz >= p.first[2] && rqz < p.last[2])) continue;
             if (MODE != 0) rowBase = truncCoord(rqz, fast) * plane + (long long)truncCoord(rqy, fast) * p.Sx;
         }
+        // z separable (rotation about z): q.z once per row, the z column's +-0 products dropped from q.x and q.y (they
+        // can only flip the sign of a zero, which neither the range test nor the truncation sees)
+        const bool zsep = p.zsep != 0 && !diag;
+        float ax = 0.f, ay = 0.f;
+        if (zsep) {
+            rqz = __fadd_rn(__fmul_rn(p.m[8], pz), p.c[2]);
+            if (!(rqz >= p.first[2] && rqz < p.last[2])) continue;
+            ax = __fmul_rn(p.m[3], py); ay = __fmul_rn(p.m[4], py);
+            if (MODE != 0) rowBase = truncCoord(rqz, fast) * plane;
+        }
         uint8_t* dp = p.d + (r * p.Dx + x0) * BD;
         uint32_t out[V];
         unsigned inside = 0;
@@ -129,6 +140,11 @@ __global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
             if (diag) {
                 qx = __fadd_rn(__fmul_rn(p.m[0], px), p.c[0]); qy = rqy; qz = rqz;
                 if (!(qx >= p.first[0] && qx < p.last[0])) continue;
+            } else if (zsep) {
+                qx = __fadd_rn(__fadd_rn(__fmul_rn(p.m[0], px), ax), p.c[0]);
+                qy = __fadd_rn(__fadd_rn(__fmul_rn(p.m[1], px), ay), p.c[1]);
+                qz = rqz;
+                if (!(qx >= p.first[0] && qx < p.last[0] && qy >= p.first[1] && qy < p.last[1])) continue;
             } else {
                 // (a*x + b*y) + c*z, then + center
                 qx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.m[0], px), __fmul_rn(p.m[3], py)), __fmul_rn(p.m[6], pz)), p.c[0]);
@@ -142,6 +158,7 @@ __global__ void __launch_bounds__(kThreads) affineKernel(AffineParams p)
                 out[i] = mapVoxel<FD, false>(sampleLinearRef<FS>(p, sx, truncCoord(qy, fast), truncCoord(qz, fast)), p.md);
             } else {
                 const long long idx = diag ? rowBase + sx
+                                    : zsep ? rowBase + (long long)truncCoord(qy, fast) * p.Sx + sx
                                            : truncCoord(qz, fast) * plane + (long long)truncCoord(qy, fast) * p.Sx + sx;
                 const uint32_t raw = loadRaw(p.s + idx * BS, BS);
                 out[i] = MODE == 2 ? raw : mapVoxel<FD, false>(unmapVoxel<FS, false>(raw, p.ms), p.md);
@@ -481,6 +498,11 @@ cudaError_t launchAffine(const LaunchCtx& c, const VolDesc& dst, const VolDesc& 
         if (!std::isfinite(m[i])) p.diag = 0;         // 0 * inf would be NaN, not +-0
     for (int a = 0; a < 3; ++a)
         if (!std::isfinite(center[a])) p.diag = 0;
+    p.zsep = (m[2] == 0.f && m[5] == 0.f && m[6] == 0.f && m[7] == 0.f) ? 1 : 0;
+    for (int i = 0; i < 9; ++i)
+        if (!std::isfinite(m[i])) p.zsep = 0;
+    for (int a = 0; a < 3; ++a)
+        if (!std::isfinite(center[a])) p.zsep = 0;
     p.fastTrunc = 1;
     for (int a = 0; a < 3; ++a)
         if (first[a] < 0 || last[a] > (1 << 23)) p.fastTrunc = 0;
