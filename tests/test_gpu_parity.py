@@ -222,6 +222,29 @@ def test_range_ops_shifted_rows(gpu):
                 assert a.a.tobytes() == b.a.tobytes(), (fmt, sdims, "clamped")
 
 
+def test_range_ops_shifted_rows_wide(gpu):
+    """Rows wide enough for whole warps (the neighbour-lane exchange kernel): every byte phase between source and
+    destination rows, ranges that start inside the row and end on its last voxel, row counts that leave the last
+    pair of rows half empty, sources of different widths."""
+    o = po.oracle()
+    for fmt in (po.UINT8, po.UINT16, po.UINT32, po.FLOAT32):
+        s1, s2 = cases.mk((528, 5, 3), fmt, 1), cases.mk((544, 6, 3), fmt, 2)
+        for xo in range(0, 17):
+            for first, last in (((0, 0, 0), (528, 5, 3)), ((3, 1, 0), (528, 4, 3)), ((16, 0, 1), (509, 5, 2))):
+                a, b = cases.mk((560, 7, 4), fmt, 3), cases.mk((560, 7, 4), fmt, 3)
+                off = (xo, 2, 1)
+                o.arith_range(po.SAFESUM, a, s1, s2, first, last, off)
+                gpu.arith_range(po.SAFESUM, b, s1, s2, first, last, off)
+                assert same_bits(b.a, a.a), (fmt, first, last, off)
+    # long rows, several CTAs along x
+    s1, s2 = cases.mk((4112, 3, 2), po.UINT16, 1), cases.mk((4112, 3, 2), po.UINT16, 2)
+    for off in ((1, 0, 0), (5, 0, 0), (7, 0, 0)):
+        a, b = cases.mk((4128, 3, 2), po.UINT16, 3), cases.mk((4128, 3, 2), po.UINT16, 3)
+        o.arith_range(po.DIFF, a, s1, s2, (0, 0, 0), (4112, 3, 2), off)
+        gpu.arith_range(po.DIFF, b, s1, s2, (0, 0, 0), (4112, 3, 2), off)
+        assert same_bits(b.a, a.a), off
+
+
 def test_scan_kernels(gpu):
     """ScanRange (3-D prefix sum of the raw voxel integers): the catalogue's directions / offsets / in-place cases,
     then shapes that take the warp-per-row x pass and the 16-byte column walk (pitches multiples of 16 bytes), ranges

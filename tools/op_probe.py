@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg)"""
+"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg | sumrange | copyrange)"""
 import ctypes
 import math
 import os
@@ -29,6 +29,11 @@ def main():
         n = min(t.numel(), v.nbytes - off)
         capi.check(lib.vktb_memcpy(v.ptr + off, t.data_ptr(), n, capi.D2D))
     sd, dd = v.desc(), d.desc()
+    s2 = sd
+    if op == "sumrange":
+        v2 = DeviceVolume(dims, fmt)
+        capi.check(lib.vktb_memcpy(v2.ptr, v.ptr, v.nbytes, capi.D2D))
+        s2 = v2.desc()
     z, l = capi.I3(0, 0, 0), capi.I3(*dims)
     F9, F3 = ctypes.c_float * 9, ctypes.c_float * 3
     half = F3(dims[0] / 2, dims[1] / 2, dims[2] / 2)
@@ -41,6 +46,11 @@ def main():
                                                           F9(1 / 1.5, 0, 0, 0, 1 / 1.5, 0, 0, 0, 1 / 1.5), half)),
         "rotate": lambda: capi.check(lib.vktb_affine_range(ctypes.byref(dd), ctypes.byref(sd), z, l,
                                                            F9(cs, -sn, 0, sn, cs, 0, 0, 0, 1), half)),
+        # sources at another 16-byte phase than the destination rows
+        "sumrange": lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(sd), ctypes.byref(s2), z,
+                                                            capi.I3(dims[0] - 8, dims[1] - 8, dims[2] - 8), capi.I3(1, 2, 3))),
+        "copyrange": lambda: capi.check(lib.vktb_copy_range(ctypes.byref(dd), ctypes.byref(sd), capi.I3(1, 1, 1),
+                                                            capi.I3(dims[0] - 7, dims[1] - 7, dims[2] - 7), z)),
         "agg": lambda: capi.check(lib.vktb_aggregates_range(ctypes.byref(sd), z, l, ctypes.byref(agg))),
     }
     run = runs[op]

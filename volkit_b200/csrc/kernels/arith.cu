@@ -1,4 +1,5 @@
 // Arithmetic family launcher: picks flat / rows / generic kernels (see arith.cuh).
+#include <cstdlib>
 #include "arith.cuh"
 #include "launch.hpp"
 
@@ -52,7 +53,18 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
                           && (long long)q.g.ny * q.g.nz < 0x7fffffffLL;
         q.shifted = phase != (reinterpret_cast<uintptr_t>(q.a.base) & 15u)
                  || phase != (reinterpret_cast<uintptr_t>(q.b.base) & 15u);
-        if (uniform)
+        // neighbour-lane exchange needs whole warps inside one row and sources that dst does not overlap
+        static const bool exchange = [] { const char* e = getenv("VKTB_ARITH_EXCHANGE"); return !(e && e[0] == '0'); }();
+        if (uniform && q.shifted && !q.alias && l.block.x >= 32 && exchange) {
+            const long long S = (long long)l.grid.y * l.block.y, sz = S / q.g.ny, sy = S - sz * q.g.ny;
+            const Operand* ops[3] = { &q.d, &q.a, &q.b };
+            for (int i = 0; i < 3; ++i) {
+                q.step[i] = sy * ops[i]->pitchY + sz * ops[i]->pitchZ;
+                q.stepWrap[i] = q.step[i] + ops[i]->pitchZ - q.g.ny * ops[i]->pitchY;
+            }
+            q.sy = (int)sy;
+            arithRowsShiftedKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
+        } else if (uniform)
             arithRowsUniformKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
         else
             arithRowsKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p);

@@ -35,6 +35,10 @@ struct ArithParams
     const uint8_t* aEnd;  // one past the last byte of each source volume (bounds the funnel-shifted loads)
     const uint8_t* bEnd;
     int     shifted;      // uniform kernel: a source row sits at another 16-byte phase than the dst row
+    // exchange kernel: byte steps of the d / a / b row pointers for one stride of gridDim.y * blockDim.y rows, without
+    // and with a y overflow into the next plane (host-computed so that the loop adds constants)
+    long long step[3], stepWrap[3];
+    int     sy;
 };
 
 // Homogeneous formats: one 128-bit vector per operand per chunk.
@@ -265,6 +269,91 @@ arithRowsUniformKernel(ArithParams p, int shift)
                 storeRaw(dp + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
                                                                   p.md, p.ma, p.mb));
         });
+}
+
+// ---- rows in one 16-byte phase, sources at another phase: every lane loads ONE aligned vector per source and takes
+// the words it misses from the next lane (whose aligned vector they are); only lanes without such a neighbour
+// (warp end, row end) load the second vector themselves.  The kernel above reads two aligned vectors per source
+// instead and recomputes every row address; this one walks its three row pointers.  blockDim.x is a multiple of 32
+// (a warp lies in one row) and no lane leaves before the last row, so the shuffles run with the full mask.  No
+// operand aliases dst.
+__device__ __forceinline__ uint4 shflDown1(const uint4& v)
+{
+    return make_uint4(__shfl_down_sync(0xffffffffu, v.x, 1), __shfl_down_sync(0xffffffffu, v.y, 1),
+                      __shfl_down_sync(0xffffffffu, v.z, 1), __shfl_down_sync(0xffffffffu, v.w, 1));
+}
+
+// bytes [sh, sh + 16) of the 32 bytes lo | hi  (sh uniform, 1..15)
+__device__ __forceinline__ uint4 window16(const uint4& lo, const uint4& hi, unsigned sh)
+{
+    uint32_t w0 = lo.x, w1 = lo.y, w2 = lo.z, w3 = lo.w, w4 = hi.x, w5 = hi.y;
+    if (sh & 8u) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = hi.z; w5 = hi.w; }
+    if (sh & 4u) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; }
+    const unsigned bits = (sh & 3u) * 8u;
+    return make_uint4(__funnelshift_r(w0, w1, bits), __funnelshift_r(w1, w2, bits),
+                      __funnelshift_r(w2, w3, bits), __funnelshift_r(w3, w4, bits));
+}
+
+template <int F, int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithRowsShiftedKernel(ArithParams p, int shift)
+{
+    constexpr int BPV = bytesPerVoxel(F);
+    constexpr int V = 16 / BPV;
+    const int lane = threadIdx.x & 31;
+    const int chunk = blockIdx.x * blockDim.x + threadIdx.x;
+    int xr = chunk * V - shift, n = V;
+    if (xr < 0) { n += xr; xr = 0; }
+    if (xr + n > p.g.nx) n = p.g.nx - xr;
+    const bool full = n == V;
+    // the next lane holds the following full chunk of this row
+    const bool nextFull = full && lane < 31 && xr + 2 * V <= p.g.nx;
+    const long long xb = (long long)xr * BPV;
+    // phase of a full chunk's first source byte inside its aligned vector: the same for every row and chunk
+    const unsigned shA = (unsigned)((reinterpret_cast<uintptr_t>(p.a.base) + (uintptr_t)(16 - shift * BPV)) & 15u);
+    const unsigned shB = (unsigned)((reinterpret_cast<uintptr_t>(p.b.base) + (uintptr_t)(16 - shift * BPV)) & 15u);
+    const unsigned rows = (unsigned)p.g.ny * (unsigned)p.g.nz;
+    const unsigned S = gridDim.y * blockDim.y;
+    unsigned r = blockIdx.y * blockDim.y + threadIdx.y;
+    if (r >= rows) return;                         // whole warps: threadIdx.y is warp-uniform
+    int z = (int)(r / (unsigned)p.g.ny), y = (int)(r - (unsigned)z * (unsigned)p.g.ny);
+    // row pointers walk by S rows; a y overflow moves them to the next plane
+    const uint8_t* pa = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + xb - (full ? (long long)shA : 0);
+    const uint8_t* pb = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + xb - (full ? (long long)shB : 0);
+    uint8_t* pd = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + xb;
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    for (; r < rows; r += S) {
+        uint4 la = zero, lb = zero;
+        if (full) { la = ldStream(pa); lb = ldStream(pb); }
+        uint4 qa = la, qb = lb;
+        if (shA != 0u) {
+            uint4 ha = shflDown1(la);
+            if (full && !nextFull) ha = ldStream(pa + 16);
+            qa = window16(la, ha, shA);
+        }
+        if (shB != 0u) {
+            uint4 hb = shflDown1(lb);
+            if (full && !nextFull) hb = ldStream(pb + 16);
+            qb = window16(lb, hb, shB);
+        }
+        if (full) {
+            uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+                vecSet<BPV>(w, i, arithOne<F, OP, IDENT>(vecGet<BPV>(qa, i), vecGet<BPV>(qb, i), p.md, p.ma, p.mb));
+            stStream(pd, make_uint4(w[0], w[1], w[2], w[3]));
+        } else {
+            for (int i = 0; i < n; ++i)
+                storeRaw(pd + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(pa + i * BPV, BPV), loadRaw(pb + i * BPV, BPV),
+                                                                  p.md, p.ma, p.mb));
+        }
+        y += p.sy;
+        const bool wrap = y >= p.g.ny;
+        if (wrap) y -= p.g.ny;
+        pd += wrap ? p.stepWrap[0] : p.step[0];
+        pa += wrap ? p.stepWrap[1] : p.step[1];
+        pb += wrap ? p.stepWrap[2] : p.step[2];
+    }
 }
 
 // ---- generic: any mix of formats (runtime codec), one voxel per thread along x ---------------------------
