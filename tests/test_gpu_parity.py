@@ -130,6 +130,22 @@ def test_arith_u8_pair_table_stream(gpu):
     assert a.a.tobytes() == b.a.tobytes()
 
 
+def test_arith_u8_pair_table_rows(gpu):
+    """UInt8 *Range calls of >= 2^24 voxels on rows in one 16-byte phase take the pair-table rows kernel: sources at
+    the dst phase and off it, partial head / tail chunks, two mappings, a range that ends on the volume's last voxel."""
+    o = po.oracle()
+    sd, dd = (528, 200, 170), (560, 204, 172)
+    s1, s2 = cases.mk(sd, po.UINT8, 1), cases.mk(sd, po.UINT8, 2, -1000.0, 3000.0)
+    for k, (first, last, off) in enumerate((((0, 0, 0), sd, (16, 2, 1)), ((0, 0, 0), sd, (3, 1, 2)),
+                                            ((5, 1, 0), sd, (0, 0, 0)), ((0, 0, 0), (523, 200, 170), (37, 4, 2)))):
+        for op in (po.SAFESUM, po.PROD, po.SAFEABSDIFF)[k % 2:][:2]:
+            lo, hi = ((0.0, 1.0), (-1000.0, 3000.0))[k % 2]
+            a, b = cases.mk(dd, po.UINT8, 3, lo, hi), cases.mk(dd, po.UINT8, 3, lo, hi)
+            o.arith_range(op, a, s1, s2, first, last, off)
+            gpu.arith_range(op, b, s1, s2, first, last, off)
+            assert a.a.tobytes() == b.a.tobytes(), (first, last, off, op)
+
+
 def test_arith_u16_edge_pairs(gpu):
     """2^16-stride sweep + all edge pairs of UInt16 x UInt16 for each op."""
     o = po.oracle()
@@ -236,6 +252,10 @@ def test_range_ops_shifted_rows_wide(gpu):
                 o.arith_range(po.SAFESUM, a, s1, s2, first, last, off)
                 gpu.arith_range(po.SAFESUM, b, s1, s2, first, last, off)
                 assert same_bits(b.a, a.a), (fmt, first, last, off)
+                a, b = cases.mk((560, 7, 4), fmt, 3), cases.mk((560, 7, 4), fmt, 3)
+                o.copy_range(a, s1, first, last, off)
+                gpu.copy_range(b, s1, first, last, off)
+                assert a.a.tobytes() == b.a.tobytes(), (fmt, first, last, off, "copy")
     # long rows, several CTAs along x
     s1, s2 = cases.mk((4112, 3, 2), po.UINT16, 1), cases.mk((4112, 3, 2), po.UINT16, 2)
     for off in ((1, 0, 0), (5, 0, 0), (7, 0, 0)):
@@ -243,6 +263,30 @@ def test_range_ops_shifted_rows_wide(gpu):
         o.arith_range(po.DIFF, a, s1, s2, (0, 0, 0), (4112, 3, 2), off)
         gpu.arith_range(po.DIFF, b, s1, s2, (0, 0, 0), (4112, 3, 2), off)
         assert same_bits(b.a, a.a), off
+        a, b = cases.mk((4128, 3, 2), po.UINT16, 3), cases.mk((4128, 3, 2), po.UINT16, 3)
+        o.copy_range(a, s1, (0, 0, 0), (4112, 3, 2), off)
+        gpu.copy_range(b, s1, (0, 0, 0), (4112, 3, 2), off)
+        assert a.a.tobytes() == b.a.tobytes(), (off, "copy")
+
+
+def test_range_ops_walking_rows(gpu, monkeypatch):
+    """The row kernels with a small grid (VKTB_MAX_GRID_Y): every thread walks many rows, its row pointers cross
+    plane boundaries (y overflow) several times, and the two-rows-in-flight pipeline drains on a half-empty pair."""
+    o = po.oracle()
+    for cap in ("3", "7"):
+        monkeypatch.setenv("VKTB_MAX_GRID_Y", cap)
+        for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+            s1, s2 = cases.mk((272, 37, 29), fmt, 1), cases.mk((272, 37, 29), fmt, 2)
+            for first, last, off in (((1, 2, 0), (270, 37, 29), (4, 1, 2)), ((0, 0, 0), (272, 37, 29), (0, 3, 1)),
+                                     ((0, 0, 3), (272, 36, 28), (9, 0, 0))):
+                a, b = cases.mk((288, 40, 31), fmt, 3), cases.mk((288, 40, 31), fmt, 3)
+                o.arith_range(po.SAFEDIFF, a, s1, s2, first, last, off)
+                gpu.arith_range(po.SAFEDIFF, b, s1, s2, first, last, off)
+                assert same_bits(b.a, a.a), (cap, fmt, first, last, off)
+                a, b = cases.mk((288, 40, 31), fmt, 3), cases.mk((288, 40, 31), fmt, 3)
+                o.copy_range(a, s1, first, last, off)
+                gpu.copy_range(b, s1, first, last, off)
+                assert a.a.tobytes() == b.a.tobytes(), (cap, fmt, first, last, off, "copy")
 
 
 def test_scan_kernels(gpu):

@@ -53,6 +53,23 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
                           && (long long)q.g.ny * q.g.nz < 0x7fffffffLL;
         q.shifted = phase != (reinterpret_cast<uintptr_t>(q.a.base) & 15u)
                  || phase != (reinterpret_cast<uintptr_t>(q.b.base) & 15u);
+        if constexpr (F == F_U8) {
+            // big UInt8 ranges: one pair-table byte per voxel instead of ~12 arithmetic instructions
+            const unsigned long long cpr = (unsigned long long)((q.g.nx + 15) / 16 + 1);
+            const unsigned long long items = (unsigned long long)q.g.ny * q.g.nz * cpr;
+            if (uniform && pl.n >= kPairTableMinVoxels && items < 0x7fffffffULL) {
+                PairRows w;
+                w.items = (unsigned)items; w.cpr = (unsigned)cpr;
+                magicDivisor((unsigned)cpr, w.mulC, w.shC);
+                magicDivisor((unsigned)q.g.ny, w.mulY, w.shY);
+                auto kern = arithRowsPairTableKernel<OP, IDENT>;
+                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPairTableBytes);
+                if (e != cudaSuccess) return e;
+                kern<<<(unsigned)c.smCount * 3u, kThreads, kPairTableBytes, c.stream>>>(q, (int)phase, w);
+                countLaunch();
+                return cudaGetLastError();
+            }
+        }
         // neighbour-lane exchange needs whole warps inside one row and sources that dst does not overlap
         static const bool exchange = [] { const char* e = getenv("VKTB_ARITH_EXCHANGE"); return !(e && e[0] == '0'); }();
         if (uniform && q.shifted && !q.alias && l.block.x >= 32 && exchange) {

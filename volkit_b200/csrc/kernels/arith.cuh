@@ -203,6 +203,89 @@ arithPairTableKernel(uint8_t* __restrict__ d, const uint8_t* a, const uint8_t* b
     }
 }
 
+// ---- rows, UInt8 x UInt8 -> UInt8 through the same pair table: *Range calls on big UInt8 volumes ------------------
+// Rows of every operand in one 16-byte phase (pitches multiples of 16 bytes).  Work items are (row, dst-aligned 16-byte
+// chunk) pairs in row-major order over a persistent grid, two in flight per thread; row and chunk come from the item
+// number by two multiply-shift divisions (host-computed magic numbers, items < 2^31).  Sources at another phase than
+// dst use the funnel-shifted loads.  The arithmetic kernels spend ~12 instructions per voxel, which caps UInt8 at
+// about half of the HBM roofline; one table byte per voxel does not.
+struct PairRows
+{
+    unsigned items, cpr;          // rows * cpr work items, cpr chunks per row
+    unsigned mulC, mulY;          // item / cpr and row / ny as (x * mul) >> sh
+    int shC, shY;
+};
+
+template <int OP, bool IDENT>
+__global__ void __launch_bounds__(kThreads)
+arithRowsPairTableKernel(ArithParams p, int shift, PairRows w)
+{
+    extern __shared__ __align__(16) uint8_t pairTab[];
+    __shared__ float lutB[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) lutB[i] = unmapVoxel<F_U8, IDENT>((uint32_t)i, p.mb);
+    __syncthreads();
+    {   // thread t builds row a = t (blockDim.x == 256), word order rotated per thread: conflict-free stores
+        const float fa = unmapVoxel<F_U8, IDENT>((uint32_t)threadIdx.x, p.ma);
+        uint32_t* row = reinterpret_cast<uint32_t*>(pairTab + threadIdx.x * 256);
+        for (int q = 0; q < 64; ++q) {
+            const int ww = (q + threadIdx.x) & 63;
+            uint32_t word = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                word |= (mapVoxel<F_U8, IDENT>(arithEval<OP>(fa, lutB[ww * 4 + k], p.md.lo, p.md.hi), p.md) & 0xffu) << (8 * k);
+            row[ww] = word;
+        }
+    }
+    __syncthreads();
+
+    struct Item { uint8_t* d; const uint8_t* a; const uint8_t* b; int n; uint4 va, vb; };
+    auto fetch = [&](unsigned item) {
+        Item it;
+        const unsigned r = (unsigned)(((unsigned long long)item * w.mulC) >> w.shC), c = item - r * w.cpr;
+        const unsigned z = (unsigned)(((unsigned long long)r * w.mulY) >> w.shY), y = r - z * (unsigned)p.g.ny;
+        int xr = (int)c * 16 - shift, n = 16;
+        if (xr < 0) { n += xr; xr = 0; }
+        if (xr + n > p.g.nx) n = p.g.nx - xr;
+        it.n = n;
+        it.d = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + xr;
+        it.a = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + xr;
+        it.b = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + xr;
+        it.va = it.vb = make_uint4(0u, 0u, 0u, 0u);
+        if (n == 16) {
+            if (p.shifted)    { it.va = ldUnalignedWithin(it.a, p.aEnd, p.alias); it.vb = ldUnalignedWithin(it.b, p.bEnd, p.alias); }
+            else if (p.alias) { it.va = ldPlain(it.a); it.vb = ldPlain(it.b); }
+            else              { it.va = ldStream(it.a); it.vb = ldStream(it.b); }
+        }
+        return it;
+    };
+    auto finish = [&](const Item& it) {
+        if (it.n == 16) {
+            const uint32_t wa[4] = { it.va.x, it.va.y, it.va.z, it.va.w }, wb[4] = { it.vb.x, it.vb.y, it.vb.z, it.vb.w };
+            uint32_t o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t r = 0u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t ia = (wa[q] >> (8 * k)) & 0xffu, ib = (wb[q] >> (8 * k)) & 0xffu;
+                    r |= (uint32_t)pairTab[ia * 256u + ib] << (8 * k);
+                }
+                o[q] = r;
+            }
+            stStream(it.d, make_uint4(o[0], o[1], o[2], o[3]));
+        } else {
+            for (int i = 0; i < it.n; ++i) it.d[i] = pairTab[(uint32_t)it.a[i] * 256u + it.b[i]];
+        }
+    };
+    const unsigned stride = gridDim.x * blockDim.x;
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (; (unsigned long long)i + stride < w.items; i += 2 * stride) {
+        const Item i0 = fetch(i), i1 = fetch(i + stride);
+        finish(i0); finish(i1);
+    }
+    if (i < w.items) finish(fetch(i));
+}
+
 // ---- rows: general 3-D range with dstOffset; chunks are cut at 16-byte boundaries of the dst row --------
 template <int F, int OP, bool IDENT>
 __global__ void __launch_bounds__(kThreads)
@@ -277,23 +360,6 @@ arithRowsUniformKernel(ArithParams p, int shift)
 // instead and recomputes every row address; this one walks its three row pointers.  blockDim.x is a multiple of 32
 // (a warp lies in one row) and no lane leaves before the last row, so the shuffles run with the full mask.  No
 // operand aliases dst.
-__device__ __forceinline__ uint4 shflDown1(const uint4& v)
-{
-    return make_uint4(__shfl_down_sync(0xffffffffu, v.x, 1), __shfl_down_sync(0xffffffffu, v.y, 1),
-                      __shfl_down_sync(0xffffffffu, v.z, 1), __shfl_down_sync(0xffffffffu, v.w, 1));
-}
-
-// bytes [sh, sh + 16) of the 32 bytes lo | hi  (sh uniform, 1..15)
-__device__ __forceinline__ uint4 window16(const uint4& lo, const uint4& hi, unsigned sh)
-{
-    uint32_t w0 = lo.x, w1 = lo.y, w2 = lo.z, w3 = lo.w, w4 = hi.x, w5 = hi.y;
-    if (sh & 8u) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = hi.z; w5 = hi.w; }
-    if (sh & 4u) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; }
-    const unsigned bits = (sh & 3u) * 8u;
-    return make_uint4(__funnelshift_r(w0, w1, bits), __funnelshift_r(w1, w2, bits),
-                      __funnelshift_r(w2, w3, bits), __funnelshift_r(w3, w4, bits));
-}
-
 template <int F, int OP, bool IDENT>
 __global__ void __launch_bounds__(kThreads)
 arithRowsShiftedKernel(ArithParams p, int shift)
@@ -308,6 +374,7 @@ arithRowsShiftedKernel(ArithParams p, int shift)
     const bool full = n == V;
     // the next lane holds the following full chunk of this row
     const bool nextFull = full && lane < 31 && xr + 2 * V <= p.g.nx;
+    const bool selfHi = full && !nextFull;
     const long long xb = (long long)xr * BPV;
     // phase of a full chunk's first source byte inside its aligned vector: the same for every row and chunk
     const unsigned shA = (unsigned)((reinterpret_cast<uintptr_t>(p.a.base) + (uintptr_t)(16 - shift * BPV)) & 15u);
@@ -323,18 +390,21 @@ arithRowsShiftedKernel(ArithParams p, int shift)
     uint8_t* pd = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + xb;
     const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
     for (; r < rows; r += S) {
-        uint4 la = zero, lb = zero;
+        // all loads of the row up front: the lanes without a neighbour fetch their second vectors now, not after the
+        // shuffles (a dependent load there would stall the whole warp for one more memory latency).  Issuing the next
+        // row's loads before this row is worked on was measured too: UInt16 unchanged, UInt8 19.1 -> 23.3 ms.
+        uint4 la = zero, lb = zero, sa = zero, sb = zero;
         if (full) { la = ldStream(pa); lb = ldStream(pb); }
+        if (selfHi && shA != 0u) sa = ldStream(pa + 16);
+        if (selfHi && shB != 0u) sb = ldStream(pb + 16);
         uint4 qa = la, qb = lb;
         if (shA != 0u) {
-            uint4 ha = shflDown1(la);
-            if (full && !nextFull) ha = ldStream(pa + 16);
-            qa = window16(la, ha, shA);
+            const uint4 ha = shflDown1(la);
+            qa = window16(la, nextFull ? ha : sa, shA);
         }
         if (shB != 0u) {
-            uint4 hb = shflDown1(lb);
-            if (full && !nextFull) hb = ldStream(pb + 16);
-            qb = window16(lb, hb, shB);
+            const uint4 hb = shflDown1(lb);
+            qb = window16(lb, nextFull ? hb : sb, shB);
         }
         if (full) {
             uint32_t w[4] = { 0u, 0u, 0u, 0u };

@@ -5,6 +5,7 @@
 // the SM count.  No tensor cores anywhere.
 #pragma once
 
+#include <cstdlib>
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -67,6 +68,25 @@ __device__ __forceinline__ uint4 ldUnalignedWithin(const uint8_t* p, const uint8
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+// neighbour-lane exchange (arithRowsShiftedKernel): the next lane's vector, and the 16
+// bytes at phase sh of two consecutive vectors
+__device__ __forceinline__ uint4 shflDown1(const uint4& v)
+{
+    return make_uint4(__shfl_down_sync(0xffffffffu, v.x, 1), __shfl_down_sync(0xffffffffu, v.y, 1),
+                      __shfl_down_sync(0xffffffffu, v.z, 1), __shfl_down_sync(0xffffffffu, v.w, 1));
+}
+
+// bytes [sh, sh + 16) of the 32 bytes lo | hi  (sh uniform, 1..15)
+__device__ __forceinline__ uint4 window16(const uint4& lo, const uint4& hi, unsigned sh)
+{
+    uint32_t w0 = lo.x, w1 = lo.y, w2 = lo.z, w3 = lo.w, w4 = hi.x, w5 = hi.y;
+    if (sh & 8u) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = hi.z; w5 = hi.w; }
+    if (sh & 4u) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; }
+    const unsigned bits = (sh & 3u) * 8u;
+    return make_uint4(__funnelshift_r(w0, w1, bits), __funnelshift_r(w1, w2, bits),
+                      __funnelshift_r(w2, w3, bits), __funnelshift_r(w3, w4, bits));
+}
+
 __device__ __forceinline__ void stStream32(void* p, uint32_t v)
 {
     asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -119,7 +139,10 @@ inline RowsLaunch rowsLaunch(int nx, long long rows, int vecElems)
     RowsLaunch l;
     l.block = dim3(tx, ty, 1);
     long long gy = (rows + ty - 1) / ty;
-    if (gy > 65535) gy = 65535;
+    // VKTB_MAX_GRID_Y (tests): a small cap makes every thread walk many rows on volumes the oracle finishes quickly
+    const char* e = getenv("VKTB_MAX_GRID_Y");
+    const long long v = e ? atoll(e) : 0, cap = v >= 1 && v <= 65535 ? v : 65535LL;
+    if (gy > cap) gy = cap;
     l.grid = dim3((chunks + tx - 1) / tx, (unsigned)gy, 1);
     return l;
 }
@@ -196,6 +219,16 @@ __device__ __forceinline__ void forEachRowChunkUniform(const Range& g, int shift
     }
 }
 
+// floor(e / d) for e < 2^31 as one widening multiply and a shift: m = ceil(2^(31+l) / d), l = ceil(log2 d).
+// The error e*r/(d*2^(31+l)) stays below 2^-l <= 1/d, so the floor never moves.
+inline void magicDivisor(unsigned d, unsigned& mul, int& sh)
+{
+    int l = 0;
+    while ((1ull << l) < d) ++l;
+    const unsigned long long p = 1ull << (31 + l);
+    mul = (unsigned)((p + d - 1) / d);
+    sh = 31 + l;
+}
 // Grid for flat (1-D) streaming kernels: enough CTAs to fill every SM several times over, capped so the
 // grid-stride loop amortises the launch; always a multiple of the SM count.
 inline unsigned flatGrid(size_t work, int perCta, int smCount, int ctasPerSm)

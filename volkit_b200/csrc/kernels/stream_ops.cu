@@ -3,6 +3,7 @@
 // Fill     reference src/vkt/Fill_serial.hpp:20-26      vol[p] = map(value), p in [first,last)       bpv B/voxel
 // Copy     reference src/vkt/Copy_serial.hpp:13-82      dst[p-first+off] = src[clamp(p)]             2 bpv (or bpv_s+bpv_d)
 // Memset   reference src/vkt/Memory_cuda.cu:15-49       dst[i*pat .. ] = pattern                     dstBytes
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -182,16 +183,6 @@ struct BoxRec
     int shX, shY;
 };
 
-// floor(e / d) for e < 2^31 as one widening multiply and a shift: m = ceil(2^(31+l) / d), l = ceil(log2 d).
-// The error e*r/(d*2^(31+l)) stays below 2^-l <= 1/d, so the floor never moves.
-inline void magicDivisor(unsigned d, unsigned& mul, int& sh)
-{
-    int l = 0;
-    while ((1ull << l) < d) ++l;
-    const unsigned long long p = 1ull << (31 + l);
-    mul = (unsigned)((p + d - 1) / d);
-    sh = 31 + l;
-}
 __device__ __forceinline__ unsigned magicDiv(unsigned e, unsigned mul, int sh)
 {
     return (unsigned)(((unsigned long long)e * mul) >> sh);
