@@ -238,7 +238,15 @@ arithRowsPairTableKernel(ArithParams p, int shift, PairRows w)
     }
     __syncthreads();
 
-    struct Item { uint8_t* d; const uint8_t* a; const uint8_t* b; int n; uint4 va, vb; };
+    // phase of a full chunk's first source byte inside its aligned vector: the same for every row and chunk
+    const unsigned shA = (unsigned)((reinterpret_cast<uintptr_t>(p.a.base) + (uintptr_t)(16 - shift)) & 15u);
+    const unsigned shB = (unsigned)((reinterpret_cast<uintptr_t>(p.b.base) + (uintptr_t)(16 - shift)) & 15u);
+    // fetch() only issues loads (the aligned vectors around the chunk); the funnel shifts wait until finish(), so the
+    // loads of both items in flight go out back to back.  bytewise: the one chunk whose second vector would leave
+    // the source buffer.
+    struct Item { uint8_t* d; const uint8_t* a; const uint8_t* b; int n; bool bytewise; uint4 la, ha, lb, hb; };
+    // through L1: a lane's second vector is the next lane's first
+    auto ld16 = [&](const uint8_t* q) { return p.alias ? ldPlain(q) : __ldg(reinterpret_cast<const uint4*>(q)); };
     auto fetch = [&](unsigned item) {
         Item it;
         const unsigned r = (unsigned)(((unsigned long long)item * w.mulC) >> w.shC), c = item - r * w.cpr;
@@ -250,17 +258,20 @@ arithRowsPairTableKernel(ArithParams p, int shift, PairRows w)
         it.d = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + xr;
         it.a = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + xr;
         it.b = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + xr;
-        it.va = it.vb = make_uint4(0u, 0u, 0u, 0u);
-        if (n == 16) {
-            if (p.shifted)    { it.va = ldUnalignedWithin(it.a, p.aEnd, p.alias); it.vb = ldUnalignedWithin(it.b, p.bEnd, p.alias); }
-            else if (p.alias) { it.va = ldPlain(it.a); it.vb = ldPlain(it.b); }
-            else              { it.va = ldStream(it.a); it.vb = ldStream(it.b); }
+        it.la = it.ha = it.lb = it.hb = make_uint4(0u, 0u, 0u, 0u);
+        it.bytewise = n == 16 && !(unalignedReadable(it.a, p.aEnd) && unalignedReadable(it.b, p.bEnd));
+        if (n == 16 && !it.bytewise) {
+            it.la = ld16(it.a - shA); it.lb = ld16(it.b - shB);
+            if (shA != 0u) it.ha = ld16(it.a - shA + 16);
+            if (shB != 0u) it.hb = ld16(it.b - shB + 16);
         }
         return it;
     };
     auto finish = [&](const Item& it) {
-        if (it.n == 16) {
-            const uint32_t wa[4] = { it.va.x, it.va.y, it.va.z, it.va.w }, wb[4] = { it.vb.x, it.vb.y, it.vb.z, it.vb.w };
+        if (it.n == 16 && !it.bytewise) {
+            const uint4 va = shA != 0u ? window16(it.la, it.ha, shA) : it.la;
+            const uint4 vb = shB != 0u ? window16(it.lb, it.hb, shB) : it.lb;
+            const uint32_t wa[4] = { va.x, va.y, va.z, va.w }, wb[4] = { vb.x, vb.y, vb.z, vb.w };
             uint32_t o[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
