@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg | sumrange | copyrange)"""
+"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg | sumrange | sumrange8 | copyrange)"""
 import ctypes
 import math
 import os
@@ -30,7 +30,7 @@ def main():
         capi.check(lib.vktb_memcpy(v.ptr + off, t.data_ptr(), n, capi.D2D))
     sd, dd = v.desc(), d.desc()
     s2 = sd
-    if op == "sumrange":
+    if op.startswith("sumrange"):
         v2 = DeviceVolume(dims, fmt)
         capi.check(lib.vktb_memcpy(v2.ptr, v.ptr, v.nbytes, capi.D2D))
         s2 = v2.desc()
@@ -49,6 +49,8 @@ def main():
         # sources at another 16-byte phase than the destination rows
         "sumrange": lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(sd), ctypes.byref(s2), z,
                                                             capi.I3(dims[0] - 8, dims[1] - 8, dims[2] - 8), capi.I3(1, 2, 3))),
+        "sumrange8": lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(sd), ctypes.byref(s2), z,
+                                                             capi.I3(dims[0] - 8, dims[1] - 8, dims[2] - 8), capi.I3(8, 8, 8))),
         "copyrange": lambda: capi.check(lib.vktb_copy_range(ctypes.byref(dd), ctypes.byref(sd), capi.I3(1, 1, 1),
                                                             capi.I3(dims[0] - 7, dims[1] - 7, dims[2] - 7), z)),
         "agg": lambda: capi.check(lib.vktb_aggregates_range(ctypes.byref(sd), z, l, ctypes.byref(agg))),
