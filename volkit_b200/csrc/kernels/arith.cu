@@ -72,8 +72,7 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
         }
         // neighbour-lane exchange needs whole warps inside one row and sources that dst does not overlap
         static const bool exchange = [] { const char* e = getenv("VKTB_ARITH_EXCHANGE"); return !(e && e[0] == '0'); }();
-        static const bool walkAligned = [] { const char* e = getenv("VKTB_ARITH_WALK_ALIGNED"); return e && e[0] == '1'; }();
-        if (uniform && (q.shifted || walkAligned) && !q.alias && l.block.x >= 32 && exchange) {
+        if (uniform && q.shifted && !q.alias && l.block.x >= 32 && exchange) {
             const long long S = (long long)l.grid.y * l.block.y, sz = S / q.g.ny, sy = S - sz * q.g.ny;
             const Operand* ops[3] = { &q.d, &q.a, &q.b };
             for (int i = 0; i < 3; ++i) {
