@@ -154,17 +154,41 @@ copyRowsUniformKernel(CopyParams p, int shift)
     constexpr int V = 16 / BPV;
     const uint8_t* s0 = p.s + (((long long)p.g.z0 * p.sy + p.g.y0) * (long long)p.sx + p.g.x0) * BPV;
     const long long spy = (long long)p.sx * BPV, spz = spy * p.sy;
-    forEachRowChunkUniform<V, 4, uint4>(p.g, shift,
+    auto edge = [&](int y, int z, int xr, int n) {
+        const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
+        uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+        for (int i = 0; i < n; ++i) storeRaw(dp + i * BPV, BPV, loadRaw(sp + i * BPV, BPV));
+    };
+    if (!p.shifted) {
+        forEachRowChunkUniform<V, 4, uint4>(p.g, shift,
+            [&](int y, int z, int xr) { return ldStream(s0 + y * spy + z * spz + (long long)xr * BPV); },
+            [&](int y, int z, int xr, const uint4& q) { stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, q); },
+            edge);
+        return;
+    }
+    // shifted: the load step only issues the two aligned vectors around the chunk (through L1: a lane's second vector
+    // is the next lane's first); the funnel shift waits for the store step, so the loads of all four rows in flight go
+    // out back to back.  The one chunk whose second vector would leave the source buffer is copied per voxel.
+    struct Pair { uint4 lo, hi; };
+    const unsigned sh = (unsigned)((reinterpret_cast<uintptr_t>(s0) + (uintptr_t)(16 - shift * BPV)) & 15u);   // != 0
+    forEachRowChunkUniform<V, 4, Pair>(p.g, shift,
         [&](int y, int z, int xr) {
             const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
-            return p.shifted ? ldUnalignedWithin(sp, p.sEnd) : ldStream(sp);
+            Pair q;
+            q.lo = q.hi = make_uint4(0u, 0u, 0u, 0u);
+            if (unalignedReadable(sp, p.sEnd)) {
+                const uint4* v = reinterpret_cast<const uint4*>(sp - sh);
+                q.lo = __ldg(v); q.hi = __ldg(v + 1);
+            }
+            return q;
         },
-        [&](int y, int z, int xr, const uint4& q) { stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, q); },
-        [&](int y, int z, int xr, int n) {
+        [&](int y, int z, int xr, const Pair& q) {
             const uint8_t* sp = s0 + y * spy + z * spz + (long long)xr * BPV;
-            uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
-            for (int i = 0; i < n; ++i) storeRaw(dp + i * BPV, BPV, loadRaw(sp + i * BPV, BPV));
-        });
+            if (unalignedReadable(sp, p.sEnd))
+                stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, window16(q.lo, q.hi, sh));
+            else edge(y, z, xr, V);
+        },
+        edge);
 }
 
 // ---------------------------------------------------------------- Copy, many boxes of one source -----------
