@@ -338,31 +338,63 @@ arithRowsUniformKernel(ArithParams p, int shift)
 {
     constexpr int BPV = bytesPerVoxel(F);
     constexpr int V = 16 / BPV;
-    forEachRowChunkUniform<V, 2, ArithPair>(p.g, shift,
+    auto emit = [&](int y, int z, int xr, const uint4& va, const uint4& vb) {
+        uint32_t w[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+        for (int i = 0; i < V; ++i)
+            vecSet<BPV>(w, i, arithOne<F, OP, IDENT>(vecGet<BPV>(va, i), vecGet<BPV>(vb, i), p.md, p.ma, p.mb));
+        stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, make_uint4(w[0], w[1], w[2], w[3]));
+    };
+    auto edge = [&](int y, int z, int xr, int n) {
+        uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+        const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
+        const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
+        for (int i = 0; i < n; ++i)
+            storeRaw(dp + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
+                                                              p.md, p.ma, p.mb));
+    };
+    if (!p.shifted) {
+        forEachRowChunkUniform<V, 2, ArithPair>(p.g, shift,
+            [&](int y, int z, int xr) {
+                const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
+                const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
+                ArithPair q;
+                if (p.alias) { q.a = ldPlain(ap); q.b = ldPlain(bp); }
+                else         { q.a = ldStream(ap); q.b = ldStream(bp); }
+                return q;
+            },
+            [&](int y, int z, int xr, const ArithPair& q) { emit(y, z, xr, q.a, q.b); },
+            edge);
+        return;
+    }
+    // a source at another phase than dst: the load step only issues the aligned vectors around the chunk (through L1:
+    // a lane's second vector is the next lane's first), the funnel shifts wait for the store step, so the loads of both
+    // rows in flight go out back to back.  The one chunk whose second vector would leave a source buffer runs per voxel.
+    struct Quad { uint4 la, ha, lb, hb; };
+    const unsigned shA = (unsigned)((reinterpret_cast<uintptr_t>(p.a.base) + (uintptr_t)(16 - shift * BPV)) & 15u);
+    const unsigned shB = (unsigned)((reinterpret_cast<uintptr_t>(p.b.base) + (uintptr_t)(16 - shift * BPV)) & 15u);
+    auto ld16 = [&](const uint8_t* q) { return p.alias ? ldPlain(q) : __ldg(reinterpret_cast<const uint4*>(q)); };
+    forEachRowChunkUniform<V, 2, Quad>(p.g, shift,
         [&](int y, int z, int xr) {
             const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
             const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
-            ArithPair q;
-            if (p.shifted)    { q.a = ldUnalignedWithin(ap, p.aEnd, p.alias); q.b = ldUnalignedWithin(bp, p.bEnd, p.alias); }
-            else if (p.alias) { q.a = ldPlain(ap); q.b = ldPlain(bp); }
-            else         { q.a = ldStream(ap); q.b = ldStream(bp); }
+            Quad q;
+            q.la = q.ha = q.lb = q.hb = make_uint4(0u, 0u, 0u, 0u);
+            if (unalignedReadable(ap, p.aEnd) && unalignedReadable(bp, p.bEnd)) {
+                q.la = ld16(ap - shA); q.lb = ld16(bp - shB);
+                if (shA != 0u) q.ha = ld16(ap - shA + 16);
+                if (shB != 0u) q.hb = ld16(bp - shB + 16);
+            }
             return q;
         },
-        [&](int y, int z, int xr, const ArithPair& q) {
-            uint32_t w[4] = { 0u, 0u, 0u, 0u };
-#pragma unroll
-            for (int i = 0; i < V; ++i)
-                vecSet<BPV>(w, i, arithOne<F, OP, IDENT>(vecGet<BPV>(q.a, i), vecGet<BPV>(q.b, i), p.md, p.ma, p.mb));
-            stStream(p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV, make_uint4(w[0], w[1], w[2], w[3]));
-        },
-        [&](int y, int z, int xr, int n) {
-            uint8_t* dp = p.d.base + y * p.d.pitchY + z * p.d.pitchZ + (long long)xr * BPV;
+        [&](int y, int z, int xr, const Quad& q) {
             const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
             const uint8_t* bp = p.b.base + y * p.b.pitchY + z * p.b.pitchZ + (long long)xr * BPV;
-            for (int i = 0; i < n; ++i)
-                storeRaw(dp + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
-                                                                  p.md, p.ma, p.mb));
-        });
+            if (unalignedReadable(ap, p.aEnd) && unalignedReadable(bp, p.bEnd))
+                emit(y, z, xr, shA != 0u ? window16(q.la, q.ha, shA) : q.la, shB != 0u ? window16(q.lb, q.hb, shB) : q.lb);
+            else edge(y, z, xr, V);
+        },
+        edge);
 }
 
 // ---- rows in one 16-byte phase, sources at another phase: every lane loads ONE aligned vector per source and takes
