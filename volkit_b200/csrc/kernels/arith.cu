@@ -82,7 +82,8 @@ cudaError_t launchHomogeneous(const LaunchCtx& c, const ArithPlan& pl)
             q.sy = (int)sy;
             arithRowsShiftedKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
         } else if (uniform)
-            arithRowsUniformKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
+            (q.shifted ? arithRowsUniformKernel<F, OP, IDENT, true> : arithRowsUniformKernel<F, OP, IDENT, false>)
+                <<<l.grid, l.block, 0, c.stream>>>(q, (int)(phase / bytesPerVoxel(F)));
         else
             arithRowsKernel<F, OP, IDENT><<<l.grid, l.block, 0, c.stream>>>(pl.p);
     }

@@ -332,7 +332,7 @@ arithRowsKernel(ArithParams p)
 // ---- rows, every row of all three operands in the same 16-byte phase: two rows (four loads) in flight ----
 struct ArithPair { uint4 a, b; };
 
-template <int F, int OP, bool IDENT>
+template <int F, int OP, bool IDENT, bool SHIFTED>
 __global__ void __launch_bounds__(kThreads)
 arithRowsUniformKernel(ArithParams p, int shift)
 {
@@ -353,7 +353,7 @@ arithRowsUniformKernel(ArithParams p, int shift)
             storeRaw(dp + i * BPV, BPV, arithOne<F, OP, IDENT>(loadRaw(ap + i * BPV, BPV), loadRaw(bp + i * BPV, BPV),
                                                               p.md, p.ma, p.mb));
     };
-    if (!p.shifted) {
+    if (!SHIFTED) {     // a template parameter: the aligned kernel keeps its 64 registers (4 CTAs per SM)
         forEachRowChunkUniform<V, 2, ArithPair>(p.g, shift,
             [&](int y, int z, int xr) {
                 const uint8_t* ap = p.a.base + y * p.a.pitchY + z * p.a.pitchZ + (long long)xr * BPV;
