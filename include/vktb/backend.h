@@ -98,7 +98,8 @@ int vktb_stream_out(const void* dev_src, size_t bytes, vktb_write_fn write, void
 /* Blocking contract of ManagedBuffer::migrate (include/cpp/vkt/ManagedBuffer.hpp:168-198): on return
  * the SOURCE may be freed or overwritten.  H2D from pageable memory is pipelined through pinned staging
  * (returns once the last chunk left the source; the DMA tail is ordered before later kernels);
- * H2D from pinned memory (vktb_host_alloc) is a single DMA.  D2H is complete on return. */
+ * H2D from pinned memory (vktb_host_alloc or foreign) is a single DMA the call waits for.  D2H is complete on
+ * return. */
 int vktb_memcpy(void* dst, const void* src, size_t bytes, int copy_kind);
 int vktb_memset_range(void* dst, const void* pattern, size_t dst_bytes, size_t pattern_bytes);
 /* pinned host memory from a reuse pool: what vkt::Allocate hands out under the CPU policy so that

@@ -47,17 +47,21 @@ def oracle_compute(sfmt, dfmt, lo_hi_s, lo_hi_d):
 def main():
     import torch
     import torch.distributed as dist
-    backend = sys.argv[1]                 # gloo | nccl
+    backend = sys.argv[1]                 # gloo | nccl | gloo-cuda (several ranks on ONE GPU, planes staged by gloo)
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    gpu = backend == "nccl"
+    gpu = backend != "gloo"
     if gpu:
-        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
-        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+        if backend == "nccl":
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+            dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+        else:
+            torch.cuda.set_device(0)
+            dist.init_process_group("gloo")
         lib = capi.load()
         capi.check(lib.vktb_set_device(torch.cuda.current_device()))
+        # a side stream as torch's current stream; the backend is NOT told: sharded.bound_stream must do the ordering
         stream = torch.cuda.Stream()
         torch.cuda.set_stream(stream)
-        capi.check(lib.vktb_set_stream(stream.cuda_stream))
     else:
         dist.init_process_group("gloo")
         lib = None

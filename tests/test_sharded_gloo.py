@@ -15,23 +15,55 @@ def free_port():
         return s.getsockname()[1]
 
 
-def launch(world, backend):
+def spawn(world, backend, extra_env=None):
     port = free_port()
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
-                   MASTER_PORT=str(port), GLOO_SOCKET_IFNAME="lo")
+                   MASTER_PORT=str(port), GLOO_SOCKET_IFNAME="lo", **(extra_env or {}))
         procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_worker.py"), backend], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    return procs
+
+
+def launch(world, backend):
+    procs = spawn(world, backend)
     outs = [p.communicate(timeout=600)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
     assert any("ok world=%d" % world in o for o in outs), outs
 
 
+def launch_expect_mismatch(world, backend):
+    """A lost halo plane (VKTB_TEST_BREAK_HALO=1: the first incoming transfer lands in a scratch buffer) must turn the
+    slab comparison red: some rank reports MISMATCH and exits non-zero.  The others may then wait in a collective for
+    the dead rank; they are killed (by their own PIDs) once the verdict is in."""
+    import time
+    procs = spawn(world, backend, {"VKTB_TEST_BREAK_HALO": "1"})
+    deadline = time.time() + 600
+    failed = None
+    while time.time() < deadline and failed is None:
+        for p in procs:
+            if p.poll() is not None and p.returncode != 0:
+                failed = p
+        if all(p.poll() is not None for p in procs):
+            break
+        time.sleep(0.2)
+    for p in procs:
+        if p.poll() is None:
+            p.kill()
+    outs = [p.communicate()[0] for p in procs]
+    assert failed is not None, "a lost halo plane went unnoticed:\n" + "\n".join(outs)
+    assert any("MISMATCH" in o for o in outs), outs
+
+
 @pytest.mark.parametrize("world", [2, 3])
 def test_resample_sharded_gloo(world):
     launch(world, "gloo")
+
+
+def test_broken_halo_is_detected_gloo():
+    launch_expect_mismatch(2, "gloo")
 
 
 def test_halo_plan_properties():

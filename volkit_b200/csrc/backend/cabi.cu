@@ -38,6 +38,29 @@ bool toDesc(const char* fn, const vktb_vol* v, VolDesc& d)
 
 int finish(const char* fn, cudaError_t e) { return e == cudaSuccess ? 0 : fail(fn, e); }
 
+// A range that leaves its volume would become an out-of-bounds device access, i.e. a sticky error that ends the
+// process's CUDA context (the host reference merely scribbles over the heap: README.md:140 leaves dst bounds to the
+// caller).  Every entry point therefore refuses such a call, like the hosted twins do (hosted.cu).
+bool emptyRange(const int32_t first[3], const int32_t last[3])
+{
+    return last[0] <= first[0] || last[1] <= first[1] || last[2] <= first[2];
+}
+
+// [first, last) + shift inside v on every axis
+bool inside(const VolDesc& v, const int32_t first[3], const int32_t last[3], const int32_t* shift = nullptr)
+{
+    for (int i = 0; i < 3; ++i) {
+        const long long s = shift ? shift[i] : 0;
+        if (first[i] + s < 0 || last[i] + s > v.dims[i]) return false;
+    }
+    return true;
+}
+
+int outside(const char* fn, const char* which)
+{
+    return fail((std::string(fn) + ": range outside the " + which + " volume").c_str());
+}
+
 // Transform registry
 const char* const kUnaryNames[kNumUnaryOps] = { "xor_coord", "invert", "checker8", "threshold" };
 const char* const kBinaryNames[kNumBinaryOps] = { "or_assign", "swap" };
@@ -53,6 +76,8 @@ int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t l
     VolDesc v;
     if (!first || !last) return fail("vktb_fill_range: null range");
     if (!toDesc("vktb_fill_range", vol, v)) return -1;
+    if (emptyRange(first, last)) return 0;
+    if (!inside(v, first, last)) return outside("vktb_fill_range", "filled");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -65,6 +90,12 @@ int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
     VolDesc dv, sv;
     if (!first || !last || !off) return fail("vktb_copy_range: null range");
     if (!toDesc("vktb_copy_range", dst, dv) || !toDesc("vktb_copy_range", src, sv)) return -1;
+    if (emptyRange(first, last)) return 0;
+    {   // src indices are clamped (Copy_serial.hpp:38-40); the dst box [off, off + last - first) is not
+        const int32_t zero[3] = { 0, 0, 0 }, ext[3] = { last[0] - first[0], last[1] - first[1], last[2] - first[2] };
+        if (!inside(dv, zero, ext, off)) return outside("vktb_copy_range", "dst");
+        if ((size_t)sv.dims[0] * sv.dims[1] * sv.dims[2] == 0) return fail("vktb_copy_range: empty source");
+    }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -82,6 +113,12 @@ int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, cons
     std::vector<VolDesc> dv((size_t)n);
     for (int i = 0; i < n; ++i)
         if (!toDesc("vktb_copy_range_batch", dsts + i, dv[(size_t)i])) return -1;
+    for (int i = 0; i < n; ++i) {
+        const int32_t *f = firsts + 3 * i, *l = lasts + 3 * i;
+        if (emptyRange(f, l)) continue;
+        const int32_t zero[3] = { 0, 0, 0 }, ext[3] = { l[0] - f[0], l[1] - f[1], l[2] - f[2] };
+        if (!inside(dv[(size_t)i], zero, ext, offs + 3 * i)) return outside("vktb_copy_range_batch", "dst");
+    }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -99,6 +136,15 @@ int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
         if (dv.data != sv.data && first[a] > last[a])
             return fail("vktb_scan_range: a right-to-left range needs dst == src (the copy of such a range is undefined)");
     }
+    {   // the scanned box, whichever way each axis runs: [min(first, last + 1), max(last, first + 1)) + off in dst
+        int32_t lo[3], hi[3];
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = first[a] < last[a] ? first[a] : last[a] + 1;
+            hi[a] = first[a] < last[a] ? last[a] : first[a] + 1;
+        }
+        if (!inside(dv, lo, hi, off)) return outside("vktb_scan_range", "dst");
+        if (dv.data != sv.data && (size_t)sv.dims[0] * sv.dims[1] * sv.dims[2] == 0) return fail("vktb_scan_range: empty source");
+    }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -113,6 +159,9 @@ int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb
     if (!first || !last || !off) return fail("vktb_arith_range: null range");
     if (!toDesc("vktb_arith_range", dst, dv) || !toDesc("vktb_arith_range", s1, av) || !toDesc("vktb_arith_range", s2, bv))
         return -1;
+    if (emptyRange(first, last)) return 0;
+    if (!inside(av, first, last) || !inside(bv, first, last)) return outside("vktb_arith_range", "source");
+    if (!inside(dv, first, last, off)) return outside("vktb_arith_range", "dst");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -125,6 +174,8 @@ int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int
     if (op < 0 || op >= kNumUnaryOps) return fail("vktb_transform_range1: unknown device op handle");
     if (!first || !last) return fail("vktb_transform_range1: null range");
     if (!toDesc("vktb_transform_range1", vol, v)) return -1;
+    if (emptyRange(first, last)) return 0;
+    if (!inside(v, first, last)) return outside("vktb_transform_range1", "transformed");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -137,6 +188,8 @@ int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int3
     if (op < 0 || op >= kNumBinaryOps) return fail("vktb_transform_range2: unknown device op handle");
     if (!first || !last) return fail("vktb_transform_range2: null range");
     if (!toDesc("vktb_transform_range2", vol1, a) || !toDesc("vktb_transform_range2", vol2, b)) return -1;
+    if (emptyRange(first, last)) return 0;
+    if (!inside(a, first, last) || !inside(b, first, last)) return outside("vktb_transform_range2", "transformed");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
@@ -186,6 +239,14 @@ int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
     if (!toDesc("vktb_flip_range", dst, dv) || !toDesc("vktb_flip_range", src, sv)) return -1;
     if (bytesPerVoxel(dv.format) != bytesPerVoxel(sv.format))
         return fail("vktb_flip_range: dest and source must have the same bytes per voxel (raw bytes are exchanged)");
+    if (emptyRange(first, last)) return 0;
+    {   // footprint of the loops as written: indices [0, last - first) and their partners last - 1 - i = [first, last)
+        const int32_t zero[3] = { 0, 0, 0 };
+        const int32_t lo[3] = { first[0] < 0 ? first[0] : 0, first[1] < 0 ? first[1] : 0, first[2] < 0 ? first[2] : 0 };
+        (void)zero;
+        if (!inside(sv, lo, last)) return outside("vktb_flip_range", "source");
+        if (!inside(dv, lo, last, off)) return outside("vktb_flip_range", "dst");
+    }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };

@@ -81,7 +81,9 @@ size_t slabTargetBytes()
     return kb > 0 ? (size_t)kb << 10 : (size_t)64 << 20;
 }
 
-inline size_t alignUp(size_t n) { return (n + 255) & ~(size_t)255; }
+// every operand of a slot ends with at least 16 spare bytes: the funnel-shifted loads of the *Range kernels read the
+// aligned vector that encloses the last source byte, which may end up to 15 bytes past the resident planes
+inline size_t alignUp(size_t n) { return (n + 16 + 255) & ~(size_t)255; }
 
 size_t planeBytes(const VolDesc& v) { return (size_t)v.dims[0] * v.dims[1] * bytesPerVoxel(v.format); }
 

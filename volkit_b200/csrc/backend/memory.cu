@@ -422,16 +422,12 @@ int vktb_memcpy(void* dst, const void* src, size_t bytes, int kind)
     cudaError_t e;
     switch (kind) {
     case VKTB_H2D:
-        if (pinnedOwns(src)) {
-            // one DMA straight out of the pool block; the block stays busy until the DMA is done, so the
-            // caller may "free" it immediately (ManagedBuffer::migrate does)
-            e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s);
-            if (e != cudaSuccess) return fail("cudaMemcpyAsync(H2D)", e);
-            pinnedMarkBusy(src, s);
-            return 0;
-        }
-        if (isPinnedHost(src)) {
-            // foreign pinned memory: DMA directly, but the source must be consumed on return
+        if (pinnedOwns(src) || isPinnedHost(src)) {
+            // pinned memory (the backend's pool or foreign): one DMA straight out of the source.  The source must be
+            // consumed on return -- the caller may overwrite it, as after the reference's cudaMemcpy (Memory.cpp:70) --
+            // so the call waits for this DMA.  (Round 1 returned early for pool blocks and only deferred their reuse;
+            // a caller refilling the buffer raced the DMA.  Nothing is lost: the next operand's upload shares the
+            // same link and the kernel needs them all.)
             e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s);
             if (e == cudaSuccess) e = cudaStreamSynchronize(s);
             return e == cudaSuccess ? 0 : fail("cudaMemcpyAsync(H2D pinned)", e);

@@ -23,6 +23,34 @@ from dataclasses import dataclass
 from . import capi
 
 
+class bound_stream:
+    """Orders the C-ABI kernels with the torch work around them (NCCL receives, copy_, zeros, all_reduce).
+
+    The backend launches on its own non-blocking stream unless told otherwise, and `req.wait()` / `copy_` only order
+    torch's CURRENT stream, so a kernel could start before its halo planes arrived or race the collective that
+    follows.  Every sharded op therefore runs its C-ABI calls inside `with bound_stream(torch, tensor)`: the backend's
+    compute stream of this thread is torch's current stream for the duration (handle 0, the legacy default stream,
+    is passed as cudaStreamLegacy = 1, because 0 means "backend-owned" to vktb_set_stream).  CPU tensors (the gloo
+    tests, which plug the oracle in) need nothing."""
+
+    def __init__(self, torch, tensor):
+        self.active = bool(getattr(tensor, "is_cuda", False))
+        self.torch = torch
+
+    def __enter__(self):
+        if self.active:
+            lib = capi.load()
+            self.prev = lib.vktb_get_stream()
+            h = self.torch.cuda.current_stream().cuda_stream
+            capi.check(lib.vktb_set_stream(h if h else 1), "vktb_set_stream")
+        return self
+
+    def __exit__(self, *exc):
+        if self.active:
+            capi.load().vktb_set_stream(self.prev)
+        return False
+
+
 def slab_range(dim_z: int, world: int, rank: int) -> tuple[int, int]:
     """Planes [z0, z1) owned by `rank`: floor(g*Z/n) .. floor((g+1)*Z/n)."""
     return rank * dim_z // world, (rank + 1) * dim_z // world
@@ -127,10 +155,17 @@ def halo_for(plan, src_dims, world, rank) -> tuple[int, int]:
     return max(0, z0 - w0), max(0, w1 - z1)
 
 
-def gather_window(src: ShardedVolume, window, transfers, dist):
-    """Makes the src planes `window` of this rank contiguous and returns the tensor holding them: in place when the
-    slab was allocated with enough halo room (foreign planes are received straight into it), else in a fresh buffer
-    (owned planes copied)."""
+def start_gather(src: ShardedVolume, window, transfers, dist):
+    """Posts the plane transfers that complete the src planes `window` of this rank and returns (buf, wait): `buf`
+    holds the window -- in place when the slab was allocated with enough halo room (foreign planes are received
+    straight into it), else a fresh buffer (owned planes copied) -- and `wait()` blocks the CURRENT STREAM (not the
+    host, on CUDA) until the foreign planes have arrived.  Work launched between the two calls that only reads owned
+    planes overlaps the exchange.
+
+    NCCL moves CUDA tensors peer to peer over NVLink.  With the gloo backend CUDA planes are staged through host
+    memory (the two-ranks-on-one-GPU test set-up of tests/test_sharded_gpu.py; NCCL refuses two ranks per device).
+    VKTB_TEST_BREAK_HALO=1 (tests only) receives the first incoming transfer into a scratch buffer, i.e. loses it."""
+    import os
     torch = src.torch
     w0, w1 = window
     mine = [t for t in transfers if t.dst_rank == src.rank]
@@ -145,14 +180,35 @@ def gather_window(src: ShardedVolume, window, transfers, dist):
         a, b = max(w0, src.z0), min(w1, src.z1)
         if a < b:
             buf[(a - w0) * src.plane_bytes:(b - w0) * src.plane_bytes].copy_(src.planes(a, b))
-    ops = []
+    staged = src.storage.is_cuda and (outgoing or mine) and dist.get_backend() == "gloo"
+    broken = os.environ.get("VKTB_TEST_BREAK_HALO") == "1"
+    ops, landed = [], []
     for t in outgoing:
-        ops.append(dist.P2POp(dist.isend, src.planes(t.z0, t.z1), t.dst_rank))
-    for t in mine:
-        ops.append(dist.P2POp(dist.irecv, buf[(t.z0 - base) * src.plane_bytes:(t.z1 - base) * src.plane_bytes], t.src_rank))
-    if ops:
-        for req in dist.batch_isend_irecv(ops):
+        view = src.planes(t.z0, t.z1)
+        ops.append(dist.P2POp(dist.isend, view.cpu() if staged else view, t.dst_rank))
+    for i, t in enumerate(mine):
+        view = buf[(t.z0 - base) * src.plane_bytes:(t.z1 - base) * src.plane_bytes]
+        if broken and i == 0:
+            view = torch.empty_like(view)
+        if staged:
+            tmp = torch.empty(view.numel(), dtype=torch.uint8)
+            landed.append((view, tmp))
+            view = tmp
+        ops.append(dist.P2POp(dist.irecv, view, t.src_rank))
+    reqs = dist.batch_isend_irecv(ops) if ops else []
+
+    def wait():
+        for req in reqs:
             req.wait()
+        for view, tmp in landed:
+            view.copy_(tmp)
+    return buf, wait
+
+
+def gather_window(src: ShardedVolume, window, transfers, dist):
+    """start_gather + wait: the tensor holding the complete window."""
+    buf, wait = start_gather(src, window, transfers, dist)
+    wait()
     return buf
 
 
@@ -162,18 +218,58 @@ def _cabi_resample_window(dst_desc, src_desc, filt, dz0, D, sz0, S):
                                         capi.I3(*S)), "vktb_resample_window")
 
 
+_interior_cache: dict = {}
+
+
+def interior_planes(filt, dz0, dz1, D, S, own0, own1, lib=None):
+    """The dst planes [i0, i1) of [dz0, dz1) whose taps all lie in the src planes [own0, own1) this rank owns.  The
+    coordinate map is monotone in z, so they are contiguous: the ends are walked inwards plane by plane (a halo is a
+    few planes thick)."""
+    key = (filt, dz0, dz1, tuple(D), tuple(S), own0, own1)
+    hit = _interior_cache.get(key)
+    if hit is not None:
+        return hit
+    same = tuple(D) == tuple(S)
+
+    def owned(z):
+        a, b = (z, z + 1) if same else resample_src_range(filt, z, z + 1, D, S, lib)
+        return own0 <= a and b <= own1
+    i0 = dz0
+    while i0 < dz1 and not owned(i0):
+        i0 += 1
+    i1 = dz1
+    while i1 > i0 and not owned(i1 - 1):
+        i1 -= 1
+    _interior_cache[key] = (i0, i1)
+    return i0, i1
+
+
 def resample_sharded(dst: ShardedVolume, src: ShardedVolume, filt: int, dist, compute=None, planner_lib=None,
-                     plan=None):
-    """dst slab <- Resample(src) with halo exchange.  Returns the number of halo bytes this rank received."""
+                     plan=None, overlap=True):
+    """dst slab <- Resample(src) with halo exchange.  The dst planes whose taps this rank owns (all but a few at the
+    slab ends) are launched first and run WHILE the halo planes travel; the boundary planes follow once they have
+    arrived.  Returns the number of halo bytes this rank received."""
     D, S = dst.dims, src.dims
     windows, transfers = plan if plan is not None else halo_plan(filt, D, S, dst.world, planner_lib)
     window = windows[dst.rank]
-    buf = gather_window(src, window, transfers, dist)
-    w0 = window[0]
-    received = sum((t.z1 - t.z0) * src.plane_bytes for t in transfers if t.dst_rank == dst.rank)
-    if dst.z1 > dst.z0:
+    run = compute or _cabi_resample_window
+    incoming = [t for t in transfers if t.dst_rank == dst.rank]
+    received = sum((t.z1 - t.z0) * src.plane_bytes for t in incoming)
+    with bound_stream(dst.torch, dst.storage):
+        buf, wait = start_gather(src, window, transfers, dist)
+        pieces = [(dst.z0, dst.z1)]
+        if incoming and overlap and dst.z1 > dst.z0:
+            i0, i1 = interior_planes(filt, dst.z0, dst.z1, D, S, src.z0, src.z1, planner_lib)
+            if i1 > i0:
+                same = tuple(D) == tuple(S)
+                need = (i0, i1) if same else resample_src_range(filt, i0, i1, D, S, planner_lib)
+                run(dst.desc(i0, i1), src.desc(need[0], need[1]), filt, i0, D, need[0], S)
+                pieces = [(dst.z0, i0), (i1, dst.z1)]
+        wait()
         sdesc = capi.vol(buf.data_ptr(), (S[0], S[1], window[1] - window[0]), src.fmt, src.lo, src.hi)
-        (compute or _cabi_resample_window)(dst.desc(), sdesc, filt, dst.z0, D, w0, S)
+        for a, b in pieces:
+            if b > a:
+                run(dst.desc(a, b), sdesc, filt, a, D, window[0], S)
     return received
 
 
@@ -231,41 +327,85 @@ def _cabi_arith_range(op, dst_desc, a_desc, b_desc, first, last, off):
                                     capi.I3(*first), capi.I3(*last), capi.I3(*off)), "vktb_arith_range")
 
 
-def copy_range_sharded(dst: ShardedVolume, src: ShardedVolume, first, last, off, dist, compute=None) -> int:
-    """dst slab <- CopyRange(src, first, last, off) with the reference's clamped src indexing.  Returns the halo
-    bytes this rank received."""
+def _split_owned(pz0, pz1, src_plane, own0, own1):
+    """[pz0, pz1) cut into (before, interior, after): interior = the p.z whose src plane src_plane(p.z) (monotone) lies
+    in the owned planes [own0, own1)."""
+    i0 = pz0
+    while i0 < pz1 and not own0 <= src_plane(i0) < own1:
+        i0 += 1
+    i1 = pz1
+    while i1 > i0 and not own0 <= src_plane(i1 - 1) < own1:
+        i1 -= 1
+    return (pz0, i0), (i0, i1), (i1, pz1)
+
+
+def copy_range_sharded(dst: ShardedVolume, src: ShardedVolume, first, last, off, dist, compute=None, overlap=True) -> int:
+    """dst slab <- CopyRange(src, first, last, off) with the reference's clamped src indexing.  The part of the
+    sub-range that reads owned src planes runs while the foreign planes travel.  Returns the halo bytes this rank
+    received."""
     assert dst.storage.data_ptr() != src.storage.data_ptr(), "sharded CopyRange needs distinct volumes"
     windows, sub, transfers = range_plan("copy", first[2], last[2], off[2], dst.dims[2], src.dims[2], dst.world)
     window = windows[dst.rank]
-    buf = gather_window(src, window, transfers, dist)
-    pz0, pz1 = sub[dst.rank]
-    if pz1 > pz0:
+    run = compute or _cabi_copy_range
+    incoming = [t for t in transfers if t.dst_rank == dst.rank]
+    with bound_stream(dst.torch, dst.storage):
+        buf, wait = start_gather(src, window, transfers, dist)
+        pz0, pz1 = sub[dst.rank]
         w0 = window[0]
-        f = (first[0], first[1], pz0 - w0)             # may be negative: clamps to the window's first plane = plane 0
-        l = (last[0], last[1], pz1 - w0)
-        o = (off[0], off[1], pz0 - first[2] + off[2] - dst.z0)
-        (compute or _cabi_copy_range)(dst.desc(), _window_desc(src, buf, window), f, l, o)
-    return sum((t.z1 - t.z0) * src.plane_bytes for t in transfers if t.dst_rank == dst.rank)
+
+        def piece(a, b, sdesc, base):
+            # src z relative to the plane `base` the descriptor starts at (may be negative / past the end: clamped
+            # to the descriptor's first / last plane, which is then the volume's)
+            if b > a:
+                run(dst.desc(), sdesc, (first[0], first[1], a - base), (last[0], last[1], b - base),
+                    (off[0], off[1], a - first[2] + off[2] - dst.z0))
+
+        clamp = lambda z: min(max(z, 0), src.dims[2] - 1)
+        before, inner, after = (pz0, pz1), (pz1, pz1), (pz1, pz1)
+        if incoming and overlap and pz1 > pz0:
+            before, inner, after = _split_owned(pz0, pz1, clamp, src.z0, src.z1)
+            if inner[1] > inner[0]:
+                # owned planes [ia, ib) as a stand-alone volume: a p.z outside [0, dims) clamps to the volume's first /
+                # last plane, which is then ia / ib - 1, i.e. the descriptor's own first / last plane
+                ia, ib = clamp(inner[0]), clamp(inner[1] - 1) + 1
+                piece(inner[0], inner[1], src.desc(ia, ib), ia)
+        wait()
+        for a, b in (before, after):
+            piece(a, b, _window_desc(src, buf, window), w0)
+    return sum((t.z1 - t.z0) * src.plane_bytes for t in incoming)
 
 
 def arith_range_sharded(op: int, dst: ShardedVolume, s1: ShardedVolume, s2: ShardedVolume, first, last, off, dist,
-                        compute=None) -> int:
+                        compute=None, overlap=True) -> int:
     """dst slab <- op(s1, s2) over [first, last) written at + off.  With off[2] == 0 and congruent volumes no plane
-    moves.  Returns the halo bytes this rank received."""
+    moves; otherwise the p.z whose source planes this rank owns run while the others' planes travel.  Returns the
+    halo bytes this rank received."""
     assert s1.dims[2] == s2.dims[2], "sources of a sharded arithmetic call must have the same number of planes"
     assert dst.storage.data_ptr() not in (s1.storage.data_ptr(), s2.storage.data_ptr()) or off[2] == 0
     windows, sub, transfers = range_plan("arith", first[2], last[2], off[2], dst.dims[2], s1.dims[2], dst.world)
     window = windows[dst.rank]
-    buf1 = gather_window(s1, window, transfers, dist)
-    buf2 = buf1 if s2 is s1 else gather_window(s2, window, transfers, dist)
-    pz0, pz1 = sub[dst.rank]
-    if pz1 > pz0:
-        f = (first[0], first[1], 0)                    # the windows start at plane pz0
-        l = (last[0], last[1], pz1 - pz0)
-        o = (off[0], off[1], pz0 + off[2] - dst.z0)
-        (compute or _cabi_arith_range)(op, dst.desc(), _window_desc(s1, buf1, window), _window_desc(s2, buf2, window),
-                                       f, l, o)
-    recv = sum((t.z1 - t.z0) for t in transfers if t.dst_rank == dst.rank)
+    run = compute or _cabi_arith_range
+    incoming = [t for t in transfers if t.dst_rank == dst.rank]
+    with bound_stream(dst.torch, dst.storage):
+        buf1, wait1 = start_gather(s1, window, transfers, dist)
+        buf2, wait2 = (buf1, lambda: None) if s2 is s1 else start_gather(s2, window, transfers, dist)
+        pz0, pz1 = sub[dst.rank]
+
+        def piece(a, b, d1, d2, base):
+            if b > a:
+                run(op, dst.desc(), d1, d2, (first[0], first[1], a - base), (last[0], last[1], b - base),
+                    (off[0], off[1], base + off[2] - dst.z0))
+
+        before, inner, after = (pz0, pz1), (pz1, pz1), (pz1, pz1)
+        if incoming and overlap and pz1 > pz0:
+            before, inner, after = _split_owned(pz0, pz1, lambda z: z, s1.z0, s1.z1)
+            piece(inner[0], inner[1], s1.desc(inner[0], inner[1]) if inner[1] > inner[0] else None,
+                  s2.desc(inner[0], inner[1]) if inner[1] > inner[0] else None, inner[0])
+        wait1()
+        wait2()
+        for a, b in (before, after):
+            piece(a, b, _window_desc(s1, buf1, window), _window_desc(s2, buf2, window), window[0])
+    recv = sum((t.z1 - t.z0) for t in incoming)
     return recv * (s1.plane_bytes + (0 if s2 is s1 else s2.plane_bytes))
 
 
@@ -287,7 +427,8 @@ def histogram_sharded(vol: ShardedVolume, first, last, num_bins: int, dist, comp
     if z1 > z0 and last[0] > first[0] and last[1] > first[1]:
         f = (first[0], first[1], z0 - vol.z0)
         l = (last[0], last[1], z1 - vol.z0)
-        (compute or _cabi_histogram_range)(vol.desc(), f, l, bins.data_ptr(), num_bins)
+        with bound_stream(torch, vol.storage):    # after the zero fill, before the all-reduce, on torch's stream
+            (compute or _cabi_histogram_range)(vol.desc(), f, l, bins.data_ptr(), num_bins)
     if dist is not None and vol.world > 1:
         dist.all_reduce(bins, op=dist.ReduceOp.SUM)
     return bins
@@ -313,7 +454,8 @@ def aggregates_sharded(vol: ShardedVolume, first, last, dist, compute=None) -> "
     if z1 > z0 and last[0] > first[0] and last[1] > first[1]:
         f = (first[0], first[1], z0 - vol.z0)
         l = (last[0], last[1], z1 - vol.z0)
-        (compute or _cabi_aggregates_partial)(vol.desc(), f, l, part)
+        with bound_stream(torch, vol.storage):
+            (compute or _cabi_aggregates_partial)(vol.desc(), f, l, part)
         part.argmin[2] += vol.z0 if part.has_min else 0          # slab -> whole-volume coordinates
         part.argmax[2] += vol.z0 if part.has_max else 0
     world = vol.world if dist is not None else 1
