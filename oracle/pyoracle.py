@@ -97,6 +97,8 @@ class _Lib:
         f("scan_range", ctypes.c_int, [p, p, I3, I3, I3])
         F3 = ctypes.c_float * 3
         f("scale", ctypes.c_int, [p, p, F3, F3])
+        if prefix == "vko_":
+            f("affine_range", ctypes.c_int, [p, p, I3, I3, ctypes.c_float * 9, F3])
         f("rotate", ctypes.c_int, [p, p, F3, ctypes.c_float, F3])
         f("apply_filter", ctypes.c_int, [p, p, ctypes.POINTER(ctypes.c_float), I3])
         if kind == "reference":
@@ -113,6 +115,13 @@ class _Lib:
         f("brick_layout", ctypes.c_size_t, [I3, I3, I3, I3, I3, i32p])
         f("brick_decompose", ctypes.c_int, [p, I3, I3, I3, ctypes.c_void_p, ctypes.c_size_t])
         if prefix == "vko_":
+            F9 = ctypes.c_float * 9
+            f("transform_range1_window", ctypes.c_int, [p, I3, I3, ctypes.c_int, ctypes.c_int32])
+            f("affine_window", ctypes.c_int, [p, ctypes.c_int32, p, ctypes.c_int32, I3, I3, I3, F9, F3])
+            f("apply_filter_window", ctypes.c_int, [p, ctypes.c_int32, p, ctypes.c_int32, I3,
+                                                    ctypes.POINTER(ctypes.c_float), I3])
+            f("scale_matrix", None, [F3, F9])
+            f("rotate_matrix", None, [F3, ctypes.c_float, F9])
             f("resample_window", ctypes.c_int, [p, p, ctypes.c_int, ctypes.c_int32, I3, ctypes.c_int32, I3])
             f("synth_fill", None, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64])
 
@@ -241,6 +250,34 @@ class _Lib:
             at += n
         return bricks
 
+    # ---- z-window forms (restatement only): plane-by-plane checks of full-size volumes
+    def transform_range1_window(self, vol: Vol, first, last, op: int, z_origin: int):
+        assert self._transform_range1_window(ctypes.byref(vol.c()), I3(*first), I3(*last), op, z_origin) == 0
+
+    def scale_matrix(self, factor):
+        m = (ctypes.c_float * 9)()
+        self._scale_matrix((ctypes.c_float * 3)(*factor), m)
+        return list(m)
+
+    def rotate_matrix(self, axis, angle):
+        m = (ctypes.c_float * 9)()
+        self._rotate_matrix((ctypes.c_float * 3)(*axis), angle, m)
+        return list(m)
+
+    def affine_range(self, dst: Vol, src: Vol, first, last, m, center):
+        assert self._affine_range(ctypes.byref(dst.c()), ctypes.byref(src.c()), I3(*first), I3(*last),
+                                  (ctypes.c_float * 9)(*m), (ctypes.c_float * 3)(*center)) == 0
+
+    def affine_window(self, dst: Vol, dz0: int, src: Vol, sz0: int, src_full, first, last, m, center):
+        assert self._affine_window(ctypes.byref(dst.c()), dz0, ctypes.byref(src.c()), sz0, I3(*src_full), I3(*first),
+                                   I3(*last), (ctypes.c_float * 9)(*m), (ctypes.c_float * 3)(*center)) == 0
+
+    def apply_filter_window(self, dst: Vol, dz0: int, src: Vol, sz0: int, full, weights: np.ndarray):
+        w = np.ascontiguousarray(weights, np.float32)
+        rc = self._apply_filter_window(ctypes.byref(dst.c()), dz0, ctypes.byref(src.c()), sz0, I3(*full),
+                                       w.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), I3(*w.shape[::-1]))
+        assert rc == 0, rc
+
     def resample_window(self, dst: Vol, src: Vol, filter: int, dz0: int, dst_full, sz0: int, src_full):
         assert self._resample_window(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter, dz0, I3(*dst_full),
                                      sz0, I3(*src_full)) == 0
@@ -258,12 +295,14 @@ def synth(n_or_dims, fmt: int, seed: int, first_voxel: int = 0) -> np.ndarray:
     return out
 
 
-def synth_numpy(n: int, fmt: int, seed: int, first_voxel: int = 0) -> np.ndarray:
-    """Vectorised numpy twin of vko_synth_fill (fast enough for 10^9 voxels)."""
+def synth_numpy(n: int, fmt: int, seed: int, first_voxel: int = 0, index: np.ndarray | None = None) -> np.ndarray:
+    """Vectorised numpy twin of vko_synth_fill (fast enough for 10^9 voxels): voxels [first_voxel, first_voxel + n),
+    or the voxels whose linear indices `index` (any shape, uint64) names."""
     M = np.uint64(0xFFFFFFFFFFFFFFFF)
     with np.errstate(over="ignore"):
         k = np.uint64((seed * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)
-        x = (np.arange(first_voxel, first_voxel + n, dtype=np.uint64) ^ k) + np.uint64(0x9E3779B97F4A7C15)
+        i = np.arange(first_voxel, first_voxel + n, dtype=np.uint64) if index is None else index.astype(np.uint64)
+        x = (i ^ k) + np.uint64(0x9E3779B97F4A7C15)
         x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
         x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
         x = x ^ (x >> np.uint64(31))

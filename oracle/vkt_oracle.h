@@ -54,6 +54,15 @@ int vko_resample_window(const vko_vol* dst, const vko_vol* src, int filter,
                         int32_t dz0, const int32_t dst_dims_full[3],
                         int32_t sz0, const int32_t src_dims_full[3]);
 
+/* z-window forms for plane-by-plane checks of full-size volumes (bench.py): the same loop bodies on windows of
+ * planes, absolute coordinates preserved; each is tested against its whole-volume twin (tests/test_oracle_windows.py) */
+int vko_transform_range1_window(const vko_vol* vol, const int32_t first[3], const int32_t last[3], int op,
+                                int32_t z_origin);
+int vko_affine_window(const vko_vol* dst, int32_t dz0, const vko_vol* src, int32_t sz0, const int32_t src_full[3],
+                      const int32_t first[3], const int32_t last[3], const float m[9], const float c[3]);
+int vko_apply_filter_window(const vko_vol* dst, int32_t dz0, const vko_vol* src, int32_t sz0, const int32_t full[3],
+                            const float* weights, const int32_t fdims[3]);
+
 /* axis 0/1/2 = vkt::Axis X/Y/Z; restated as written, see vkt_oracle.c */
 int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
                    const int32_t off[3], int axis);
