@@ -124,7 +124,8 @@ def _ref_worker(args):
 
 
 def cpu_rate(edge, procs, steps=1, warmup=0):
-    """GVoxels/s of the reference CPU path: `procs` processes, each SafeSum on an edge^3 sub-volume per step."""
+    """GVoxels/s of the reference CPU path: `procs` processes, each SafeSum on an edge^3 sub-volume per step.
+    Returns (rate, seconds per step, kind, steps timed, warm-ups run)."""
     import multiprocessing as mp
     from oracle import pyoracle as po
     kind = "reference" if po.have_reference() else "port"
@@ -136,14 +137,27 @@ def cpu_rate(edge, procs, steps=1, warmup=0):
                 times.append(t)
     else:
         ctx = mp.get_context("fork")
-        with ctx.Pool(procs) as pool:
+        pool = ctx.Pool(procs)
+        try:
             for s in range(warmup + steps):
                 # workers synthesise their own inputs, then time the op alone; a step lasts as long as its slowest worker
                 ts = pool.map(_ref_worker, [(edge, s * procs + i, kind) for i in range(procs)])
                 if s >= warmup:
                     times.append(max(ts))
+        finally:
+            # close + join (not the context manager's terminate): the workers exit through their atexit hooks, so
+            # the driver's loaded-library record sees oracle/_ref/libvkt_ref.so in this arm
+            pool.close()
+            pool.join()
     sec = float(np.mean(times))
-    return procs * edge ** 3 / sec / 1e9, sec, kind
+    return procs * edge ** 3 / sec / 1e9, sec, kind, len(times), warmup
+
+
+def config_dict(size, world):
+    """`config` of the JSON line: identical in both arms (the driver compares them)."""
+    return {"workload": f"SafeSum {size}^3 UInt16 per GPU (z-slabs of a {size}x{size}x{world * size} volume)",
+            "l2": "inputs (3 x %.1f GiB per GPU) far larger than the 126 MB L2: no flush needed" % (size ** 3 * 2 / 2 ** 30),
+            "parallelism": f"z-slab x{world}, no data-path collective"}
 
 
 def run_reference(args):
@@ -152,14 +166,17 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     edge = 256
-    val, sec, kind = cpu_rate(edge, cores, steps=max(1, min(args.steps, 5)), warmup=min(args.warmup, 1))
+    # EXACTLY the steps and warm-ups asked for: a step is `cores` x edge^3 voxels (about 0.8 s), so the driver's
+    # --steps 20 --warmup 5 ends within half a minute; the sample is named in cpu_baseline.sample
+    val, sec, kind, timed, warmed = cpu_rate(edge, cores, steps=max(1, args.steps), warmup=max(0, args.warmup))
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "steps": timed, "warmup": warmed, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 arithmetic on u16 voxels", "data": "synthetic",
-        "config": {"workload": f"SafeSum {args.size}^3 UInt16 per GPU", "sample": f"{cores} x {edge}^3 UInt16 per step"},
+        "config": config_dict(args.size, args.gpus),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": f"{cores} processes x SafeSum {edge}^3 UInt16 (reference serial path, one process per core)"},
+                         "sample": f"{cores} processes x SafeSum {edge}^3 UInt16 per step (reference serial path, one "
+                                   f"process per core), {timed} steps after {warmed} warm-ups"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -297,12 +314,37 @@ def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
 
     ms_serial = time_steps(torch, step_serial, max(1, steps // 2), warmup, dist)
     sample_serial = grab()
+
+    # what an UNMODIFIED reference caller gets: pageable malloc memory (Allocate_serial, Memory_serial.hpp:13-16)
+    # migrated through the 4 x 16 MiB pinned staging ring, kernel, staged D2H.  Timed on the first eighth of the planes
+    # (the per-voxel rate does not depend on the slab height; keeps another 3 full volumes out of host memory).
+    pz = max(1, size // 8)
+    sub_bytes = size * size * pz * 2
+    pag = [np.empty(sub_bytes, np.uint8) for _ in range(3)]
+    ctypes.memmove(pag[0].ctypes.data, host[0], sub_bytes)        # also faults the pages in
+    ctypes.memmove(pag[1].ctypes.data, host[1], sub_bytes)
+    pag[2][:] = 0
+    lp = capi.I3(size, size, pz)
+
+    def step_pageable():
+        a, b, d = dv((size, size, pz), capi.UINT16), dv((size, size, pz), capi.UINT16), dv((size, size, pz), capi.UINT16)
+        capi.check(lib.vktb_memcpy(a.ptr, pag[0].ctypes.data, sub_bytes, capi.H2D))
+        capi.check(lib.vktb_memcpy(b.ptr, pag[1].ctypes.data, sub_bytes, capi.H2D))
+        capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(d.desc()), ctypes.byref(a.desc()),
+                                        ctypes.byref(b.desc()), z, lp, z))
+        capi.check(lib.vktb_memcpy(pag[2].ctypes.data, d.ptr, sub_bytes, capi.D2H))
+        a.free(); b.free(); d.free()
+
+    ms_pageable = time_steps(torch, step_pageable, 2, 1, dist)
+    pageable = {"ms": ms_pageable, "voxels": size * size * pz,
+                "same_bytes_as_pinned": bool(pag[2][:size * size * 2].tobytes() == sample_serial.tobytes())}
+    del pag
     ctypes.memset(host[2], 0, size * size * 2)
     ms = time_steps(torch, step_streamed, steps, warmup, dist)
     sample = grab()
     for h in host:
         capi.check(lib.vktb_host_free(h))
-    return ms, ms_serial, 2 * vol_bytes, vol_bytes, sample, sample_serial
+    return ms, ms_serial, 2 * vol_bytes, vol_bytes, sample, sample_serial, pageable
 
 
 def run_ours(args):
@@ -363,18 +405,19 @@ def run_ours(args):
     launches = launch_count() - l0 - args.warmup
     clocks = sampler.stop() if rank == 0 else {}
 
-    # parity at full size: sampled z-planes vs the oracle on regenerated inputs
-    plane = S * S
-    planes = sorted({0, 1, S // 3, S // 2, S - 1})
-    ok = True
-    for zp in planes:
-        av = po.Vol(po.synth_numpy(plane, po.UINT16, seed_a, first_voxel + zp * plane).reshape(1, S, S), po.UINT16)
-        bv = po.Vol(po.synth_numpy(plane, po.UINT16, seed_b, first_voxel + zp * plane).reshape(1, S, S), po.UINT16)
+    # parity at full size: sampled z-planes (first, last, eight random) vs the oracle on regenerated inputs
+    from bench_parity import Parity, sample_planes
+    par = Parity(lib, capi)
+    planes = sample_planes(S)
+
+    def expected_plane(zp):
+        av = po.Vol(par.regen(seed_a, po.UINT16, dims, zp, 1, first_voxel), po.UINT16)
+        bv = po.Vol(par.regen(seed_b, po.UINT16, dims, zp, 1, first_voxel), po.UINT16)
         ref = po.empty((S, S, 1), po.UINT16)
         po.oracle().arith_range(po.SAFESUM, ref, av, bv, (0, 0, 0), (S, S, 1))
-        got = np.empty((1, S, S), np.uint16)
-        capi.check(lib.vktb_memcpy(got.ctypes.data, d.ptr + zp * plane * 2, plane * 2, capi.D2H))
-        ok = ok and got.tobytes() == ref.a.tobytes()
+        return ref.a
+
+    ok = par.check(f"SafeSum {S}^3 UInt16", planes, lambda zp: par.fetch(d.ptr, dims, po.UINT16, zp), expected_plane)
 
     value = world * nvox / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
@@ -404,7 +447,7 @@ def run_ours(args):
                 torch.cuda.synchronize()
                 del t
         e_steps = max(2, min(args.steps, 4))
-        e_ms, e_ms_serial, h2d, d2h, smp, smp_serial = run_e2e(torch, lib, capi, DeviceVolume, Se, e_steps, 1, dist, a, b)
+        e_ms, e_ms_serial, h2d, d2h, smp, smp_serial, pageable = run_e2e(torch, lib, capi, DeviceVolume, Se, e_steps, 1, dist, a, b)
         if smp.tobytes() != smp_serial.tobytes():
             raise SystemExit("bench: streamed and serial end-to-end results differ")
         e2e = {"value": world * Se ** 3 / (e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
@@ -415,9 +458,15 @@ def run_ours(args):
                "serial_migrate_ms": e_ms_serial,
                "serial_migrate_workload": "vktb_memcpy H2D x2 -> vktb_arith_range -> vktb_memcpy D2H (whole buffers, "
                                           "what ManagedBuffer::migrate() does)",
+               "pageable_migrate_value": world * pageable["voxels"] / (pageable["ms"] * 1e-3) / 1e9,
+               "pageable_migrate_ms": pageable["ms"],
+               "pageable_migrate_workload": f"pageable malloc buffers, {Se}x{Se}x{max(1, Se // 8)} UInt16 slab: vktb_memcpy "
+                                            "H2D x2 through the pinned staging ring -> vktb_arith_range -> staged D2H "
+                                            "(what an unmodified reference caller's migrate() does)",
+               "pageable_same_bytes_as_pinned": pageable["same_bytes_as_pinned"],
                "host_mem_limited": Se != S and need > 0}
 
-    ops = None
+    ops, resample_lines = None, {}
     want_ops = args.ops == 1 or (args.ops == -1 and world == 1)
     if want_ops:
         a.free(); b.free()
@@ -426,7 +475,7 @@ def run_ours(args):
         except Exception:
             pass
         from bench_ops import run_ops
-        ops = run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps)
+        ops, resample_lines = run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, parity=par)
 
     sharded_ops = None
     if world > 1 and args.sharded != 0:
@@ -445,24 +494,38 @@ def run_ours(args):
     cpu = None
     if rank == 0:
         edge = args.cpu_sample
-        v, sec, kind = cpu_rate(edge, 1, steps=1, warmup=0)
+        v, sec, kind, _, _ = cpu_rate(edge, 1, steps=1, warmup=0)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": kind,
                "sample": f"SafeSum {edge}^3 UInt16, reference serial path, 1 thread, {sec:.1f} s"}
+
+    # `roofline` is a key the driver keeps: the headline kernel, then one entry per Resample direction of BASELINE
+    # config 3 (the metric names both ops) and the verdict of every full-size parity check of this run
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "traffic_source": traffic_src, "traffic_measured_in_run": False,
+                "peak_source": peak_src, "kernel": "arithFlatKernel<UInt16,SafeSum>",
+                "algorithmic_bytes_per_voxel": 6, "frac_of_8TBs_nominal": achieved / 8000.0}
+    for direction, e in resample_lines.items():
+        De = S // 2 if direction == "down" else S * 3 // 2
+        t_bytes, t_src = recorded_traffic(f"resampleRowRunKernel<UInt16,{direction}>", S)
+        roofline[f"resample_{direction}"] = {
+            "op": e["op"], "kernel": "resamplePlanKernel + resampleRowRunKernel<UInt16,UInt16,MOVE>",
+            "algorithmic_bytes": e["alg_bytes"],
+            "algorithmic_bytes_formula": "src rows hit x Sx x 2 B (whole rows of the one tap) + Dx*Dy*Dz x 2 B",
+            "src_rows_hit_fraction": e["src_rows_hit_fraction"], "ms": e["ms"], "achieved": e["alg_gb_s"],
+            "frac": e["frac_of_measured_peak"], "gvoxels_s": e["gvoxels_s"], "traffic": t_bytes, "traffic_source": t_src,
+            "traffic_measured_in_run": False, "parity": e.get("parity"), "dst_edge": De}
+    roofline["parity"] = par.summary()
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 arithmetic on u16 voxels", "data": "synthetic",
-            "config": {"workload": f"SafeSum {S}^3 UInt16 per GPU (z-slab {rank} of a {S}x{S}x{world * S} volume)",
-                       "l2": "inputs (3 x %.1f GiB) far larger than the 126 MB L2: no flush needed" % (nvox * 2 / 2 ** 30),
-                       "parallelism": f"z-slab x{world}, no data-path collective"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                         "kernel": "arithFlatKernel<UInt16,SafeSum>",
-                         "algorithmic_bytes_per_voxel": 6, "frac_of_8TBs_nominal": achieved / 8000.0},
+            "config": config_dict(S, world),
+            "roofline": roofline,
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "parity": {"bit_exact_planes": planes, "ok": bool(ok)}, "ops": ops, "ops_sharded": sharded_ops,
+            "parity": dict(par.summary(), bit_exact_planes=planes, ok=bool(ok), per_op=par.results),
+            "ops": ops, "ops_sharded": sharded_ops,
         }
         print(json.dumps(line))
     if dist is not None:

@@ -68,7 +68,7 @@ class Parity:
                 same = bool((gn == en).all()) and g[~gn].tobytes() == e[~en].tobytes()
             if not same:
                 ok = False
-                bad.append(int(z))
+                bad.append(z if isinstance(z, (tuple, list)) else int(z))
         self.results[name] = {"ok": ok, "planes": len(planes)}
         if bad:
             self.results[name]["mismatched_planes"] = bad[:8]

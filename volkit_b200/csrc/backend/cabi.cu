@@ -4,6 +4,7 @@
 #include <cfloat>
 #include <cmath>
 #include <vector>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -38,7 +39,7 @@ bool toDesc(const char* fn, const vktb_vol* v, VolDesc& d)
 
 int finish(const char* fn, cudaError_t e) { return e == cudaSuccess ? 0 : fail(fn, e); }
 
-// A range that leaves its volume would become an out-of-bounds device access, i.e. a sticky error that ends the
+// A range that leaves its volume's BUFFER would become an out-of-bounds device access, i.e. a sticky error that ends the
 // process's CUDA context (the host reference merely scribbles over the heap: README.md:140 leaves dst bounds to the
 // caller).  Every entry point therefore refuses such a call, like the hosted twins do (hosted.cu).
 bool emptyRange(const int32_t first[3], const int32_t last[3])
@@ -46,14 +47,21 @@ bool emptyRange(const int32_t first[3], const int32_t last[3])
     return last[0] <= first[0] || last[1] <= first[1] || last[2] <= first[2];
 }
 
-// [first, last) + shift inside v on every axis
+// Memory safety of [first, last) + shift in v, in the reference's own terms: it addresses voxels by the LINEAR index
+// (z * dimY + y) * dimX + x without looking at the axes (StructuredVolume.cpp:311-317), so a box may legally run past a
+// row end into the next row (the oracle and the kernels do the same pitch arithmetic).  What must hold is that the
+// lowest and the highest linear index of the box lie inside the buffer; both corners are monotone in every coordinate.
 bool inside(const VolDesc& v, const int32_t first[3], const int32_t last[3], const int32_t* shift = nullptr)
 {
+    const long long X = v.dims[0], Y = v.dims[1], Z = v.dims[2];
+    long long lo[3], hi[3];
     for (int i = 0; i < 3; ++i) {
         const long long s = shift ? shift[i] : 0;
-        if (first[i] + s < 0 || last[i] + s > v.dims[i]) return false;
+        lo[i] = first[i] + s;
+        hi[i] = (long long)last[i] - 1 + s;
     }
-    return true;
+    const long long lowest = (lo[2] * Y + lo[1]) * X + lo[0], highest = (hi[2] * Y + hi[1]) * X + hi[0];
+    return lowest >= 0 && highest < X * Y * Z;
 }
 
 int outside(const char* fn, const char* which)
