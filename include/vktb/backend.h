@@ -129,6 +129,20 @@ int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts,
                           const int32_t* lasts, const int32_t* offs);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  vktb_copy_range_batch
+ * with the same arguments, semantics and results, but nothing on its path allocates (no cudaMalloc / cudaFree /
+ * stream-ordered allocation, no host heap): the box table, which vktb_copy_range_batch allocates per call, lives in
+ * a file-scope device array of vktb_copy_range_batch_noalloc_max() = 4096 records (288 KiB, resident on every GPU
+ * that loads the library until the process exits).  Limits: n <= 4096 (larger batches fail with a message; split
+ * them or use vktb_copy_range_batch); every box must have the source's format and mapping (bytewise boxes only).
+ * All calls share the array, which keeps the previous call's table: nothing in it needs clearing (a call overwrites
+ * the records it uses, stream-ordered before its kernels), but calls whose kernels OVERLAP on the GPU -- different
+ * streams or host threads -- race on it; issue them on one stream. */
+int vktb_copy_range_batch_noalloc(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts,
+                                  const int32_t* lasts, const int32_t* offs);
+int vktb_copy_range_batch_noalloc_max(void);
+
 /* {Sum..SafeAbsDiff}Range_cuda  src/vkt/Arithmetic_cuda.hpp:10-98; semantics of ArithmeticOp,
  * src/vkt/Arithmetic_serial.hpp:15-45: dst[p + off] = map(f(unmap(s1[p]), unmap(s2[p]))), p absolute */
 int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2,

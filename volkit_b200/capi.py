@@ -72,6 +72,9 @@ SIGNATURES = {
     "vktb_copy_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3]),
     "vktb_copy_range_batch": (ctypes.c_int, [ctypes.c_int, _VP, _VP, ctypes.POINTER(ctypes.c_int32),
                                              ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
+    "vktb_copy_range_batch_noalloc": (ctypes.c_int, [ctypes.c_int, _VP, _VP, ctypes.POINTER(ctypes.c_int32),
+                                                     ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
+    "vktb_copy_range_batch_noalloc_max": (ctypes.c_int, []),
     "vktb_scan_range": (ctypes.c_int, [_VP, _VP, I3, I3, I3]),
     "vktb_arith_range": (ctypes.c_int, [ctypes.c_int, _VP, _VP, _VP, I3, I3, I3]),
     "vktb_transform_range1": (ctypes.c_int, [_VP, I3, I3, ctypes.c_int]),

@@ -133,6 +133,48 @@ int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, cons
     return finish("vktb_copy_range_batch", launchCopyBatch(c, n, dv.data(), sv, firsts, lasts, offs));
 }
 
+// No counterpart in the reference: see include/vktb/backend.h.  Nothing on this path calls cudaMalloc / cudaFree (or
+// any allocating routine): the descriptors are converted into a fixed array, the box table lives in a file-scope
+// device array of kernels/stream_ops.cu.
+int vktb_copy_range_batch_noalloc_max(void) { return copyBatchNoAllocMaxBoxes(); }
+
+int vktb_copy_range_batch_noalloc(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts,
+                                  const int32_t* lasts, const int32_t* offs)
+{
+    const char* fn = "vktb_copy_range_batch_noalloc";
+    if (n < 0) return fail("vktb_copy_range_batch_noalloc: negative count");
+    if (n == 0) return 0;
+    const int maxBoxes = copyBatchNoAllocMaxBoxes();
+    if (n > maxBoxes) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "vktb_copy_range_batch_noalloc: %d boxes exceed the static scratch table of %d "
+                 "(use vktb_copy_range_batch, or split the batch)", n, maxBoxes);
+        return fail(msg);
+    }
+    if (!dsts || !firsts || !lasts || !offs) return fail("vktb_copy_range_batch_noalloc: null argument");
+    VolDesc sv;
+    if (!toDesc(fn, src, sv)) return -1;
+    static std::mutex descMutex;
+    static VolDesc dv[4096];
+    static_assert(sizeof(dv) / sizeof(dv[0]) >= 4096, "descriptor array");
+    if (maxBoxes > 4096) return fail("vktb_copy_range_batch_noalloc: internal table size mismatch");
+    std::lock_guard<std::mutex> lock(descMutex);
+    for (int i = 0; i < n; ++i) {
+        if (!toDesc(fn, dsts + i, dv[i])) return -1;
+        if (!(dv[i].format == sv.format && dsts[i].lo == src->lo && dsts[i].hi == src->hi))
+            return fail("vktb_copy_range_batch_noalloc: every box must have the source's format and mapping "
+                        "(converting boxes take vktb_copy_range_batch)");
+        const int32_t *f = firsts + 3 * i, *l = lasts + 3 * i;
+        if (emptyRange(f, l)) continue;
+        const int32_t zero[3] = { 0, 0, 0 }, ext[3] = { l[0] - f[0], l[1] - f[1], l[2] - f[2] };
+        if (!inside(dv[i], zero, ext, offs + 3 * i)) return outside(fn, "dst");
+    }
+    DeviceCtx* d = currentDevice();     // makes the thread's device current: the scratch address is per device
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish(fn, launchCopyBatchNoAlloc(c, n, dv, sv, firsts, lasts, offs));
+}
+
 int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                     const int32_t off[3])
 {

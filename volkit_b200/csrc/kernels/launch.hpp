@@ -38,6 +38,11 @@ cudaError_t launchCopy(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
                        const int32_t last[3], const int32_t off[3]);
 cudaError_t launchCopyBatch(const LaunchCtx&, int n, const VolDesc* dsts, const VolDesc& src, const int32_t* firsts,
                             const int32_t* lasts, const int32_t* offs);
+// the same batch with its box table in a file-scope device array: no allocation (at most copyBatchNoAllocMaxBoxes()
+// boxes, bytewise boxes only: cudaErrorInvalidValue / cudaErrorNotSupported otherwise)
+int copyBatchNoAllocMaxBoxes();
+cudaError_t launchCopyBatchNoAlloc(const LaunchCtx&, int n, const VolDesc* dsts, const VolDesc& src, const int32_t* firsts,
+                                   const int32_t* lasts, const int32_t* offs);
 cudaError_t launchArith(const LaunchCtx&, int op, const VolDesc& dst, const VolDesc& s1, const VolDesc& s2,
                         const int32_t first[3], const int32_t last[3], const int32_t off[3]);
 cudaError_t launchTransform1(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], int op);

@@ -5,6 +5,7 @@
 // Memset   reference src/vkt/Memory_cuda.cu:15-49       dst[i*pat .. ] = pattern                     dstBytes
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -670,6 +671,120 @@ cudaError_t launchCopyBatch(const LaunchCtx& c, int n, const VolDesc* dsts, cons
         if (e != cudaSuccess) break;
     }
     cudaFreeAsync(dev, c.stream);
+    return e;
+}
+
+// ---- the same batch with NO allocation anywhere (vktb_copy_range_batch_noalloc) ---------------------------------------
+// For callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+// box table -- the one piece of scratch memory launchCopyBatch allocates per call -- lives in a file-scope device
+// array instead: kNoAllocMaxBoxes records, resident on every GPU that loads the library until the process exits.
+// In host code `g_boxScratch` is only a stand-in for the symbol; the device address comes from cudaGetSymbolAddress,
+// asked once per device with that device current.  The host-side table is a static array under a mutex, so the call
+// makes no host heap allocation either.  Every call shares the device array: calls whose kernels overlap on the GPU
+// (two streams, two host threads) race on it; nothing in it has to start at zero -- the n records a call uses are
+// overwritten by that call's table upload, which is stream-ordered before its kernels and after the previous call's.
+constexpr int kNoAllocMaxBoxes = 4096;
+static __device__ __align__(256) unsigned char g_boxScratch[(size_t)kNoAllocMaxBoxes * sizeof(BoxRec)];
+
+namespace {
+std::mutex g_noAllocMutex;
+BoxRec*    g_boxScratchAddr[64] = {};          // per device ordinal, from cudaGetSymbolAddress
+BoxRec     g_hostBoxes[kNoAllocMaxBoxes];      // flat boxes from the front, row-wise boxes from the back
+}
+
+int copyBatchNoAllocMaxBoxes() { return kNoAllocMaxBoxes; }
+
+cudaError_t launchCopyBatchNoAlloc(const LaunchCtx& c, int n, const VolDesc* dsts, const VolDesc& src, const int32_t* firsts,
+                                   const int32_t* lasts, const int32_t* offs)
+{
+    if (n <= 0) return cudaSuccess;
+    if (n > kNoAllocMaxBoxes) return cudaErrorInvalidValue;
+    if (src.dims[0] <= 0 || src.dims[1] <= 0 || src.dims[2] <= 0) return cudaErrorInvalidValue;
+    const int bs = bytesPerVoxel(src.format);
+    std::lock_guard<std::mutex> lock(g_noAllocMutex);
+
+    // set-up, once per device, with that device current (the C-ABI entry made it so)
+    int ord = -1;
+    cudaError_t e = cudaGetDevice(&ord);
+    if (e != cudaSuccess) return e;
+    if (ord < 0 || ord >= 64) return cudaErrorInvalidDevice;
+    if (!g_boxScratchAddr[ord]) {
+        void* addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_boxScratch);
+        if (e != cudaSuccess) return e;
+        g_boxScratchAddr[ord] = static_cast<BoxRec*>(addr);
+    }
+    BoxRec* dev = g_boxScratchAddr[ord];
+
+    int nFlat = 0, nRows = 0, maxNx = 0, maxNz = 0;
+    long long maxPlane = 0;
+    unsigned maxVox = 0;
+    for (int i = 0; i < n; ++i) {
+        const VolDesc& dst = dsts[i];
+        const int32_t* f = firsts + 3 * i; const int32_t* l = lasts + 3 * i; const int32_t* o = offs + 3 * i;
+        // converting boxes would need one launchCopy each; this entry point is the bytewise batch only
+        if (!(dst.format == src.format && dst.map.lo == src.map.lo && dst.map.hi == src.map.hi)) return cudaErrorNotSupported;
+        BoxRec r;
+        r.nx = l[0] - f[0]; r.ny = l[1] - f[1]; r.nz = l[2] - f[2];
+        if (r.nx <= 0 || r.ny <= 0 || r.nz <= 0) continue;
+        const Operand d = operandAt(dst, o[0], o[1], o[2]);
+        r.d = d.base; r.pitchY = d.pitchY; r.pitchZ = d.pitchZ;
+        r.x0 = f[0]; r.y0 = f[1]; r.z0 = f[2];
+        r.nvox = 0; r.mulX = r.mulY = 0; r.shX = r.shY = 0;
+        const long long vox = (long long)r.nx * r.ny * r.nz;
+        Range g; g.nx = r.nx; g.ny = r.ny; g.nz = r.nz; g.x0 = g.y0 = g.z0 = 0;
+        if (contiguous(dst, g) && vox < (long long)65535 * kThreads * 4 * (16 / bs)) {
+            r.nvox = (unsigned)vox;
+            magicDivisor((unsigned)r.nx, r.mulX, r.shX);
+            magicDivisor((unsigned)r.ny, r.mulY, r.shY);
+            g_hostBoxes[nFlat++] = r;
+            maxVox = r.nvox > maxVox ? r.nvox : maxVox;
+            continue;
+        }
+        g_hostBoxes[kNoAllocMaxBoxes - 1 - nRows++] = r;
+        maxNx = r.nx > maxNx ? r.nx : maxNx;
+        maxNz = r.nz > maxNz ? r.nz : maxNz;
+        const long long plane = (long long)r.nx * r.ny * bs;
+        maxPlane = plane > maxPlane ? plane : maxPlane;
+    }
+    if (nFlat == 0 && nRows == 0) return cudaSuccess;
+    // pageable source: cudaMemcpyAsync returns once the bytes left the host array (staged), so the next call may
+    // rebuild it; on the device both uploads and the kernels are ordered by the stream
+    if (nFlat) {
+        e = cudaMemcpyAsync(dev, g_hostBoxes, (size_t)nFlat * sizeof(BoxRec), cudaMemcpyHostToDevice, c.stream);
+        if (e != cudaSuccess) return e;
+    }
+    BoxRec* devRows = dev + (kNoAllocMaxBoxes - nRows);
+    if (nRows) {
+        e = cudaMemcpyAsync(devRows, g_hostBoxes + (kNoAllocMaxBoxes - nRows), (size_t)nRows * sizeof(BoxRec),
+                            cudaMemcpyHostToDevice, c.stream);
+        if (e != cudaSuccess) return e;
+    }
+    const uint8_t* sEnd = src.data + (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bs;
+    if (nFlat) {
+        const unsigned perCta = kThreads * 4 * (16 / bs);
+        const unsigned gx = (maxVox + (16 / bs) + perCta - 1) / perCta;
+        dim3 grid((unsigned)nFlat, gx, 1);
+        if (bs == 1) copyBoxesFlatKernel<1><<<grid, kThreads, 0, c.stream>>>(dev, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+        else if (bs == 2) copyBoxesFlatKernel<2><<<grid, kThreads, 0, c.stream>>>(dev, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+        else copyBoxesFlatKernel<4><<<grid, kThreads, 0, c.stream>>>(dev, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2]);
+        countLaunch();
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (nRows) {
+        // row-wise boxes were stored back to front: the kernel indexes them by blockIdx.y in any order
+        int zPer = (int)((65536 + maxPlane - 1) / maxPlane);
+        if (zPer < 1) zPer = 1;
+        while (zPer > 1 && (long long)nRows * ((maxNz + zPer - 1) / zPer) < 2LL * c.smCount * 8) zPer = (zPer + 1) / 2;
+        const RowsLaunch l = rowsLaunch(maxNx, 1, 16 / bs);
+        dim3 grid((unsigned)((maxNz + zPer - 1) / zPer), (unsigned)nRows, 1);
+        if (bs == 1) copyBoxesKernel<1><<<grid, l.block, 0, c.stream>>>(devRows, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        else if (bs == 2) copyBoxesKernel<2><<<grid, l.block, 0, c.stream>>>(devRows, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        else copyBoxesKernel<4><<<grid, l.block, 0, c.stream>>>(devRows, src.data, sEnd, src.dims[0], src.dims[1], src.dims[2], zPer);
+        countLaunch();
+        e = cudaGetLastError();
+    }
     return e;
 }
 
