@@ -488,8 +488,9 @@ def run_ours(args):
         capi.check(lib.vktb_trim_pools())   # hand the pooled device memory back before torch allocates the slabs
         from bench_sharded import run_sharded_ops
         from volkit_b200 import sharded as sharded_mod
+        par_sh = Parity(lib, capi, threads=max(2, (os.cpu_count() or 8) // world))
         sharded_ops = run_sharded_ops(torch, dist, lib, capi, sharded_mod.ShardedVolume, sharded_mod, rank, world, peak,
-                                      time_steps, edge=args.shard_edge)
+                                      time_steps, edge=args.shard_edge, parity=par_sh)
 
     cpu = None
     if rank == 0:
@@ -515,6 +516,12 @@ def run_ours(args):
             "frac": e["frac_of_measured_peak"], "gvoxels_s": e["gvoxels_s"], "traffic": t_bytes, "traffic_source": t_src,
             "traffic_measured_in_run": False, "parity": e.get("parity"), "dst_edge": De}
     roofline["parity"] = par.summary()
+    if sharded_ops is not None:
+        # verdicts are AND-ed over the ranks inside run_sharded_ops; the summary counts this rank's planes
+        sh = {k: v.get("parity") for k, v in sharded_ops.items() if isinstance(v, dict) and "parity" in v}
+        roofline["parity_sharded"] = {"all": all(sh.values()) if sh else None, "ops": len(sh),
+                                      "failed": [k for k, v in sh.items() if not v],
+                                      "planes_checked_on_rank0": sharded_ops.get("_parity", {}).get("planes")}
 
     if rank == 0:
         line = {

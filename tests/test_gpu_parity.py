@@ -163,6 +163,56 @@ def test_arith_u16_edge_pairs(gpu):
             assert a.a.tobytes() == b.a.tobytes(), (op, lo, hi)
 
 
+def test_config2_512cube_uint16(gpu):
+    """BASELINE config 2 AS WRITTEN: 512^3 UInt16 SafeSum / SafeDiff / CopyRange with dstOffset on one B200 vs the CPU
+    path, bit-exact over the WHOLE volume.  The oracle runs on 16-plane z-slabs in a thread pool (ctypes releases the
+    GIL); a slab of a dense volume is a contiguous sub-volume, so slab results concatenate to the whole-volume result."""
+    from concurrent.futures import ThreadPoolExecutor
+    o = po.oracle()
+    E = 512
+    dims = (E, E, E)
+    s1 = po.Vol(po.synth_numpy(E ** 3, po.UINT16, 1).reshape(E, E, E), po.UINT16)
+    s2 = po.Vol(po.synth_numpy(E ** 3, po.UINT16, 2).reshape(E, E, E), po.UINT16)
+    slabs = [(z, min(z + 16, E)) for z in range(0, E, 16)]
+    pool = ThreadPoolExecutor(min(32, os.cpu_count() or 1))
+    for op in (po.SAFESUM, po.SAFEDIFF):
+        want = po.empty(dims, po.UINT16)
+
+        def one(zz, op=op, want=want):
+            z0, z1 = zz
+            o.arith_range(op, po.Vol(want.a[z0:z1], po.UINT16), po.Vol(s1.a[z0:z1], po.UINT16), po.Vol(s2.a[z0:z1], po.UINT16),
+                          (0, 0, 0), (E, E, z1 - z0))
+        list(pool.map(one, slabs))
+        got = po.empty(dims, po.UINT16)
+        gpu.arith_range(op, got, s1, s2, (0, 0, 0), dims)
+        assert got.a.tobytes() == want.a.tobytes(), po.ARITH_NAMES[op]
+    # CopyRange first (0,0,0), last (504,504,504), dstOffset (8,8,8) (SURVEY.md a8), dst pre-filled with seed 3
+    m = E - 8
+    pre = po.synth_numpy(E ** 3, po.UINT16, 3).reshape(E, E, E)
+    want, got = po.Vol(pre.copy(), po.UINT16), po.Vol(pre.copy(), po.UINT16)
+
+    def copy_one(zz):
+        z0, z1 = zz[0], min(zz[1], m)
+        if z1 > z0:
+            o.copy_range(po.Vol(want.a[8 + z0:8 + z1], po.UINT16), po.Vol(s1.a[z0:z1], po.UINT16), (0, 0, 0), (m, m, z1 - z0), (8, 8, 0))
+    list(pool.map(copy_one, slabs))
+    gpu.copy_range(got, s1, (0, 0, 0), (m, m, m), (8, 8, 8))
+    assert got.a.tobytes() == want.a.tobytes()
+    assert got.a[:8].tobytes() == pre[:8].tobytes() and got.a[100, :8].tobytes() == pre[100, :8].tobytes()   # untouched border
+    # the same with the clamped source border: first < 0
+    want, got = po.Vol(pre.copy(), po.UINT16), po.Vol(pre.copy(), po.UINT16)
+
+    def clamp_one(zz):
+        # dst plane 8 + (pz + 3) <- src plane clamp(pz), pz in [-3, 400): slab by dst planes
+        for pz in range(zz[0] - 3, min(zz[1], 403) - 3):
+            sz = min(max(pz, 0), E - 1)
+            o.copy_range(po.Vol(want.a[pz + 11:pz + 12], po.UINT16), po.Vol(s1.a[sz:sz + 1], po.UINT16), (-3, -2, 0), (400, 410, 1), (8, 8, 0))
+    list(pool.map(clamp_one, slabs))
+    gpu.copy_range(got, s1, (-3, -2, -3), (400, 410, 400), (8, 8, 8))
+    assert got.a.tobytes() == want.a.tobytes()
+    pool.shutdown()
+
+
 @pytest.mark.parametrize("fmt", cases.FMT4)
 def test_config2_256cube(gpu, fmt):
     """BASELINE config 2 shape at 256^3: SafeSum/SafeDiff whole volume, CopyRange with dstOffset."""

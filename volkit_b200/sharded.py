@@ -409,6 +409,27 @@ def arith_range_sharded(op: int, dst: ShardedVolume, s1: ShardedVolume, s2: Shar
     return recv * (s1.plane_bytes + (0 if s2 is s1 else s2.plane_bytes))
 
 
+# ---- Transform of a sharded volume: the op must see ABSOLUTE coordinates ----------------------------------------------
+
+def _cabi_transform_range1(vol_desc, first, last, op):
+    lib = capi.load()
+    capi.check(lib.vktb_transform_range1(ctypes.byref(vol_desc), capi.I3(*first), capi.I3(*last), op),
+               "vktb_transform_range1")
+
+
+def transform_sharded(vol: ShardedVolume, first, last, op: int, compute=None):
+    """TransformRange (reference src/vkt/Transform_serial.hpp:15-50) on this rank's planes of [first, last).  The op
+    receives the voxel's coordinates in the WHOLE volume, so the slab is described with the full dims and a data
+    pointer displaced by z0 planes (only the owned planes are ever dereferenced); no communication."""
+    z0, z1 = max(first[2], vol.z0), min(last[2], vol.z1)
+    if z1 <= z0 or last[0] <= first[0] or last[1] <= first[1]:
+        return
+    base = vol.planes(vol.z0, vol.z1).data_ptr() - vol.z0 * vol.plane_bytes
+    desc = capi.vol(base, vol.dims, vol.fmt, vol.lo, vol.hi)
+    with bound_stream(vol.torch, vol.storage):
+        (compute or _cabi_transform_range1)(desc, (first[0], first[1], z0), (last[0], last[1], z1), op)
+
+
 # ---- Histogram of a sharded volume: the one real exchange step of the path -- a SUM all-reduce of the bins -------------
 
 def _cabi_histogram_range(vol_desc, first, last, bins_ptr, num_bins):
