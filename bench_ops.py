@@ -152,6 +152,28 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, parity=None, st
            lambda: capi.check(lib.vktb_transform_range1(ctypes.byref(dd), z3, l3, 0)),
            prepare=copy_a, check=lambda nm: check_transform(nm, d, po.UINT16, dims, 1, 0))
 
+    # a user's OWN op (tests/user_ops/ops.cu: the reference example's MakeCheckered<3>), registered from its cubin
+    import os
+    udir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "user_ops", "build")
+    if os.path.exists(os.path.join(udir, "user_ops.cubin")) and os.path.exists(os.path.join(udir, "libuser_ops_host.so")):
+        img = open(os.path.join(udir, "user_ops.cubin"), "rb").read()
+        hnd = ctypes.c_int(-1)
+        capi.check(lib.vktb_register_unary_op_image(img, len(img), b"checkered3", ctypes.byref(hnd)), "register user op")
+        host_ops = ctypes.CDLL(os.path.join(udir, "libuser_ops_host.so"))
+        host_fn = ctypes.cast(host_ops.checkered3, ctypes.c_void_p).value
+
+        def check_user(name):
+            def expected(z):
+                v = vol1(parity.regen(1, po.UINT16, dims, z), po.UINT16)
+                o.transform_fn1(v, (0, 0, 0), (S, S, 1), host_fn, z)       # the host twin of the same source
+                return v.a
+            return parity.check(name, sample_planes(S), lambda z: parity.fetch(d.ptr, dims, po.UINT16, z), expected)
+
+        record(f"Transform user op checkered3 (cubin) {S}^3 UInt16", n, 4 * n,
+               lambda: capi.check(lib.vktb_transform_range1(ctypes.byref(dd), z3, l3, hnd.value)),
+               "the user's op inlined into the kernel its own image carries (include/vktb/transform_op.cuh)",
+               prepare=copy_a, check=check_user)
+
     # ---- SURVEY 8(f) rows ---------------------------------------------------------------------------------------
     def check_flip(name, axis):
         """axis X mirrors x inside a plane; axis Y mirrors y AND z (the reference as written): dst planes z and

@@ -7,6 +7,7 @@
 // "swap").  An unbound pointer makes Transform return InvalidValue; it never falls back to the CPU.
 #pragma once
 
+#include <cstddef>
 #include <cstdint>
 
 #include "Voxel.hpp"
@@ -32,4 +33,11 @@ namespace vkt
     // volkit-b200 extension: bind a host op to the device op that computes the same function
     VKTAPI Error BindDeviceOp(TransformUnaryOp hostOp, char const* deviceOpName);
     VKTAPI Error BindDeviceOp(TransformBinaryOp hostOp, char const* deviceOpName);
+    // ... or to the user's OWN op: the device image (cubin / PTX / fatbin) or CUDA C source of the same function written
+    // with VKTB_UNARY_OP / VKTB_BINARY_OP(name, ...) of <vktb/transform_op.cuh>.  Afterwards Transform(volume, hostOp)
+    // runs under Device::GPU like any other algorithm.
+    VKTAPI Error BindDeviceOpImage(TransformUnaryOp hostOp, void const* image, std::size_t size, char const* name);
+    VKTAPI Error BindDeviceOpImage(TransformBinaryOp hostOp, void const* image, std::size_t size, char const* name);
+    VKTAPI Error BindDeviceOpSource(TransformUnaryOp hostOp, char const* cudaSource, char const* name);
+    VKTAPI Error BindDeviceOpSource(TransformBinaryOp hostOp, char const* cudaSource, char const* name);
 } // vkt

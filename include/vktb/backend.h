@@ -275,6 +275,18 @@ int vktb_hosted_resample(const vktb_vol* dst, const vktb_vol* src, int filter);
  * Unbound host pointers make Transform fail with InvalidValue under the GPU policy (no CPU fallback). */
 int vktb_unary_op_by_name(const char* name, int* op);     /* "xor_coord", "invert", "checker8", "threshold" */
 int vktb_binary_op_by_name(const char* name, int* op);    /* "or_assign", "swap" */
+/* A user's OWN op (the reference's contract is an arbitrary TransformUnaryOp / TransformBinaryOp,
+ * include/cpp/vkt/Transform.hpp:16-25): written once with VKTB_UNARY_OP / VKTB_BINARY_OP of vktb/transform_op.cuh, it
+ * compiles for the host into the plain function and for sm_100a into the kernel vktb_unary_<name> /
+ * vktb_binary_<name> that carries it inlined.  `image` is that cubin / PTX / fatbin (nvcc -cubin -gencode
+ * arch=compute_100a,code=sm_100a --fmad=false); `_source` takes the CUDA C text and compiles it with NVRTC when
+ * libnvrtc can be loaded (vktb_nvrtc_available()).  The returned handle is used like a built-in one: bind the host
+ * function to it and the unchanged vkt::Transform(volume, hostFn) runs on the GPU. */
+int vktb_register_unary_op_image(const void* image, size_t size, const char* name, int* op);
+int vktb_register_binary_op_image(const void* image, size_t size, const char* name, int* op);
+int vktb_register_unary_op_source(const char* cuda_source, const char* name, int* op);
+int vktb_register_binary_op_source(const char* cuda_source, const char* name, int* op);
+int vktb_nvrtc_available(void);
 int vktb_bind_unary_op(const void* host_fn, int op);
 int vktb_bind_binary_op(const void* host_fn, int op);
 int vktb_lookup_unary_op(const void* host_fn, int* op);   /* non-zero if unbound */

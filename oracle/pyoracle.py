@@ -102,6 +102,8 @@ class _Lib:
         f("rotate", ctypes.c_int, [p, p, F3, ctypes.c_float, F3])
         f("apply_filter", ctypes.c_int, [p, p, ctypes.POINTER(ctypes.c_float), I3])
         if kind == "reference":
+            f("transform_fn1", ctypes.c_int, [p, I3, I3, ctypes.c_void_p])
+            f("transform_fn2", ctypes.c_int, [p, p, I3, I3, ctypes.c_void_p])
             f("write_range", ctypes.c_int, [p, I3, I3, ctypes.c_char_p])
             f("read_range", ctypes.c_int, [p, I3, I3, ctypes.c_char_p])
             f("write", ctypes.c_int, [p, ctypes.c_char_p])
@@ -117,6 +119,7 @@ class _Lib:
         if prefix == "vko_":
             F9 = ctypes.c_float * 9
             f("transform_range1_window", ctypes.c_int, [p, I3, I3, ctypes.c_int, ctypes.c_int32])
+            f("transform_fn1", ctypes.c_int, [p, I3, I3, ctypes.c_void_p, ctypes.c_int32])
             f("affine_window", ctypes.c_int, [p, ctypes.c_int32, p, ctypes.c_int32, I3, I3, I3, F9, F3])
             f("apply_filter_window", ctypes.c_int, [p, ctypes.c_int32, p, ctypes.c_int32, I3,
                                                     ctypes.POINTER(ctypes.c_float), I3])
@@ -156,6 +159,18 @@ class _Lib:
 
     def transform_range2(self, v1: Vol, v2: Vol, first, last, op: int):
         assert self._transform_range2(ctypes.byref(v1.c()), ctypes.byref(v2.c()), I3(*first), I3(*last), op) == 0
+
+    def transform_fn1(self, vol: Vol, first, last, fn_ptr: int, z_origin: int = 0):
+        """TransformRange with a caller-supplied host function (address of a TransformUnaryOp); z_origin (restatement
+        only) makes `vol` a z-window of a larger volume"""
+        if self.kind == "reference":
+            assert z_origin == 0
+            assert self._transform_fn1(ctypes.byref(vol.c()), I3(*first), I3(*last), fn_ptr) == 0
+        else:
+            assert self._transform_fn1(ctypes.byref(vol.c()), I3(*first), I3(*last), fn_ptr, z_origin) == 0
+
+    def transform_fn2(self, v1: Vol, v2: Vol, first, last, fn_ptr: int):
+        assert self._transform_fn2(ctypes.byref(v1.c()), ctypes.byref(v2.c()), I3(*first), I3(*last), fn_ptr) == 0
 
     def resample(self, dst: Vol, src: Vol, filter: int):
         assert self._resample(ctypes.byref(dst.c()), ctypes.byref(src.c()), filter) == 0

@@ -237,6 +237,27 @@ int ref_transform_range1(RefVol const* vol, int32_t const* first, int32_t const*
     return 0;
 }
 
+// A caller-supplied op (tests/test_user_ops.py: the host twin of a VKTB_UNARY_OP, compiled by g++) run by the
+// UNMODIFIED reference: vkt::TransformRange with that function pointer.
+int ref_transform_fn1(RefVol const* vol, int32_t const* first, int32_t const* last, void* fn)
+{
+    if (!fn) return -1;
+    Staged s(vol);
+    vkt::TransformRange(s.vol, v3(first), v3(last), (vkt::TransformUnaryOp)fn);
+    s.writeBack();
+    return 0;
+}
+
+int ref_transform_fn2(RefVol const* vol1, RefVol const* vol2, int32_t const* first, int32_t const* last, void* fn)
+{
+    if (!fn) return -1;
+    Staged a(vol1), b(vol2);
+    vkt::TransformRange_serial(a.vol, b.vol, v3(first), v3(last), (vkt::TransformBinaryOp)fn);
+    a.writeBack();
+    b.writeBack();
+    return 0;
+}
+
 // The reference declares but never defines the C++ binary overloads (include/cpp/vkt/Transform.hpp:30-62);
 // the binary form is only reachable through the C API (src/vkt/Transform.cpp:117-153).
 // so the shim calls the serial body directly (src/vkt/Transform_serial.hpp:53-103), which is what

@@ -63,6 +63,11 @@ int vko_affine_window(const vko_vol* dst, int32_t dz0, const vko_vol* src, int32
 int vko_apply_filter_window(const vko_vol* dst, int32_t dz0, const vko_vol* src, int32_t sz0, const int32_t full[3],
                             const float* weights, const int32_t fdims[3]);
 
+/* Transform with a caller-supplied op (layout of vkt::VoxelView, include/cpp/vkt/Voxel.hpp:15-21) */
+typedef struct vko_voxel_view { uint8_t* bytes; int32_t dataFormat; float mappingLo, mappingHi; } vko_voxel_view;
+typedef void (*vko_unary_fn)(int32_t x, int32_t y, int32_t z, vko_voxel_view voxel);
+int vko_transform_fn1(const vko_vol* vol, const int32_t first[3], const int32_t last[3], vko_unary_fn fn, int32_t z_origin);
+
 /* axis 0/1/2 = vkt::Axis X/Y/Z; restated as written, see vkt_oracle.c */
 int vko_flip_range(const vko_vol* dst, const vko_vol* src, const int32_t first[3], const int32_t last[3],
                    const int32_t off[3], int axis);

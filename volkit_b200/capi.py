@@ -99,6 +99,11 @@ SIGNATURES = {
     "vktb_hosted_resample": (ctypes.c_int, [_VP, _VP, ctypes.c_int]),
     "vktb_unary_op_by_name": (ctypes.c_int, [ctypes.c_char_p, _P(ctypes.c_int)]),
     "vktb_binary_op_by_name": (ctypes.c_int, [ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_register_unary_op_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_register_binary_op_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_register_unary_op_source": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_register_binary_op_source": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_char_p, _P(ctypes.c_int)]),
+    "vktb_nvrtc_available": (ctypes.c_int, []),
     "vktb_bind_unary_op": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "vktb_bind_binary_op": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "vktb_lookup_unary_op": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),

@@ -11,6 +11,7 @@
 
 #include "../../../include/vktb/backend.h"
 #include "../kernels/launch.hpp"
+#include "user_ops.hpp"
 
 using namespace vktb;
 
@@ -221,7 +222,8 @@ int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb
 int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op)
 {
     VolDesc v;
-    if (op < 0 || op >= kNumUnaryOps) return fail("vktb_transform_range1: unknown device op handle");
+    const bool user = op >= kUserOpBase;
+    if (user ? !userOpValid(op, false) : (op < 0 || op >= kNumUnaryOps)) return fail("vktb_transform_range1: unknown device op handle");
     if (!first || !last) return fail("vktb_transform_range1: null range");
     if (!toDesc("vktb_transform_range1", vol, v)) return -1;
     if (emptyRange(first, last)) return 0;
@@ -229,13 +231,15 @@ int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
+    if (user) return finish("vktb_transform_range1 (user op)", launchUserTransform(c, op, v, nullptr, first, last));
     return finish("vktb_transform_range1", launchTransform1(c, v, first, last, op));
 }
 
 int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int32_t first[3], const int32_t last[3], int op)
 {
     VolDesc a, b;
-    if (op < 0 || op >= kNumBinaryOps) return fail("vktb_transform_range2: unknown device op handle");
+    const bool user = op >= kUserOpBase;
+    if (user ? !userOpValid(op, true) : (op < 0 || op >= kNumBinaryOps)) return fail("vktb_transform_range2: unknown device op handle");
     if (!first || !last) return fail("vktb_transform_range2: null range");
     if (!toDesc("vktb_transform_range2", vol1, a) || !toDesc("vktb_transform_range2", vol2, b)) return -1;
     if (emptyRange(first, last)) return 0;
@@ -243,6 +247,7 @@ int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int3
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     LaunchCtx c{ currentStream(d), d->smCount };
+    if (user) return finish("vktb_transform_range2 (user op)", launchUserTransform(c, op, a, &b, first, last));
     return finish("vktb_transform_range2", launchTransform2(c, a, b, first, last, op));
 }
 
@@ -536,7 +541,7 @@ int vktb_binary_op_by_name(const char* name, int* op)
 
 int vktb_bind_unary_op(const void* hostFn, int op)
 {
-    if (!hostFn || op < 0 || op >= kNumUnaryOps) return fail("vktb_bind_unary_op: bad arguments");
+    if (!hostFn || op < 0 || (op >= kNumUnaryOps && !userOpValid(op, false))) return fail("vktb_bind_unary_op: bad arguments");
     std::lock_guard<std::mutex> lock(g_opMutex);
     g_unaryBound[hostFn] = op;
     return 0;
@@ -544,7 +549,7 @@ int vktb_bind_unary_op(const void* hostFn, int op)
 
 int vktb_bind_binary_op(const void* hostFn, int op)
 {
-    if (!hostFn || op < 0 || op >= kNumBinaryOps) return fail("vktb_bind_binary_op: bad arguments");
+    if (!hostFn || op < 0 || (op >= kNumBinaryOps && !userOpValid(op, true))) return fail("vktb_bind_binary_op: bad arguments");
     std::lock_guard<std::mutex> lock(g_opMutex);
     g_binaryBound[hostFn] = op;
     return 0;

@@ -260,6 +260,38 @@ namespace
         return NoError;
     }
 
+    Error BindDeviceOpImage(TransformUnaryOp hostOp, void const* image, std::size_t size, char const* name)
+    {
+        int op = -1;
+        if (vktb_register_unary_op_image(image, size, name, &op) != 0 || vktb_bind_unary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOpImage");
+        return NoError;
+    }
+
+    Error BindDeviceOpImage(TransformBinaryOp hostOp, void const* image, std::size_t size, char const* name)
+    {
+        int op = -1;
+        if (vktb_register_binary_op_image(image, size, name, &op) != 0 || vktb_bind_binary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOpImage");
+        return NoError;
+    }
+
+    Error BindDeviceOpSource(TransformUnaryOp hostOp, char const* cudaSource, char const* name)
+    {
+        int op = -1;
+        if (vktb_register_unary_op_source(cudaSource, name, &op) != 0 || vktb_bind_unary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOpSource");
+        return NoError;
+    }
+
+    Error BindDeviceOpSource(TransformBinaryOp hostOp, char const* cudaSource, char const* name)
+    {
+        int op = -1;
+        if (vktb_register_binary_op_source(cudaSource, name, &op) != 0 || vktb_bind_binary_op((void const*)hostOp, op) != 0)
+            return host::backendError("BindDeviceOpSource");
+        return NoError;
+    }
+
     //---------------------------------------------------------------------------------------------------------
     // Resample (reference src/vkt/Resample.cpp:22-31)
     //---------------------------------------------------------------------------------------------------------
