@@ -298,6 +298,57 @@ class _Lib:
                                      sz0, I3(*src_full)) == 0
 
 
+_cache: dict = {}
+
+
+class _RenderLib:
+    """the headless ray-marcher of either checker: oracle/libvkt_oracle.so (vko_render_raymarch) or the reference's own
+    kernel compiled into oracle/_ref/libvkt_ref_render.so (ref_render_raymarch)"""
+
+    def __init__(self, lib, prefix):
+        F3 = ctypes.c_float * 3
+        self.fn = getattr(lib, prefix + "render_raymarch")
+        self.fn.restype = ctypes.c_int
+        self.fn.argtypes = [ctypes.POINTER(CVol), ctypes.c_void_p, ctypes.c_int, F3, F3, F3, ctypes.c_float, ctypes.c_int,
+                            ctypes.c_int, ctypes.c_float, ctypes.c_int, F3, ctypes.c_void_p, ctypes.c_void_p]
+
+    def raymarch(self, vol: Vol, lut, eye, center, up, fovy_deg, w, h, dt=1.0, srgb=True, dist=(1.0, 1.0, 1.0)):
+        """(rgba32f (h, w, 4), rgba8 (h, w, 4)); lut = (n, 4) float32 array or None"""
+        F3 = ctypes.c_float * 3
+        f32, u8 = np.zeros((h, w, 4), np.float32), np.zeros((h, w, 4), np.uint8)
+        l = None if lut is None else np.ascontiguousarray(lut, np.float32)
+        rc = self.fn(ctypes.byref(vol.c()), None if l is None else l.ctypes.data, 0 if l is None else l.shape[0], F3(*eye),
+                     F3(*center), F3(*up), fovy_deg, w, h, dt, 1 if srgb else 0, F3(*dist), f32.ctypes.data, u8.ctypes.data)
+        assert rc == 0, rc
+        return f32, u8
+
+
+def render_oracle() -> _RenderLib:
+    return _RenderLib(oracle().lib, "vko_")
+
+
+def have_reference_render() -> bool:
+    return os.path.exists(os.path.join(HERE, "_ref", "libvkt_ref_render.so"))
+
+
+def render_reference() -> _RenderLib:
+    if "rr" not in _cache:
+        _cache["rr"] = ctypes.CDLL(os.path.join(HERE, "_ref", "libvkt_ref_render.so"))
+    return _RenderLib(_cache["rr"], "ref_")
+
+
+def default_camera(dims, w, h, dist=(1.0, 1.0, 1.0), reference=False):
+    """(eye, center, up) of the viewer's default camera (45 degrees, view_all)"""
+    F3 = ctypes.c_float * 3
+    e, c, u = F3(), F3(), F3()
+    if reference:
+        render_reference()
+        _cache["rr"].ref_render_default_camera(I3(*dims), F3(*dist), w, h, e, c, u)
+    else:
+        oracle().lib.vko_render_default_camera(I3(*dims), F3(*dist), e, c, u)
+    return tuple(e), tuple(c), tuple(u)
+
+
 def synth(n_or_dims, fmt: int, seed: int, first_voxel: int = 0) -> np.ndarray:
     """SURVEY.md 8(d) counter-based inputs: element i <- splitmix64(i ^ seed*phi)."""
     lib = oracle()
@@ -327,7 +378,6 @@ def synth_numpy(n: int, fmt: int, seed: int, first_voxel: int = 0, index: np.nda
     return x.astype(DTYPES[fmt])
 
 
-_cache: dict = {}
 
 
 def build(ref: bool = True) -> None:

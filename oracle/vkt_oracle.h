@@ -109,6 +109,15 @@ size_t vko_brick_layout(const int32_t src_dims[3], const int32_t brick[3], const
 int vko_brick_decompose(const vko_vol* src, const int32_t brick[3], const int32_t halo_neg[3],
                         const int32_t halo_pos[3], uint8_t* out, size_t out_bytes);
 
+/* Headless ray-marcher (vkt_render_oracle.c): absorption + emission along pixel-centre rays of a pinhole camera,
+ * Nearest-filtered volume and RGBA look-up table (lut: lut_n x 4 floats, or NULL = grey ramp), one frame.  Output
+ * rgba32f (w * h * 4 floats, row 0 = bottom row as in the reference's render target) and optionally rgba8. */
+int vko_render_supported_format(int format);
+int vko_render_raymarch(const vko_vol* vol, const float* lut, int lut_n, const float eye[3], const float center[3],
+                        const float up[3], float fovy_degrees, int w, int h, float dt, int srgb, const float dist[3],
+                        float* rgba32f, uint8_t* rgba8);
+void vko_render_default_camera(const int32_t dims[3], const float dist[3], float eye[3], float center[3], float up[3]);
+
 /* synthetic inputs of SURVEY.md 8(d): element i of a volume with seed s gets the low bits of
  * splitmix64(i ^ s*0x9E3779B97F4A7C15); Float32 gets (h>>40)*2^-24 in [0,1). */
 void vko_synth_fill(void* data, size_t first_voxel, size_t n_voxels, int format, uint64_t seed);
