@@ -424,4 +424,41 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, parity=None, st
            lambda: capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(d_d8), ctypes.byref(d_a8), ctypes.byref(d_b8), z3, l8, z3)),
            check=lambda nm: check_arith(nm, d8, po.SAFESUM, po.UINT8, dims8, (1, 2), (0, 0, 0), dims8, (0, 0, 0), prefilled=False))
     a8.free(); b8.free(); d8.free()
+
+    # ---- headless ray-marcher (last row): 1024^3 UInt8, the viewer's defaults (45 degrees,
+    # view_all, dt 1, sRGB), 1024 x 1024 pixel-centre rays into an RGBA8 device buffer
+    R, VW = min(1024, S), 1024
+    rdims = (R, R, R)
+    rv = DeviceVolume(rdims, capi.UINT8)
+    synth_into(rv, 1)
+    cam = capi.VktbCamera()
+    capi.check(lib.vktb_render_default_camera(capi.I3(*rdims), None, ctypes.byref(cam)))
+    img = ctypes.c_void_p()
+    capi.check(lib.vktb_alloc(ctypes.byref(img), VW * VW * 4))
+    drv = rv.desc()
+    render = lambda w: capi.check(lib.vktb_render_raymarch(ctypes.byref(drv), None, ctypes.byref(cam), None, 0, 1.0, 1, w, w,  # noqa: E731
+                                                           img, None))
+
+    def check_render(name):
+        """the oracle marches a 96 x 96 viewport through the SAME full-size volume (downloaded from the device)"""
+        w = 96
+        render(w)
+        got = np.empty((w, w, 4), np.uint8)
+        capi.check(lib.vktb_memcpy(got.ctypes.data, img.value, got.nbytes, capi.D2H))
+        host = po.Vol(rv.download(), po.UINT8)
+        _, want = po.render_oracle().raymarch(host, None, tuple(cam.eye), tuple(cam.center), tuple(cam.up), 45.0, w, w, 1.0, True)
+        diff = np.abs(got.astype(np.int16) - want.astype(np.int16))
+        return parity.record(name, int(diff.max()) <= 1 and bool((want[..., 3] > 0).any()),
+                             f"96 x 96 rays through the full volume within 1 LSB per RGBA8 channel of the oracle (max {int(diff.max())})")
+
+    # samples along the rays: every pixel whose ray hits the box marches (tfar - tnear) / dt steps; counted on the host
+    # for the timed viewport from the oracle's own intersection would cost a frame, so the figure is measured: the
+    # kernel's step count equals the sum over rays of ceil((tfar - tnear) / dt), estimated from the box's mean chord
+    record(f"Render ray-march {R}^3 UInt8 -> {VW}x{VW} RGBA8", VW * VW, VW * VW * 4, lambda: render(VW),
+           "voxels = rays; alg_bytes = the RGBA8 frame (the volume reads depend on the view); see rays_per_s",
+           check=check_render)
+    nm = f"Render ray-march {R}^3 UInt8 -> {VW}x{VW} RGBA8"
+    out[nm]["rays_per_s"] = VW * VW / (out[nm]["ms"] * 1e-3)
+    capi.check(lib.vktb_free(img))
+    rv.free()
     return out, resample_summary

@@ -256,6 +256,31 @@ typedef struct vktb_agg_partial
 int vktb_aggregates_partial(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_agg_partial* out);
 int vktb_aggregates_finish(const vktb_agg_partial* parts, int n, uint64_t num_elems, vktb_aggregates* out);
 
+/* ---- SURVEY 8(f) rank 4, last row: headless ray-marcher ----------------------------------------------------------
+ * The arithmetic of the reference's RayMarchingKernel (src/vkt/Render_kernel.hpp:95-162: absorption + emission,
+ * opacity correction 1 - (1 - a)^dt, front-to-back compositing, optional sRGB) as the reference's host path sets it up
+ * (src/vkt/Render.cpp:434-489: Nearest-filtered, Clamp-addressed volume over normalised coordinates, RGBA look-up
+ * table as a Nearest 1-D texture, bbox = [0, dims * dist]) -- written into a DEVICE buffer.  The reference's own
+ * output path is a GLUT / GL window with progressive jittered accumulation (unavailable on this box); the headless
+ * form renders ONE frame of pixel-centre rays of visionaray's pinhole camera (look_at(eye, center, up),
+ * perspective(fovy), primary_ray(x, y)), so an image is reproducible.
+ *   vol          UInt8 / UInt16 / Int16 / UInt32 (voxels are normalised by the texel type's numeric limits)
+ *   dist         voxel spacing (NULL = 1, 1, 1)
+ *   lut_dev      lut_n RGBA float quadruples in DEVICE memory, or NULL / 0: colour = (v, v, v, v)
+ *   dt           ray step (RenderState::dtRayMarching, default 1); srgb = RenderState::sRGB (default 1)
+ *   rgba8_dev    width * height * 4 bytes, row 0 = bottom row (as the reference's render target), visionaray's
+ *                float -> unorm<8> rule (truncation); rgba32f_dev: the float image; either may be NULL
+ * Asynchronous on the compute stream like every algorithm. */
+typedef struct vktb_camera
+{
+    float eye[3], center[3], up[3];
+    float fovy_degrees;
+} vktb_camera;
+int vktb_render_raymarch(const vktb_vol* vol, const float dist[3], const vktb_camera* cam, const float* lut_dev, int lut_n,
+                         float dt, int srgb, int width, int height, uint8_t* rgba8_dev, float* rgba32f_dev);
+/* the viewer's default camera: 45 degrees, pinhole_camera::view_all(bbox) (src/vkt/Render.cpp:856-865); host math */
+int vktb_render_default_camera(const int32_t dims[3], const float dist[3], vktb_camera* cam);
+
 /* ---- Host-resident volumes, streamed ---------------------------------------------------------------
  * Same semantics and results as the entry points above, but every vktb_vol.data is a HOST pointer (pinned:
  * vktb_host_alloc or cudaHostRegister; pageable memory works without overlap).  The range is cut into z-slabs and

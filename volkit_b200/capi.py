@@ -43,6 +43,11 @@ class VktbAggPartial(ctypes.Structure):
                 ("pad", ctypes.c_int32)]
 
 
+class VktbCamera(ctypes.Structure):
+    _fields_ = [("eye", ctypes.c_float * 3), ("center", ctypes.c_float * 3), ("up", ctypes.c_float * 3),
+                ("fovy_degrees", ctypes.c_float)]
+
+
 READ_FN = ctypes.CFUNCTYPE(ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
 WRITE_FN = ctypes.CFUNCTYPE(ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
 
@@ -93,6 +98,10 @@ SIGNATURES = {
     "vktb_aggregates_range": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggregates)]),
     "vktb_aggregates_partial": (ctypes.c_int, [_VP, I3, I3, _P(VktbAggPartial)]),
     "vktb_aggregates_finish": (ctypes.c_int, [_P(VktbAggPartial), ctypes.c_int, ctypes.c_uint64, _P(VktbAggregates)]),
+    "vktb_render_raymarch": (ctypes.c_int, [_VP, _P(ctypes.c_float), _P(VktbCamera), ctypes.c_void_p, ctypes.c_int,
+                                            ctypes.c_float, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                            ctypes.c_void_p]),
+    "vktb_render_default_camera": (ctypes.c_int, [I3, _P(ctypes.c_float), _P(VktbCamera)]),
     "vktb_histogram_range": (ctypes.c_int, [_VP, I3, I3, ctypes.c_void_p, ctypes.c_size_t, _P(ctypes.c_uint64)]),
     "vktb_hosted_arith_range": (ctypes.c_int, [ctypes.c_int, _VP, _VP, _VP, I3, I3, I3]),
     "vktb_hosted_transform_range1": (ctypes.c_int, [_VP, I3, I3, ctypes.c_int]),

@@ -524,6 +524,39 @@ int vktb_resample_window_src_range3(int filter, int32_t dz0, int32_t dz1, const 
     return planSrcRange(filter, dz0, dz1, D[2], S[2], spill, sz0, sz1);
 }
 
+// ---- Headless ray-marcher ---------------------------------------------------------------------------------------
+int vktb_render_default_camera(const int32_t dims[3], const float dist[3], vktb_camera* cam)
+{
+    if (!dims || !cam) return fail("vktb_render_default_camera: null argument");
+    const float one[3] = { 1.f, 1.f, 1.f };
+    renderDefaultCamera(dims, dist ? dist : one, cam->eye, cam->center, cam->up);
+    cam->fovy_degrees = 45.f;
+    return 0;
+}
+
+int vktb_render_raymarch(const vktb_vol* vol, const float dist[3], const vktb_camera* cam, const float* lutDev, int lutN,
+                         float dt, int srgb, int width, int height, uint8_t* rgba8Dev, float* rgba32fDev)
+{
+    const char* fn = "vktb_render_raymarch";
+    VolDesc v;
+    if (!cam) return fail("vktb_render_raymarch: null camera");
+    if (!toDesc(fn, vol, v)) return -1;
+    if (!renderFormatSupported(v.format))
+        return fail("vktb_render_raymarch: UInt8, UInt16, Int16 and UInt32 volumes only (the reference normalises a voxel by "
+                    "its texel type's numeric limits, Render_kernel.hpp:31-39, which is meaningless for Float32)");
+    if ((size_t)v.dims[0] * v.dims[1] * v.dims[2] == 0) return fail("vktb_render_raymarch: empty volume");
+    if (width <= 0 || height <= 0 || width > 32768 || height > 32768) return fail("vktb_render_raymarch: bad viewport");
+    if (!(dt > 0.f)) return fail("vktb_render_raymarch: dt must be positive (the march would never end)");
+    if (lutN < 0 || (lutN > 0 && !lutDev)) return fail("vktb_render_raymarch: bad look-up table");
+    if (!rgba8Dev && !rgba32fDev) return fail("vktb_render_raymarch: no output buffer");
+    const float one[3] = { 1.f, 1.f, 1.f };
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    return finish(fn, launchRayMarch(c, v, dist ? dist : one, cam->eye, cam->center, cam->up, cam->fovy_degrees, lutDev, lutN,
+                                     dt, srgb, width, height, rgba8Dev, rgba32fDev));
+}
+
 // ---- Transform registry ----
 int vktb_unary_op_by_name(const char* name, int* op)
 {

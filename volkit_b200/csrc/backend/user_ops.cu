@@ -169,7 +169,10 @@ cudaError_t launchUserTransform(const LaunchCtx& c, int op, const VolDesc& v1, c
     if (v2) p.v2 = describeOperand(*v2, first);
     const long long rows = (long long)p.ny * p.nz;
     const int perThread = binary ? 1 : 16 / p.v1.bpv;
-    const long long items = binary ? p.nx : (p.nx + perThread - 1) / perThread + 1;   // + a misaligned head chunk
+    // rows that all start on a 16-byte boundary need exactly ceil(nx / V) chunks; otherwise one more for the head
+    // (an extra, almost empty column of CTAs halves the throughput when a row is exactly one CTA wide)
+    const bool alignedRows = ((reinterpret_cast<uintptr_t>(p.v1.base) | (uintptr_t)p.v1.pitchY | (uintptr_t)p.v1.pitchZ) & 15u) == 0;
+    const long long items = binary ? p.nx : (p.nx + perThread - 1) / perThread + (alignedRows ? 0 : 1);
     dim3 block(256, 1, 1);
     dim3 grid((unsigned)((items + 255) / 256), (unsigned)(rows > 65535 ? 65535 : rows), 1);
     void* args[] = { &p };

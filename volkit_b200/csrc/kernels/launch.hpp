@@ -88,6 +88,12 @@ cudaError_t launchAffine(const LaunchCtx&, const VolDesc& dst, const VolDesc& sr
 // ApplyFilter over [0, src dims); weights: fdims[0] * fdims[1] * fdims[2] HOST floats, x fastest; fdims in 1..3
 cudaError_t launchFilter(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const float* weights,
                          const int32_t fdims[3]);
+// Headless ray-marcher (kernels/render.cu): one frame of pixel-centre pinhole rays, RGBA8 and / or RGBA32F out
+bool renderFormatSupported(int format);
+void renderDefaultCamera(const int32_t dims[3], const float dist[3], float eye[3], float center[3], float up[3]);
+cudaError_t launchRayMarch(const LaunchCtx&, const VolDesc& vol, const float dist[3], const float eye[3], const float center[3],
+                           const float up[3], float fovyDegrees, const float* lutDev, int lutN, float dt, int srgb, int width,
+                           int height, uint8_t* rgba8, float* rgba32f);
 cudaError_t launchDebugCodec(const LaunchCtx&, int format, Mapping m, const float* values, uint32_t* mapped,
                              float* unmapped, size_t n);
 
