@@ -70,6 +70,23 @@ const char* vktb_last_error(void);                 /* per-thread, never NULL */
 int         vktb_device_count(int* n);
 int         vktb_set_device(int ordinal);          /* device used by the calling thread (default 0) */
 int         vktb_get_device(int* ordinal);
+/* Several GPUs of one box behind this same ABI, in ONE process.  vktb_set_devices names the
+ * device group (all ids need peer access to each other: NVLink / NVSwitch); the calling thread's device becomes ids[0].
+ * From then on vktb_alloc places an allocation of at least VKTB_SHARD_MIN_MB MiB (default 1024) as ONE address range
+ * whose physical memory is striped over the group in equal contiguous parts (z is the slowest axis, so a part is a
+ * z-slab), accessible from every device: the single data pointer of the reference's ManagedBuffer
+ * (include/cpp/vkt/ManagedBuffer.hpp:168-198) spans the GPUs.  Then
+ *   - vktb_fill_range, vktb_copy_range, vktb_arith_range, vktb_transform_range1/2 and vktb_resample(_window) whose
+ *     operands are all striped run on every device at once, each on the dst planes that start in its stripe; a source
+ *     plane or Resample tap in a neighbour's stripe is a peer load over NVLink inside the kernel (no halo copy);
+ *   - vktb_memcpy to / from a striped range drives every device's copy engine on its own byte range concurrently --
+ *     migrate() of a sharded volume;
+ *   - every other entry point runs on ids[0] and reaches the other stripes through peer access (correct, not scaled).
+ * The caller sees one stream as before: the devices' work is forked from and joined to it by events.
+ * vktb_set_devices(ids, 1) returns to one device.  Striped volumes must be freed before the group changes. */
+int         vktb_set_devices(const int* ids, int n);
+int         vktb_get_devices(int* ids, int capacity, int* n);
+int         vktb_is_striped(const void* ptr, int* stripes);   /* 1 if ptr lies in a striped allocation */
 /* number of kernels this library has launched so far (all threads); evidence for "gpu_launches" */
 uint64_t    vktb_launch_count(void);
 /* the compute stream (a cudaStream_t) of the calling thread's device; vktb_set_stream(NULL) restores

@@ -60,6 +60,9 @@ SIGNATURES = {
     "vktb_device_count": (ctypes.c_int, [_P(ctypes.c_int)]),
     "vktb_set_device": (ctypes.c_int, [ctypes.c_int]),
     "vktb_get_device": (ctypes.c_int, [_P(ctypes.c_int)]),
+    "vktb_set_devices": (ctypes.c_int, [_P(ctypes.c_int), ctypes.c_int]),
+    "vktb_get_devices": (ctypes.c_int, [_P(ctypes.c_int), ctypes.c_int, _P(ctypes.c_int)]),
+    "vktb_is_striped": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),
     "vktb_launch_count": (ctypes.c_uint64, []),
     "vktb_get_stream": (ctypes.c_void_p, []),
     "vktb_set_stream": (ctypes.c_int, [ctypes.c_void_p]),

@@ -12,12 +12,27 @@
 #include "../../../include/vktb/backend.h"
 #include "../kernels/launch.hpp"
 #include "user_ops.hpp"
+#include "multi.hpp"
 
 using namespace vktb;
 
 namespace {
 
 bool supportedFormat(int f) { return f == F_U8 || f == F_U16 || f == F_U32 || f == F_F32 || f == F_INT16; }
+
+size_t planeBytesOf(const VolDesc& v) { return (size_t)v.dims[0] * v.dims[1] * bytesPerVoxel(v.format); }
+
+// The striped allocation a call fans out over: dst lives in one and every other operand is striped too (a pooled
+// operand belongs to one device's memory pool, which the other devices' kernels cannot be assumed to reach).
+const StripedAlloc* fanOutTarget(const VolDesc& dst, std::initializer_list<const VolDesc*> others)
+{
+    if (groupSize() < 2) return nullptr;
+    const StripedAlloc* a = findStriped(dst.data);
+    if (!a || a->stripes.size() < 2) return nullptr;
+    for (const VolDesc* o : others)
+        if (o && !findStriped(o->data)) return nullptr;
+    return a;
+}
 
 // vktb_vol -> VolDesc; returns false (error set) on bad input
 bool toDesc(const char* fn, const vktb_vol* v, VolDesc& d)
@@ -89,6 +104,13 @@ int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t l
     if (!inside(v, first, last)) return outside("vktb_fill_range", "filled");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    if (const StripedAlloc* a = fanOutTarget(v, {})) {
+        return finish("vktb_fill_range", forEachStripe(a, v.data, planeBytesOf(v), first[2], last[2],
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], z0 }, l[3] = { last[0], last[1], z1 };
+                return launchFill(cg, v, f, l, value);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     return finish("vktb_fill_range", launchFill(c, v, first, last, value));
 }
@@ -107,6 +129,15 @@ int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
     }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    if (const StripedAlloc* a = overlaps(dv, sv) ? nullptr : fanOutTarget(dv, { &sv })) {
+        const long long shift = (long long)off[2] - first[2];            // dst plane = p.z + shift
+        return finish("vktb_copy_range", forEachStripe(a, dv.data, planeBytesOf(dv), first[2] + shift, last[2] + shift,
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], (int32_t)(z0 - shift) }, l[3] = { last[0], last[1], (int32_t)(z1 - shift) };
+                const int32_t o[3] = { off[0], off[1], z0 };
+                return launchCopy(cg, dv, sv, f, l, o);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     return finish("vktb_copy_range", launchCopy(c, dv, sv, first, last, off));
 }
@@ -215,6 +246,15 @@ int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb
     if (!inside(dv, first, last, off)) return outside("vktb_arith_range", "dst");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    const bool shifted = off[0] || off[1] || off[2];
+    const bool aliasShifted = shifted && (overlaps(dv, av) || overlaps(dv, bv));   // order-dependent: one device, as before
+    if (const StripedAlloc* a = aliasShifted ? nullptr : fanOutTarget(dv, { &av, &bv })) {
+        return finish("vktb_arith_range", forEachStripe(a, dv.data, planeBytesOf(dv), (long long)first[2] + off[2], (long long)last[2] + off[2],
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], z0 - off[2] }, l[3] = { last[0], last[1], z1 - off[2] };
+                return launchArith(cg, op, dv, av, bv, f, l, off);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     return finish("vktb_arith_range", launchArith(c, op, dv, av, bv, first, last, off));
 }
@@ -230,6 +270,13 @@ int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int
     if (!inside(v, first, last)) return outside("vktb_transform_range1", "transformed");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    if (const StripedAlloc* a = fanOutTarget(v, {})) {
+        return finish("vktb_transform_range1", forEachStripe(a, v.data, planeBytesOf(v), first[2], last[2],
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], z0 }, l[3] = { last[0], last[1], z1 };   // absolute coordinates
+                return user ? launchUserTransform(cg, op, v, nullptr, f, l) : launchTransform1(cg, v, f, l, op);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     if (user) return finish("vktb_transform_range1 (user op)", launchUserTransform(c, op, v, nullptr, first, last));
     return finish("vktb_transform_range1", launchTransform1(c, v, first, last, op));
@@ -246,6 +293,13 @@ int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int3
     if (!inside(a, first, last) || !inside(b, first, last)) return outside("vktb_transform_range2", "transformed");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    if (const StripedAlloc* sa = fanOutTarget(a, { &b })) {
+        return finish("vktb_transform_range2", forEachStripe(sa, a.data, planeBytesOf(a), first[2], last[2],
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], z0 }, l[3] = { last[0], last[1], z1 };
+                return user ? launchUserTransform(cg, op, a, &b, f, l) : launchTransform2(cg, a, b, f, l, op);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     if (user) return finish("vktb_transform_range2 (user op)", launchUserTransform(c, op, a, &b, first, last));
     return finish("vktb_transform_range2", launchTransform2(c, a, b, first, last, op));
@@ -275,6 +329,17 @@ int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter, i
     }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    if (const StripedAlloc* a = overlaps(dv, sv) ? nullptr : fanOutTarget(dv, { &sv })) {
+        // dst planes by stripe; the src window stays whole: a tap in the neighbour's stripe is a peer load
+        const size_t pd = planeBytesOf(dv);
+        return finish("vktb_resample", forEachStripe(a, dv.data, pd, 0, dv.dims[2],
+            [&](const LaunchCtx& cg, int z0, int z1) {
+                VolDesc w = dv;
+                w.data = dv.data + (size_t)z0 * pd;
+                w.dims[2] = z1 - z0;
+                return launchResample(cg, w, sv, filter, dstZ0 + z0, dstFull, srcZ0, srcFull);
+            }));
+    }
     LaunchCtx c{ currentStream(d), d->smCount };
     return finish("vktb_resample", launchResample(c, dv, sv, filter, dstZ0, dstFull, srcZ0, srcFull));
 }

@@ -51,6 +51,9 @@ struct DeviceCtx
 
 // Returns nullptr (and sets the thread's error string) when no usable GPU exists: there is no CPU fallback.
 DeviceCtx* currentDevice();
+DeviceCtx* deviceCtx(int ordinal);                    // any device; makes it current
+int  currentOrdinal();
+void setCurrentOrdinal(int ordinal);
 cudaStream_t currentStream(DeviceCtx* d);
 
 void setError(const std::string& msg);

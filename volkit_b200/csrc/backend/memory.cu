@@ -7,6 +7,7 @@
 
 #include "../../../include/vktb/backend.h"
 #include "../kernels/launch.hpp"
+#include "multi.hpp"
 
 namespace vktb {
 
@@ -28,9 +29,9 @@ int fail(const char* what) { t_error = what; return -1; }
 static std::mutex g_devMutex;
 static DeviceCtx* g_devices[64] = {};
 
-DeviceCtx* currentDevice()
+// context of device `ord`, created on first use; makes the device current.  nullptr + error string on failure.
+DeviceCtx* deviceCtx(int ord)
 {
-    const int ord = t_device;
     if (ord < 0 || ord >= 64) { fail("vktb: device ordinal out of range"); return nullptr; }
     DeviceCtx* d = g_devices[ord];
     if (d && d->ready) {
@@ -71,6 +72,10 @@ DeviceCtx* currentDevice()
     g_devices[ord] = d;
     return d;
 }
+
+DeviceCtx* currentDevice() { return deviceCtx(t_device); }
+int currentOrdinal() { return t_device; }
+void setCurrentOrdinal(int ord) { t_device = ord; }
 
 cudaStream_t currentStream(DeviceCtx* d) { return t_hasOverride ? t_streamOverride : d->compute; }
 
@@ -381,6 +386,8 @@ int vktb_alloc(void** ptr, size_t bytes)
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     if (bytes == 0) bytes = 1;   // like malloc(0) in the reference's Allocate_serial: a unique, freeable pointer
+    // with a device group (vktb_set_devices) large volumes are striped over its GPUs: one pointer, all devices
+    if (groupSize() > 1 && bytes >= shardMinBytes()) return stripedAlloc(ptr, bytes);
     cudaError_t e = cudaMallocAsync(ptr, bytes, currentStream(d));
     if (e != cudaSuccess) { *ptr = nullptr; return fail("vktb_alloc", e); }
     std::lock_guard<std::mutex> lock(d->allocMutex);
@@ -394,6 +401,10 @@ int vktb_free(void* ptr)
     if (!ptr) return 0;
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    {
+        int rc = 0;
+        if (stripedFree(ptr, &rc)) return rc;
+    }
     {
         std::lock_guard<std::mutex> lock(d->allocMutex);
         auto it = d->deviceAllocs.find(ptr);
@@ -418,6 +429,11 @@ int vktb_memcpy(void* dst, const void* src, size_t bytes, int kind)
     if (kind == VKTB_H2H) { memmove(dst, src, bytes); return 0; }
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
+    {
+        // a striped volume: every device's copy engine moves its own byte range (migrate() of a sharded volume)
+        int rc = 0;
+        if (stripedMemcpy(dst, src, bytes, kind, &rc)) return rc;
+    }
     cudaStream_t s = currentStream(d);
     cudaError_t e;
     switch (kind) {
