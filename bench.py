@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--shard-edge", type=int, default=4096, help="edge of the sharded volumes timed at N > 1")
     ap.add_argument("--sharded", type=int, default=-1, help="1/0: time the sharded-volume table (default: on at N > 1)")
+    ap.add_argument("--single-process", dest="single_process", type=int, default=-1,
+                    help="1/0: at N > 1 rank 0 also runs the one-process multi-GPU table (default: on)")
     return ap.parse_args()
 
 
@@ -492,6 +494,28 @@ def run_ours(args):
         sharded_ops = run_sharded_ops(torch, dist, lib, capi, sharded_mod.ShardedVolume, sharded_mod, rank, world, peak,
                                       time_steps, edge=args.shard_edge, parity=par_sh)
 
+    # the SAME box through one process: rank 0 names all N GPUs as a device group (vktb_set_devices) and runs the
+    # striped-volume table; the other ranks have freed their memory and wait on the rendezvous store (a host-side wait:
+    # an NCCL barrier would keep a spinning kernel on the very GPUs being measured)
+    multi_ops = None
+    if world > 1 and args.sharded != 0 and args.single_process != 0:
+        torch.cuda.empty_cache()
+        capi.check(lib.vktb_trim_pools())
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        store = dist.distributed_c10d._get_default_store()
+        if rank == 0:
+            try:
+                from bench_multi import run_multi
+                par_m = Parity(lib, capi)
+                multi_ops = run_multi(torch, lib, capi, world, peak, time_steps, edge=args.shard_edge, parity=par_m)
+            except Exception as exc:   # the line must still be printed; the failure is recorded in it
+                multi_ops = {"error": repr(exc)}
+            store.set("vktb_multi_done", "1")
+        else:
+            store.wait(["vktb_multi_done"])
+
     cpu = None
     if rank == 0:
         edge = args.cpu_sample
@@ -516,6 +540,10 @@ def run_ours(args):
             "frac": e["frac_of_measured_peak"], "gvoxels_s": e["gvoxels_s"], "traffic": t_bytes, "traffic_source": t_src,
             "traffic_measured_in_run": False, "parity": e.get("parity"), "dst_edge": De}
     roofline["parity"] = par.summary()
+    if multi_ops is not None:
+        mp = {k: v.get("parity") for k, v in multi_ops.items() if isinstance(v, dict) and "parity" in v}
+        roofline["parity_single_process"] = {"all": (all(mp.values()) if mp else None) and "error" not in multi_ops, "ops": len(mp),
+                                             "failed": [k for k, v in mp.items() if not v], "error": multi_ops.get("error")}
     if sharded_ops is not None:
         # verdicts are AND-ed over the ranks inside run_sharded_ops; the summary counts this rank's planes
         sh = {k: v.get("parity") for k, v in sharded_ops.items() if isinstance(v, dict) and "parity" in v}
@@ -532,7 +560,7 @@ def run_ours(args):
             "roofline": roofline,
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "parity": dict(par.summary(), bit_exact_planes=planes, ok=bool(ok), per_op=par.results),
-            "ops": ops, "ops_sharded": sharded_ops,
+            "ops": ops, "ops_sharded": sharded_ops, "ops_single_process": multi_ops,
         }
         print(json.dumps(line))
     if dist is not None:
