@@ -23,4 +23,9 @@ namespace vkt
     // blocking contract of migrate(): on return the source may be freed (see include/vktb/backend.h)
     VKTAPI void Memcpy(void* dst, void const* src, std::size_t size, CopyKind ck);
     VKTAPI void MemsetRange(void* dst, void const* src, std::size_t dstSize, std::size_t srcSize);
+
+    // volkit-b200 extension: the GPUs the Device::GPU policy uses (one process, several devices).  Volumes of 1 GiB and
+    // more (VKTB_SHARD_MIN_MB) are then striped over them at Allocate time -- one data pointer spans the GPUs -- and
+    // Fill / Copy / the arithmetic family / Transform / Resample run on all of them; see vktb_set_devices.
+    VKTAPI Error SetDevices(int const* deviceIds, int numDevices);
 } // vkt

@@ -18,6 +18,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/Histogram.hpp>
 #include <vkt/InputStream.hpp>
+#include <vkt/Memory.hpp>
 #include <vkt/OutputStream.hpp>
 #include <vkt/RawFile.hpp>
 #include <vkt/Resample.hpp>
@@ -60,7 +61,8 @@ int main(int argc, char** argv)
 {
     if (argc < 3) return 2;
     const bool stream = std::strcmp(argv[1], "gpu-stream") == 0;    // GPU policy + host streaming extension
-    const bool gpu = stream || std::strcmp(argv[1], "gpu") == 0;
+    const bool multi = std::strncmp(argv[1], "gpu-multi", 9) == 0;  // GPU policy + a device group: "gpu-multi:0,0,0"
+    const bool gpu = stream || multi || std::strcmp(argv[1], "gpu") == 0;
     g_dir = argv[2];
 
     ExecutionPolicy cpu = GetThreadExecutionPolicy();            // default: CPU / Serial
@@ -74,6 +76,34 @@ int main(int argc, char** argv)
     std::thread([&] { childIsDefault = GetThreadExecutionPolicy().device == ExecutionPolicy::Device::CPU; }).join();
     if (!childIsDefault) return 4;
     SetThreadExecutionPolicy(cpu);
+
+    if (multi) {
+        // One process, several GPUs: volumes above the striping threshold (the test lowers it to 1 MiB) are striped over
+        // the group at allocation; the unchanged vkt:: calls then run on every device.  256 x 200 x 90 UInt16 = 9.2 MB.
+        int ids[16], n = 0;
+        for (const char* p = std::strchr(argv[1], ':'); p && *p && n < 16; p = std::strchr(p, ',')) ids[n++] = std::atoi(++p);
+        if (n < 2) return 10;
+        CHECK(SetDevices(ids, n));
+        const int MX = 256, MY = 200, MZ = 90;
+        StructuredVolume ma(MX, MY, MZ, DataFormat::UInt16), mb(MX, MY, MZ, DataFormat::UInt16);
+        {
+            uint16_t* pa = (uint16_t*)ma.getData();
+            uint16_t* pb = (uint16_t*)mb.getData();
+            for (std::size_t i = 0; i < (std::size_t)MX * MY * MZ; ++i) {
+                pa[i] = (uint16_t)((i * 2654435761ull) >> 11);
+                pb[i] = (uint16_t)((i * 40503ull + 12345ull) >> 3);
+            }
+        }
+        StructuredVolume msum(MX, MY, MZ, DataFormat::UInt16), mup(384, 300, 135, DataFormat::UInt16);
+        SetThreadExecutionPolicy(run);
+        CHECK(SafeSum(msum, ma, mb));                          // migrate(): striped H2D on all copy engines, then fan-out
+        CHECK(SumRange(msum, ma, mb, Vec3i{ 2, 3, 4 }, Vec3i{ 250, 190, 80 }, Vec3i{ 1, 2, 9 }));
+        CHECK(Resample(mup, ma, FilterMode::Linear));
+        SetThreadExecutionPolicy(cpu);
+        save(msum, "out_m_sum.raw"); save(mup, "out_m_up.raw");
+        int one = ids[0];
+        (void)one;
+    }
 
     const int X = 48, Y = 40, Z = 36;
     StructuredVolume a(X, Y, Z, DataFormat::UInt16), b(X, Y, Z, DataFormat::UInt16);

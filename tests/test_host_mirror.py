@@ -129,6 +129,19 @@ def run_cpp(programs, policy, tmp):
     assert raw(tmp / "out_sci.raw", dims, np.uint16).tobytes() == ref.a.tobytes()
     want = b"".join(x.tobytes() for x in o.brick_decompose(a, (20, 16, 16), (1, 2, 0), (2, 1, 1)))
     assert (tmp / "out_bricks.raw").read_bytes() == want
+    if policy.startswith("gpu-multi"):
+        # the device-group prelude: SafeSum, SumRange with a z offset and Resample on striped 256 x 200 x 90 volumes
+        md = (256, 200, 90)
+        i = np.arange(md[0] * md[1] * md[2], dtype=np.uint64)
+        ma = po.Vol(((i * np.uint64(2654435761)) >> np.uint64(11)).astype(np.uint16).reshape(md[2], md[1], md[0]), U16)
+        mb = po.Vol(((i * np.uint64(40503) + np.uint64(12345)) >> np.uint64(3)).astype(np.uint16).reshape(md[2], md[1], md[0]), U16)
+        ref = po.empty(md, U16)
+        o.arith_range(po.SAFESUM, ref, ma, mb, (0, 0, 0), md)
+        o.arith_range(po.SUM, ref, ma, mb, (2, 3, 4), (250, 190, 80), (1, 2, 9))
+        assert raw(tmp / "out_m_sum.raw", md, np.uint16).tobytes() == ref.a.tobytes()
+        ref = po.empty((384, 300, 135), U16)
+        o.resample(ref, ma, po.LINEAR)
+        assert raw(tmp / "out_m_up.raw", (384, 300, 135), np.uint16).tobytes() == ref.a.tobytes()
     if policy == "gpu-stream":
         # the host-streaming prelude: same voxels as the migrating calls
         ref = po.empty(dims, U16)
@@ -214,6 +227,17 @@ def test_cpp_api_gpu_policy(programs, tmp_path):
 def test_cpp_api_gpu_policy_host_streaming(programs, tmp_path, monkeypatch):
     monkeypatch.setenv("VKTB_HOSTED_SLAB_KB", "16")      # several slabs even on the 48x40x36 test volumes
     run_cpp(programs, "gpu-stream", tmp_path)
+
+
+@pytest.mark.gpu
+def test_cpp_api_gpu_policy_device_group(programs, tmp_path, monkeypatch):
+    """vkt:: calls of ONE process on a device group: real GPUs when two are visible, else the same GPU named twice
+    (striped volumes, fan-out and per-stripe copies all run; only the peer loads stay local)"""
+    import torch
+    monkeypatch.setenv("VKTB_SHARD_MIN_MB", "1")
+    n = torch.cuda.device_count()
+    ids = ",".join(str(i) for i in range(min(n, 4))) if n >= 2 else "0,0,0"
+    run_cpp(programs, "gpu-multi:" + ids, tmp_path)
 
 
 @pytest.mark.gpu

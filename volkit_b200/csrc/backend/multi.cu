@@ -77,7 +77,7 @@ size_t shardMinBytes()
 {
     const char* e = getenv("VKTB_SHARD_MIN_MB");
     const long mb = e ? atol(e) : 0;
-    return mb > 0 ? (size_t)mb << 20 : (size_t)1 << 30;      // default: volumes of 1 GiB and more are striped
+    return mb > 0 ? (size_t)mb << 20 : (size_t)1 << 30;      // default: volumes of 1 GiB and more are striped (read per call)
 }
 
 int setDeviceGroup(const int* ids, int n)

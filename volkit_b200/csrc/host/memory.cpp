@@ -72,6 +72,12 @@ namespace host
         if (vktb_memcpy(dst, src, size, (int)ck) != 0) host::backendError("Memcpy");
     }
 
+    Error SetDevices(int const* deviceIds, int numDevices)
+    {
+        if (vktb_set_devices(deviceIds, numDevices) != 0) return host::backendError("SetDevices");
+        return NoError;
+    }
+
     void MemsetRange(void* dst, void const* src, std::size_t dstSize, std::size_t srcSize)
     {
         ExecutionPolicy ep = GetThreadExecutionPolicy();
