@@ -317,6 +317,33 @@ def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
     ms_serial = time_steps(torch, step_serial, max(1, steps // 2), warmup, dist)
     sample_serial = grab()
 
+    # the box's ceiling for this traffic pattern: the same pinned buffers, two uploads and one download running full
+    # duplex on two streams, every rank at once, NO kernel and no slab pipeline -- bare cudaMemcpyAsync through torch
+    up_s, down_s = torch.cuda.Stream(), torch.cuda.Stream()
+    try:
+        # torch views of the SAME pinned host buffers (cudaHostAlloc memory: torch sees it as pinned) and device tensors
+        hts = [torch.frombuffer((ctypes.c_uint8 * vol_bytes).from_address(h), dtype=torch.uint8) for h in host]
+        dts = [torch.empty(vol_bytes, dtype=torch.uint8, device="cuda") for _ in range(3)]
+
+        def step_bare():
+            cur = torch.cuda.current_stream()
+            up_s.wait_stream(cur); down_s.wait_stream(cur)
+            with torch.cuda.stream(up_s):
+                dts[0].copy_(hts[0], non_blocking=True)
+                dts[1].copy_(hts[1], non_blocking=True)
+            with torch.cuda.stream(down_s):
+                hts[2].copy_(dts[2], non_blocking=True)
+            cur.wait_stream(up_s); cur.wait_stream(down_s)
+
+        keep = grab()                                   # the bare download overwrites host[2]
+        ms_bare = time_steps(torch, step_bare, max(2, steps // 2), 1, dist)
+        ctypes.memmove(host[2], keep.ctypes.data, keep.nbytes)
+        del dts, hts
+        torch.cuda.empty_cache()
+    except Exception as exc:
+        print(f"bench: bare-copy probe skipped: {exc!r}", file=sys.stderr)
+        ms_bare = None
+
     # what an UNMODIFIED reference caller gets: pageable malloc memory (Allocate_serial, Memory_serial.hpp:13-16)
     # migrated through the 4 x 16 MiB pinned staging ring, kernel, staged D2H.  Timed on the first eighth of the planes
     # (the per-voxel rate does not depend on the slab height; keeps another 3 full volumes out of host memory).
@@ -338,7 +365,7 @@ def run_e2e(torch, lib, capi, dv, size, steps, warmup, dist, src_a, src_b):
         a.free(); b.free(); d.free()
 
     ms_pageable = time_steps(torch, step_pageable, 2, 1, dist)
-    pageable = {"ms": ms_pageable, "voxels": size * size * pz,
+    pageable = {"ms": ms_pageable, "voxels": size * size * pz, "bare_copy_ms": ms_bare,
                 "same_bytes_as_pinned": bool(pag[2][:size * size * 2].tobytes() == sample_serial.tobytes())}
     del pag
     ctypes.memset(host[2], 0, size * size * 2)
@@ -460,6 +487,11 @@ def run_ours(args):
                "serial_migrate_ms": e_ms_serial,
                "serial_migrate_workload": "vktb_memcpy H2D x2 -> vktb_arith_range -> vktb_memcpy D2H (whole buffers, "
                                           "what ManagedBuffer::migrate() does)",
+               "copy_ceiling_value": (world * Se ** 3 / (pageable["bare_copy_ms"] * 1e-3) / 1e9) if pageable.get("bare_copy_ms") else None,
+               "copy_ceiling_ms": pageable.get("bare_copy_ms"),
+               "copy_ceiling_note": "bare cudaMemcpyAsync of the same pinned buffers (2 x H2D on one stream, D2H on another, "
+                                    "all ranks at once, no kernel): what the host side of this box allows for the pattern",
+               "frac_of_copy_ceiling": (pageable["bare_copy_ms"] / e_ms) if pageable.get("bare_copy_ms") else None,
                "pageable_migrate_value": world * pageable["voxels"] / (pageable["ms"] * 1e-3) / 1e9,
                "pageable_migrate_ms": pageable["ms"],
                "pageable_migrate_workload": f"pageable malloc buffers, {Se}x{Se}x{max(1, Se // 8)} UInt16 slab: vktb_memcpy "
