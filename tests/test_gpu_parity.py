@@ -937,6 +937,25 @@ def test_empty_and_degenerate_ranges(gpu):
     assert int(one.a[0, 0, 0]) == 127
 
 
+def test_pageable_round_trip_through_the_copy_pool(gpu):
+    """pageable host memory travels through the pinned staging ring; chunks of 2 MiB and more are cut into parts copied
+    by several threads (memory.cu CopyPool): a 70 MB array of odd length comes back byte for byte, several times"""
+    from volkit_b200 import capi
+    lib = gpu.lib
+    n = 70 * 1000 * 1000 + 13
+    for seed in (1, 2, 3):
+        a = po.synth_numpy(n, po.UINT8, seed)
+        p = ctypes.c_void_p()
+        capi.check(lib.vktb_alloc(ctypes.byref(p), n))
+        capi.check(lib.vktb_memcpy(p, a.ctypes.data, n, capi.H2D))
+        a_copy = a.copy()
+        a[:] = 0                                            # the source may be overwritten on return
+        back = np.empty(n, np.uint8)
+        capi.check(lib.vktb_memcpy(back.ctypes.data, p, n, capi.D2H))
+        assert back.tobytes() == a_copy.tobytes()
+        capi.check(lib.vktb_free(p))
+
+
 def test_memset_and_pools(gpu):
     from volkit_b200 import capi
     from volkit_b200.device import DeviceVolume

@@ -41,7 +41,7 @@ def run_cpp(programs, policy, tmp):
     a, b = cases.mk(dims, U16, 1), cases.mk(dims, U16, 2)
     a.a.tofile(tmp / "a.raw")
     b.a.tofile(tmp / "b.raw")
-    r = subprocess.run([programs["cpp"], policy, str(tmp)], capture_output=True, text=True)
+    r = subprocess.run([programs["cpp"], policy, str(tmp)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout, r.stderr)
 
     full = ((0, 0, 0), dims)
@@ -157,7 +157,7 @@ def run_cpp(programs, policy, tmp):
 
 def run_c(programs, policy, tmp):
     o = po.oracle()
-    r = subprocess.run([programs["c"], policy, str(tmp)], capture_output=True, text=True)
+    r = subprocess.run([programs["c"], policy, str(tmp)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout, r.stderr)
     dims = (40, 32, 24)
     full = ((0, 0, 0), dims)

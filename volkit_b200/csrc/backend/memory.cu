@@ -2,8 +2,11 @@
 #include "context.hpp"
 
 #include <algorithm>
+#include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "../../../include/vktb/backend.h"
 #include "../kernels/launch.hpp"
@@ -20,6 +23,9 @@ static thread_local bool t_hasOverride = false;
 void setError(const std::string& msg) { t_error = msg; }
 int fail(const char* what, cudaError_t e)
 {
+    // the error is reported HERE: clear the runtime's (non-sticky) last-error slot, or a later launcher's
+    // cudaGetLastError() would blame its own, successful launch for it
+    cudaGetLastError();
     t_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
     return (int)e ? (int)e : -1;
 }
@@ -246,6 +252,75 @@ int vktb_sync(void)
 // ================================================================ C-ABI: memory ==========================
 namespace {
 
+// ---- staging copies on several cores ---------------------------------------------------------------------------------
+// Pageable host memory reaches the device through the pinned staging ring; ONE core moves about 10 GB/s, a fifth of
+// what the link takes, so a 16 MiB chunk is cut into parts copied by a small pool of persistent threads (the caller
+// copies the first part itself).  VKTB_COPY_THREADS overrides the pool size (1 = the old single-threaded copy).
+class CopyPool
+{
+public:
+    // never destroyed: the detached workers wait on its condition variable for the life of the process, and
+    // destroying a condition variable with waiters blocks at exit (glibc)
+    static CopyPool& get() { static CopyPool* p = new CopyPool; return *p; }
+
+    void copy(void* dst, const void* src, size_t n)
+    {
+        const int parts = (int)std::min<size_t>((size_t)workers_.size() + 1, n / ((size_t)1 << 20));
+        if (parts <= 1) { memcpy(dst, src, n); return; }
+        std::lock_guard<std::mutex> one(callMutex_);            // one split copy at a time
+        const size_t per = ((n / parts) + 63) & ~(size_t)63;
+        {
+            std::lock_guard<std::mutex> l(m_);
+            dst_ = (uint8_t*)dst; src_ = (const uint8_t*)src; n_ = n; per_ = per;
+            next_ = 1; pending_ = parts - 1; parts_ = parts;
+            ++generation_;
+        }
+        cv_.notify_all();
+        memcpy(dst, src, std::min(per, n));                      // part 0 on the calling thread
+        std::unique_lock<std::mutex> l(m_);
+        done_.wait(l, [&] { return pending_ == 0; });
+    }
+
+private:
+    CopyPool()
+    {
+        const char* e = getenv("VKTB_COPY_THREADS");
+        int want = e ? atoi(e) : 0;
+        if (want <= 0) {
+            const unsigned hw = std::thread::hardware_concurrency();
+            want = (int)std::min(8u, std::max(1u, hw / 4));
+        }
+        for (int i = 1; i < want; ++i) workers_.emplace_back([this] { run(); });
+        for (auto& t : workers_) t.detach();                     // process-lifetime pool
+    }
+
+    void run()
+    {
+        unsigned long long seen = 0;
+        for (;;) {
+            int part;
+            {
+                std::unique_lock<std::mutex> l(m_);
+                cv_.wait(l, [&] { return generation_ != seen && next_ < parts_; });
+                part = next_++;
+                if (next_ >= parts_) seen = generation_;
+            }
+            const size_t off = (size_t)part * per_;
+            if (off < n_) memcpy(dst_ + off, src_ + off, std::min(per_, n_ - off));
+            std::lock_guard<std::mutex> l(m_);
+            if (--pending_ == 0) done_.notify_all();
+        }
+    }
+
+    std::vector<std::thread> workers_;
+    std::mutex m_, callMutex_;
+    std::condition_variable cv_, done_;
+    uint8_t* dst_ = nullptr; const uint8_t* src_ = nullptr;
+    size_t n_ = 0, per_ = 0;
+    int next_ = 0, parts_ = 0, pending_ = 0;
+    unsigned long long generation_ = 0;
+};
+
 // pageable host -> device through the staging ring; returns once the source has been fully read
 int stagedH2D(DeviceCtx* d, uint8_t* dst, const uint8_t* src, size_t bytes)
 {
@@ -262,7 +337,7 @@ int stagedH2D(DeviceCtx* d, uint8_t* dst, const uint8_t* src, size_t bytes)
     for (size_t off = 0; off < bytes; off += kStageBytes, slot = (slot + 1) % kStageSlots) {
         const size_t n = std::min(kStageBytes, bytes - off);
         if (d->stageInFlight[slot]) { cudaEventSynchronize(d->stageDone[slot]); d->stageInFlight[slot] = false; }
-        memcpy(d->stage[slot], src + off, n);
+        CopyPool::get().copy(d->stage[slot], src + off, n);
         cudaError_t e = cudaMemcpyAsync(dst + off, d->stage[slot], n, cudaMemcpyHostToDevice, cs);
         if (e != cudaSuccess) return fail("cudaMemcpyAsync(H2D staged)", e);
         cudaEventRecord(d->stageDone[slot], cs);
@@ -300,7 +375,7 @@ int stagedD2H(DeviceCtx* d, uint8_t* dst, const uint8_t* src, size_t bytes)
         const int slot = (int)(drained % kStageSlots);
         cudaError_t e = cudaEventSynchronize(d->stageDone[slot]);
         if (e != cudaSuccess) return fail("D2H staged wait", e);
-        memcpy(dst + off, d->stage[slot], n);
+        CopyPool::get().copy(dst + off, d->stage[slot], n);
         ++drained;
     }
     return 0;
