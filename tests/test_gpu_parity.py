@@ -937,6 +937,61 @@ def test_empty_and_degenerate_ranges(gpu):
     assert int(one.a[0, 0, 0]) == 127
 
 
+def test_resample_f32_linear_gate(gpu):
+    """Float32 under reference-faithful Linear: clean data takes scan -> one-tap rows -> gated (skipped) march; ONE
+    Inf, NaN or -0 anywhere in the source flips the gate and the exact 8-tap march recomputes everything.  Bit-exact
+    against the oracle either way (the poisoned voxels sit where they are the +1 taps of other voxels: 0 * Inf = NaN
+    must spread exactly as in the reference, and -0 + +0 = +0 must lose its sign)."""
+    o = po.oracle()
+    S, D = (64, 48, 40), (96, 72, 60)          # 2:3 up-sampling, 16-byte aligned rows
+    base = po.synth(S, po.FLOAT32, 7)
+    base[0, 0, 0] = 0.0                          # a +0 voxel is clean
+    poisons = [None,
+               ((5, 7, 9), np.float32(np.inf)), ((39, 47, 63), np.float32(np.nan)), ((20, 3, 1), np.float32(-0.0)),
+               ((0, 0, 1), np.float32(-np.inf))]
+    for dfmt in (po.FLOAT32, po.UINT16):
+        for poison in poisons:
+            a = base.copy()
+            if poison is not None:
+                a[poison[0]] = poison[1]
+            src = po.Vol(a, po.FLOAT32)
+            want, got = po.empty(D, dfmt), po.empty(D, dfmt)
+            o.resample(want, src, po.LINEAR)
+            gpu.resample(got, src, po.LINEAR)
+            assert same_bits(got.a, want.a), (dfmt, poison)
+    # a whole plane of NaN
+    a = base.copy()
+    a[21, :, :] = np.float32(np.nan)
+    src = po.Vol(a, po.FLOAT32)
+    want, got = po.empty(D, po.FLOAT32), po.empty(D, po.FLOAT32)
+    o.resample(want, src, po.LINEAR)
+    gpu.resample(got, src, po.LINEAR)
+    assert same_bits(got.a, want.a)
+    # z-window form (sharded / striped volumes): dst planes [12, 30) read src planes [8, 21); the poison sits ONLY in
+    # src plane 20 = the +1 tap plane of the last dst plane, which no dst plane of the window maps to as its lo plane
+    # (the row pipeline never stages it: the small separate scan has to see it)
+    from volkit_b200 import capi
+    from volkit_b200.device import DeviceVolume
+    lib = gpu.lib
+    dz0, dz1 = 12, 30
+    s0, s1 = ctypes.c_int32(), ctypes.c_int32()
+    capi.check(lib.vktb_resample_window_src_range3(capi.LINEAR, dz0, dz1, capi.I3(*D), capi.I3(*S), ctypes.byref(s0), ctypes.byref(s1)))
+    assert int(29 / 60 * 40) == 19 and s0.value <= 8 and s1.value >= 21
+    for poison_plane, value in ((20, np.float32(np.inf)), (None, None), (s0.value, np.float32(-0.0))):
+        a = base.copy()
+        if poison_plane is not None:
+            a[poison_plane, 11, 13] = value
+        win = np.ascontiguousarray(a[s0.value:s1.value])
+        want = po.empty((D[0], D[1], dz1 - dz0), po.FLOAT32)
+        o.resample_window(want, po.Vol(win, po.FLOAT32), po.LINEAR, dz0, D, s0.value, S)
+        dsrc = DeviceVolume.from_numpy(win, capi.FLOAT32)
+        ddst = DeviceVolume((D[0], D[1], dz1 - dz0), capi.FLOAT32)
+        capi.check(lib.vktb_resample_window(ctypes.byref(ddst.desc()), ctypes.byref(dsrc.desc()), capi.LINEAR, dz0, capi.I3(*D),
+                                            s0.value, capi.I3(*S)), "resample window")
+        assert same_bits(ddst.download(), want.a), (poison_plane,)
+        dsrc.free(); ddst.free()
+
+
 def test_pageable_round_trip_through_the_copy_pool(gpu):
     """pageable host memory travels through the pinned staging ring; chunks of 2 MiB and more are cut into parts copied
     by several threads (memory.cu CopyPool): a 70 MB array of odd length comes back byte for byte, several times"""

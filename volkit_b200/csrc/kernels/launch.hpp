@@ -51,11 +51,11 @@ cudaError_t launchTransform2(const LaunchCtx&, const VolDesc& v1, const VolDesc&
 cudaError_t launchResample(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, int filter,
                            int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
 cudaError_t launchResampleRowRuns(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
-                                  int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
+                                  int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3], unsigned* tapFlag = nullptr);
 cudaError_t launchScaleRowRuns(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const float m[3],
                                const float center[3], const int32_t first[3], const int32_t last[3]);
 cudaError_t launchResampleMarch(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, int mode /*1 Linear8, 2 trilinear*/,
-                                int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3]);
+                                int dstZ0, const int32_t dstFull[3], int srcZ0, const int32_t srcFull[3], const unsigned* gate = nullptr);
 cudaError_t launchConvertFlat(const LaunchCtx&, const VolDesc& dst, uint8_t* d, const VolDesc& src, const uint8_t* s, size_t n);
 cudaError_t launchConvertRows(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3],
                               const int32_t last[3], const int32_t off[3]);

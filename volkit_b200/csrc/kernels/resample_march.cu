@@ -141,6 +141,7 @@ struct MarchParams
     int spillOff;           // byte offset of the spill column (byS rows x 16 bytes) inside a slot
     int zpackOff;           // int offset of the int4 per-plane records in tab
     const int* tab;
+    const unsigned* gate;   // when set: the kernel runs only if *gate != 0 (see launchResample: Float32 Linear)
     Mapping md, ms;
 };
 
@@ -169,6 +170,7 @@ template <int FS, int FD, int MODE, bool IDENT>
 __global__ void __launch_bounds__(kMarchThreads)
 resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapSpill, MarchParams p)
 {
+    if (p.gate && *p.gate == 0u) return;     // uniform: the one-tap result already in dst is exact (launchResample)
     constexpr int BS = bytesPerVoxel(FS), BD = bytesPerVoxel(FD);
     constexpr int VPT = marchVoxelsPerThread(BD);
     constexpr int SB = VPT * BD;             // bytes per store
@@ -455,7 +457,7 @@ cudaError_t launchMarchDst(const LaunchCtx& c, const CUtensorMap* tm, const Marc
 // 8-tap resample (mode 1 = reference-faithful Linear, 2 = true trilinear) through the TMA z-march.  Returns
 // cudaErrorNotSupported when the operands do not qualify; the caller then uses the direct-gather kernel.
 cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, int mode,
-                                int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3])
+                                int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3], const unsigned* gate)
 {
     const int bs = bytesPerVoxel(src.format), bd = bytesPerVoxel(dst.format);
     const int dzCount = dst.dims[2], szCount = src.dims[2];
@@ -475,6 +477,7 @@ cudaError_t launchResampleMarch(const LaunchCtx& c, const VolDesc& dst, const Vo
     p.Dx = D[0]; p.Dy = D[1]; p.dzCount = dzCount;
     p.Sx = S[0]; p.Sy = S[1]; p.szCount = szCount;
     p.md = dst.map; p.ms = src.map;
+    p.gate = gate;
     p.BXv = kLanesX * marchVoxelsPerThread(bd);
     p.tilesX = (D[0] + p.BXv - 1) / p.BXv;
     // src brick extents: floor(tile * S / D) + 3 covers lo .. hi of the tile (hi may be lo + 2 after rounding)

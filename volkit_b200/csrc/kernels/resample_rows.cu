@@ -119,6 +119,7 @@ struct RowRunParams
     int stages;                // src stages in flight (<= kMaxStages)
     int srcStageRow;           // bytes reserved per src row segment in a stage (multiple of 16)
     const int* tab;
+    unsigned* tapFlag;         // Float32 sources only: set to 1 when a staged src value is Inf, NaN or -0 (resample.cu)
     Mapping md, ms;
 };
 
@@ -218,6 +219,7 @@ resampleRowRunKernel(RowRunParams p)
     }
 
     long long k = 0;
+    bool badTap = false;
     for (long long item = g; item < nItems; item += G, ++k) {
         const int stage = (int)(k % S);
         if (t < 32) {
@@ -230,6 +232,19 @@ resampleRowRunKernel(RowRunParams p)
         const int r0 = yg * p.R, nr = min(p.R, nyr - r0);
         const int z0 = zStart[zr], z1 = zStart[zr + 1];
         const uint8_t* sb = smem + stage * stageBytes;
+        if (FS == F_F32 && p.tapFlag) {
+            // every staged src value is looked at once (the whole source, when the axis maps are onto): Inf / NaN / -0
+            for (int r = 0; r < nr; ++r) {
+                const uint4* row = reinterpret_cast<const uint4*>(sb + r * p.srcStageRow);
+                for (int v = t; v < srcBytes / 16; v += kRowThreads) {
+                    const uint4 q = row[v];
+                    badTap |= (q.x & 0x7f800000u) == 0x7f800000u || q.x == 0x80000000u
+                           || (q.y & 0x7f800000u) == 0x7f800000u || q.y == 0x80000000u
+                           || (q.z & 0x7f800000u) == 0x7f800000u || q.z == 0x80000000u
+                           || (q.w & 0x7f800000u) == 0x7f800000u || q.w == 0x80000000u;
+                }
+            }
+        }
         for (int r = 0; r < nr; ++r) {
             const uint8_t* srow = sb + r * p.srcStageRow;
             const int y0 = yStart[r0 + r], y1 = yStart[r0 + r + 1];
@@ -256,6 +271,7 @@ resampleRowRunKernel(RowRunParams p)
         __syncwarp();
         if ((t & 31) == 0) mbarArrive(smemAddr(&empty[stage]));
     }
+    if (FS == F_F32 && badTap) atomicOr(p.tapFlag, 1u);
 }
 
 template <int FS, int FD, bool MOVE>
@@ -288,7 +304,7 @@ cudaError_t launchRowRunDst(const LaunchCtx& c, const RowRunParams& p, int fd, s
 // slope: a dst tile of w voxels taps at most w * spanNum / spanDen + 2 src voxels)
 static cudaError_t launchRowRunsMapped(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src, int dstZ0,
                                        const int32_t D[3], int srcZ0, const int32_t S[3], const AxisMap maps[3],
-                                       long long spanNum, long long spanDen, bool up)
+                                       long long spanNum, long long spanDen, bool up, unsigned* tapFlag = nullptr)
 {
     const int bs = bytesPerVoxel(src.format), bd = bytesPerVoxel(dst.format);
     const int dzCount = dst.dims[2];
@@ -304,6 +320,7 @@ static cudaError_t launchRowRunsMapped(const LaunchCtx& c, const VolDesc& dst, c
     p.Dx = D[0]; p.Dy = D[1]; p.dzCount = dzCount;
     p.Sx = S[0]; p.Sy = S[1]; p.srcZ0 = srcZ0;
     p.md = dst.map; p.ms = src.map;
+    p.tapFlag = src.format == F_F32 ? tapFlag : nullptr;
 
     // x tile: at most kMaxChunks 16-byte dst chunks per thread (8 KiB of dst)
     int tileW = kMaxChunks * kRowThreads * (16 / bd);
@@ -376,12 +393,12 @@ static cudaError_t launchRowRunsMapped(const LaunchCtx& c, const VolDesc& dst, c
 // One-tap resample through the TMA row pipeline.  Returns cudaErrorNotSupported when the operands do not
 // qualify (unaligned rows, Int16, giant dims); the caller then uses the direct-gather kernel.
 cudaError_t launchResampleRowRuns(const LaunchCtx& c, const VolDesc& dst, const VolDesc& src,
-                                  int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3])
+                                  int dstZ0, const int32_t D[3], int srcZ0, const int32_t S[3], unsigned* tapFlag)
 {
     // (D-1)/float(D)*S < S holds in binary32 below 2^24 (checked by the core), so every tap lies inside the src row
     AxisMap maps[3];
     for (int a = 0; a < 3; ++a) maps[a] = AxisMap{ 0, D[a], S[a], 0.f, 0.f };
-    return launchRowRunsMapped(c, dst, src, dstZ0, D, srcZ0, S, maps, S[0], D[0], D[0] > S[0]);
+    return launchRowRunsMapped(c, dst, src, dstZ0, D, srcZ0, S, maps, S[0], D[0], D[0] > S[0], tapFlag);
 }
 
 // Scale (diagonal affine gather, one-tap modes) whose EVERY dst voxel maps inside the source: a separable monotone
