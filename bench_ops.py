@@ -423,6 +423,32 @@ def run_ops(torch, lib, capi, DeviceVolume, S, peak, time_steps, parity=None, st
     record(f"SafeSum {tag}", n8, 3 * n8,
            lambda: capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(d_d8), ctypes.byref(d_a8), ctypes.byref(d_b8), z3, l8, z3)),
            check=lambda nm: check_arith(nm, d8, po.SAFESUM, po.UINT8, dims8, (1, 2), (0, 0, 0), dims8, (0, 0, 0), prefilled=False))
+    bins8 = ctypes.c_void_p()
+    capi.check(lib.vktb_alloc(ctypes.byref(bins8), 256 * 8))
+
+    def check_hist8(name):
+        """all voxels: byte-value counts (torch.bincount, checker side) x the oracle's value -> bin table == bins"""
+        table = np.full(256, -1, np.int64)
+        tv = po.Vol(np.arange(256, dtype=np.uint8).reshape(1, 1, 256), po.UINT8)
+        for v in range(256):
+            hb, dropped = o.histogram_range(tv, (v, 0, 0), (v + 1, 1, 1), 256)
+            if not dropped:
+                table[v] = int(np.argmax(hb))
+        counts = torch.zeros(256, dtype=torch.int64, device="cuda")
+        vals = torch.as_tensor(_Raw(a8.ptr, n8, "|u1"), device="cuda")
+        for f0 in range(0, n8, 1 << 28):
+            counts += torch.bincount(vals[f0:f0 + (1 << 28)].to(torch.int32), minlength=256)
+        tt = torch.from_numpy(table).cuda()
+        want = torch.zeros(256, dtype=torch.int64, device="cuda").index_add_(0, tt.clamp(min=0), counts * (tt >= 0))
+        got = np.empty(256, np.uint64)
+        capi.check(lib.vktb_memcpy(got.ctypes.data, bins8.value, 256 * 8, capi.D2H))
+        torch.cuda.empty_cache()
+        return parity.record(name, got.astype(np.int64).tolist() == want.cpu().tolist() and int(got.sum()) == n8,
+                             "all voxels: value counts x the oracle's value->bin table == bins")
+
+    record(f"Histogram 256 bins {tag}", n8, n8,
+           lambda: capi.check(lib.vktb_histogram_range(ctypes.byref(d_a8), z3, l8, bins8, 256, None)), check=check_hist8)
+    capi.check(lib.vktb_free(bins8))
     a8.free(); b8.free(); d8.free()
 
     # ---- headless ray-marcher (SURVEY 8(f) rank 4, last row): 1024^3 UInt8, the viewer's defaults (45 degrees,

@@ -937,6 +937,27 @@ def test_empty_and_degenerate_ranges(gpu):
     assert int(one.a[0, 0, 0]) == 127
 
 
+def test_histogram_private_counters(gpu):
+    """up to 256 bins over a contiguous range of >= 2^22 voxels: the lane-private counter kernel (no atomics; UInt8
+    counts byte values and bins them in the flush).  Exact against the oracle: random data, a constant volume (every
+    vote of a group hits the same counter), non-identity mappings whose bins fall partly outside [0, numBins) (the
+    reference writes out of bounds there: dropped and counted), odd bin counts, a range that starts off a 16-byte
+    boundary (whole planes from plane 1 of a volume with an odd plane size)."""
+    o = po.oracle()
+    for fmt, dims in ((po.UINT8, (255, 257, 70)), (po.UINT16, (256, 256, 70)), (po.UINT32, (256, 128, 130)),
+                      (po.FLOAT32, (128, 256, 130))):
+        data = po.synth(dims, fmt, 9)
+        const = np.full_like(data, 77)
+        for arr, lo, hi, nb in ((data, 0.0, 1.0, 256), (data, 0.0, 1.0, 37), (const, 0.0, 1.0, 256),
+                                (data, 0.25, 0.75, 200), (data, -1.0, 2.0, 255)):
+            vol = po.Vol(arr, fmt, lo, hi)
+            for first in ((0, 0, 0), (0, 0, 1)):
+                want, wdrop = o.histogram_range(vol, first, dims, nb)
+                got, gdrop = gpu.histogram_range(vol, first, dims, nb)
+                assert got.tobytes() == want.tobytes() and gdrop == wdrop, (fmt, lo, hi, nb, first)
+                assert int(got.sum()) + gdrop == dims[0] * dims[1] * (dims[2] - first[2])
+
+
 def test_resample_f32_linear_gate(gpu):
     """Float32 under reference-faithful Linear: clean data takes scan -> one-tap rows -> gated (skipped) march; ONE
     Inf, NaN or -0 anywhere in the source flips the gate and the exact 8-tap march recomputes everything.  Bit-exact
