@@ -335,6 +335,9 @@ int vktb_lookup_unary_op(const void* host_fn, int* op);   /* non-zero if unbound
 int vktb_lookup_binary_op(const void* host_fn, int* op);
 
 /* ---- scalar codec on the device (1 thread): used by tests to pin the float/convert emulation ----- */
+/* whether map_dst's division by (hi - lo) runs in the reciprocal-and-two-FMA form for this mapping: 1 after the
+ * exhaustive proof against __fdiv_rn (all 2^32 dividends, once per divisor and process) succeeded, else 0 */
+int vktb_debug_div_proven(float lo, float hi, int* proven);
 int vktb_debug_map_unmap(int format, float lo, float hi, const float* values_dev, uint32_t* mapped_dev,
                          float* unmapped_dev, size_t n);
 

@@ -937,6 +937,37 @@ def test_empty_and_degenerate_ranges(gpu):
     assert int(one.a[0, 0, 0]) == 127
 
 
+def test_arith_mapped_proven_division(gpu):
+    """map_dst divides by hi - lo once per voxel.  From 2^22 voxels on, the flat kernel uses the reciprocal-and-two-FMA
+    form for divisors it has PROVEN against __fdiv_rn on all 2^32 dividends (arith.cu proveDivisor).  Bit-exact against
+    the oracle for several ranges (4000, 3, 0.7, 1e-3 .. 1e3, a negative one) and for ops whose results span zero,
+    tiny, huge, Inf and NaN before the division (Quot by zero, Prod of large values)."""
+    from concurrent.futures import ThreadPoolExecutor
+    o = po.oracle()
+    dims = (256, 256, 70)
+    pool = ThreadPoolExecutor(min(16, os.cpu_count() or 1))
+    slabs = [(z, min(z + 5, dims[2])) for z in range(0, dims[2], 5)]
+    for fmt in (po.UINT16, po.FLOAT32):
+        s1, s2 = po.synth(dims, fmt, 1), po.synth(dims, fmt, 2)
+        if fmt == po.FLOAT32:
+            s1 = (s1 * np.float32(4000.0) - np.float32(1000.0)).astype(np.float32)
+            s2[::7, ::3, ::5] = 0.0                     # Quot by zero -> Inf / NaN in front of the division
+        for (lo, hi), ops in (((-1000.0, 3000.0), (po.SAFEPROD, po.QUOT, po.SUM)), ((0.0, 3.0), (po.SAFEQUOT, po.PROD)),
+                              ((0.1, 0.8), (po.DIFF,)), ((1e-3, 1e3), (po.QUOT,)), ((2.0, -5.0), (po.SAFESUM,))):
+            a, b = po.Vol(s1, fmt, lo, hi), po.Vol(s2, fmt)
+            for op in ops:
+                want, got = po.empty(dims, fmt, lo, hi), po.empty(dims, fmt, lo, hi)
+
+                def one(zz, op=op, want=want, a=a, b=b):
+                    z0, z1 = zz
+                    o.arith_range(op, po.Vol(want.a[z0:z1], fmt, lo, hi), po.Vol(a.a[z0:z1], fmt, lo, hi), po.Vol(b.a[z0:z1], fmt),
+                                  (0, 0, 0), (dims[0], dims[1], z1 - z0))
+                list(pool.map(one, slabs))
+                gpu.arith_range(op, got, a, b, (0, 0, 0), dims)
+                assert same_bits(got.a, want.a), (fmt, lo, hi, op)
+    pool.shutdown()
+
+
 def test_histogram_private_counters(gpu):
     """up to 256 bins over a contiguous range of >= 2^22 voxels: the lane-private counter kernel (no atomics; UInt8
     counts byte values and bins them in the flush).  Exact against the oracle: random data, a constant volume (every

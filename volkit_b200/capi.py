@@ -120,6 +120,7 @@ SIGNATURES = {
     "vktb_bind_binary_op": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "vktb_lookup_unary_op": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),
     "vktb_lookup_binary_op": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_int)]),
+    "vktb_debug_div_proven": (ctypes.c_int, [ctypes.c_float, ctypes.c_float, _P(ctypes.c_int)]),
     "vktb_debug_map_unmap": (ctypes.c_int, [ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_void_p,
                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]),
 }

@@ -673,6 +673,16 @@ int vktb_lookup_binary_op(const void* hostFn, int* op)
     return 0;
 }
 
+int vktb_debug_div_proven(float lo, float hi, int* proven)
+{
+    if (!proven) return fail("vktb_debug_div_proven: null argument");
+    DeviceCtx* d = currentDevice();
+    if (!d) return -1;
+    LaunchCtx c{ currentStream(d), d->smCount };
+    *proven = divisorProven(c, lo, hi);
+    return 0;
+}
+
 int vktb_debug_map_unmap(int format, float lo, float hi, const float* values, uint32_t* mapped, float* unmapped, size_t n)
 {
     if (!supportedFormat(format)) return fail("vktb_debug_map_unmap: unsupported format");

@@ -1,5 +1,8 @@
 // Arithmetic family launcher: picks flat / rows / generic kernels (see arith.cuh).
 #include <cstdlib>
+#include <mutex>
+#include <unordered_map>
+#include <cstring>
 #include "arith.cuh"
 #include "launch.hpp"
 
@@ -119,6 +122,65 @@ cudaError_t dispatchFormat(const LaunchCtx& c, const ArithPlan& pl)
 
 } // namespace
 
+// ---- proof of divProven for one divisor ------------------------------------------------------------------------------
+// Every binary32 dividend (2^32 bit patterns): divProven(x, d, RN(1/d)) against __fdiv_rn(x, d), bit for bit (NaN
+// results only have to be NaN on both sides, as everywhere in this library).  About 3 ms on a B200, once per divisor
+// and process; the verdict is cached.  VKTB_NO_PROVEN_DIV=1 keeps the IEEE division (A/B runs).
+__global__ void __launch_bounds__(256)
+divProofKernel(float d, float y, unsigned long long* bad)
+{
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned mism = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32); i += stride) {
+        const float x = __uint_as_float((uint32_t)i);
+        const float a = divProven(x, d, y), b = __fdiv_rn(x, d);
+        const bool same = __float_as_uint(a) == __float_as_uint(b) || (a != a && b != b);
+        mism += same ? 0u : 1u;
+    }
+    if (mism) atomicAdd(bad, (unsigned long long)mism);
+}
+
+static void proveDivisor(const LaunchCtx& c, Mapping& m)
+{
+    static std::mutex mu;
+    static std::unordered_map<uint32_t, int> proven;     // range bits -> 1 proven, 0 refuted / not provable
+    if (m.identity || m.exactRecip != 0 || m.invRange == 0.f) return;
+    static const bool off = getenv("VKTB_NO_PROVEN_DIV") != nullptr;
+    if (off) return;
+    uint32_t bits;
+    memcpy(&bits, &m.range, 4);
+    {
+        std::lock_guard<std::mutex> l(mu);
+        auto it = proven.find(bits);
+        if (it != proven.end()) { if (it->second) m.exactRecip = 2; return; }
+    }
+    int ok = 0;
+    unsigned long long* bad = nullptr;
+    if (cudaMallocAsync((void**)&bad, sizeof(*bad), c.stream) == cudaSuccess) {
+        unsigned long long h = ~0ull;
+        cudaMemsetAsync(bad, 0, sizeof(*bad), c.stream);
+        divProofKernel<<<(unsigned)c.smCount * 8u, 256, 0, c.stream>>>(m.range, m.invRange, bad);
+        countLaunch();
+        if (cudaMemcpyAsync(&h, bad, sizeof(h), cudaMemcpyDeviceToHost, c.stream) == cudaSuccess
+            && cudaStreamSynchronize(c.stream) == cudaSuccess)
+            ok = h == 0ull ? 1 : 0;
+        else
+            cudaGetLastError();
+        cudaFreeAsync(bad, c.stream);
+    }
+    std::lock_guard<std::mutex> l(mu);
+    proven[bits] = ok;
+    if (ok) m.exactRecip = 2;
+}
+
+// 1 / 0: whether x / (hi - lo) runs in the proven reciprocal form for this mapping (tests, notes)
+int divisorProven(const LaunchCtx& c, float lo, float hi)
+{
+    Mapping m = makeMapping(lo, hi);
+    proveDivisor(c, m);
+    return m.exactRecip == 2 ? 1 : 0;
+}
+
 cudaError_t launchArith(const LaunchCtx& c, int op, const VolDesc& dst, const VolDesc& s1, const VolDesc& s2,
                         const int32_t first[3], const int32_t last[3], const int32_t off[3])
 {
@@ -144,6 +206,8 @@ cudaError_t launchArith(const LaunchCtx& c, int op, const VolDesc& dst, const Vo
     pl.flat = pl.homogeneous && contiguous(dst, g) && contiguous(s1, g) && contiguous(s2, g)
            && ad == (reinterpret_cast<uintptr_t>(pl.p.a.base) & 15u)
            && ad == (reinterpret_cast<uintptr_t>(pl.p.b.base) & 15u);
+    // the one division per voxel is map_dst's (v - lo) / (hi - lo): the flat kernel has a loop for proven divisors
+    if (pl.flat && !pl.identity && pl.n >= ((size_t)1 << 22)) proveDivisor(c, pl.p.md);
 
     switch (op) {
     case 0: return dispatchFormat<0>(c, pl);

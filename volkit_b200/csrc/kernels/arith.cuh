@@ -7,6 +7,8 @@
 // Algorithmic traffic: bpv_s1 + bpv_s2 + bpv_dst bytes per voxel, every byte touched exactly once.
 #pragma once
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "voxel_codec.cuh"
 
@@ -42,7 +44,7 @@ struct ArithParams
 };
 
 // Homogeneous formats: one 128-bit vector per operand per chunk.
-template <int F, int OP, bool IDENT>
+template <int F, int OP, bool IDENT, bool PROVEN = false>
 __device__ __forceinline__ uint4 arithVec(const uint4& va, const uint4& vb, const Mapping& md,
                                           const Mapping& ma, const Mapping& mb, const float* lutA, const float* lutB)
 {
@@ -56,7 +58,7 @@ __device__ __forceinline__ uint4 arithVec(const uint4& va, const uint4& vb, cons
         if (F == F_U8) { fa = lutA[ra]; fb = lutB[rb]; }
         else { fa = unmapVoxel<F, IDENT>(ra, ma); fb = unmapVoxel<F, IDENT>(rb, mb); }
         float r = arithEval<OP>(fa, fb, md.lo, md.hi);
-        vecSet<BPV>(w, i, mapVoxel<F, IDENT>(r, md));
+        vecSet<BPV>(w, i, mapVoxel<F, IDENT, PROVEN>(r, md));
     }
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
@@ -98,22 +100,28 @@ arithFlatKernel(uint8_t* __restrict__ d, const uint8_t* a, const uint8_t* b, siz
     const uint8_t* bv = b + head * BPV;
     uint8_t* dv = d + head * BPV;
 
-    size_t i = tid;
-    // two vectors per operand in flight per thread
-    for (; i + stride < nvec; i += 2 * stride) {
-        uint4 a0, b0, a1, b1;
-        if (alias) { a0 = ldPlain(av + i * 16); b0 = ldPlain(bv + i * 16);
-                     a1 = ldPlain(av + (i + stride) * 16); b1 = ldPlain(bv + (i + stride) * 16); }
-        else       { a0 = ldStream(av + i * 16); b0 = ldStream(bv + i * 16);
-                     a1 = ldStream(av + (i + stride) * 16); b1 = ldStream(bv + (i + stride) * 16); }
-        stStream(dv + i * 16, arithVec<F, OP, IDENT>(a0, b0, md, ma, mb, lutA, lutB));
-        stStream(dv + (i + stride) * 16, arithVec<F, OP, IDENT>(a1, b1, md, ma, mb, lutA, lutB));
-    }
-    for (; i < nvec; i += stride) {
-        uint4 a0 = alias ? ldPlain(av + i * 16) : ldStream(av + i * 16);
-        uint4 b0 = alias ? ldPlain(bv + i * 16) : ldStream(bv + i * 16);
-        stStream(dv + i * 16, arithVec<F, OP, IDENT>(a0, b0, md, ma, mb, lutA, lutB));
-    }
+    // two vectors per operand in flight per thread; the division mode of map_dst is fixed for the launch, so the
+    // loops exist twice: with the proven reciprocal form (md.exactRecip == 2, see voxel_codec.cuh) and without
+    auto body = [&](auto provenTag) {
+        constexpr bool PROVEN = decltype(provenTag)::value;
+        size_t i = tid;
+        for (; i + stride < nvec; i += 2 * stride) {
+            uint4 a0, b0, a1, b1;
+            if (alias) { a0 = ldPlain(av + i * 16); b0 = ldPlain(bv + i * 16);
+                         a1 = ldPlain(av + (i + stride) * 16); b1 = ldPlain(bv + (i + stride) * 16); }
+            else       { a0 = ldStream(av + i * 16); b0 = ldStream(bv + i * 16);
+                         a1 = ldStream(av + (i + stride) * 16); b1 = ldStream(bv + (i + stride) * 16); }
+            stStream(dv + i * 16, arithVec<F, OP, IDENT, PROVEN>(a0, b0, md, ma, mb, lutA, lutB));
+            stStream(dv + (i + stride) * 16, arithVec<F, OP, IDENT, PROVEN>(a1, b1, md, ma, mb, lutA, lutB));
+        }
+        for (; i < nvec; i += stride) {
+            uint4 a0 = alias ? ldPlain(av + i * 16) : ldStream(av + i * 16);
+            uint4 b0 = alias ? ldPlain(bv + i * 16) : ldStream(bv + i * 16);
+            stStream(dv + i * 16, arithVec<F, OP, IDENT, PROVEN>(a0, b0, md, ma, mb, lutA, lutB));
+        }
+    };
+    if (!IDENT && md.exactRecip == 2) body(std::true_type{});
+    else body(std::false_type{});
     // head + tail voxels (at most 2*(V-1)), one per thread of the first CTA(s)
     const size_t nEdge = head + (n - tail0);
     for (size_t e = tid; e < nEdge; e += stride) {

@@ -45,6 +45,7 @@ cudaError_t launchCopyBatchNoAlloc(const LaunchCtx&, int n, const VolDesc* dsts,
                                    const int32_t* lasts, const int32_t* offs);
 cudaError_t launchArith(const LaunchCtx&, int op, const VolDesc& dst, const VolDesc& s1, const VolDesc& s2,
                         const int32_t first[3], const int32_t last[3], const int32_t off[3]);
+int divisorProven(const LaunchCtx&, float lo, float hi);
 cudaError_t launchTransform1(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3], int op);
 cudaError_t launchTransform2(const LaunchCtx&, const VolDesc& v1, const VolDesc& v2, const int32_t first[3],
                              const int32_t last[3], int op);

@@ -27,7 +27,9 @@ Mapping makeMapping(float lo, float hi)
     const uint32_t expo = (bits >> 23) & 0xffu, mant = bits & 0x7fffffu;
     // power of two, normal, with a normal reciprocal (2^-126 .. 2^126); sign may be either
     m.exactRecip = (mant == 0 && expo >= 1 && expo <= 253) ? 1 : 0;
-    m.invRange = m.exactRecip ? 1.0f / rr : 0.f;
+    // RN(1 / range) (an IEEE division on the host); used as is for powers of two, and by divProven once the divisor has
+    // been proven (proveDivisor, arith.cu)
+    m.invRange = (expo >= 1 && expo <= 253) ? 1.0f / rr : 0.f;
     uint32_t lb, hb; memcpy(&lb, &lo, 4); memcpy(&hb, &hi, 4);
     m.identity = (lb == 0u && hb == 0x3f800000u) ? 1 : 0;
     return m;

@@ -32,8 +32,9 @@ struct Mapping
 {
     float lo, hi;
     float range;      // hi - lo (computed in binary32 on the host, identical to the device result)
-    float invRange;   // 1/(hi-lo) when exactRecip, else unused
-    int   exactRecip; // hi-lo is a power of two with a representable reciprocal: x/range == x*invRange
+    float invRange;   // RN(1/(hi-lo)) when exactRecip != 0, else unused
+    int   exactRecip; // 1: hi-lo is a power of two with a representable reciprocal: x/range == x*invRange for every x
+                      // 2: x/range == divProven(x) for EVERY binary32 x, proven exhaustively on the device (arith.cu)
     int   identity;   // lo == +0.0f && hi == 1.0f (bit pattern): unmap/map reduce to pure scaling
 };
 
@@ -67,13 +68,36 @@ __device__ __forceinline__ uint32_t x86Cvtt64Low32(float f)
     return (f >= 9223372036854775808.0f) ? 0u : (uint32_t)(unsigned long long)r;
 }
 
+// ---- IEEE division by the mapping range ---------------------------------------------------------------
+// x / d for a divisor that stays the same for a whole volume.  With y = RN(1/d): q0 = RN(x*y), the residual
+// r = fma(-q0, d, x) is exact while nothing underflows or overflows, and q = fma(r, y, q0) is the correctly rounded
+// quotient for all but a few exceptional divisors (the last step of the classic reciprocal-based division; it needs
+// real FMAs, which --fmad=false does not take away from explicit fmaf calls).  "All but a few" is not bit-exact, so the
+// form is only used for divisors for which it has been PROVEN: arith.cu compares it with __fdiv_rn for all 2^32
+// dividends once per divisor.  Dividends outside [2^-63, 2^64) other than +-0 take the IEEE division (residual not
+// exact there).  Three arithmetic instructions instead of the ~11 plus a guarded slow-path call of __fdiv_rn.
+__device__ __forceinline__ float divProven(float x, float d, float y)
+{
+    const uint32_t mag = __float_as_uint(x) & 0x7fffffffu;
+    const float q0 = __fmul_rn(x, y);
+    if (mag - 0x20000000u < 0x3f800000u) {                     // exponent field in [64, 191)
+        const float r = __fmaf_rn(-q0, d, x);
+        return __fmaf_rn(r, y, q0);
+    }
+    // +-0 / d is the signed zero x * y already (the correction step would turn -0 into +0: caught by the proof)
+    return mag == 0u ? q0 : __fdiv_rn(x, d);
+}
+
 // ---- map: float -> raw (returned in the low bits of a uint32) ---------------------------------------
-template <int F, bool IDENT>
+// PROVEN: the launcher has checked m.exactRecip == 2 once for the whole launch (arithFlatKernel); every other kernel
+// uses the default and treats a proven divisor like any other (IEEE division): still exact, just not faster.
+template <int F, bool IDENT, bool PROVEN = false>
 __device__ __forceinline__ uint32_t mapVoxel(float value, const Mapping& m)
 {
     if (!IDENT) {
         value = __fsub_rn(value, m.lo);
-        value = m.exactRecip ? __fmul_rn(value, m.invRange) : __fdiv_rn(value, m.range);
+        if (PROVEN) value = divProven(value, m.range, m.invRange);
+        else value = m.exactRecip == 1 ? __fmul_rn(value, m.invRange) : __fdiv_rn(value, m.range);
     }
     // IDENT: (v - +0) == v and v / 1 == v for every v (incl. -0, NaN payloads aside)
     if (F == F_U8)    return x86Cvtt32Low16(__fmul_rn(value, 255.999f)) & 0xffu;
