@@ -106,6 +106,29 @@ def run_multi(torch, lib, capi, n_gpus, peak, time_steps, edge=4096, steps=3, wa
     record(f"SafeSum {tag}", n, 3 * n,
            lambda: capi.check(lib.vktb_arith_range(capi.SAFESUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z3, l3, z3)),
            check=lambda nm: parity.check(nm, planes_of(d), fetch(d, U8), arith_plane))
+    # *Range with a z offset: dst plane z reads source plane z - 8 -- across a stripe boundary that is a peer load
+    # inside the kernel (the multi-process form moves 8 planes per source and boundary with NCCL first)
+    ZOFF = 8
+    nr = E * E * (E - ZOFF)
+
+    def sumrange_plane(z):
+        dpl = po.Vol(pre.copy(), U8)
+        pz = z - ZOFF
+        if 0 <= pz < E - ZOFF:
+            o.arith_range(po.SUM, dpl, po.Vol(parity.regen(1, U8, dims, pz), U8), po.Vol(parity.regen(2, U8, dims, pz), U8),
+                          (0, 0, 0), (E, E, 1))
+        return dpl.a
+
+    def planes_zoff(vol):
+        bnd = stripe_boundaries(vol)
+        extra = [z + k for z in bnd for k in range(0, ZOFF + 2)]
+        return sorted(set(planes_of(vol)) | {z for z in extra if 0 <= z < vol.dims[2]})
+
+    record(f"SumRange dstOffset (0,0,{ZOFF}) {tag}", nr, 3 * nr,
+           lambda: capi.check(lib.vktb_arith_range(capi.SUM, ctypes.byref(dd), ctypes.byref(da), ctypes.byref(db), z3,
+                                                   capi.I3(E, E, E - ZOFF), capi.I3(0, 0, ZOFF))),
+           prepare=lambda: capi.check(lib.vktb_fill_range(ctypes.byref(dd), z3, l3, 0.25)),
+           check=lambda nm: parity.check(nm, planes_zoff(d), fetch(d, U8), sumrange_plane))
     a.free(); b.free(); d.free()
 
     # ---- Resample ---------------------------------------------------------------------------------------------------

@@ -421,6 +421,30 @@ def test_brick_decompose_batch(gpu):
         assert same_bits(g.a, w.a), i
 
 
+def test_brick_decompose_tma_staged_and_direct(gpu, monkeypatch):
+    """The TMA-staged brick kernel (copy_bricks.cu) and the direct-load kernel it replaces, both against the oracle:
+    sources the tensor map can describe (row pitch a multiple of 16 bytes), halos wider than a vector and wider than
+    the brick, bricks cropped at the far border, halo voxels clamped on all six sides, rows shorter than a vector,
+    planes-per-CTA counts that do and do not divide the brick depth."""
+    o = po.oracle()
+    cfgs = [((64, 48, 40), (32, 16, 16), (1, 1, 1), (1, 1, 1)), ((64, 48, 40), (24, 20, 12), (5, 3, 2), (9, 4, 7)),
+            ((32, 16, 12), (8, 8, 4), (12, 10, 6), (11, 9, 5)), ((48, 8, 70), (48, 8, 66), (2, 2, 2), (2, 2, 2)),
+            ((16, 6, 9), (3, 2, 4), (0, 1, 0), (1, 0, 2)), ((256, 4, 3), (250, 4, 3), (3, 0, 0), (3, 0, 0))]
+    for fmt in (po.UINT8, po.UINT16, po.FLOAT32):
+        for sdims, brick, neg, pos in cfgs:
+            v = cases.mk(sdims, fmt, 7, -1000.0, 3000.0)
+            want = o.brick_decompose(v, brick, neg, pos)
+            for env in ({}, {"VKTB_BRICK_KZ": "1"}, {"VKTB_BRICK_KZ": "5"}, {"VKTB_BRICK_NO_TMA": "1"}):
+                for k in ("VKTB_BRICK_KZ", "VKTB_BRICK_NO_TMA"):
+                    monkeypatch.delenv(k, raising=False)
+                for k, val in env.items():
+                    monkeypatch.setenv(k, val)
+                got = gpu.brick_decompose(v, brick, neg, pos)
+                assert len(want) == len(got)
+                for i, (a, b) in enumerate(zip(want, got)):
+                    assert a.shape == b.shape and a.tobytes() == b.tobytes(), (fmt, sdims, brick, neg, pos, env, i)
+
+
 def test_transform_flat_and_rows(gpu):
     """Transform over contiguous ranges (flat stream kernel: whole volumes, whole planes, part of one plane) and over
     boxed ranges (row kernel); odd row lengths make vectors straddle rows and misalign the range start."""

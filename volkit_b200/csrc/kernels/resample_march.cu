@@ -25,6 +25,7 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "copy_boxes.hpp"
 #include "launch.hpp"
 #include "tma.cuh"
 #include "voxel_codec.cuh"
@@ -395,28 +396,6 @@ resampleMarchKernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// libcuda is never linked: the driver entry point is fetched through the runtime
-EncodeTiledFn encodeTiled()
-{
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-        else
-            cudaGetLastError();
-    }
-    return fn;
-}
-
 template <int FS, int FD, int MODE, bool IDENT>
 cudaError_t launchMarch(const LaunchCtx& c, const CUtensorMap* tm, const MarchParams& p, size_t smemBytes, unsigned grid)
 {
@@ -453,6 +432,24 @@ cudaError_t launchMarchDst(const LaunchCtx& c, const CUtensorMap* tm, const Marc
 }
 
 } // namespace
+
+// libcuda is never linked: the driver entry point is fetched through the runtime
+EncodeTiledFn encodeTiled()
+{
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
 
 // 8-tap resample (mode 1 = reference-faithful Linear, 2 = true trilinear) through the TMA z-march.  Returns
 // cudaErrorNotSupported when the operands do not qualify; the caller then uses the direct-gather kernel.

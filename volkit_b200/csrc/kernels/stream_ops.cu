@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "copy_boxes.hpp"
 #include "launch.hpp"
 #include "voxel_codec.cuh"
 
@@ -199,17 +200,6 @@ copyRowsUniformKernel(CopyParams p, int shift)
 // last) calls; at 64^3 bricks a 2048^3 volume makes 32768 of them, far too many launches.  One launch instead:
 // blockIdx.y picks the box, blockIdx.x a group of its z planes; rows are walked two at a time (two 128-bit loads in
 // flight per thread), chunks cut at 16-byte boundaries of the dst row, the src side clamped and funnel-shifted.
-struct BoxRec
-{
-    uint8_t*  d;                // dst voxel that receives the box's first voxel
-    long long pitchY, pitchZ;   // dst pitches in bytes
-    int nx, ny, nz;             // extents of [first, last)
-    int x0, y0, z0;             // first (may be negative: clamped)
-    unsigned nvox;              // flat kernel: nx*ny*nz (< 2^31)
-    unsigned mulX, mulY;        // e / nx == (e * mulX) >> shX for e < 2^31 (likewise ny): no division per vector
-    int shX, shY;
-};
-
 __device__ __forceinline__ unsigned magicDiv(unsigned e, unsigned mul, int sh)
 {
     return (unsigned)(((unsigned long long)e * mul) >> sh);
@@ -640,7 +630,14 @@ cudaError_t launchCopyBatch(const LaunchCtx& c, int n, const VolDesc* dsts, cons
     if (e != cudaSuccess) { cudaFreeAsync(dev, c.stream); return e; }
     const uint8_t* sEnd = src.data + (size_t)src.dims[0] * src.dims[1] * src.dims[2] * bs;
 
+    bool staged = false;
     if (nFlat) {
+        // bricks staged through shared memory by the TMA unit (copy_bricks.cu) where the operands qualify
+        e = launchCopyBricksTma(c, dev, flats.data(), nFlat, src.data, bs, src.dims);
+        staged = e == cudaSuccess;
+        if (e == cudaErrorNotSupported) e = cudaSuccess;
+    }
+    if (nFlat && !staged && e == cudaSuccess) {
         const unsigned perCta = kThreads * 4 * (16 / bs);                 // voxels per CTA
         const unsigned gx = (maxVox + (16 / bs) + perCta - 1) / perCta;   // + one vector for a misaligned head
         const size_t perLaunch = 0x7fffffff;
