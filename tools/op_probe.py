@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg | sumrange | sumrange8 | copyrange)"""
+"""Times one C-ABI op on device-resident volumes.  usage: op_probe.py OP X Y Z FMT   (OP: filter | scale | rotate | agg | scan | sumrange | sumrange8 | copyrange)"""
 import ctypes
 import math
 import os
@@ -53,6 +53,7 @@ def main():
                                                              capi.I3(dims[0] - 8, dims[1] - 8, dims[2] - 8), capi.I3(8, 8, 8))),
         "copyrange": lambda: capi.check(lib.vktb_copy_range(ctypes.byref(dd), ctypes.byref(sd), capi.I3(1, 1, 1),
                                                             capi.I3(dims[0] - 7, dims[1] - 7, dims[2] - 7), z)),
+        "scan": lambda: capi.check(lib.vktb_scan_range(ctypes.byref(sd), ctypes.byref(sd), z, l, z)),
         "agg": lambda: capi.check(lib.vktb_aggregates_range(ctypes.byref(sd), z, l, ctypes.byref(agg))),
     }
     run = runs[op]
