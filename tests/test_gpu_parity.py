@@ -393,43 +393,6 @@ def test_scan_kernels(gpu):
         assert a.a.tobytes() == b.a.tobytes(), dfmt
 
 
-def test_scan_single_pass_band_wavefront(gpu, monkeypatch):
-    """The single-pass Scan (scanBandKernel: row bands marching z, the y prefix handed from band to band through
-    flags) forced onto small volumes: one band, many bands, bands of one row, a cropped last band, rows of 1 / 2 / 4
-    vectors per thread, y and z running backwards, aligned sub-ranges, in place and dst != src; compared with the
-    oracle and with the multi-pass kernels (VKTB_SCAN_SINGLE=0)."""
-    o = po.oracle()
-    shapes = [((128, 40, 24), (0, 0, 0), (128, 40, 24)), ((64, 37, 9), (0, 0, 0), (64, 37, 9)),
-              ((64, 32, 16), (0, 31, 15), (64, -1, -1)), ((96, 20, 6), (16, 3, 1), (80, 19, 6)),
-              ((4352, 5, 3), (0, 0, 0), (4352, 5, 3)), ((16, 300, 4), (0, 0, 0), (16, 300, 4)),
-              ((32, 2, 2), (0, 0, 0), (32, 2, 2)), ((2048, 9, 40), (0, 0, 0), (2048, 9, 40))]
-    for fmt in (po.UINT8, po.UINT16, po.UINT32, po.FLOAT32):
-        for dims, first, last in shapes:
-            src = cases.mk(dims, fmt, 11)
-            want = src.copy()
-            o.scan_range(want, want, first, last)
-            for rows in (None, "1", "3", "7"):
-                monkeypatch.setenv("VKTB_SCAN_SINGLE", "force")
-                if rows is None:
-                    monkeypatch.delenv("VKTB_SCAN_BAND_ROWS", raising=False)
-                else:
-                    monkeypatch.setenv("VKTB_SCAN_BAND_ROWS", rows)
-                got = src.copy()
-                gpu.scan_range(got, got, first, last)
-                assert want.a.tobytes() == got.a.tobytes(), (fmt, dims, first, last, rows)
-            monkeypatch.delenv("VKTB_SCAN_BAND_ROWS", raising=False)
-            monkeypatch.setenv("VKTB_SCAN_SINGLE", "0")
-            got = src.copy()
-            gpu.scan_range(got, got, first, last)
-            assert want.a.tobytes() == got.a.tobytes(), (fmt, dims, first, last, "multi-pass")
-            if all(f < l for f, l in zip(first, last)):
-                monkeypatch.setenv("VKTB_SCAN_SINGLE", "force")
-                a, b = cases.mk(dims, fmt, 6), cases.mk(dims, fmt, 6)
-                o.scan_range(a, src, first, last)
-                gpu.scan_range(b, src, first, last)
-                assert a.a.tobytes() == b.a.tobytes(), (fmt, dims, first, last, "copy")
-
-
 def test_brick_decompose_batch(gpu):
     """BrickDecompose as one vktb_copy_range_batch launch: cropped border bricks, halos clamped at the volume border,
     brick rows at every 16-byte phase; plus a batch that mixes bytewise and converting boxes and empty boxes."""

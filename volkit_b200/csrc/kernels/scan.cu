@@ -16,11 +16,14 @@
 //         column sums in registers -- two passes over the volume instead of three
 // Packed adds (__vadd4 / __vadd2) keep 16 / 8 voxels per 128-bit register for UInt8 / UInt16.
 // Algorithmic traffic: 2 bpv per voxel for the ideal single pass; the passes move 4 bpv (fused x+y) or 6 bpv.
-#include <cstdlib>
-
+// A true single pass was built and measured (commit "Experiment: single-pass Scan as a wavefront of row bands",
+// profiles/r02_scan_single_pass_experiment.log): CTAs own bands of rows for all planes, keep the z running sum in
+// shared memory and hand the y prefix from band to band through release / acquire flags.  Bit-exact, but 14.1 - 17.5 ms
+// against 11.1 ms for the two passes at 2048^3 UInt16 (6.1 against 2.2 ms at 1024^3): a band's plane step is 6 - 8 us
+// of dependent latency (bulk-load wait, three barriers, a device-wide fence behind its stores, the flag round trip
+// through L2) with only one to three CTAs per SM to hide it, where the memory time of the step is 2.6 us.
 #include "common.cuh"
 #include "launch.hpp"
-#include "tma.cuh"
 #include "voxel_codec.cuh"
 
 namespace vktb {
@@ -212,160 +215,6 @@ cudaError_t launchPlaneXY(const LaunchCtx& c, const ScanParams& p, int nvec)
     return cudaGetLastError();
 }
 
-// ---- single pass: x + y + z in ONE read and ONE write of the volume ---------------------------------------------
-// The three prefix sums commute (integer adds mod 2^k): z first, then x, then y.
-//   * the dst rows are cut into BANDS of R consecutive rows; a CTA owns one band for ALL planes and marches z.  The
-//     z prefix of its rows is a running sum that never leaves the CTA (shared memory, one private slot per thread);
-//   * x prefix of the z-summed rows: the CTA owns whole rows -- packed prefix inside the thread's vectors, shuffle scan,
-//     warp totals through shared memory -- for all R rows before ONE barrier;
-//   * y prefix: a running column sum down the band's rows that starts from the LAST OUTPUT ROW OF THE BAND ABOVE in
-//     the same plane.  That row is ordinary dst data: the band above stores it, fences and raises flag[band] = z + 1;
-//     this band polls the flag (acquire), reads the row through L2 and adds it.  Bands form a wavefront: band b works
-//     on plane z while band b - 1 is already at z + 1, so in steady state the wait is over before it starts.  Band
-//     indices are handed out by an atomic ticket, so a band only ever waits for CTAs that are already running
-//     (no co-residency assumption, no cooperative launch).
-//   * the next plane's rows arrive by cp.async.bulk (SASS UBLKCP) into the other half of a two-stage buffer while
-//     this plane is scanned.
-// Traffic: 2 bpv per voxel plus one extra row per band and plane from L2 (1/R of the reads).
-struct BandParams
-{
-    ScanParams s;
-    int nvec;          // 16-byte vectors per row
-    int R;             // rows per band
-    int nBands;
-    unsigned* sync;    // [0]: ticket, [1 + b]: planes band b has finished (device scratch, zeroed per launch)
-};
-
-__device__ __forceinline__ unsigned ldAcquire(const unsigned* p)
-{
-    unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void stRelease(unsigned* p, unsigned v)
-{
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
-}
-
-template <int BPV, int VPT>
-__global__ void __launch_bounds__(kThreads)
-scanBandKernel(BandParams p)
-{
-    extern __shared__ __align__(128) uint8_t bandSmem[];
-    constexpr int kWarps = kThreads / 32;
-    const int t = threadIdx.x;
-    const unsigned lane = t & 31u, warp = t >> 5;
-    const int rowBytes = p.nvec * 16;
-    // layout: [0,16) two mbarriers | [16,20) band id | warp totals [R][8] | exclusive warp prefixes [R][8] | zsum | stage x 2
-    uint64_t* full = reinterpret_cast<uint64_t*>(bandSmem);
-    int* bandSlot = reinterpret_cast<int*>(bandSmem + 16);
-    uint32_t* warpTot = reinterpret_cast<uint32_t*>(bandSmem + 128);
-    uint32_t* warpPre = warpTot + p.R * kWarps;
-    uint8_t* zsum = bandSmem + 128 + ((size_t)p.R * kWarps * 8 + 127) / 128 * 128;
-    uint8_t* stage = zsum + (size_t)p.R * rowBytes;
-    const size_t stageBytes = (size_t)p.R * rowBytes;
-
-    if (t == 0) {
-        *bandSlot = (int)atomicAdd(p.sync, 1u);
-        mbarInit(smemAddr(&full[0]), 1);
-        mbarInit(smemAddr(&full[1]), 1);
-        fenceBarrierInit();
-    }
-    __syncthreads();
-    const int band = *bandSlot;
-    if (band >= p.nBands) return;
-    const int r0 = band * p.R, Rb = min(p.R, p.s.ny - r0);
-    const int v0 = t * VPT;
-    uint8_t* bandBase = p.s.d + r0 * p.s.pitchY;
-
-    auto issue = [&](int z) {      // thread 0: the band's rows of plane z -> stage[z & 1]
-        const uint32_t bar = smemAddr(&full[z & 1]);
-        mbarArriveExpectTx(bar, (uint32_t)(Rb * rowBytes));
-        uint8_t* dstS = stage + (size_t)(z & 1) * stageBytes;
-        const uint8_t* src = bandBase + z * p.s.pitchZ;
-        for (int r = 0; r < Rb; ++r) bulkLoad(smemAddr(dstS + (size_t)r * rowBytes), src + r * p.s.pitchY, (uint32_t)rowBytes, bar);
-    };
-    for (int i = t; i < Rb * p.nvec; i += kThreads) reinterpret_cast<uint4*>(zsum)[i] = make_uint4(0u, 0u, 0u, 0u);
-    if (t == 0) issue(0);
-    // a thread only ever touches its own zsum slots, but the zeroing above ran with another thread mapping
-    __syncthreads();
-
-    for (int z = 0; z < p.s.nz; ++z) {
-        uint8_t* st = stage + (size_t)(z & 1) * stageBytes;
-        if (t == 0 && z + 1 < p.s.nz) issue(z + 1);
-        mbarWait(smemAddr(&full[z & 1]), (uint32_t)((z >> 1) & 1));
-        // ---- phase 1: z running sum, x prefix up to the warp, for every row of the band
-        for (int r = 0; r < Rb; ++r) {
-            uint4 w[VPT];
-            uint32_t tot = 0u;
-#pragma unroll
-            for (int k = 0; k < VPT; ++k) {
-                uint4 zs = make_uint4(0u, 0u, 0u, 0u);
-                if (v0 + k < p.nvec) {
-                    const size_t o = (size_t)r * rowBytes + (size_t)(v0 + k) * 16;
-                    zs = addPacked4<BPV>(*reinterpret_cast<const uint4*>(zsum + o), *reinterpret_cast<const uint4*>(st + o));
-                    *reinterpret_cast<uint4*>(zsum + o) = zs;
-                }
-                w[k].x = addPacked<BPV>(wordScan<BPV>(zs.x), tot);
-                w[k].y = addPacked<BPV>(wordScan<BPV>(zs.y), lastBroadcast<BPV>(w[k].x));
-                w[k].z = addPacked<BPV>(wordScan<BPV>(zs.z), lastBroadcast<BPV>(w[k].y));
-                w[k].w = addPacked<BPV>(wordScan<BPV>(zs.w), lastBroadcast<BPV>(w[k].z));
-                tot = lastBroadcast<BPV>(w[k].w);
-            }
-#pragma unroll
-            for (int dlt = 1; dlt < 32; dlt <<= 1) {
-                const uint32_t up = __shfl_up_sync(0xffffffffu, tot, dlt);
-                if ((int)lane >= dlt) tot = addPacked<BPV>(tot, up);
-            }
-            uint32_t before = __shfl_up_sync(0xffffffffu, tot, 1);
-            if (lane == 0) before = 0u;
-            if (lane == 31) warpTot[r * kWarps + warp] = tot;
-            const uint4 b4 = make_uint4(before, before, before, before);
-#pragma unroll
-            for (int k = 0; k < VPT; ++k)
-                if (v0 + k < p.nvec)
-                    *reinterpret_cast<uint4*>(st + (size_t)r * rowBytes + (size_t)(v0 + k) * 16) = addPacked4<BPV>(w[k], b4);
-        }
-        // the band above must have published this plane before its last row is read
-        if (t == 0 && band > 0) {
-            const unsigned* flag = p.sync + 1 + (band - 1);
-            while (ldAcquire(flag) < (unsigned)(z + 1)) __nanosleep(40);
-        }
-        __syncthreads();
-        uint4 col[VPT];
-#pragma unroll
-        for (int k = 0; k < VPT; ++k) {
-            col[k] = make_uint4(0u, 0u, 0u, 0u);
-            if (band > 0 && v0 + k < p.nvec)
-                col[k] = __ldcg(reinterpret_cast<const uint4*>(bandBase + z * p.s.pitchZ - p.s.pitchY + (size_t)(v0 + k) * 16));
-        }
-        if (t < Rb * kWarps) {
-            const int r = t / kWarps, i = t - r * kWarps;
-            uint32_t acc = 0u;
-            for (int j = 0; j < i; ++j) acc = addPacked<BPV>(acc, warpTot[r * kWarps + j]);
-            warpPre[t] = acc;
-        }
-        __syncthreads();
-        // ---- phase 2: add the warps in front, run the column sum down the rows, store
-        uint8_t* drow = bandBase + z * p.s.pitchZ;
-        for (int r = 0; r < Rb; ++r) {
-            const uint32_t b = warpPre[r * kWarps + warp];
-            const uint4 b4 = make_uint4(b, b, b, b);
-#pragma unroll
-            for (int k = 0; k < VPT; ++k)
-                if (v0 + k < p.nvec) {
-                    const size_t o = (size_t)r * rowBytes + (size_t)(v0 + k) * 16;
-                    col[k] = addPacked4<BPV>(col[k], addPacked4<BPV>(*reinterpret_cast<const uint4*>(st + o), b4));
-                    stStream(drow + r * p.s.pitchY + (size_t)(v0 + k) * 16, col[k]);
-                }
-        }
-        __threadfence();                 // this thread's part of the band's last row is visible device-wide ...
-        fenceProxyAsyncSmem();           // ... and its writes to the stage precede the bulk load that reuses it
-        __syncthreads();
-        if (t == 0) stRelease(p.sync + 1 + band, (unsigned)(z + 1));
-    }
-}
-
 // ---- y / z pass: a running packed sum walks `steps` lines that lie `stepPitch` bytes apart -----------------------
 // Thread = one aligned 16-byte column chunk of line family (o1, o2); every line of the range has the same 16-byte
 // phase (launcher), so the chunk is the same byte window [c0, c1) of every line.
@@ -462,70 +311,12 @@ cudaError_t lines(const LaunchCtx& c, uint8_t* d, int bpv, int steps, long long 
     return cudaGetLastError();
 }
 
-// Single pass (scanBandKernel) when x runs left to right, rows are whole aligned vectors that a CTA can own, and the
-// volume is deep enough for the band wavefront to fill (every band starts one plane after the one above it).
-// cudaErrorNotSupported: use the multi-pass path.
-template <int BPV>
-cudaError_t launchBand(const LaunchCtx& c, const ScanParams& p)
-{
-    const char* mode = getenv("VKTB_SCAN_SINGLE");       // "0": off, "force": no depth threshold (tests)
-    if (mode && mode[0] == '0') return cudaErrorNotSupported;
-    const bool force = mode && mode[0] == 'f';
-    const long long rowBytes = (long long)p.nx * BPV;
-    const long long ay = p.pitchY < 0 ? -p.pitchY : p.pitchY, az = p.pitchZ < 0 ? -p.pitchZ : p.pitchZ;
-    if (p.stepX <= 0 || (reinterpret_cast<uintptr_t>(p.d) & 15u) || rowBytes % 16 || ay % 16 || az % 16) return cudaErrorNotSupported;
-    const long long nvec = rowBytes / 16;
-    if (nvec > kThreads * 4 || p.ny < 2 || p.nz < 2) return cudaErrorNotSupported;
-    // rows per band: as many bands as 3 (2, 1) CTAs per SM can hold
-    const long long smemPerSm = 220 * 1024;
-    int R = 0, perSm = 0;
-    if (const char* e = getenv("VKTB_SCAN_BAND_ROWS")) {
-        R = atoi(e);
-        perSm = 1;
-        if (R < 1 || 128 + 128 + (long long)R * 64 + 3LL * R * rowBytes > smemPerSm) return cudaErrorNotSupported;
-    } else {
-        for (int k = 3; k >= 1 && !R; --k) {
-            const long long bands = (long long)c.smCount * k;
-            const long long r = (p.ny + bands - 1) / bands;
-            const long long smem = 128 + 128 + r * 64 + 3 * r * rowBytes;
-            if (smem * k <= smemPerSm) { R = (int)r; perSm = k; }
-        }
-        if (!R) return cudaErrorNotSupported;
-    }
-    if (R > kThreads / 8) return cudaErrorNotSupported;   // one thread per (row, warp) builds the warp prefixes
-    const int nBands = (p.ny + R - 1) / R;
-    if (!force && ((long long)p.nz * perSm < 4LL * nBands || p.ny < c.smCount)) return cudaErrorNotSupported;
-    const size_t smemBytes = 128 + ((size_t)R * 64 + 127) / 128 * 128 + 3 * (size_t)R * rowBytes;
-
-    BandParams b;
-    b.s = p; b.nvec = (int)nvec; b.R = R; b.nBands = nBands;
-    unsigned* sync = nullptr;
-    const size_t syncBytes = (size_t)(1 + nBands) * sizeof(unsigned);
-    cudaError_t e = cudaMallocAsync((void**)&sync, syncBytes, c.stream);
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(sync, 0, syncBytes, c.stream);
-    if (e != cudaSuccess) { cudaFreeAsync(sync, c.stream); return e; }
-    b.sync = sync;
-    auto launch = [&](auto kern) {
-        cudaError_t le = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        if (le != cudaSuccess) return le;
-        kern<<<(unsigned)nBands, kThreads, smemBytes, c.stream>>>(b);
-        countLaunch();
-        return cudaGetLastError();
-    };
-    e = nvec <= kThreads ? launch(scanBandKernel<BPV, 1>) : nvec <= kThreads * 2 ? launch(scanBandKernel<BPV, 2>)
-                                                                                 : launch(scanBandKernel<BPV, 4>);
-    cudaFreeAsync(sync, c.stream);
-    return e;
-}
-
 template <int BPV>
 cudaError_t scanBpv(const LaunchCtx& c, const ScanParams& p, bool alignedBuffer)
 {
     const long long rowBytes = (long long)p.nx * BPV;
     const long long ay = p.pitchY < 0 ? -p.pitchY : p.pitchY, az = p.pitchZ < 0 ? -p.pitchZ : p.pitchZ;
-    cudaError_t e = launchBand<BPV>(c, p);
-    if (e != cudaErrorNotSupported) return e;
+    cudaError_t e;
     // ---- x and y in one pass when a CTA can own a plane's rows (and there are enough planes to fill the machine)
     bool fusedXY = false;
     if (p.nx > 1 && p.ny > 1 && p.stepX > 0 && (reinterpret_cast<uintptr_t>(p.d) & 15u) == 0 && rowBytes % 16 == 0
