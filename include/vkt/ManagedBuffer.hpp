@@ -87,6 +87,8 @@ namespace vkt
                 return;
             T* moved = nullptr;
             Allocate((void**)&moved, size_ * sizeof(T));                       // on the new device
+            if (!moved)
+                return;   // out of memory there: the bytes stay where they are (host::describe reports it to the caller)
             Memcpy(moved, data_, size_ * sizeof(T),
                    ep.device == ExecutionPolicy::Device::GPU ? CopyKind::HostToDevice : CopyKind::DeviceToHost);
             SetThreadExecutionPolicy(lastAllocationPolicy_);                   // free with the backend that allocated
@@ -105,6 +107,8 @@ namespace vkt
                 return;
             T* fresh = nullptr;
             Allocate((void**)&fresh, size_ * sizeof(T));
+            if (!fresh)
+                return;
             SetThreadExecutionPolicy(lastAllocationPolicy_);
             Free(data_);
             SetThreadExecutionPolicy(ep);

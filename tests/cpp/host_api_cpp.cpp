@@ -1,7 +1,7 @@
 // Exercises the C++ host mirror (include/vkt/*.hpp) the way the reference's examples do
 // (src/examples/CoreAlgorithms.c, Arithmetic.cpp, ExecutionPolicy.cpp): volumes are created and filled on the CPU,
 // the thread's ExecutionPolicy is switched, algorithms run, results are read back after switching to CPU again.
-// usage: host_api_cpp <cpu|gpu|gpu-stream> <dir>      inputs <dir>/a.raw, b.raw (48x40x36 UInt16); outputs <dir>/out_*.raw
+// usage: host_api_cpp <cpu|gpu|gpu-stream|gpu-multi:ids|gpu-oom> <dir>      inputs <dir>/a.raw, b.raw (48x40x36 UInt16); outputs <dir>/out_*.raw
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -76,6 +76,32 @@ int main(int argc, char** argv)
     std::thread([&] { childIsDefault = GetThreadExecutionPolicy().device == ExecutionPolicy::Device::CPU; }).join();
     if (!childIsDefault) return 4;
     SetThreadExecutionPolicy(cpu);
+
+    if (std::strcmp(argv[1], "gpu-oom") == 0) {
+        // Fault injection: the allocator fails the migration of `v`; the call must return
+        // InvalidValue, the volume must keep its bytes on the host, and the same call must succeed afterwards.
+        const int N = 32;
+        StructuredVolume v(N, N, N, DataFormat::UInt16), w(N, N, N, DataFormat::UInt16), r(N, N, N, DataFormat::UInt16);
+        CHECK(Fill(v, .25f));
+        CHECK(Fill(w, .5f));
+        ExecutionPolicy g = cpu;
+        g.device = ExecutionPolicy::Device::GPU;
+        SetThreadExecutionPolicy(g);
+        setenv("VKTB_FAIL_ALLOC_AT", "2", 1);                  // r migrates (allocation 1), v cannot (allocation 2)
+        Error e = SafeSum(r, v, w);
+        unsetenv("VKTB_FAIL_ALLOC_AT");
+        if (e != InvalidValue) { std::fprintf(stderr, "expected InvalidValue, got %d\n", (int)e); return 11; }
+        if (!v.residesOnHost()) { std::fprintf(stderr, "the volume left the host although its migration failed\n"); return 12; }
+        CHECK(SafeSum(r, v, w));                               // no injection: the same call works, nothing was lost
+        SetThreadExecutionPolicy(cpu);
+        const uint16_t* pr = (const uint16_t*)r.getData();
+        const uint16_t* pv = (const uint16_t*)v.getData();
+        StructuredVolume want(N, N, N, DataFormat::UInt16);
+        CHECK(SafeSum(want, v, w));
+        if (std::memcmp(pr, want.getData(), r.getSizeInBytes()) != 0 || pv[0] == 0) return 13;
+        std::printf("oom ok\n");
+        return 0;
+    }
 
     if (multi) {
         // One process, several GPUs: volumes above the striping threshold (the test lowers it to 1 MiB) are striped over

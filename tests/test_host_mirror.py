@@ -241,6 +241,31 @@ def test_cpp_api_gpu_policy_device_group(programs, tmp_path, monkeypatch):
 
 
 @pytest.mark.gpu
+def test_cpp_api_gpu_policy_allocation_failure(programs, tmp_path):
+    """fault injection (VKTB_FAIL_ALLOC_AT): a migrate() that cannot allocate leaves the volume on the host, the vkt::
+    call returns InvalidValue, and the same call succeeds once memory is available again"""
+    r = subprocess.run([programs["cpp"], "gpu-oom", str(tmp_path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "oom ok" in r.stdout, (r.returncode, r.stdout, r.stderr)
+    assert "injected by VKTB_FAIL_ALLOC_AT" in r.stderr      # the backend's message reaches the caller's stderr
+
+
+@pytest.mark.gpu
+def test_c_abi_allocation_failure_is_reported(monkeypatch):
+    import ctypes
+    from volkit_b200 import capi
+    lib = capi.load()
+    capi.check(lib.vktb_set_device(0))
+    monkeypatch.setenv("VKTB_FAIL_ALLOC_AT", "2")
+    p1, p2, p3 = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+    assert lib.vktb_alloc(ctypes.byref(p1), 1 << 20) == 0
+    assert lib.vktb_alloc(ctypes.byref(p2), 1 << 20) != 0 and not p2.value
+    assert b"out of memory (injected" in lib.vktb_last_error()
+    assert lib.vktb_alloc(ctypes.byref(p3), 1 << 20) == 0      # only the n-th call fails
+    monkeypatch.delenv("VKTB_FAIL_ALLOC_AT")
+    capi.check(lib.vktb_free(p1)); capi.check(lib.vktb_free(p3))
+
+
+@pytest.mark.gpu
 def test_c99_api_gpu_policy(programs, tmp_path):
     run_c(programs, "gpu", tmp_path)
 

@@ -97,6 +97,7 @@ extern "C" {
 
 int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], float value)
 {
+    VKTB_API_RANGE();
     VolDesc v;
     if (!first || !last) return fail("vktb_fill_range: null range");
     if (!toDesc("vktb_fill_range", vol, v)) return -1;
@@ -118,6 +119,7 @@ int vktb_fill_range(const vktb_vol* vol, const int32_t first[3], const int32_t l
 int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                     const int32_t off[3])
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (!first || !last || !off) return fail("vktb_copy_range: null range");
     if (!toDesc("vktb_copy_range", dst, dv) || !toDesc("vktb_copy_range", src, sv)) return -1;
@@ -145,6 +147,7 @@ int vktb_copy_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_copy_range_batch(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts, const int32_t* lasts,
                           const int32_t* offs)
 {
+    VKTB_API_RANGE();
     if (n < 0) return fail("vktb_copy_range_batch: negative count");
     if (n == 0) return 0;
     if (!dsts || !firsts || !lasts || !offs) return fail("vktb_copy_range_batch: null argument");
@@ -173,6 +176,7 @@ int vktb_copy_range_batch_noalloc_max(void) { return copyBatchNoAllocMaxBoxes();
 int vktb_copy_range_batch_noalloc(int n, const vktb_vol* dsts, const vktb_vol* src, const int32_t* firsts,
                                   const int32_t* lasts, const int32_t* offs)
 {
+    VKTB_API_RANGE();
     const char* fn = "vktb_copy_range_batch_noalloc";
     if (n < 0) return fail("vktb_copy_range_batch_noalloc: negative count");
     if (n == 0) return 0;
@@ -210,6 +214,7 @@ int vktb_copy_range_batch_noalloc(int n, const vktb_vol* dsts, const vktb_vol* s
 int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                     const int32_t off[3])
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (!first || !last || !off) return fail("vktb_scan_range: null range");
     if (!toDesc("vktb_scan_range", dst, dv) || !toDesc("vktb_scan_range", src, sv)) return -1;
@@ -236,6 +241,7 @@ int vktb_scan_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2, const int32_t first[3],
                      const int32_t last[3], const int32_t off[3])
 {
+    VKTB_API_RANGE();
     VolDesc dv, av, bv;
     if (op < 0 || op > VKTB_SAFEABSDIFF) return fail("vktb_arith_range: bad op");
     if (!first || !last || !off) return fail("vktb_arith_range: null range");
@@ -261,6 +267,7 @@ int vktb_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb
 
 int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op)
 {
+    VKTB_API_RANGE();
     VolDesc v;
     const bool user = op >= kUserOpBase;
     if (user ? !userOpValid(op, false) : (op < 0 || op >= kNumUnaryOps)) return fail("vktb_transform_range1: unknown device op handle");
@@ -284,6 +291,7 @@ int vktb_transform_range1(const vktb_vol* vol, const int32_t first[3], const int
 
 int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int32_t first[3], const int32_t last[3], int op)
 {
+    VKTB_API_RANGE();
     VolDesc a, b;
     const bool user = op >= kUserOpBase;
     if (user ? !userOpValid(op, true) : (op < 0 || op >= kNumBinaryOps)) return fail("vktb_transform_range2: unknown device op handle");
@@ -308,6 +316,7 @@ int vktb_transform_range2(const vktb_vol* vol1, const vktb_vol* vol2, const int3
 int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter, int32_t dstZ0, const int32_t dstFull[3],
                          int32_t srcZ0, const int32_t srcFull[3])
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (filter < 0 || filter > VKTB_TRILINEAR) return fail("vktb_resample: bad filter mode");
     if (!dstFull || !srcFull) return fail("vktb_resample_window: null dims");
@@ -346,6 +355,7 @@ int vktb_resample_window(const vktb_vol* dst, const vktb_vol* src, int filter, i
 
 int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
 {
+    VKTB_API_RANGE();
     if (!dst || !src) return fail("vktb_resample: null volume");
     return vktb_resample_window(dst, src, filter, 0, dst->dims, 0, src->dims);
 }
@@ -353,6 +363,7 @@ int vktb_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
 int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                     const int32_t off[3], int axis)
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (axis < 0 || axis > 2) return fail("vktb_flip_range: bad axis");
     if (!first || !last || !off) return fail("vktb_flip_range: null range");
@@ -376,6 +387,7 @@ int vktb_flip_range(const vktb_vol* dst, const vktb_vol* src, const int32_t firs
 int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], uint64_t* bins,
                          size_t numBins, uint64_t* droppedHost)
 {
+    VKTB_API_RANGE();
     VolDesc v;
     if (!first || !last || !bins) return fail("vktb_histogram_range: null argument");
     if (numBins == 0 || numBins > ((size_t)1 << 24)) return fail("vktb_histogram_range: numBins must be in [1, 2^24]");
@@ -417,6 +429,7 @@ static cudaError_t privateCopyIfOverlapping(const VolDesc& dst, VolDesc& src, cu
 int vktb_affine_range(const vktb_vol* dst, const vktb_vol* src, const int32_t first[3], const int32_t last[3],
                       const float matrix[9], const float center[3])
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (!first || !last || !matrix || !center) return fail("vktb_affine_range: null argument");
     if (!toDesc("vktb_affine_range", dst, dv) || !toDesc("vktb_affine_range", src, sv)) return -1;
@@ -433,6 +446,7 @@ int vktb_affine_range(const vktb_vol* dst, const vktb_vol* src, const int32_t fi
 
 int vktb_apply_filter(const vktb_vol* dst, const vktb_vol* src, const float* weights, const int32_t fdims[3], int /*addressMode*/)
 {
+    VKTB_API_RANGE();
     VolDesc dv, sv;
     if (!weights || !fdims) return fail("vktb_apply_filter: null argument");
     if (!toDesc("vktb_apply_filter", dst, dv) || !toDesc("vktb_apply_filter", src, sv)) return -1;
@@ -461,6 +475,7 @@ static void emptyPartial(vktb_agg_partial* o)
 
 int vktb_aggregates_partial(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_agg_partial* out)
 {
+    VKTB_API_RANGE();
     static_assert(sizeof(vktb_agg_partial) == 88, "vktb_agg_partial layout");
     VolDesc v;
     if (!first || !last || !out) return fail("vktb_aggregates_partial: null argument");
@@ -502,6 +517,7 @@ int vktb_aggregates_partial(const vktb_vol* vol, const int32_t first[3], const i
 
 int vktb_aggregates_finish(const vktb_agg_partial* parts, int n, uint64_t numElems, vktb_aggregates* out)
 {
+    VKTB_API_RANGE();
     if (!out || n < 0 || (n > 0 && !parts)) return fail("vktb_aggregates_finish: bad arguments");
     std::memset(out, 0, sizeof(*out));
     out->min = FLT_MAX; out->max = -FLT_MAX;
@@ -538,6 +554,7 @@ int vktb_aggregates_finish(const vktb_agg_partial* parts, int n, uint64_t numEle
 
 int vktb_aggregates_range(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], vktb_aggregates* out)
 {
+    VKTB_API_RANGE();
     static_assert(sizeof(vktb_aggregates) == 52, "vktb_aggregates must match vkt::Aggregates");
     if (!vol || !out) return fail("vktb_aggregates_range: null argument");
     vktb_agg_partial p;
@@ -573,6 +590,7 @@ static int planSrcRange(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t
 // z-only form: assumes the reference's unclamped hi.x tap (Linear) may spill into the following plane
 int vktb_resample_window_src_range(int filter, int32_t dz0, int32_t dz1, int32_t D, int32_t S, int32_t* sz0, int32_t* sz1)
 {
+    VKTB_API_RANGE();
     return planSrcRange(filter, dz0, dz1, D, S, true, sz0, sz1);
 }
 
@@ -582,6 +600,7 @@ int vktb_resample_window_src_range(int filter, int32_t dz0, int32_t dz1, int32_t
 int vktb_resample_window_src_range3(int filter, int32_t dz0, int32_t dz1, const int32_t D[3], const int32_t S[3],
                                     int32_t* sz0, int32_t* sz1)
 {
+    VKTB_API_RANGE();
     if (!D || !S) return fail("vktb_resample_window_src_range3: null dims");
     bool spill = false;
     if (filter == VKTB_LINEAR && D[0] > 0 && D[1] > 0 && S[0] > 0 && S[1] > 0)
@@ -592,6 +611,7 @@ int vktb_resample_window_src_range3(int filter, int32_t dz0, int32_t dz1, const 
 // ---- Headless ray-marcher ---------------------------------------------------------------------------------------
 int vktb_render_default_camera(const int32_t dims[3], const float dist[3], vktb_camera* cam)
 {
+    VKTB_API_RANGE();
     if (!dims || !cam) return fail("vktb_render_default_camera: null argument");
     const float one[3] = { 1.f, 1.f, 1.f };
     renderDefaultCamera(dims, dist ? dist : one, cam->eye, cam->center, cam->up);
@@ -602,6 +622,7 @@ int vktb_render_default_camera(const int32_t dims[3], const float dist[3], vktb_
 int vktb_render_raymarch(const vktb_vol* vol, const float dist[3], const vktb_camera* cam, const float* lutDev, int lutN,
                          float dt, int srgb, int width, int height, uint8_t* rgba8Dev, float* rgba32fDev)
 {
+    VKTB_API_RANGE();
     const char* fn = "vktb_render_raymarch";
     VolDesc v;
     if (!cam) return fail("vktb_render_raymarch: null camera");
@@ -625,6 +646,7 @@ int vktb_render_raymarch(const vktb_vol* vol, const float dist[3], const vktb_ca
 // ---- Transform registry ----
 int vktb_unary_op_by_name(const char* name, int* op)
 {
+    VKTB_API_RANGE();
     if (!name || !op) return fail("vktb_unary_op_by_name: null argument");
     for (int i = 0; i < kNumUnaryOps; ++i) if (!strcmp(name, kUnaryNames[i])) { *op = i; return 0; }
     return fail("vktb_unary_op_by_name: no such built-in device op");
@@ -632,6 +654,7 @@ int vktb_unary_op_by_name(const char* name, int* op)
 
 int vktb_binary_op_by_name(const char* name, int* op)
 {
+    VKTB_API_RANGE();
     if (!name || !op) return fail("vktb_binary_op_by_name: null argument");
     for (int i = 0; i < kNumBinaryOps; ++i) if (!strcmp(name, kBinaryNames[i])) { *op = i; return 0; }
     return fail("vktb_binary_op_by_name: no such built-in device op");
@@ -639,6 +662,7 @@ int vktb_binary_op_by_name(const char* name, int* op)
 
 int vktb_bind_unary_op(const void* hostFn, int op)
 {
+    VKTB_API_RANGE();
     if (!hostFn || op < 0 || (op >= kNumUnaryOps && !userOpValid(op, false))) return fail("vktb_bind_unary_op: bad arguments");
     std::lock_guard<std::mutex> lock(g_opMutex);
     g_unaryBound[hostFn] = op;
@@ -647,6 +671,7 @@ int vktb_bind_unary_op(const void* hostFn, int op)
 
 int vktb_bind_binary_op(const void* hostFn, int op)
 {
+    VKTB_API_RANGE();
     if (!hostFn || op < 0 || (op >= kNumBinaryOps && !userOpValid(op, true))) return fail("vktb_bind_binary_op: bad arguments");
     std::lock_guard<std::mutex> lock(g_opMutex);
     g_binaryBound[hostFn] = op;
@@ -655,6 +680,7 @@ int vktb_bind_binary_op(const void* hostFn, int op)
 
 int vktb_lookup_unary_op(const void* hostFn, int* op)
 {
+    VKTB_API_RANGE();
     std::lock_guard<std::mutex> lock(g_opMutex);
     auto it = g_unaryBound.find(hostFn);
     if (it == g_unaryBound.end() || !op)
@@ -665,6 +691,7 @@ int vktb_lookup_unary_op(const void* hostFn, int* op)
 
 int vktb_lookup_binary_op(const void* hostFn, int* op)
 {
+    VKTB_API_RANGE();
     std::lock_guard<std::mutex> lock(g_opMutex);
     auto it = g_binaryBound.find(hostFn);
     if (it == g_binaryBound.end() || !op)
@@ -675,6 +702,7 @@ int vktb_lookup_binary_op(const void* hostFn, int* op)
 
 int vktb_debug_div_proven(float lo, float hi, int* proven)
 {
+    VKTB_API_RANGE();
     if (!proven) return fail("vktb_debug_div_proven: null argument");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
@@ -685,6 +713,7 @@ int vktb_debug_div_proven(float lo, float hi, int* proven)
 
 int vktb_debug_map_unmap(int format, float lo, float hi, const float* values, uint32_t* mapped, float* unmapped, size_t n)
 {
+    VKTB_API_RANGE();
     if (!supportedFormat(format)) return fail("vktb_debug_map_unmap: unsupported format");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;

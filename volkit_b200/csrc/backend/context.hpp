@@ -56,6 +56,19 @@ int  currentOrdinal();
 void setCurrentOrdinal(int ordinal);
 cudaStream_t currentStream(DeviceCtx* d);
 
+// NVTX range around every C-ABI entry point (tracing): nvtx3 is header-only and binds to a profiler's
+// injection library at run time; without one a range is a load and a predictable branch
+struct ApiRange
+{
+    explicit ApiRange(const char* name);
+    ~ApiRange();
+};
+#define VKTB_API_RANGE() ::vktb::ApiRange vktbApiRange__(__func__)
+
+// Fault injection: with VKTB_FAIL_ALLOC_AT=n in the environment the n-th vktb_alloc made while the
+// variable is set fails like an out-of-memory condition; exercises the error path up to vkt::InvalidValue
+bool injectAllocFailure();
+
 void setError(const std::string& msg);
 int  fail(const char* what, cudaError_t e);
 int  fail(const char* what);

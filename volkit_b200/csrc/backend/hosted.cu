@@ -195,6 +195,7 @@ extern "C" {
 int vktb_hosted_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, const vktb_vol* s2, const int32_t first[3],
                             const int32_t last[3], const int32_t off[3])
 {
+    VKTB_API_RANGE();
     const char* fn = "vktb_hosted_arith_range";
     VolDesc dv, av, bv;
     if (op < 0 || op > VKTB_SAFEABSDIFF) return fail("vktb_hosted_arith_range: bad op");
@@ -238,6 +239,7 @@ int vktb_hosted_arith_range(int op, const vktb_vol* dst, const vktb_vol* s1, con
 
 int vktb_hosted_transform_range1(const vktb_vol* vol, const int32_t first[3], const int32_t last[3], int op)
 {
+    VKTB_API_RANGE();
     const char* fn = "vktb_hosted_transform_range1";
     VolDesc v;
     if (op < 0 || op >= kNumUnaryOps) return fail("vktb_hosted_transform_range1: unknown device op handle");
@@ -264,6 +266,7 @@ int vktb_hosted_transform_range1(const vktb_vol* vol, const int32_t first[3], co
 
 int vktb_hosted_resample(const vktb_vol* dst, const vktb_vol* src, int filter)
 {
+    VKTB_API_RANGE();
     const char* fn = "vktb_hosted_resample";
     VolDesc dv, sv;
     if (filter < 0 || filter > VKTB_TRILINEAR) return fail("vktb_hosted_resample: bad filter mode");

@@ -1,4 +1,9 @@
 // Device-buffer manager behind vktb_alloc / vktb_free / vktb_memcpy / vktb_host_alloc (see context.hpp).
+#include <atomic>
+#include <cstdlib>
+
+#include <nvtx3/nvToolsExt.h>
+
 #include "context.hpp"
 
 #include <algorithm>
@@ -13,6 +18,17 @@
 #include "multi.hpp"
 
 namespace vktb {
+
+ApiRange::ApiRange(const char* name) { nvtxRangePushA(name); }
+ApiRange::~ApiRange() { nvtxRangePop(); }
+
+bool injectAllocFailure()
+{
+    static std::atomic<long> count{0};
+    const char* e = getenv("VKTB_FAIL_ALLOC_AT");
+    if (!e) { count.store(0); return false; }
+    return count.fetch_add(1) + 1 == atol(e);
+}
 
 // ------------------------------------------------------------------ errors ------------------------------
 static thread_local std::string t_error;
@@ -208,6 +224,7 @@ const char* vktb_last_error(void) { return t_error.c_str(); }
 
 int vktb_device_count(int* n)
 {
+    VKTB_API_RANGE();
     if (!n) return fail("vktb_device_count: null argument");
     cudaError_t e = cudaGetDeviceCount(n);
     if (e != cudaSuccess) { *n = 0; return fail("cudaGetDeviceCount", e); }
@@ -216,6 +233,7 @@ int vktb_device_count(int* n)
 
 int vktb_set_device(int ordinal)
 {
+    VKTB_API_RANGE();
     if (ordinal < 0 || ordinal >= 64) return fail("vktb_set_device: ordinal out of range");
     t_device = ordinal;
     return currentDevice() ? 0 : -1;
@@ -233,6 +251,7 @@ void* vktb_get_stream(void)
 
 int vktb_set_stream(void* s)
 {
+    VKTB_API_RANGE();
     if (s) { t_streamOverride = (cudaStream_t)s; t_hasOverride = true; }
     else { t_streamOverride = nullptr; t_hasOverride = false; }
     return 0;
@@ -240,6 +259,7 @@ int vktb_set_stream(void* s)
 
 int vktb_sync(void)
 {
+    VKTB_API_RANGE();
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     cudaError_t e = cudaStreamSynchronize(d->copy);
@@ -456,8 +476,10 @@ extern "C" {
 
 int vktb_alloc(void** ptr, size_t bytes)
 {
+    VKTB_API_RANGE();
     if (!ptr) return fail("vktb_alloc: null argument");
     *ptr = nullptr;
+    if (injectAllocFailure()) return fail("vktb_alloc: out of memory (injected by VKTB_FAIL_ALLOC_AT)");
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     if (bytes == 0) bytes = 1;   // like malloc(0) in the reference's Allocate_serial: a unique, freeable pointer
@@ -473,6 +495,7 @@ int vktb_alloc(void** ptr, size_t bytes)
 
 int vktb_free(void* ptr)
 {
+    VKTB_API_RANGE();
     if (!ptr) return 0;
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
@@ -499,6 +522,7 @@ int vktb_free(void* ptr)
 
 int vktb_memcpy(void* dst, const void* src, size_t bytes, int kind)
 {
+    VKTB_API_RANGE();
     if (bytes == 0) return 0;
     if (!dst || !src) return fail("vktb_memcpy: null pointer");
     if (kind == VKTB_H2H) { memmove(dst, src, bytes); return 0; }
@@ -540,6 +564,7 @@ int vktb_memcpy(void* dst, const void* src, size_t bytes, int kind)
 
 int vktb_stream_in(void* devDst, size_t bytes, vktb_read_fn read, void* ctx, size_t* sum)
 {
+    VKTB_API_RANGE();
     if (sum) *sum = 0;
     if (bytes == 0) return 0;
     if (!devDst || !read) return fail("vktb_stream_in: null argument");
@@ -550,6 +575,7 @@ int vktb_stream_in(void* devDst, size_t bytes, vktb_read_fn read, void* ctx, siz
 
 int vktb_stream_out(const void* devSrc, size_t bytes, vktb_write_fn write, void* ctx, size_t* sum)
 {
+    VKTB_API_RANGE();
     if (sum) *sum = 0;
     if (bytes == 0) return 0;
     if (!devSrc || !write) return fail("vktb_stream_out: null argument");
@@ -560,6 +586,7 @@ int vktb_stream_out(const void* devSrc, size_t bytes, vktb_write_fn write, void*
 
 int vktb_memset_range(void* dst, const void* pattern, size_t dstBytes, size_t patBytes)
 {
+    VKTB_API_RANGE();
     if (dstBytes == 0) return 0;
     if (!dst || !pattern || patBytes == 0) return fail("vktb_memset_range: bad arguments");
     DeviceCtx* d = currentDevice();
@@ -578,6 +605,7 @@ int vktb_memset_range(void* dst, const void* pattern, size_t dstBytes, size_t pa
 
 int vktb_host_alloc(void** ptr, size_t bytes)
 {
+    VKTB_API_RANGE();
     if (!ptr) return fail("vktb_host_alloc: null argument");
     if (!currentDevice()) return -1;
     return pinnedAlloc(ptr, bytes);
@@ -589,6 +617,7 @@ int vktb_host_owns(const void* ptr) { return ptr && pinnedOwns(ptr) ? 1 : 0; }
 
 int vktb_mem_stats(size_t* devInUse, size_t* devReserved, size_t* pinInUse, size_t* pinReserved)
 {
+    VKTB_API_RANGE();
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     if (devInUse) { std::lock_guard<std::mutex> lock(d->allocMutex); *devInUse = d->deviceBytes; }
@@ -604,6 +633,7 @@ int vktb_mem_stats(size_t* devInUse, size_t* devReserved, size_t* pinInUse, size
 
 int vktb_trim_pools(void)
 {
+    VKTB_API_RANGE();
     DeviceCtx* d = currentDevice();
     if (!d) return -1;
     cudaStreamSynchronize(d->copy);

@@ -317,6 +317,7 @@ int vktb_set_devices(const int* ids, int n) { return setDeviceGroup(ids, n); }
 
 int vktb_get_devices(int* ids, int capacity, int* n)
 {
+    VKTB_API_RANGE();
     if (!n) return fail("vktb_get_devices: null argument");
     *n = groupSize();
     for (int i = 0; ids && i < *n && i < capacity; ++i) ids[i] = groupDevice(i);
@@ -325,6 +326,7 @@ int vktb_get_devices(int* ids, int capacity, int* n)
 
 int vktb_is_striped(const void* ptr, int* stripes)
 {
+    VKTB_API_RANGE();
     const StripedAlloc* a = findStriped(ptr);
     if (stripes) *stripes = a ? (int)a->stripes.size() : 0;
     return a ? 1 : 0;

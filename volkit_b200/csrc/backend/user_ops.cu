@@ -189,10 +189,12 @@ extern "C" {
 
 int vktb_register_unary_op_image(const void* image, size_t size, const char* name, int* op)
 {
+    VKTB_API_RANGE();
     return registerImage(image, size, name, false, op);
 }
 int vktb_register_binary_op_image(const void* image, size_t size, const char* name, int* op)
 {
+    VKTB_API_RANGE();
     return registerImage(image, size, name, true, op);
 }
 int vktb_register_unary_op_source(const char* source, const char* name, int* op) { return registerSource(source, name, false, op); }

@@ -33,6 +33,10 @@ namespace host
     {
         vktb_vol d;
         d.data = v.getData();
+        // a migration that could not allocate leaves the bytes on the other device: hand the backend a null volume, it
+        // refuses the call and the front returns InvalidValue (no kernel ever sees a pointer of the wrong device)
+        if (v.residesOnHost() == onGpu(GetThreadExecutionPolicy()))
+            d.data = nullptr;
         Vec3i dims = v.getDims();
         d.dims[0] = dims.x; d.dims[1] = dims.y; d.dims[2] = dims.z;
         d.format = (int32_t)v.getDataFormat();

@@ -13,12 +13,13 @@ namespace host
 {
     bool deviceUsable()
     {
-        static int state = -1;   // -1 unknown, 0 no, 1 yes
-        if (state < 0) {
+        // decided once; a function-local static is initialised under the compiler's guard, so threads that arrive
+        // together do not race (ThreadSanitizer flagged the unguarded form: tests/test_sanitizers.py)
+        static const bool usable = [] {
             int n = 0;
-            state = (vktb_device_count(&n) == 0 && n > 0 && vktb_set_device(0) == 0) ? 1 : 0;
-        }
-        return state == 1;
+            return vktb_device_count(&n) == 0 && n > 0 && vktb_set_device(0) == 0;
+        }();
+        return usable;
     }
 
     Error backendError(char const* what)
@@ -29,12 +30,11 @@ namespace host
 
     static bool pinnedHostWanted()
     {
-        static int want = -1;
-        if (want < 0) {
+        static const bool want = [] {
             char const* e = std::getenv("VKT_B200_PINNED");
-            want = (e && e[0] == '0') ? 0 : 1;
-        }
-        return want == 1 && deviceUsable();
+            return !(e && e[0] == '0');
+        }();
+        return want && deviceUsable();
     }
 } // host
 
