@@ -194,6 +194,52 @@ def cli_pipeline(device):
     assert out[44:] == ref.tobytes()
 
 
+REF_CLI = os.path.join(ROOT, "oracle", "_ref", "vkt_ref_cli")
+CLI_STAGES = ["declare-sv --dims 64 64 64 --data-format uint8", "fill --value 0.1",
+              "fill-range --value 1 --first 0 0 0 --last 8 8 8", "resample --dims 32 32 32 --data-format uint16"]
+# sha256 of the 65580 bytes the REFERENCE's own tool (oracle/_ref/vkt_ref_cli = src/cli/main.cpp, unmodified) writes at the
+# end of BASELINE config 1, and its 44-byte header; made by tests/golden/make_cli_golden.py where /root/reference exists
+CLI_GOLDEN = os.path.join(ROOT, "tests", "golden", "cli_config1.json")
+
+
+def run_pipe(tools, device="cpu"):
+    """stage i runs with tools[i]; returns the bytes after every stage"""
+    env = dict(os.environ, VKT_B200_DEVICE=device)
+    outs, data = [], b""
+    for tool, stage in zip(tools, CLI_STAGES):
+        r = subprocess.run([tool] + stage.split(), input=data, capture_output=True, env=env, timeout=300)
+        assert r.returncode == 0, (tool, stage, r.stderr)
+        data = r.stdout
+        outs.append(data)
+    return outs
+
+
+@pytest.mark.needs_ref
+def test_cli_pipe_bytes_equal_the_reference_tool():
+    """the pipe format, checked against bytes the reference CLI wrote (not against a reading of its source): after every
+    command of config 1, and with the two tools mixed in one pipeline in both orders"""
+    if not os.path.exists(REF_CLI):
+        pytest.skip("oracle/_ref/vkt_ref_cli not built")
+    mine = os.path.join(LIB, "vkt")
+    ref = run_pipe([REF_CLI] * 4)
+    got = run_pipe([mine] * 4)
+    for i, (a, b) in enumerate(zip(ref, got)):
+        assert a == b, f"stage {i} ({CLI_STAGES[i]}) differs from the reference tool"
+    assert run_pipe([REF_CLI, mine, REF_CLI, mine])[-1] == ref[-1]
+    assert run_pipe([mine, REF_CLI, mine, REF_CLI])[-1] == ref[-1]
+    import hashlib, json
+    g = json.load(open(CLI_GOLDEN))
+    assert hashlib.sha256(ref[-1]).hexdigest() == g["sha256"] and ref[-1][:44].hex() == g["header_hex"], \
+        "tests/golden/cli_config1.json is stale: rerun tests/golden/make_cli_golden.py"
+
+
+def test_cli_config1_cpu_matches_the_reference_tools_bytes():
+    import hashlib, json
+    g = json.load(open(CLI_GOLDEN))
+    out = run_pipe([os.path.join(LIB, "vkt")] * 4)[-1]
+    assert len(out) == g["bytes"] and out[:44].hex() == g["header_hex"] and hashlib.sha256(out).hexdigest() == g["sha256"]
+
+
 def test_cpp_api_cpu_policy(programs, tmp_path):
     run_cpp(programs, "cpu", tmp_path)
 
@@ -273,3 +319,10 @@ def test_c99_api_gpu_policy(programs, tmp_path):
 @pytest.mark.gpu
 def test_cli_config1_gpu():
     cli_pipeline("gpu")
+    import hashlib, json
+    g = json.load(open(CLI_GOLDEN))
+    out = run_pipe([os.path.join(LIB, "vkt")] * 4, "gpu")[-1]
+    assert out[:44].hex() == g["header_hex"] and hashlib.sha256(out).hexdigest() == g["sha256"], \
+        "the GPU policy's pipe differs from the bytes the reference tool writes"
+    if os.path.exists(REF_CLI):      # travels with the snapshot: the reference tool itself, run on this box
+        assert run_pipe([REF_CLI] * 4)[-1] == out
