@@ -992,19 +992,20 @@ def test_arith_mapped_proven_division(gpu):
     pool.shutdown()
 
 
-def test_histogram_private_counters(gpu):
-    """up to 256 bins over a contiguous range of >= 2^22 voxels: the lane-private counter kernel (no atomics; UInt8
-    counts byte values and bins them in the flush).  Exact against the oracle: random data, a constant volume (every
-    vote of a group hits the same counter), non-identity mappings whose bins fall partly outside [0, numBins) (the
-    reference writes out of bounds there: dropped and counted), odd bin counts, a range that starts off a 16-byte
-    boundary (whole planes from plane 1 of a volume with an odd plane size)."""
+def test_histogram_integer_bins_and_byte_values(gpu):
+    """histograms of a few million voxels through the shortcuts of histogramKernel: identity-mapped UInt16 with up to
+    256 bins takes (raw * numBins) >> 16, UInt8 counts byte values and bins each value's total once, with the exact float
+    expression.  Exact against the oracle: random data, a constant volume (a whole warp hits one bin), non-identity
+    mappings whose bins fall partly outside [0, numBins) (the reference writes out of bounds there: dropped and counted),
+    odd bin counts, more than 256 bins, a range that starts off a 16-byte boundary (whole planes from plane 1 of a volume
+    with an odd plane size)."""
     o = po.oracle()
     for fmt, dims in ((po.UINT8, (255, 257, 70)), (po.UINT16, (256, 256, 70)), (po.UINT32, (256, 128, 130)),
                       (po.FLOAT32, (128, 256, 130))):
         data = po.synth(dims, fmt, 9)
         const = np.full_like(data, 77)
         for arr, lo, hi, nb in ((data, 0.0, 1.0, 256), (data, 0.0, 1.0, 37), (const, 0.0, 1.0, 256),
-                                (data, 0.25, 0.75, 200), (data, -1.0, 2.0, 255)):
+                                (data, 0.25, 0.75, 200), (data, -1.0, 2.0, 255), (data, 0.0, 1.0, 257), (data, 0.0, 1.0, 1000)):
             vol = po.Vol(arr, fmt, lo, hi)
             for first in ((0, 0, 0), (0, 0, 1)):
                 want, wdrop = o.histogram_range(vol, first, dims, nb)

@@ -172,6 +172,14 @@ __device__ __forceinline__ int histBin(float val, const HistParams& p)
 // SHARED: per-CTA 32-bit counters in shared memory, REPL copies of every bin laid out as sh[bin * REPL + lane % REPL].
 // With REPL = 32 lane l only ever touches bank l: no bank conflicts and no same-address serialisation inside a warp
 // whatever the data looks like (a warp of equal voxels would otherwise serialise 32-fold).
+// What bounds this kernel is the BIN COMPUTATION, not the shared-memory reductions (round 2 measured it: with the
+// reference's float expression per voxel 2048^3 UInt16 takes 7.5 ms; a kernel with lane-private 16-bit counters and no
+// atomics at all, built on the opposite assumption, took the same 7.5 ms and 4.5 ms with an integer bin -- this kernel
+// with the same integer bin takes 2.98 ms):
+//   * identity-mapped UInt16, up to 256 bins: unmap = raw * 2^-16 exactly (65535.999f rounds to 65536), lo = 0, scale =
+//     numBins exactly, and raw * numBins < 2^24 is exact in binary32, so the reference's bin IS (raw * numBins) >> 16;
+//   * UInt8, any mapping, any bin count: the kernel counts the 256 byte VALUES (extract, one reduction, nothing else);
+//     each value's total goes through the exact float bin expression once, at the end.
 // FLAT: the range is one contiguous run of p.n voxels (grid-stride over 128-bit vectors, four in flight); otherwise
 // one CTA walks rows.
 template <int F, bool IDENT, bool SHARED, bool FLAT>
@@ -180,8 +188,12 @@ histogramKernel(HistParams p, int replShift)
 {
     constexpr int BPV = bytesPerVoxel(F);
     constexpr int V = 16 / BPV;
+    // UInt8 with shared counters: count the 256 byte VALUES (one shared-memory reduction per voxel, nothing else); each
+    // value's count goes through the exact bin expression once, at the end
+    constexpr bool kByValue = F == F_U8 && SHARED;
     extern __shared__ uint32_t sh[];
-    const unsigned nCounters = p.numBins << replShift;
+    const unsigned nRows = kByValue ? 256u : p.numBins;
+    const unsigned nCounters = nRows << replShift;
     const unsigned myCopy = threadIdx.x & ((1u << replShift) - 1u);
     if (SHARED) {
         for (unsigned i = threadIdx.x; i < nCounters; i += blockDim.x) sh[i] = 0u;
@@ -189,7 +201,10 @@ histogramKernel(HistParams p, int replShift)
     }
     unsigned drops = 0;
     auto count = [&](uint32_t raw) {
-        const int b = histBin<F>(unmapVoxel<F, IDENT>(raw, p.m), p);
+        if (kByValue) { atomicAdd(&sh[(raw << replShift) + myCopy], 1u); return; }
+        int b;
+        if (F == F_U16 && IDENT && p.numBins <= 256u) b = (int)((raw * p.numBins) >> 16);   // exact, see above
+        else b = histBin<F>(unmapVoxel<F, IDENT>(raw, p.m), p);
         if (b < 0) { ++drops; return; }
         if (SHARED) atomicAdd(&sh[((unsigned)b << replShift) + myCopy], 1u);
         else atomicAdd(&p.bins[b], 1ull);
@@ -244,148 +259,15 @@ histogramKernel(HistParams p, int replShift)
     if (drops) atomicAdd(p.dropped, (unsigned long long)drops);
     if (SHARED) {
         __syncthreads();
-        for (unsigned i = threadIdx.x; i < p.numBins; i += blockDim.x) {
+        for (unsigned i = threadIdx.x; i < nRows; i += blockDim.x) {
             unsigned long long sum = 0;
             for (unsigned k = 0; k < (1u << replShift); ++k) sum += sh[(i << replShift) + ((k + i) & ((1u << replShift) - 1u))];
-            if (sum) atomicAdd(&p.bins[i], sum);
+            if (!sum) continue;
+            const int b = kByValue ? histBin<F>(unmapVoxel<F, IDENT>(i, p.m), p) : (int)i;
+            if (b >= 0) atomicAdd(&p.bins[b], sum);
+            else atomicAdd(p.dropped, sum);
         }
     }
-}
-
-// ---- up to 256 bins, contiguous range: lane-private counters, no atomics (round 2) ---------------------------------------
-// The kernel above is bound by the shared-memory ATOMIC rate (ncu: 7.5 ms for 2048^3 UInt16 = 35 % of the HBM peak,
-// 10 % for UInt8).  Here every lane of every warp owns a private column of 16-bit counters, sh[warp][row][lane]:
-// nobody else touches a lane's counters, so a vote is a plain load / add / store.  Votes are taken four at a time: the
-// four counters are loaded first, each is stored back as counter + (number of the four votes that hit the same row)
-// -- duplicates all store the same, correct value -- which keeps four loads in flight per lane and needs no branch
-// whatever the data looks like (a constant background is the common real-world case).  Row 256 collects the voxels
-// whose bin falls outside [0, numBins): no branch for them either.  A warp flushes its columns into the CTA's 32-bit
-// totals before a counter can reach 2^16.  6 warps x 257 rows x 32 lanes x 2 B = 96 KiB per CTA, two CTAs per SM; the
-// next four vectors are loaded while the current four are counted.  UInt8 volumes count raw byte VALUES (row = byte);
-// the 256 value counts go through the exact bin computation once, at the end.
-// (First version: 32-bit counters, one CTA of 6 warps per SM, no prefetch: 13.3 ms -- too few bytes in flight.  The
-// kernels are instruction-issue bound, not atomic bound: with the float bin computation this one ran at 7.58 ms, the
-// same as the atomic kernel; the integer bin of identity UInt16 brought 4.49 ms.  Packing rows r, r ^ 1 of a lane
-// into one 32-bit word so that lane l always sits on bank l was measured and not kept: 6.27 ms, the extra address
-// arithmetic costs more than the 2-way conflicts of the per-row packing.)
-constexpr int kPrivWarps = 6;
-constexpr int kPrivRows = 257;
-
-template <int F, bool IDENT>
-__global__ void __launch_bounds__(kPrivWarps * 32, 2)
-histogramPrivateKernel(HistParams p)
-{
-    constexpr int BPV = bytesPerVoxel(F);
-    constexpr int V = 16 / BPV;
-    constexpr bool kByValue = F == F_U8;
-    constexpr unsigned kFlushEvery = 65535u / (4u * V) - 1u;      // warp iterations (4 vectors each) between flushes
-    extern __shared__ __align__(16) unsigned short sh16[];
-    __shared__ unsigned total[kPrivRows];
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    unsigned short* mine = sh16 + warp * (kPrivRows * 32) + lane;        // row r: mine[r * 32]
-    for (unsigned i = threadIdx.x; i < kPrivWarps * kPrivRows * 32; i += blockDim.x) sh16[i] = 0;
-    for (unsigned i = threadIdx.x; i < kPrivRows; i += blockDim.x) total[i] = 0u;
-    __syncthreads();
-
-    auto rowOf = [&](uint32_t raw) -> unsigned {
-        if (kByValue) return raw;
-        // identity-mapped UInt16: unmap = raw * 2^-16 exactly (65535.999f rounds to 65536), lo = 0, scale = numBins
-        // exactly, and raw * numBins < 2^24 is exact in binary32: the reference's bin is (raw * numBins) >> 16
-        if (F == F_U16 && IDENT) return (raw * p.numBins) >> 16;
-        const int b = histBin<F>(unmapVoxel<F, IDENT>(raw, p.m), p);
-        return b < 0 ? 256u : (unsigned)b;
-    };
-    auto vote4 = [&](unsigned r0, unsigned r1, unsigned r2, unsigned r3) {
-        const unsigned c0 = mine[r0 * 32], c1 = mine[r1 * 32], c2 = mine[r2 * 32], c3 = mine[r3 * 32];
-        const unsigned e01 = r0 == r1, e02 = r0 == r2, e03 = r0 == r3, e12 = r1 == r2, e13 = r1 == r3, e23 = r2 == r3;
-        mine[r0 * 32] = (unsigned short)(c0 + 1u + e01 + e02 + e03);
-        mine[r1 * 32] = (unsigned short)(c1 + 1u + e01 + e12 + e13);
-        mine[r2 * 32] = (unsigned short)(c2 + 1u + e02 + e12 + e23);
-        mine[r3 * 32] = (unsigned short)(c3 + 1u + e03 + e13 + e23);
-    };
-    auto voteVec = [&](const uint4& q) {
-#pragma unroll
-        for (int i = 0; i < V; i += 4)
-            vote4(rowOf(vecGet<BPV>(q, i)), rowOf(vecGet<BPV>(q, i + 1)), rowOf(vecGet<BPV>(q, i + 2)), rowOf(vecGet<BPV>(q, i + 3)));
-    };
-    // a warp's columns -> the CTA's 32-bit totals (shared atomics: 257 per flush, nothing next to the votes)
-    auto flushWarp = [&]() {
-        __syncwarp();
-        unsigned short* tab = sh16 + warp * (kPrivRows * 32);
-        for (unsigned r = lane; r < kPrivRows; r += 32u) {
-            unsigned sum = 0;
-            for (unsigned k = 0; k < 32u; ++k) {
-                const unsigned idx = r * 32 + ((k + r) & 31u);
-                sum += tab[idx];
-                tab[idx] = 0;
-            }
-            if (sum) atomicAdd(&total[r], sum);
-        }
-        __syncwarp();
-    };
-
-    const size_t n = p.n;
-    size_t head = ((16u - (reinterpret_cast<uintptr_t>(p.s) & 15u)) & 15u) / BPV;
-    if (head > n) head = n;
-    const size_t nvec = (n - head) / V, tail0 = head + nvec * V;
-    const uint8_t* body = p.s + head * BPV;
-    // warp-uniform work: chunk j = 128 consecutive vectors, lane l takes vectors l, l + 32, l + 64, l + 96 of it
-    const size_t nChunks = nvec / 128;
-    const size_t warpId = (size_t)blockIdx.x * kPrivWarps + warp, nWarps = (size_t)gridDim.x * kPrivWarps;
-    unsigned sinceFlush = 0;
-    size_t j = warpId;
-    uint4 q0, q1, q2, q3;
-    if (j < nChunks) {
-        const uint8_t* c = body + (j * 128 + lane) * 16;
-        q0 = ldStream(c); q1 = ldStream(c + 512); q2 = ldStream(c + 1024); q3 = ldStream(c + 1536);
-    }
-    while (j < nChunks) {
-        const size_t jn = j + nWarps;
-        uint4 n0 = q0, n1 = q1, n2 = q2, n3 = q3;
-        if (jn < nChunks) {                                        // the next chunk travels while this one is counted
-            const uint8_t* c = body + (jn * 128 + lane) * 16;
-            n0 = ldStream(c); n1 = ldStream(c + 512); n2 = ldStream(c + 1024); n3 = ldStream(c + 1536);
-        }
-        voteVec(q0); voteVec(q1); voteVec(q2); voteVec(q3);
-        if (++sinceFlush >= kFlushEvery) { flushWarp(); sinceFlush = 0; }
-        q0 = n0; q1 = n1; q2 = n2; q3 = n3;
-        j = jn;
-    }
-    flushWarp();
-    // what is left: the vectors past the last whole chunk and the scalar head / tail, one voxel at a time
-    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t v = nChunks * 128 + tid; v < nvec; v += stride) {
-        const uint4 q = ldStream(body + v * 16);
-#pragma unroll
-        for (int i = 0; i < V; ++i) atomicAdd(&total[rowOf(vecGet<BPV>(q, i))], 1u);
-    }
-    const size_t nEdge = head + (n - tail0);
-    for (size_t e = tid; e < nEdge; e += stride) {
-        const size_t k = e < head ? e : tail0 + (e - head);
-        atomicAdd(&total[rowOf(loadRaw(p.s + k * BPV, BPV))], 1u);
-    }
-    __syncthreads();
-    for (unsigned r = threadIdx.x; r < kPrivRows; r += blockDim.x) {
-        const unsigned long long sum = total[r];
-        if (!sum) continue;
-        int b = (int)r;
-        if (kByValue) b = r < 256u ? histBin<F>(unmapVoxel<F, IDENT>(r, p.m), p) : -1;      // the byte value's bin, exactly
-        else if (r == 256u) b = -1;
-        if (b >= 0 && (unsigned)b < p.numBins) atomicAdd(&p.bins[b], sum);
-        else atomicAdd(p.dropped, sum);
-    }
-}
-
-template <int F, bool IDENT>
-cudaError_t launchHistPrivate(const LaunchCtx& c, const HistParams& p)
-{
-    auto k = histogramPrivateKernel<F, IDENT>;
-    const size_t shBytes = (size_t)kPrivWarps * kPrivRows * 32 * sizeof(unsigned short);
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shBytes);
-    if (e != cudaSuccess) return e;
-    k<<<(unsigned)c.smCount * 2u, kPrivWarps * 32, shBytes, c.stream>>>(p);
-    countLaunch();
-    return cudaGetLastError();
 }
 
 template <int F, bool IDENT, bool SHARED>
@@ -404,17 +286,14 @@ cudaError_t launchHistK(const LaunchCtx& c, const HistParams& p, unsigned grid, 
 template <int F>
 cudaError_t launchHistF(const LaunchCtx& c, const HistParams& p)
 {
-    // up to 256 bins over a contiguous range of at least 2^22 voxels: lane-private counters (above); VKTB_HIST_ATOMIC=1
-    // keeps the atomic kernel for A/B runs
-    if (p.flat && p.numBins <= 256u && p.n >= ((size_t)1 << 22) && p.n < ((size_t)1 << 39) && !getenv("VKTB_HIST_ATOMIC"))
-        return p.m.identity ? launchHistPrivate<F, true>(c, p) : launchHistPrivate<F, false>(c, p);
     const long long rows = (long long)p.ny * p.nz;
     constexpr size_t kMaxShared = 96 * 1024;
-    const bool shared = (size_t)p.numBins * 4 <= kMaxShared;
+    const size_t rowsSh = F == F_U8 ? 256 : p.numBins;            // UInt8 counts byte values, whatever numBins is
+    const bool shared = rowsSh * 4 <= kMaxShared;
     // as many copies per bin as fit in 32 KiB (so several CTAs stay resident), at most one per lane
     int replShift = 0;
-    while (shared && replShift < 5 && ((size_t)p.numBins * 4 << (replShift + 1)) <= 32 * 1024) ++replShift;
-    const size_t shBytes = shared ? ((size_t)p.numBins * 4 << replShift) : 0;
+    while (shared && replShift < 5 && ((rowsSh * 4) << (replShift + 1)) <= 32 * 1024) ++replShift;
+    const size_t shBytes = shared ? ((rowsSh * 4) << replShift) : 0;
     // persistent: a few CTAs per SM, every CTA flushes its shared counters once
     long long grid = (long long)c.smCount * 6;
     if (!p.flat && grid > rows) grid = rows;
