@@ -121,7 +121,8 @@ def run_multi(torch, lib, capi, n_gpus, peak, time_steps, edge=4096, steps=3, wa
 
     def planes_zoff(vol):
         bnd = stripe_boundaries(vol)
-        extra = [z + k for z in bnd for k in range(0, ZOFF + 2)]
+        # dst planes [b, b + ZOFF) of the device behind boundary b read source planes of the device in front of it
+        extra = [z + k for z in bnd for k in (-1, 0, 1, ZOFF - 1, ZOFF, ZOFF + 1)]
         return sorted(set(planes_of(vol)) | {z for z in extra if 0 <= z < vol.dims[2]})
 
     record(f"SumRange dstOffset (0,0,{ZOFF}) {tag}", nr, 3 * nr,
