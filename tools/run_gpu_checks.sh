@@ -9,7 +9,7 @@
 #   smoke      __graft_entry__.smoke()
 #   bench      python bench.py                       (N = 1, the driver's command)
 #   refbench   python bench.py --impl reference
-#   launches   ncu launch list of the bench command  (only after `bench` exited 0 without ncu)
+#   launches   ncu launch list of the bench command without its host-streaming leg (only after `bench` exited 0 without ncu)
 #   ncu:REGEX  one `ncu --set full` capture of the kernels matching REGEX in `bench.py --ops 1 --steps 1 --warmup 1`
 #   probe:ARGS python tools/op_probe.py ARGS          (ARGS with commas for spaces, e.g. probe:sumrange,2040,2040,2040,u8)
 set -u
@@ -23,8 +23,8 @@ for s in $STEPS; do
     smoke)    timeout 300 python __graft_entry__.py smoke > $OUT/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" ;;
     bench)    timeout 900 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?" ;;
     refbench) timeout 600 python bench.py --impl reference > $OUT/${TAG}_refbench.json 2> $OUT/${TAG}_refbench.err; echo "refbench rc=$?" ;;
-    launches) timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
-                --log-file $OUT/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 > $OUT/${TAG}_launches.log 2>&1; echo "launches rc=$?" ;;
+    launches) timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:Kernel|vktb_' -c 1000 --csv \
+                --log-file $OUT/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-e2e > $OUT/${TAG}_launches.log 2>&1; echo "launches rc=$?" ;;
     ncu:*)    timeout 900 ncu --set full --clock-control none --import-source on -k regex:${s#ncu:} -c 3 -f \
                 -o $OUT/${TAG}_$(echo ${s#ncu:} | tr -c 'A-Za-z0-9' _) python bench.py --steps 1 --warmup 1 --no-e2e \
                 > $OUT/${TAG}_ncu.log 2>&1; echo "ncu rc=$?" ;;
