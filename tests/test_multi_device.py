@@ -158,3 +158,37 @@ def test_striped_volumes_fan_out_and_match_the_oracle(striped_env, gi):
     one = (ctypes.c_int * 1)(0)
     assert lib.vktb_set_devices(one, 1) != 0 and b"striped volumes are alive" in lib.vktb_last_error()
     keep.free()
+
+
+@pytest.mark.parametrize("gi", [0, 1])
+def test_histogram_of_a_striped_volume(striped_env, gi):
+    """vktb_histogram_range on a striped volume: every device counts the planes that start in its stripe into its own
+    bins, the parts are added on the calling device.  Whole volume and a sub-range whose first / last plane fall inside
+    stripes, identity and non-identity mapping (voxels outside the bins are dropped and counted), against the oracle."""
+    lib, capi = striped_env
+    gs = groups()
+    if gi >= len(gs):
+        pytest.skip("needs two GPUs")
+    set_group(lib, capi, gs[gi])
+    o = po.oracle()
+    I3 = capi.I3
+    for fmt, cf, dims in ((po.UINT16, capi.UINT16, (300, 220, 97)), (po.UINT8, capi.UINT8, (512, 300, 61))):
+        a = po.synth(dims, fmt, 4)
+        for lo, hi, nb in ((0.0, 1.0, 256), (0.25, 0.75, 100), (0.0, 1.0, 5000)):
+            dv = up(capi, a, cf, lo, hi)
+            st = ctypes.c_int()
+            assert lib.vktb_is_striped(dv.ptr, ctypes.byref(st)) == 1 and st.value == len(gs[gi])
+            for first, last in (((0, 0, 0), dims), ((3, 2, 5), (dims[0] - 1, dims[1] - 4, dims[2] - 7))):
+                want, wdrop = o.histogram_range(po.Vol(a, fmt, lo, hi), first, last, nb)
+                bins = ctypes.c_void_p()
+                capi.check(lib.vktb_alloc(ctypes.byref(bins), nb * 8))
+                dropped = ctypes.c_uint64(123)
+                before = lib.vktb_launch_count()
+                capi.check(lib.vktb_histogram_range(ctypes.byref(dv.desc()), I3(*first), I3(*last), bins, nb, ctypes.byref(dropped)),
+                           "vktb_histogram_range (striped)")
+                assert lib.vktb_launch_count() - before >= 3      # at least two stripes counted, and the combine
+                got = np.zeros(nb, np.uint64)
+                capi.check(lib.vktb_memcpy(got.ctypes.data, bins, nb * 8, capi.D2H))
+                capi.check(lib.vktb_free(bins))
+                assert got.tobytes() == want.tobytes() and int(dropped.value) == wdrop, (fmt, lo, hi, nb, first)
+            dv.free()

@@ -399,7 +399,36 @@ int vktb_histogram_range(const vktb_vol* vol, const int32_t first[3], const int3
     unsigned long long* dropped = nullptr;
     cudaError_t e = cudaMallocAsync((void**)&dropped, sizeof(unsigned long long), s);
     if (e != cudaSuccess) return fail("vktb_histogram_range", e);
-    e = launchHistogram(c, v, first, last, reinterpret_cast<unsigned long long*>(bins), numBins, dropped);
+    const StripedAlloc* a = emptyRange(first, last) ? nullptr : fanOutTarget(v, {});
+    if (a) {
+        // a striped volume: every device counts the planes that start in its stripe into bins of its own, the partial
+        // bins travel to the calling device (peer copies) and are added there -- the one-process form of the per-rank
+        // bins + all-reduce of volkit_b200/sharded.py
+        const size_t rec = numBins + 1;                       // bins, then the dropped voxels
+        unsigned long long* parts = nullptr;
+        e = cudaMallocAsync((void**)&parts, a->stripes.size() * rec * sizeof(unsigned long long), s);
+        int nParts = 0;
+        if (e == cudaSuccess)
+            e = forEachStripe(a, v.data, planeBytesOf(v), first[2], last[2], [&](const LaunchCtx& cg, int z0, int z1) {
+                const int32_t f[3] = { first[0], first[1], z0 }, l[3] = { last[0], last[1], z1 };
+                int dev = 0;
+                cudaGetDevice(&dev);
+                unsigned long long* mine = nullptr;
+                cudaError_t pe = cudaMallocAsync((void**)&mine, rec * sizeof(unsigned long long), cg.stream);
+                if (pe != cudaSuccess) return pe;
+                pe = launchHistogram(cg, v, f, l, mine, numBins, mine + numBins);
+                if (pe == cudaSuccess)
+                    pe = cudaMemcpyPeerAsync(parts + (size_t)nParts * rec, d->ordinal, mine, dev, rec * sizeof(unsigned long long), cg.stream);
+                ++nParts;
+                cudaFreeAsync(mine, cg.stream);
+                return pe;
+            });
+        if (e == cudaSuccess)
+            e = launchHistCombine(c, reinterpret_cast<unsigned long long*>(bins), dropped, parts, nParts, numBins);
+        if (parts) cudaFreeAsync(parts, s);
+    } else {
+        e = launchHistogram(c, v, first, last, reinterpret_cast<unsigned long long*>(bins), numBins, dropped);
+    }
     if (e == cudaSuccess && droppedHost) {
         unsigned long long h = 0;
         e = cudaMemcpyAsync(&h, dropped, sizeof(h), cudaMemcpyDeviceToHost, s);

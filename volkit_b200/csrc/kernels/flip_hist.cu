@@ -368,4 +368,27 @@ cudaError_t launchHistogram(const LaunchCtx& c, const VolDesc& vol, const int32_
     return cudaErrorInvalidValue;
 }
 
+// ---- several devices: bins[i] = sum over the parts (vktb_histogram_range on a striped volume, cabi.cu) ---------------------
+// parts: nParts records of numBins + 1 counters (the bins, then the dropped voxels), already on this device
+__global__ void __launch_bounds__(kThreads)
+histCombineKernel(unsigned long long* __restrict__ bins, unsigned long long* __restrict__ dropped,
+                  const unsigned long long* __restrict__ parts, int nParts, size_t numBins)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i <= numBins; i += (size_t)gridDim.x * blockDim.x) {
+        unsigned long long sum = 0;
+        for (int k = 0; k < nParts; ++k) sum += parts[(size_t)k * (numBins + 1) + i];
+        if (i < numBins) bins[i] = sum;
+        else *dropped = sum;
+    }
+}
+
+cudaError_t launchHistCombine(const LaunchCtx& c, unsigned long long* bins, unsigned long long* dropped,
+                              const unsigned long long* parts, int nParts, size_t numBins)
+{
+    const size_t ctas = (numBins + 1 + kThreads - 1) / kThreads;
+    histCombineKernel<<<(unsigned)(ctas < 1024 ? ctas : 1024), kThreads, 0, c.stream>>>(bins, dropped, parts, nParts, numBins);
+    countLaunch();
+    return cudaGetLastError();
+}
+
 } // namespace vktb

@@ -65,6 +65,8 @@ cudaError_t launchFlip(const LaunchCtx&, const VolDesc& dst, const VolDesc& src,
                        const int32_t off[3], int axis);
 cudaError_t launchHistogram(const LaunchCtx&, const VolDesc& vol, const int32_t first[3], const int32_t last[3],
                             unsigned long long* bins, size_t numBins, unsigned long long* droppedDev);
+cudaError_t launchHistCombine(const LaunchCtx& c, unsigned long long* bins, unsigned long long* dropped,
+                              const unsigned long long* parts, int nParts, size_t numBins);
 cudaError_t launchScan(const LaunchCtx&, const VolDesc& dst, const VolDesc& src, const int32_t first[3], const int32_t last[3],
                        const int32_t off[3]);
 // Aggregates: combinable moments of a range (kernels/aggregates.cu).  minIdx / maxIdx are linear indices inside the
