@@ -40,6 +40,10 @@ VKTAPI void vktStructuredVolumeSetBytes(vktStructuredVolume volume, int32_t x, i
 VKTAPI void vktStructuredVolumeGetBytes(vktStructuredVolume volume, int32_t x, int32_t y, int32_t z, uint8_t* data);
 VKTAPI uint8_t vktStructuredVolumeGetBytesPerVoxel(vktStructuredVolume volume);
 VKTAPI size_t vktStructuredVolumeGetSizeInBytes(vktStructuredVolume volume);
+/* handle of the volume's entry in the managed-resource registry (reference include/c/vkt/ManagedResource.h:16,
+ * StructuredVolume.h:118; declared there, defined nowhere) */
+typedef uint32_t vktResourceHandle;
+VKTAPI vktResourceHandle vktStructuredVolumeGetResourceHandle(vktStructuredVolume volume);
 VKTAPI void vktStructuredVolumeMigrate(vktStructuredVolume volume);
 
 #ifdef __cplusplus

@@ -52,6 +52,12 @@ int main(int argc, char** argv)
     if (gpu) VKT_SAFE_CALL(vktBindDeviceOp1(transformOp1, "xor_coord"));
     VKT_SAFE_CALL(vktTransformRangeSV1(volume, 2, 2, 2, 30, 30, 20, transformOp1));
     vktStructuredVolumeCreateCopy(&volume3, volume);
+    /* every volume is a managed resource with a handle of its own */
+    if (vktStructuredVolumeGetResourceHandle(volume3) == vktStructuredVolumeGetResourceHandle(volume)
+        || vktStructuredVolumeGetResourceHandle(volume) == vktStructuredVolumeGetResourceHandle(volume2)) {
+        fprintf(stderr, "two volumes share a resource handle\n");
+        return 5;
+    }
     VKT_SAFE_CALL(vktSafeSumSV(volume3, volume, volume2));
     VKT_SAFE_CALL(vktAbsDiffRangeSV(volume2, volume, volume3, 1, 1, 1, 39, 31, 23, 0, 0, 0));
     /* BrickDecompose as in reference src/examples/Decompose.c: 16^3 bricks, halo 1 on every side */

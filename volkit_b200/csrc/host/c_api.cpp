@@ -141,6 +141,7 @@ void vktStructuredVolumeSetBytes(vktStructuredVolume v, int32_t x, int32_t y, in
 void vktStructuredVolumeGetBytes(vktStructuredVolume v, int32_t x, int32_t y, int32_t z, uint8_t* d) { v->volume.getBytes(x, y, z, d); }
 uint8_t vktStructuredVolumeGetBytesPerVoxel(vktStructuredVolume v) { return v->volume.getBytesPerVoxel(); }
 size_t vktStructuredVolumeGetSizeInBytes(vktStructuredVolume v) { return v->volume.getSizeInBytes(); }
+vktResourceHandle vktStructuredVolumeGetResourceHandle(vktStructuredVolume v) { return v->volume.getResourceHandle(); }
 void vktStructuredVolumeMigrate(vktStructuredVolume v) { v->volume.migrate(); }
 
 //--- Fill / Copy -----------------------------------------------------------------------------------------------
