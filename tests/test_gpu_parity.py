@@ -393,6 +393,17 @@ def test_scan_kernels(gpu):
         assert a.a.tobytes() == b.a.tobytes(), dfmt
 
 
+@pytest.mark.parametrize("sweep,n", [("sweep_fill_transform", 300), ("sweep_copy_range", 300), ("sweep_arithmetic", 400),
+                                     ("sweep_resample", 300), ("sweep_flip_scan_histogram_bricks", 300),
+                                     ("sweep_scale_rotate_filter", 200)])
+def test_random_sweep_against_the_oracle(gpu, sweep, n):
+    """tests/fuzz_sweeps.py through the C-ABI: the same seeded random cases that pin the restatement on the compiled
+    reference (tests/test_oracle_fuzz.py), CUDA path against restatement -- including the corners the reference leaves
+    undefined and the restatement defines (dropped histogram voxels, the tap one voxel past the source buffer)."""
+    import fuzz_sweeps as fz
+    getattr(fz, sweep)(po.oracle(), gpu, n, False)
+
+
 def test_brick_decompose_batch(gpu):
     """BrickDecompose as one vktb_copy_range_batch launch: cropped border bricks, halos clamped at the volume border,
     brick rows at every 16-byte phase; plus a batch that mixes bytewise and converting boxes and empty boxes."""
