@@ -393,9 +393,9 @@ def test_scan_kernels(gpu):
         assert a.a.tobytes() == b.a.tobytes(), dfmt
 
 
-@pytest.mark.parametrize("sweep,n", [("sweep_fill_transform", 300), ("sweep_copy_range", 300), ("sweep_arithmetic", 400),
-                                     ("sweep_resample", 300), ("sweep_flip_scan_histogram_bricks", 300),
-                                     ("sweep_scale_rotate_filter", 200)])
+@pytest.mark.parametrize("sweep,n", [("sweep_fill_transform", 1000), ("sweep_copy_range", 1000), ("sweep_arithmetic", 1200),
+                                     ("sweep_resample", 1000), ("sweep_flip_scan_histogram_bricks", 1000),
+                                     ("sweep_scale_rotate_filter", 600)])
 def test_random_sweep_against_the_oracle(gpu, sweep, n):
     """tests/fuzz_sweeps.py through the C-ABI: the same seeded random cases that pin the restatement on the compiled
     reference (tests/test_oracle_fuzz.py), CUDA path against restatement -- including the corners the reference leaves
