@@ -131,6 +131,39 @@ def sweep_resample(o, r, n, reference):
         assert same(a.a, b.a), (sfmt, dfmt, sdims, ddims, filt)
 
 
+def sweep_resample_aligned(o, r, n, reference):
+    """rows of whole 16-byte vectors, 16 .. 96 voxels per axis: the shapes that reach the bulk-copy row pipeline and the TMA
+    z-march instead of the direct-gather kernel"""
+    rng = np.random.RandomState(707)
+    for i in range(n):
+        sfmt, dfmt = FMTS[rng.randint(4)], FMTS[rng.randint(4)]
+        sdims, ddims = tuple(8 * v for v in rdims(rng, 2, 10)), tuple(8 * v for v in rdims(rng, 2, 12))
+        if rng.randint(6) == 0:
+            ddims = sdims                                  # the equal-dims branch (a converting copy)
+        filt = (po.NEAREST, po.LINEAR)[rng.randint(2)]
+        src = cases.mk(sdims, sfmt, i, *rmap(rng))
+        if sfmt == po.FLOAT32 and rng.randint(3) == 0:     # special values travel through the 8-tap chain
+            flat = src.a.reshape(-1)
+            flat[rng.randint(flat.size)] = [np.inf, -np.inf, np.nan, -0.0][rng.randint(4)]
+        dlo, dhi = rmap(rng)
+        a, b = cases.mk(ddims, dfmt, 700 + i, dlo, dhi), cases.mk(ddims, dfmt, 700 + i, dlo, dhi)
+        o.resample(a, src, filt)
+        r.resample(b, src, filt)
+        if reference and sfmt == po.FLOAT32 and filt == po.LINEAR and ddims != sdims:
+            # The reference's unclamped hi.x tap (x = Sx) in the last row of the last plane reads one voxel past the end
+            # of the source buffer (heap contents; the restatement defines it as 0 bytes, oracle/vkt_oracle.c win_get).
+            # Its weight is 0, so the result only differs when the heap happens to hold an Inf / NaN pattern there --
+            # which this sweep did hit.  The dst voxels with that tap (lo.x = Sx - 1, hi.y = Sy - 1, hi.z = Sz - 1, the
+            # hi taps being lo + 1 clamped) are left out.
+            f32 = np.float32
+            lo3 = [(np.arange(D, dtype=f32) / f32(D) * f32(S)).astype(np.int32) for D, S in zip(ddims, sdims)]
+            ix, iy, iz = lo3[0] == sdims[0] - 1, lo3[1] >= sdims[1] - 2, lo3[2] >= sdims[2] - 2
+            corner = iz[:, None, None] & iy[None, :, None] & ix[None, None, :]
+            a.a[corner] = 0
+            b.a[corner] = 0
+        assert same(a.a, b.a), (sfmt, dfmt, sdims, ddims, filt)
+
+
 def sweep_flip_scan_histogram_bricks(o, r, n, reference):
     rng = np.random.RandomState(505)
     for i in range(n):

@@ -394,7 +394,7 @@ def test_scan_kernels(gpu):
 
 
 @pytest.mark.parametrize("sweep,n", [("sweep_fill_transform", 1000), ("sweep_copy_range", 1000), ("sweep_arithmetic", 1200),
-                                     ("sweep_resample", 1000), ("sweep_flip_scan_histogram_bricks", 1000),
+                                     ("sweep_resample", 1000), ("sweep_resample_aligned", 120), ("sweep_flip_scan_histogram_bricks", 1000),
                                      ("sweep_scale_rotate_filter", 600)])
 def test_random_sweep_against_the_oracle(gpu, sweep, n):
     """tests/fuzz_sweeps.py through the C-ABI: the same seeded random cases that pin the restatement on the compiled
