@@ -240,6 +240,33 @@ def test_cli_config1_cpu_matches_the_reference_tools_bytes():
     assert len(out) == g["bytes"] and out[:44].hex() == g["header_hex"] and hashlib.sha256(out).hexdigest() == g["sha256"]
 
 
+SWEEPS = [("sweep_fill_transform", 400), ("sweep_copy_range", 400), ("sweep_arithmetic", 500), ("sweep_resample", 400),
+          ("sweep_resample_aligned", 20), ("sweep_flip_scan_histogram_bricks", 500), ("sweep_scale_rotate_filter", 400)]
+
+
+@pytest.mark.parametrize("sweep,n", SWEEPS)
+def test_random_sweep_through_the_c_api_cpu_policy(sweep, n):
+    """tests/fuzz_sweeps.py through the host mirror's C API (vkt*SV calls on vktStructuredVolume handles) under the CPU
+    policy: the serial bodies of volkit_b200/csrc/host/serial.cpp against the restatement, random cases"""
+    import fuzz_sweeps as fz
+    from host_adapter import HostMirror
+    getattr(fz, sweep)(po.oracle(), HostMirror("cpu"), n, False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sweep,n", SWEEPS)
+def test_random_sweep_through_the_c_api_gpu_policy(sweep, n):
+    """the same cases under Device::GPU: create on the host, switch the policy, vkt*SV (migrate -> C-ABI -> kernels), switch
+    back, read -- the whole drop-in stack as a reference user drives it, against the restatement"""
+    import fuzz_sweeps as fz
+    from host_adapter import HostMirror
+    from volkit_b200 import capi
+    lib = capi.load()
+    before = lib.vktb_launch_count()
+    getattr(fz, sweep)(po.oracle(), HostMirror("gpu"), n, False)
+    assert lib.vktb_launch_count() - before >= n // 2, "the GPU policy did not launch kernels"
+
+
 def test_cpp_api_cpu_policy(programs, tmp_path):
     run_cpp(programs, "cpu", tmp_path)
 
