@@ -259,3 +259,24 @@ def sweep_scale_rotate_filter(o, r, n, reference):
             r.apply_filter(b, src, w)
             what = ("filter", fd)
         assert same(a.a, b.a), (what, sfmt, dfmt, sdims, ddims, center)
+
+
+def sweep_aggregates(o, r, n, reference):
+    """ComputeAggregatesRange word for word (min, max, mean, stddev, var, sum, prod, argmin, argmax): only for backends that
+    accumulate sequentially in binary32 like the reference (the restatement, the compiled reference, the host mirror's CPU
+    policy); the CUDA path has its own tolerance contract (tests/cases.py check_aggregates)"""
+    rng = np.random.RandomState(808)
+    for i in range(n):
+        fmt = FMTS[rng.randint(4)]
+        dims = rdims(rng, 1, 10)
+        lo, hi = rmap(rng)
+        v = cases.mk(dims, fmt, i, lo, hi)
+        if fmt == po.FLOAT32 and rng.randint(3) == 0:
+            flat = v.a.reshape(-1)
+            flat[rng.randint(flat.size)] = [np.inf, -np.inf, np.nan, -0.0, 0.0][rng.randint(5)]
+        first, last = rrange(rng, dims)
+        if rng.randint(3) == 0:
+            first, last = (0, 0, 0), dims
+        wa, wb = o.aggregates_range(v, first, last), r.aggregates_range(v, first, last)
+        a, b = np.frombuffer(wa.words(), np.float32, 7), np.frombuffer(wb.words(), np.float32, 7)
+        assert same(a, b) and wa.words()[28:] == wb.words()[28:], (fmt, dims, lo, hi, first, last, a, b)

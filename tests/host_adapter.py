@@ -3,10 +3,10 @@ tests/fuzz_sweeps.py can drive the WHOLE stack the way a reference user does: vo
 policy, the thread's policy is switched, the vkt*SV call runs (under Device::GPU that is migrate() -> C-ABI -> kernels),
 the result is read back after switching to the CPU policy again.
 
-Covered: Fill, Copy, the ten arithmetic ops, Resample, Flip, Scan, Scale, Rotate and Transform with the host ops 0..2 of the
-oracle's catalogue written as Python callbacks (bound to the built-in device ops by name for the GPU policy).  Histogram,
-ApplyFilter and BrickDecompose have no plain-C entry point taking one volume and are left to the other tests: the sweeps
-skip what an adapter does not implement."""
+Covered: Fill, Copy, the ten arithmetic ops, Resample, Flip, Scan, Scale, Rotate, ComputeAggregates (CPU policy) and
+Transform with the host ops 0..2 of the oracle's catalogue written as Python callbacks (bound to the built-in device ops
+by name for the GPU policy).  Histogram, ApplyFilter and BrickDecompose have no plain-C entry point taking one volume and
+are left to the other tests: the sweeps skip what an adapter does not implement."""
 import ctypes
 import os
 
@@ -74,6 +74,7 @@ class HostMirror:
         L.vktBindDeviceOp1.argtypes = [UNARY, ctypes.c_char_p]
         L.vktScaleSV.argtypes = [ctypes.c_void_p] * 2 + [Vec3f, Vec3f]
         L.vktRotateSV.argtypes = [ctypes.c_void_p] * 2 + [Vec3f, ctypes.c_float, Vec3f]
+        L.vktComputeAggregatesRangeSV.argtypes = [ctypes.c_void_p, ctypes.c_void_p] + i6
         for name in ARITH:
             getattr(L, f"vkt{name}RangeSV").argtypes = [ctypes.c_void_p] * 3 + i9
         self.cpu_policy = L.vktGetThreadExecutionPolicy()
@@ -139,6 +140,13 @@ class HostMirror:
 
     def scale(self, dst, src, factor, center):
         self._call(self.lib.vktScaleSV, [dst, src], [dst], Vec3f(*factor), Vec3f(*center))
+
+    def aggregates_range(self, vol, first, last):
+        if self.gpu:
+            raise NotImplementedError("the CUDA path follows a tolerance contract: tests/cases.py check_aggregates")
+        a = po.Aggregates()
+        self._call(self.lib.vktComputeAggregatesRangeSV, [vol], [], ctypes.byref(a), *first, *last)
+        return a
 
     def rotate(self, dst, src, axis, angle, center):
         self._call(self.lib.vktRotateSV, [dst, src], [dst], Vec3f(*axis), ctypes.c_float(angle), Vec3f(*center))

@@ -253,6 +253,13 @@ def test_random_sweep_through_the_c_api_cpu_policy(sweep, n):
     getattr(fz, sweep)(po.oracle(), HostMirror("cpu"), n, False)
 
 
+def test_random_aggregates_through_the_c_api_cpu_policy():
+    """ComputeAggregatesRange of the host mirror's CPU policy: the reference's sequential binary32 accumulation, word for word"""
+    import fuzz_sweeps as fz
+    from host_adapter import HostMirror
+    fz.sweep_aggregates(po.oracle(), HostMirror("cpu"), 400, False)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("sweep,n", SWEEPS)
 def test_random_sweep_through_the_c_api_gpu_policy(sweep, n):
