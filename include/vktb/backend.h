@@ -81,6 +81,8 @@ int         vktb_get_device(int* ordinal);
  *     plane or Resample tap in a neighbour's stripe is a peer load over NVLink inside the kernel (no halo copy);
  *   - vktb_memcpy to / from a striped range drives every device's copy engine on its own byte range concurrently --
  *     migrate() of a sharded volume;
+ *   - vktb_histogram_range of a striped volume counts on every device (the planes that start in its stripe) and adds the
+ *     partial bins on the calling device;
  *   - every other entry point runs on ids[0] and reaches the other stripes through peer access (correct, not scaled).
  * The caller sees one stream as before: the devices' work is forked from and joined to it by events.
  * vktb_set_devices(ids, 1) returns to one device.  Striped volumes must be freed before the group changes. */
