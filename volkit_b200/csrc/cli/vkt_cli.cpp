@@ -1,8 +1,11 @@
-// `vkt` command-line tool, hot-path subset: declare-sv | fill | fill-range | resample | dump, piping a structured
+// `vkt` command-line tool, hot-path subset: declare-sv | fill | fill-range | flip | flip-range | resample | dump | dump-range
+// (+ set-header, an empty stub in the reference too), piping a structured
 // volume over stdin/stdout in the reference's binary pipe format (reference src/cli/main.cpp:32-88):
 //     u32 magic = 1, u32 assetType = 0, i32 dims[3], u32 dataFormat, f32 dist[3], f32 mapping[2], raw voxels
 // Commands, options, defaults and range checks follow reference src/cli/main.cpp:111-335 (options), :402-442
-// (declare-sv), :521-574 (fill / fill-range), :701-740 (resample, always FilterMode::Nearest), :445-519 (dump).
+// (declare-sv), :521-574 (fill / fill-range), :575-620 (flip / flip-range), :701-740 (resample, always
+// FilterMode::Nearest), :443-519 (dump), :741-747 (set-header).  read / write need the reference's VolumeFile (Boost), render its
+// OpenGL viewer: not built.
 //
 // volkit-b200 addition: the execution policy of every stage is chosen with `--device cpu|gpu` or the environment
 // variable VKT_B200_DEVICE (default cpu, as in the reference where the CLI never sets a policy).  Under the GPU
@@ -10,6 +13,7 @@
 // in 16 MiB pieces straight into the backend's pinned staging ring while the previous pieces are on their way to
 // the device, and the result leaves the same way -- the stage never holds a host copy of the volume.
 #include <algorithm>
+#include <cctype>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -18,6 +22,7 @@
 
 #include <vkt/ExecutionPolicy.hpp>
 #include <vkt/Fill.hpp>
+#include <vkt/Flip.hpp>
 #include <vkt/InputStream.hpp>
 #include <vkt/OutputStream.hpp>
 #include <vkt/Resample.hpp>
@@ -46,6 +51,7 @@ struct Options
     Vec2f mapping{ 0.f, 0.f };
     Vec3i first{ 0, 0, 0 }, last{ 0, 0, 0 };
     float value = 0.f;
+    Axis axis = Axis::X;
     std::string device;
 };
 
@@ -66,7 +72,8 @@ bool parse(int argc, char** argv, Options& o)
 {
     if (argc < 2) return fail("Usage: vkt <command> [<args>]");
     o.command = argv[1];
-    static const char* known[] = { "declare-sv", "dump", "dump-range", "fill", "fill-range", "resample" };
+    static const char* known[] = { "declare-sv", "dump", "dump-range", "fill", "fill-range", "flip", "flip-range", "resample",
+                                   "set-header" };
     if (std::find_if(std::begin(known), std::end(known), [&](const char* k) { return o.command == k; }) == std::end(known)) {
         std::fprintf(stderr, "Usage: vkt <command> [<args>]\n  Command \"%s\" unknown\n", argv[1]);
         return false;
@@ -83,7 +90,14 @@ bool parse(int argc, char** argv, Options& o)
         else if (opt == "-first" || opt == "--first") { if (!need(i, 3, argv[i])) return false; o.first = { std::atoi(argv[i + 1]), std::atoi(argv[i + 2]), std::atoi(argv[i + 3]) }; i += 3; }
         else if (opt == "-last" || opt == "--last") { if (!need(i, 3, argv[i])) return false; o.last = { std::atoi(argv[i + 1]), std::atoi(argv[i + 2]), std::atoi(argv[i + 3]) }; i += 3; }
         else if (opt == "-vm" || opt == "--voxel-mapping") { if (!need(i, 2, argv[i])) return false; o.mapping = { (float)std::atof(argv[i + 1]), (float)std::atof(argv[i + 2]) }; i += 2; }
-        else if (opt == "-v" || opt == "--value") { if (!need(i, 1, argv[i])) return false; o.value = (float)std::atof(argv[++i]); }
+        else if (opt == "-val" || opt == "-v" || opt == "--value") { if (!need(i, 1, argv[i])) return false; o.value = (float)std::atof(argv[++i]); }
+        else if (opt == "-ax" || opt == "--axis") {
+            if (!need(i, 1, argv[i])) return false;
+            const char* a = argv[++i];
+            const int c = std::strlen(a) == 1 ? std::tolower((unsigned char)a[0]) : 0;
+            if (c == 'x') o.axis = Axis::X; else if (c == 'y') o.axis = Axis::Y; else if (c == 'z') o.axis = Axis::Z;
+            else { std::fprintf(stderr, "Invalid argument: %s\n", a); return false; }
+        }
         else if (opt == "--device") { if (!need(i, 1, argv[i])) return false; o.device = argv[++i]; }
         else { std::fprintf(stderr, "Unknown option %s\n", argv[i]); return false; }
     }
@@ -188,6 +202,24 @@ int main(int argc, char** argv)
         if (e != NoError) return EXIT_FAILURE;
         writeVolume(volume);
         SetThreadExecutionPolicy(cpuPolicy);
+    } else if (o.command == "flip" || o.command == "flip-range") {
+        SetThreadExecutionPolicy(runPolicy);
+        StructuredVolume source;
+        if (!readVolume(source) || !checkParams(source)) return EXIT_FAILURE;
+        StructuredVolume dest(source);
+        const long long range = (long long)(o.last.x - o.first.x) * (o.last.y - o.first.y) * (o.last.z - o.first.z);
+        if (o.command == "flip-range") {
+            if (range <= 0) { fail("Invalid range"); return EXIT_FAILURE; }
+            if (o.first.x < 0 || o.first.y < 0 || o.first.z < 0) { fail("Range underflow"); return EXIT_FAILURE; }
+            Vec3i d = source.getDims();
+            if (o.last.x > d.x || o.last.y > d.y || o.last.z > d.z) { fail("Range overflow"); return EXIT_FAILURE; }
+        }
+        Error e = range > 0 ? FlipRange(dest, source, o.first, o.last, o.axis) : Flip(dest, source, o.axis);
+        if (e != NoError) return EXIT_FAILURE;
+        writeVolume(dest);
+        SetThreadExecutionPolicy(cpuPolicy);
+    } else if (o.command == "set-header") {
+        // the reference's command reads nothing and writes nothing (src/cli/main.cpp:741-747)
     } else if (o.command == "resample") {
         SetThreadExecutionPolicy(runPolicy);
         StructuredVolume src;
