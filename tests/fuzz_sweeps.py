@@ -280,3 +280,21 @@ def sweep_aggregates(o, r, n, reference):
         wa, wb = o.aggregates_range(v, first, last), r.aggregates_range(v, first, last)
         a, b = np.frombuffer(wa.words(), np.float32, 7), np.frombuffer(wb.words(), np.float32, 7)
         assert same(a, b) and wa.words()[28:] == wb.words()[28:], (fmt, dims, lo, hi, first, last, a, b)
+
+
+def sweep_transform2(o, r, n, reference):
+    """TransformRange with a binary op (both volumes are modified), same and mixed formats"""
+    rng = np.random.RandomState(909)
+    for i in range(n):
+        f1, f2 = FMTS[rng.randint(4)], FMTS[rng.randint(4)]
+        dims = rdims(rng, 1, 12)
+        first, last = rrange(rng, dims)
+        op = int(rng.randint(2))
+        m1, m2 = rmap(rng), rmap(rng)
+        a1, a2 = cases.mk(dims, f1, i, *m1), cases.mk(dims, f2, 400 + i, *m2)
+        b1, b2 = a1.copy(), a2.copy()
+        if not hasattr(r, "transform_range2"):
+            continue
+        o.transform_range2(a1, a2, first, last, op)
+        r.transform_range2(b1, b2, first, last, op)
+        assert same(a1.a, b1.a) and same(a2.a, b2.a), (f1, f2, dims, first, last, op)

@@ -14,6 +14,6 @@ pytestmark = pytest.mark.needs_ref
 
 @pytest.mark.parametrize("sweep,n", [(fz.sweep_fill_transform, 400), (fz.sweep_copy_range, 500), (fz.sweep_arithmetic, 600),
                                      (fz.sweep_resample, 400), (fz.sweep_resample_aligned, 25), (fz.sweep_flip_scan_histogram_bricks, 400),
-                                     (fz.sweep_scale_rotate_filter, 300), (fz.sweep_aggregates, 500)], ids=lambda v: getattr(v, "__name__", str(v)))
+                                     (fz.sweep_scale_rotate_filter, 300), (fz.sweep_aggregates, 500), (fz.sweep_transform2, 300)], ids=lambda v: getattr(v, "__name__", str(v)))
 def test_restatement_equals_the_compiled_reference(sweep, n):
     sweep(po.oracle(), po.reference(), n, True)
