@@ -270,6 +270,40 @@ def test_cli_flip_dump_and_option_spellings_equal_the_reference_tool():
 
 
 @pytest.mark.needs_ref
+def test_cli_raw_files_equal_the_reference_tool(tmp_path):
+    """`read -i` and `dump -i` of raw files (dims and format parsed from the name) byte for byte as the reference's own
+    tool -- built with the reference's VolumeFile.cpp and RawFile.cpp; `write -o` round trip; the two cases where the
+    reference tool crashes (a missing raw file, and every `write`: its VolumeFile opens raw files read-only) are errors /
+    work here"""
+    if not os.path.exists(REF_CLI):
+        pytest.skip("oracle/_ref/vkt_ref_cli not built")
+    mine = os.path.join(LIB, "vkt")
+    env = dict(os.environ, VKT_B200_DEVICE="cpu")
+    rng = np.random.RandomState(3)
+    files = {"vol_20x12x20_uint16.raw": rng.randint(0, 65536, 20 * 12 * 20).astype(np.uint16),
+             "small_9x7x5_uint8.raw": rng.randint(0, 256, 9 * 7 * 5).astype(np.uint8),
+             "f_6x5x4_float32.raw": rng.standard_normal(6 * 5 * 4).astype(np.float32)}
+    for name, data in files.items():
+        data.tofile(tmp_path / name)
+        for cmd in ("read", "dump", "dump-range --first 1 1 1 --last 4 3 3"):
+            a = subprocess.run([REF_CLI] + cmd.split() + ["-i", name], capture_output=True, env=env, cwd=tmp_path, timeout=60)
+            b = subprocess.run([mine] + cmd.split() + ["-i", name], capture_output=True, env=env, cwd=tmp_path, timeout=60)
+            assert a.returncode == b.returncode == 0 and a.stdout == b.stdout and len(a.stdout) > 44, (name, cmd, b.stderr)
+    # write: the volume comes back from the file it was written to
+    vol = subprocess.run([mine, "read", "-i", "vol_20x12x20_uint16.raw"], capture_output=True, env=env, cwd=tmp_path).stdout
+    w = subprocess.run([mine, "write", "-o", "out_20x12x20_uint16.raw"], input=vol, capture_output=True, env=env, cwd=tmp_path)
+    assert w.returncode == 0 and (tmp_path / "out_20x12x20_uint16.raw").read_bytes() == files["vol_20x12x20_uint16.raw"].tobytes()
+    # errors: same message and exit code where the reference tool reports one; an error instead of its crash otherwise
+    for args in (["read"], ["read", "-i", "foo.txt"], ["write"]):
+        a = subprocess.run([REF_CLI] + args, input=vol, capture_output=True, env=env, cwd=tmp_path, timeout=60)
+        b = subprocess.run([mine] + args, input=vol, capture_output=True, env=env, cwd=tmp_path, timeout=60)
+        assert a.returncode == b.returncode == 1 and a.stderr == b.stderr, (args, a.stderr, b.stderr)
+    a = subprocess.run([REF_CLI, "read", "-i", "nothere_4x4x4_uint8.raw"], capture_output=True, env=env, cwd=tmp_path, timeout=60)
+    b = subprocess.run([mine, "read", "-i", "nothere_4x4x4_uint8.raw"], capture_output=True, env=env, cwd=tmp_path, timeout=60)
+    assert a.returncode < 0 and b.returncode == 1 and b"Cannot open input file" in b.stderr      # the reference: SIGSEGV
+
+
+@pytest.mark.needs_ref
 def test_cli_reads_non_cubic_volumes_where_the_reference_tool_does_not():
     """The reference's pipe reader builds the volume as (dims.x, dims.y, dims.X) (src/cli/main.cpp:66): any stage that reads a
     volume with dims.x != dims.z gets the wrong depth (20 x 12 x 9 comes out of `fill` as 20 x 12 x 20 with a tail of

@@ -4,8 +4,11 @@
 //     u32 magic = 1, u32 assetType = 0, i32 dims[3], u32 dataFormat, f32 dist[3], f32 mapping[2], raw voxels
 // Commands, options, defaults and range checks follow reference src/cli/main.cpp:111-335 (options), :402-442
 // (declare-sv), :521-574 (fill / fill-range), :575-620 (flip / flip-range), :701-740 (resample, always
-// FilterMode::Nearest), :443-519 (dump), :741-747 (set-header).  read / write need the reference's VolumeFile (Boost), render its
-// OpenGL viewer: not built.
+// FilterMode::Nearest), :443-519 (dump, also from a file with -i), :630-656 (read), :741-747 (set-header), :748-781 (write).
+// Files: raw volumes only ("<name>_<X>x<Y>x<Z>_<format>.raw", vkt::RawFile); the reference's VolumeFile also knows Nifti and
+// Virvo when built with those libraries.  Where the reference tool crashes -- a raw file that does not exist, and every `write`
+// (its VolumeFile opens raw files read-only, src/vkt/VolumeFile.cpp:73) -- this tool reports the error / writes the file.
+// render needs the reference's OpenGL viewer: not built.
 //
 // volkit-b200 addition: the execution policy of every stage is chosen with `--device cpu|gpu` or the environment
 // variable VKT_B200_DEVICE (default cpu, as in the reference where the CLI never sets a policy).  Under the GPU
@@ -25,6 +28,7 @@
 #include <vkt/Flip.hpp>
 #include <vkt/InputStream.hpp>
 #include <vkt/OutputStream.hpp>
+#include <vkt/RawFile.hpp>
 #include <vkt/Resample.hpp>
 #include <vkt/StructuredVolume.hpp>
 
@@ -52,6 +56,7 @@ struct Options
     Vec3i first{ 0, 0, 0 }, last{ 0, 0, 0 };
     float value = 0.f;
     Axis axis = Axis::X;
+    std::string inputFile, outputFile;
     std::string device;
 };
 
@@ -72,8 +77,8 @@ bool parse(int argc, char** argv, Options& o)
 {
     if (argc < 2) return fail("Usage: vkt <command> [<args>]");
     o.command = argv[1];
-    static const char* known[] = { "declare-sv", "dump", "dump-range", "fill", "fill-range", "flip", "flip-range", "resample",
-                                   "set-header" };
+    static const char* known[] = { "declare-sv", "dump", "dump-range", "fill", "fill-range", "flip", "flip-range", "read", "resample",
+                                   "set-header", "write" };
     if (std::find_if(std::begin(known), std::end(known), [&](const char* k) { return o.command == k; }) == std::end(known)) {
         std::fprintf(stderr, "Usage: vkt <command> [<args>]\n  Command \"%s\" unknown\n", argv[1]);
         return false;
@@ -98,6 +103,8 @@ bool parse(int argc, char** argv, Options& o)
             if (c == 'x') o.axis = Axis::X; else if (c == 'y') o.axis = Axis::Y; else if (c == 'z') o.axis = Axis::Z;
             else { std::fprintf(stderr, "Invalid argument: %s\n", a); return false; }
         }
+        else if (opt == "-i" || opt == "--input") { if (!need(i, 1, argv[i])) return false; o.inputFile = argv[++i]; }
+        else if (opt == "-o" || opt == "--output") { if (!need(i, 1, argv[i])) return false; o.outputFile = argv[++i]; }
         else if (opt == "--device") { if (!need(i, 1, argv[i])) return false; o.device = argv[++i]; }
         else { std::fprintf(stderr, "Unknown option %s\n", argv[i]); return false; }
     }
@@ -149,6 +156,30 @@ void writeVolume(StructuredVolume& volume)
     OutputStream os(out);
     os.write(volume);
     os.flush();
+}
+
+// "<name>.raw" / ".RAW" (reference src/vkt/VolumeFile.cpp:24-33); the other formats need libraries that are not built in
+bool isRawName(const std::string& name)
+{
+    const std::size_t slash = name.find_last_of('/'), dot = name.find_last_of('.');
+    if (dot == std::string::npos || (slash != std::string::npos && dot < slash)) return false;
+    const std::string ext = name.substr(dot);
+    return ext == ".raw" || ext == ".RAW";
+}
+
+// a raw file into a volume allocated under the calling thread's policy (dims and format come from the file name)
+bool readRawFile(const std::string& name, StructuredVolume& volume)
+{
+    FILE* probe = isRawName(name) ? std::fopen(name.c_str(), "rb") : nullptr;
+    if (!probe) { std::fprintf(stderr, "Cannot open input file: %s\n", name.c_str()); return false; }
+    std::fclose(probe);
+    RawFile file(name.c_str(), "rb");
+    Vec3i d = file.getDims();
+    if ((long long)d.x * d.y * d.z < 1) { std::fprintf(stderr, "Invalid dimensions: %s\n", name.c_str()); return false; }
+    if (file.getDataFormat() == DataFormat::Unspecified) { std::fprintf(stderr, "Invalid data format: %s\n", name.c_str()); return false; }
+    volume = StructuredVolume(d.x, d.y, d.z, file.getDataFormat(), 1.f, 1.f, 1.f, 0.f, 1.f);
+    InputStream(file).read(volume);     // RawFile::read returns an item count (RawFile.hpp): the code is not a byte count check
+    return true;
 }
 
 bool checkParams(StructuredVolume& v)
@@ -218,6 +249,23 @@ int main(int argc, char** argv)
         if (e != NoError) return EXIT_FAILURE;
         writeVolume(dest);
         SetThreadExecutionPolicy(cpuPolicy);
+    } else if (o.command == "read") {
+        if (o.inputFile.empty()) { fail("Input file missing"); return EXIT_FAILURE; }
+        SetThreadExecutionPolicy(runPolicy);
+        StructuredVolume volume;
+        if (!readRawFile(o.inputFile, volume)) return EXIT_FAILURE;
+        writeVolume(volume);
+        SetThreadExecutionPolicy(cpuPolicy);
+    } else if (o.command == "write") {
+        if (o.outputFile.empty()) { fail("Output file missing"); return EXIT_FAILURE; }
+        StructuredVolume volume;
+        if (!readVolume(volume) || !checkParams(volume)) return EXIT_FAILURE;
+        if (!isRawName(o.outputFile)) { std::fprintf(stderr, "Cannot open output file: %s\n", o.outputFile.c_str()); return EXIT_FAILURE; }
+        RawFile file(o.outputFile.c_str(), "wb");
+        if (!file.good()) { std::fprintf(stderr, "Cannot open output file: %s\n", o.outputFile.c_str()); return EXIT_FAILURE; }
+        OutputStream os(file);
+        os.write(volume);
+        os.flush();
     } else if (o.command == "set-header") {
         // the reference's command reads nothing and writes nothing (src/cli/main.cpp:741-747)
     } else if (o.command == "resample") {
@@ -235,7 +283,7 @@ int main(int argc, char** argv)
         SetThreadExecutionPolicy(cpuPolicy);
     } else {   // dump / dump-range
         StructuredVolume volume;
-        if (!readVolume(volume)) return EXIT_FAILURE;
+        if (o.inputFile.empty() ? !readVolume(volume) : !readRawFile(o.inputFile, volume)) return EXIT_FAILURE;
         const long long range = (long long)(o.last.x - o.first.x) * (o.last.y - o.first.y) * (o.last.z - o.first.z);
         if (o.command == "dump-range" && range <= 0) { fail("Invalid range"); return EXIT_FAILURE; }
         Vec3i d = volume.getDims(); Vec3f s = volume.getDist(); Vec2f m = volume.getVoxelMapping();
