@@ -16,6 +16,7 @@
 //
 // Every call runs under the reference's default thread policy {CPU, Serial}.
 
+#include <malloc.h>
 #include <cstdint>
 #include <cstring>
 #include <cstdlib>
@@ -70,6 +71,15 @@ struct Staged
     {
         bytes = vol.getSizeInBytes();
         if (bytes) std::memcpy(vol.getData(), d->data, bytes);
+        // The reference's sampleLinear reads ONE voxel past the end of a source volume (its unclamped hi.x tap in the last
+        // row of the last plane, weight 0: StructuredVolumeView.hpp:90-99).  That voxel lies in the slack of the malloc
+        // chunk (Allocate_serial is a plain malloc), i.e. it holds whatever an earlier allocation left there -- an Inf or
+        // NaN bit pattern turns the result of the tapping dst voxels into NaN and made a test flaky.  Zero the slack:
+        // the tap then reads a finite 0, which is also what the restatement defines it to be.
+        if (bytes) {
+            const size_t usable = malloc_usable_size(vol.getData());
+            if (usable > bytes) std::memset((char*)vol.getData() + bytes, 0, usable - bytes);
+        }
     }
 
     void writeBack() { if (bytes) std::memcpy(desc->data, vol.getData(), bytes); }
@@ -278,7 +288,7 @@ int ref_resample(RefVol const* dst, RefVol const* src, int filter)
 {
     // Note: under Linear the reference's unclamped hi.x tap reads one voxel past the end of src at
     // the very last src voxel (StructuredVolumeView.hpp:90-99); the value is multiplied by weight 0.
-    // The read stays inside the malloc chunk (glibc rounds chunks up to 16n+8 bytes).
+    // The read stays inside the malloc chunk (glibc rounds chunks up to 16n+8 bytes); Staged zeroes that slack.
     Staged d(dst), s(src);
     vkt::Resample(d.vol, s.vol, filter ? vkt::FilterMode::Linear : vkt::FilterMode::Nearest);
     d.writeBack();
